@@ -1,0 +1,177 @@
+"""Generate tests/golden/*.npz by running the UNMODIFIED reference on seeded inputs.
+
+TEST INFRASTRUCTURE.  Runs only in the build container (needs /root/reference, which does
+not exist on the GPU box); the vectors it writes are committed.
+
+    python oracle/gen_golden.py            # rewrites tests/golden/
+
+Import stubs: matplotlib (models/utils/estimation.py:5) and the
+``models.IterativeLocalCostVolume.utils.utils`` scipy import are satisfied by what the
+container has or by empty stand-in modules; no reference arithmetic is touched.
+"""
+import os
+import sys
+import types
+
+import numpy as np
+import torch
+
+REF = os.environ.get("SF_REFERENCE", "/root/reference")
+OUT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tests", "golden")
+
+
+def _stub(name, **attrs):
+    m = types.ModuleType(name)
+    for k, v in attrs.items():
+        setattr(m, k, v)
+    sys.modules[name] = m
+    return m
+
+
+def import_reference():
+    if "matplotlib" not in sys.modules:
+        try:
+            import matplotlib.pyplot  # noqa: F401
+        except Exception:
+            mp = _stub("matplotlib")
+            mp.pyplot = _stub("matplotlib.pyplot")
+    sys.path.insert(0, REF)
+    from models.utils.build_cost_volume import CostVolume
+    from models.utils.estimation import DisparityEstimation, DisparityEstimationWithProb
+    from models.LocalCostVolume.Attempts import fixed_local_cost_volume as flc
+    from models.LocalCostVolume.Attempts import variance_local_cost_volume as vlc
+    from models.LocalCostVolume.Attempts import update as upd
+    from models.CrossAttentionCostVolume.GWC_Cost_Volume import build_gwc_volume
+    from models.IterativeLocalCostVolume.corr.corr import CorrBlock1D
+    from models.utils.upsample import upsample_convex8
+    from utils.disparity_warper import disp_warp, meshgrid, normalize_coords
+    return dict(CostVolume=CostVolume, DisparityEstimation=DisparityEstimation,
+                DisparityEstimationWithProb=DisparityEstimationWithProb, flc=flc, vlc=vlc, upd=upd,
+                build_gwc_volume=build_gwc_volume, CorrBlock1D=CorrBlock1D,
+                upsample_convex8=upsample_convex8, disp_warp=disp_warp, meshgrid=meshgrid,
+                normalize_coords=normalize_coords)
+
+
+def save(name, **arrs):
+    os.makedirs(OUT, exist_ok=True)
+    np.savez_compressed(os.path.join(OUT, name + ".npz"),
+                        **{k: (v.detach().cpu().numpy() if torch.is_tensor(v) else np.asarray(v))
+                           for k, v in arrs.items()})
+
+
+def sampler_trace(mod, cv, cand):
+    """Re-run the reference's own ste_ceil/ste_floor + clamp + long on the reference's candidates."""
+    D = cv.shape[1]
+    ic = torch.clamp(mod.ste_ceil(cand), min=0, max=D - 1).long()
+    jf = torch.clamp(mod.ste_floor(cand), min=0, max=D - 1).long()
+    return jf, ic
+
+
+def main():
+    R = import_reference()
+    torch.manual_seed(1024)  # scripts/run.sh:31
+
+    # ---- a1 / a1' / a2 cost volumes ------------------------------------------------
+    for tag, (B, C, H, W, D) in {"small": (2, 16, 5, 40, 8), "odd": (1, 12, 3, 37, 6),
+                                 "wide_d": (1, 8, 2, 12, 16)}.items():
+        L, Rt = torch.randn(B, C, H, W), torch.randn(B, C, H, W)
+        save("corr_volume_" + tag, left=L, right=Rt, D=D,
+             corr=R["CostVolume"](D, "correlation")(L, Rt),
+             diff=R["CostVolume"](D, "difference")(L, Rt),
+             concat=R["CostVolume"](D, "concat")(L, Rt),
+             gwc=R["build_gwc_volume"](L, Rt, D, 4))
+
+    # ---- a3 soft-argmin ------------------------------------------------------------
+    cv = torch.abs(torch.randn(2, 24, 6, 40) * 3 - 2)  # pure_learning_method.py:170 style
+    d_sim = R["DisparityEstimation"](24, True)(cv)
+    d_cost = R["DisparityEstimation"](24, False)(cv)
+    d_p, prob = R["DisparityEstimationWithProb"](24, True)(cv)
+    save("soft_argmin", cv=cv, disp_sim=d_sim, disp_cost=d_cost, prob=prob)
+
+    # ---- a4 fixed window (radius 2, 20 points: baseline.py:38) ----------------------
+    flc = R["flc"]
+    cur = (torch.rand(2, 1, 6, 40) * 23)
+    cur[0, 0, 0, :8] = torch.tensor([0., 1., 2., 3.5, 21., 20.999, 23., 10.])  # edges of validity
+    for cvalid in (True, False):
+        mod = flc.LocalCostVolume(radius=2, sample_points=20)
+        out = mod(cv, cur, cvalid)
+        # candidates exactly as LocalCostVolume.forward computes them (:20-45)
+        lo, up = cur - 2, cur + 2
+        if cvalid:
+            inv = torch.clamp((lo < 0).float() + (up >= 23).float(), max=1.0)
+        else:
+            lo, up = torch.clamp(lo, min=0), torch.clamp(up, min=0, max=24)
+        step = (up - lo) * 1.0 / 20
+        cand = lo + torch.arange(21).type_as(cv).view(1, 21, 1, 1) * step
+        if cvalid:
+            cand = cand * (1 - inv) + inv * cur.repeat(1, 21, 1, 1)
+        jf, ic = sampler_trace(flc, cv, cand)
+        save("local_window_valid%d" % int(cvalid), cv=cv, cur=cur, radius=2, n_points=20,
+             out=out, cand=cand, idx_floor=jf, idx_ceil=ic,
+             local=flc.build_cost_volume_from_volume(cv, cand))
+
+    # arbitrary candidates through build_cost_volume_from_volume (incl. out of range, integers)
+    cand = torch.rand(2, 9, 6, 40) * 30 - 3
+    cand[:, 0] = torch.round(cand[:, 0])
+    jf, ic = sampler_trace(flc, cv, cand)
+    save("sample_volume", cv=cv, cand=cand, idx_floor=jf, idx_ceil=ic,
+         local=flc.build_cost_volume_from_volume(cv, cand))
+
+    # ---- a5 variance window ----------------------------------------------------------
+    vlc = R["vlc"]
+    cvv = torch.randn(2, 24, 6, 40)
+    curv = R["DisparityEstimation"](24, True)(cvv).unsqueeze(1)
+    for cvalid in (True, False):
+        save("variance_window_valid%d" % int(cvalid), cv=cvv, cur=curv, gamma=1.0, n_points=20,
+             out=vlc.Variance_Based_Local_Cost_Volume(1, 20)(cvv, curv, cvalid),
+             sigma=vlc.GetVarince(torch.softmax(cvv, 1), curv))
+
+    # ---- a6 DLC window tail + uncertainty volume (update.py:279-313, :86) -------------
+    upd = R["upd"]
+    lo_b, up_b = torch.relu(torch.randn(2, 1, 6, 40)) * 3, torch.relu(torch.randn(2, 1, 6, 40)) * 3
+    for cvalid in (True, False):
+        lo, up = cur - lo_b, cur + up_b
+        if cvalid:
+            inv = torch.clamp((lo < 0).float() + (up >= 23).float(), max=1.0)
+        else:
+            lo, up = torch.clamp(lo, min=0), torch.clamp(up, min=0, max=24)
+        step = (up - lo) * 1.0 / 20
+        cand = lo + torch.arange(21).type_as(cv).view(1, 21, 1, 1) * step
+        if cvalid:
+            cand = cand * (1 - inv) + inv * cur.repeat(1, 21, 1, 1)
+        local = upd.build_cost_volume_from_volume(cv, cand)
+        out = torch.sum(torch.softmax(local, 1) * cand, 1).unsqueeze(1)
+        jf, ic = sampler_trace(upd, cv, cand)
+        save("dlc_window_valid%d" % int(cvalid), cv=cv, cur=cur, lo=lo_b, up=up_b, n_points=20,
+             out=out, cand=cand, idx_floor=jf, idx_ceil=ic)
+    dcand = torch.arange(24).view(1, 24, 1, 1).repeat(1, 1, 6, 40).type_as(cur)
+    unc = torch.softmax(cv, 1) * dcand * (dcand - cur) * (dcand - cur)
+    save("uncertainty", cv=cv, cur=cur, unc=unc)
+
+    # ---- a7 warp ----------------------------------------------------------------------
+    img = torch.randn(2, 3, 6, 40)
+    dw = torch.rand(2, 1, 6, 40) * 12
+    dw[0, 0, 0, :4] = torch.tensor([0., 0.5, 39., 45.])
+    grid = R["normalize_coords"](R["meshgrid"](img) + torch.cat((-dw, torch.zeros_like(dw)), 1))
+    wb, mb = R["disp_warp"](img, dw)
+    wz, mz = R["disp_warp"](img, dw, padding_mode="zeros")
+    save("disp_warp", img=img, disp=dw, grid=grid, warped_border=wb, mask_border=mb,
+         warped_zeros=wz, mask_zeros=mz)
+
+    # ---- a8 / a9 CorrBlock1D ------------------------------------------------------------
+    f1, f2 = torch.randn(2, 16, 3, 24), torch.randn(2, 16, 3, 24)
+    blk = R["CorrBlock1D"](f1, f2, num_levels=3, radius=2)
+    xs = torch.arange(24).float().view(1, 1, 1, 24).repeat(2, 1, 3, 1)
+    coords = torch.cat((xs - torch.rand(2, 1, 3, 24) * 8, torch.zeros(2, 1, 3, 24)), 1)
+    coords[0, 0, 0, :4] = torch.tensor([0., 3., 23., -2.5])
+    save("corr1d", f1=f1, f2=f2, coords=coords, radius=2, num_levels=3,
+         lookup=blk(coords), **{"pyr%d" % i: p for i, p in enumerate(blk.corr_pyramid)})
+
+    # ---- f1 convex upsampling -------------------------------------------------------------
+    dlow, msk = torch.rand(1, 1, 3, 5) * 10, torch.randn(1, 576, 3, 5)
+    save("upsample_convex8", disp=dlow, mask=msk, out=R["upsample_convex8"](dlow, msk))
+    print("golden vectors written to", os.path.normpath(OUT))
+
+
+if __name__ == "__main__":
+    main()
