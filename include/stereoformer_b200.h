@@ -1,0 +1,117 @@
+/* stereoformer_b200 -- C ABI of the B200-native stereo-matching hot path.
+ *
+ * Plain pointers and sizes only; every pointer is a DEVICE pointer unless the name starts
+ * with `h_` or the function name ends in `_host`.  All tensors are dense, row-major NCHW,
+ * fp32 unless noted.  `stream` is a cudaStream_t passed as void*.  Every function returns
+ * SF_OK (0) or an error code; sf_last_error() returns the message (thread-local).
+ * Nothing here allocates device memory except the sf_ctx_* host-buffer front end.
+ *
+ * Each entry point names the reference interface it replaces (paths relative to the
+ * Magicboomliu/StereoFormer repository root).
+ */
+#ifndef STEREOFORMER_B200_H
+#define STEREOFORMER_B200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SF_ABI_VERSION 1
+#define SF_API __attribute__((visibility("default")))
+
+/* algo selector of sf_corr_volume_f32 */
+#define SF_ALGO_AUTO 0
+#define SF_ALGO_TMA 1     /* persistent TMA + mbarrier kernel (needs W % 4 == 0, 16-B aligned pointers) */
+#define SF_ALGO_GENERIC 2 /* shape-agnostic CUDA kernel (any W / alignment) */
+
+/* window modes of sf_local_window_f32 */
+#define SF_WIN_FIXED 0    /* fixed_local_cost_volume.py: bounds = disp -/+ radius                  */
+#define SF_WIN_VARIANCE 1 /* variance_local_cost_volume.py: bounds = disp -/+ gamma * sigma        */
+#define SF_WIN_OFFSETS 2  /* Attempts/update.py:279-282: bounds = disp - lo, disp + up (tensors)   */
+#define SF_WIN_ABSOLUTE 3 /* pure_learning_method.py:112: lo/up ARE the bounds                     */
+
+/* scalar-division rounding (tensor / python scalar): PyTorch CPU divides, PyTorch CUDA multiplies
+ * by the reciprocal.  Affects the last bit of sampling coordinates. */
+#define SF_DIV_TRUE 0
+#define SF_DIV_RECIP 1
+
+SF_API const char* sf_last_error(void);
+SF_API int sf_abi_version(void);
+SF_API int sf_device_sm_count(void);
+
+/* a1/a2: CostVolume('correlation').forward  models/utils/build_cost_volume.py:39-47 (groups = 1, out [B,D,H,W]);
+ * build_gwc_volume  models/CrossAttentionCostVolume/GWC_Cost_Volume.py:14-24 (groups = G, out [B,G,D,H,W]). */
+SF_API int sf_corr_volume_f32(const float* left, const float* right, float* out, int B, int C, int H, int W, int D,
+                       int groups, int algo, void* stream);
+
+/* a1': CostVolume('difference' | 'concat').forward  models/utils/build_cost_volume.py:21-37.
+ * out [B, C or 2C, D, H, W]; bit-exact. */
+SF_API int sf_shift_volume_f32(const float* left, const float* right, float* out, int B, int C, int H, int W, int D,
+                        int concat, void* stream);
+
+/* a3: DisparityEstimation(.WithProb).forward  models/utils/estimation.py:14-62 (disparity_regression,
+ * models/utils/submodule.py:23-27).  disp [B,H,W]; prob [B,D,H,W] or NULL. */
+SF_API int sf_soft_argmin_f32(const float* cv, float* disp, float* prob, int B, int D, int H, int W,
+                              int match_similarity, void* stream);
+
+/* a4/a5/a6: LocalCostVolume.forward  models/LocalCostVolume/Attempts/fixed_local_cost_volume.py:18-58;
+ * Variance_Based_Local_Cost_Volume.forward  variance_local_cost_volume.py:34-78; the window tail of
+ * DisparityUpdateDLC(WithMask).forward  Attempts/update.py:279-313 and PureLearningLocalCostVolume.forward
+ * pure_learning_method.py:112-143.  `mode` is one of SF_WIN_*.  disp may be NULL: the current disparity is then
+ * the soft-argmin of cv (fused a3+a4, LowCNN baseline.py:118-127) and is written to disp0_out when given.
+ * Optional debug outputs [B,n_points+1,H,W]: candidates (fp32), floor / ceil indices (int32), sampled volume. */
+SF_API int sf_local_window_f32(const float* cv, const float* disp, const float* lo, const float* up, float* out,
+                               float* disp0_out, float* dbg_cand, int* dbg_idx_floor, int* dbg_idx_ceil,
+                               float* dbg_local, int B, int D, int H, int W, int mode, float radius, float gamma,
+                               int n_points, int consider_valid, int div_mode, void* stream);
+
+/* build_cost_volume_from_volume(old_volume, sampling_candidates)  fixed_local_cost_volume.py:61-80 (defined
+ * identically in 5 reference files).  cand/out [B,K,H,W]; bit-exact; idx_* optional int32 [B,K,H,W]. */
+SF_API int sf_sample_volume_f32(const float* cv, const float* cand, float* out, int* idx_floor, int* idx_ceil, int B,
+                                int D, int K, int H, int W, void* stream);
+
+/* a7: disp_warp(img, disp, padding_mode)  utils/disparity_warper.py:83-106.  border != 0 -> 'border', else 'zeros'.
+ * mask [B,C,H,W] or NULL.  dbg_grid / dbg_src: optional [B,H,W,2] normalised grid / pixel-space source coordinate.
+ * neg_flag: optional device int set to 1 when any disparity is negative (the reference asserts, :93). */
+SF_API int sf_disp_warp_f32(const float* img, const float* disp, float* warped, float* mask, float* dbg_grid,
+                            float* dbg_src, int B, int C, int H, int W, int border, int div_mode, int* neg_flag,
+                            void* stream);
+
+/* a6 (i),(iii),(iv): BasicGuidanceNet.forward up to the conv encoders  Attempts/update.py:68-86.
+ * left/right [B,C,H,W] already at the disparity resolution; err [B,C,H,W]; unc [B,D,H,W]. */
+SF_API int sf_guidance_f32(const float* cv, const float* disp, const float* left, const float* right, float* err,
+                           float* unc, int B, int D, int C, int H, int W, int div_mode, int* neg_flag, void* stream);
+
+/* a8: CorrBlock1D.__init__ / corr  models/IterativeLocalCostVolume/corr/corr.py:55-76,103-111.
+ * levels: HOST array of n_out device pointers, level l is [B*H*W1, W2 >> l]. */
+SF_API int sf_corr1d_pyramid_f32(const float* f1, const float* f2, float* const* levels, int n_out, int B, int C,
+                                 int H, int W1, int W2, int algo, void* stream);
+
+/* a9: CorrBlock1D.__call__  corr.py:78-101 + bilinear_sampler  utils/utils.py:59-76.
+ * levels / widths: HOST arrays; coords [B,2,H,W1]; out [B,num_levels*(2r+1),H,W1]; dbg_* optional, same shape. */
+SF_API int sf_corr1d_lookup_f32(const float* const* levels, const int* widths, int num_levels, int radius,
+                                const float* coords, float* out, float* dbg_x0, float* dbg_src, int B, int H, int W1,
+                                int div_mode, void* stream);
+
+/* a10: DCN.modulated_deform_conv_forward  deform/src/vision.cpp:8 -> deform/src/modulated_deform_conv.h:10-44 ->
+ * deform/src/cuda/modulated_deform_conv_cuda.cu:19-121; mask == NULL gives DCN.deform_conv_forward
+ * (deform/src/deform_conv.h:10-25).  out [B,Cout,Ho,Wo] with the reference's output-size formula. */
+SF_API int sf_dcn_forward_f32(const float* input, const float* weight, const float* bias, const float* offset,
+                              const float* mask, float* out, int B, int Cin, int H, int W, int Cout, int kh, int kw,
+                              int stride_h, int stride_w, int pad_h, int pad_w, int dil_h, int dil_w, int group,
+                              int deformable_group, void* stream);
+
+/* a11: epipolar row cross-attention (reference file is empty; SPEC-DERIVED from north_star).  q,k,v,out are
+ * bf16 [B,C,H,W]; scores optional fp32 [B,band,H,W] (-inf outside the band). */
+SF_API int sf_epipolar_attn_bf16(const void* q, const void* k, const void* v, void* out, float* scores, int B, int C,
+                                 int H, int W, int band, int algo, void* stream);
+
+/* f1: upsample_convex8  models/utils/upsample.py:22-38 (factor 8) / RAFT upsample_flow (factor 4).
+ * disp [N,1,H,W], mask [N,9*F*F,H,W], out [N,1,F*H,F*W]. */
+SF_API int sf_upsample_convex_f32(const float* disp, const float* mask, float* out, int N, int H, int W, int factor,
+                                  void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -28,7 +28,7 @@ import torch.nn.functional as F
 def _sdiv(t, s, recip=False):
     """tensor / python-scalar with CPU (true division) or CUDA (x * (1/s)) rounding."""
     if recip:
-        return t * (torch.tensor(1.0, dtype=t.dtype) / torch.tensor(float(s), dtype=t.dtype))
+        return t * (torch.tensor(1.0, dtype=t.dtype) / torch.tensor(float(s), dtype=t.dtype)).to(t.device)
     return t / float(s)
 
 
@@ -80,7 +80,7 @@ def soft_argmin(cv, match_similarity=True, with_prob=False):
     """models/utils/estimation.py:14-33 (and :44-62 with the probability volume)."""
     assert cv.dim() == 4
     prob = F.softmax(cv if match_similarity else -cv, dim=1)
-    cand = torch.arange(cv.size(1), dtype=cv.dtype).view(1, -1, 1, 1)
+    cand = torch.arange(cv.size(1), dtype=cv.dtype, device=cv.device).view(1, -1, 1, 1)
     disp = torch.sum(prob * cand, dim=1)
     return (disp, prob) if with_prob else disp
 
@@ -108,7 +108,7 @@ def window_candidates(lower, upper, cur_disp, D, n_points, consider_valid,
         lower = torch.clamp(lower, min=0, max=D - 1)
         upper = torch.clamp(upper, min=0, max=D - 1)
     step = _sdiv((upper - lower) * 1.0, n_points, recip)
-    k = torch.arange(n_points + 1, dtype=lower.dtype).view(1, -1, 1, 1)
+    k = torch.arange(n_points + 1, dtype=lower.dtype, device=lower.device).view(1, -1, 1, 1)
     cand = lower + k * step
     if consider_valid:
         cand = cand * (1 - inv) + inv * cur_disp.repeat(1, n_points + 1, 1, 1)
@@ -154,7 +154,7 @@ def local_cost_volume(old_volume, cur_disp, radius, n_points, consider_valid=Fal
 
 def disparity_sigma(prob, cur_disp):
     """GetVarince, variance_local_cost_volume.py:12-25."""
-    d = torch.arange(prob.size(1), dtype=prob.dtype).view(1, -1, 1, 1)
+    d = torch.arange(prob.size(1), dtype=prob.dtype, device=prob.device).view(1, -1, 1, 1)
     err = (d - cur_disp) * (d - cur_disp)
     return torch.sqrt(torch.sum(prob * err, dim=1)).unsqueeze(1)
 
@@ -167,7 +167,7 @@ def variance_local_cost_volume(old_volume, cur_disp, gamma, n_points, consider_v
     upper = cur_disp + gamma * sigma
     extra = None
     if consider_valid:
-        xs = torch.arange(W, dtype=cur_disp.dtype).view(1, 1, 1, W)
+        xs = torch.arange(W, dtype=cur_disp.dtype, device=cur_disp.device).view(1, 1, 1, W)
         extra = (upper > xs).float()
     cand, _ = window_candidates(lower, upper, cur_disp, D, n_points, consider_valid,
                                 "variance", extra, recip=recip)
@@ -186,7 +186,7 @@ def dlc_window(old_volume, cur_disp, lo, up, n_points, consider_valid=True, reci
 def uncertainty_volume(old_volume, cur_disp):
     """BasicGuidanceNet.forward, Attempts/update.py:71-72,86: softmax(cv) * d * (d-disp) * (d-disp)."""
     prob = F.softmax(old_volume, dim=1)
-    d = torch.arange(old_volume.size(1), dtype=cur_disp.dtype).view(1, -1, 1, 1)
+    d = torch.arange(old_volume.size(1), dtype=cur_disp.dtype, device=cur_disp.device).view(1, -1, 1, 1)
     return prob * d * (d - cur_disp) * (d - cur_disp)
 
 
@@ -198,8 +198,8 @@ def warp_grid(disp, H, W, recip=False):
     to F.grid_sample: gx = 2*((x - disp)/(W-1)) - 1, gy = 2*(y/(H-1)) - 1.
     """
     dt = disp.dtype
-    xs = torch.arange(W, dtype=dt).view(1, 1, W).expand(1, H, W)
-    ys = torch.arange(H, dtype=dt).view(1, H, 1).expand(1, H, W)
+    xs = torch.arange(W, dtype=dt, device=disp.device).view(1, 1, W).expand(1, H, W)
+    ys = torch.arange(H, dtype=dt, device=disp.device).view(1, H, 1).expand(1, H, W)
     sx = xs + (-disp[:, 0])
     sy = ys + torch.zeros_like(disp[:, 0])
     gx = 2 * _sdiv(sx, W - 1, recip) - 1
@@ -248,7 +248,7 @@ def corr1d_pyramid(f1, f2, num_levels=4):
     B, C, H, W1 = f1.shape
     W2 = f2.shape[-1]
     corr = torch.einsum("aijk,aijh->ajkh", f1, f2).reshape(B, H, W1, 1, W2)
-    corr = corr / torch.sqrt(torch.tensor(C).float())
+    corr = corr / torch.sqrt(torch.tensor(C).float()).to(corr.device)
     corr = corr.reshape(B * H * W1, 1, 1, W2)
     pyr = [corr]
     for _ in range(num_levels):
@@ -260,7 +260,7 @@ def corr1d_pyramid(f1, f2, num_levels=4):
 def corr1d_lookup_coords(coords_x, level, radius, Wl, recip=False):
     """corr.py:88-90 + utils/utils.py:62-64: x0 = dx + x/2^i, normalised 2*x0/(Wl-1) - 1.
     coords_x: [N] flattened x coordinates.  Returns (x0 [N,2r+1], xgrid [N,2r+1])."""
-    dx = torch.linspace(-radius, radius, 2 * radius + 1).view(1, -1)
+    dx = torch.linspace(-radius, radius, 2 * radius + 1).view(1, -1).to(coords_x.device)
     x0 = dx + coords_x.view(-1, 1) / 2 ** level
     xg = _sdiv(2 * x0, Wl - 1, recip) - 1
     return x0, xg

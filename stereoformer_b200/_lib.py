@@ -1,0 +1,68 @@
+"""ctypes binding of libsfb200.so (the C ABI declared in include/stereoformer_b200.h).
+
+There is no CPU fallback: if the library is missing or does not load, importing an operator
+raises.  Build it with ``python -m stereoformer_b200.build`` (or ``__graft_entry__.build()``).
+"""
+import ctypes
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libsfb200.so")
+
+SF_ALGO_AUTO, SF_ALGO_TMA, SF_ALGO_GENERIC = 0, 1, 2
+SF_WIN_FIXED, SF_WIN_VARIANCE, SF_WIN_OFFSETS, SF_WIN_ABSOLUTE = 0, 1, 2, 3
+SF_DIV_TRUE, SF_DIV_RECIP = 0, 1
+
+_c_int, _c_float, _p = ctypes.c_int, ctypes.c_float, ctypes.c_void_p
+
+# name -> argtypes; mirrors include/stereoformer_b200.h (tests/test_abi.py checks both against the .so)
+SIGNATURES = {
+    "sf_corr_volume_f32": [_p, _p, _p] + [_c_int] * 7 + [_p],
+    "sf_shift_volume_f32": [_p, _p, _p] + [_c_int] * 6 + [_p],
+    "sf_soft_argmin_f32": [_p, _p, _p] + [_c_int] * 5 + [_p],
+    "sf_local_window_f32": [_p] * 10 + [_c_int] * 5 + [_c_float, _c_float] + [_c_int] * 3 + [_p],
+    "sf_sample_volume_f32": [_p] * 5 + [_c_int] * 5 + [_p],
+    "sf_disp_warp_f32": [_p] * 6 + [_c_int] * 6 + [_p, _p],
+    "sf_guidance_f32": [_p] * 6 + [_c_int] * 6 + [_p, _p],
+    "sf_corr1d_pyramid_f32": [_p, _p, _p] + [_c_int] * 7 + [_p],
+    "sf_corr1d_lookup_f32": [_p, _p, _c_int, _c_int, _p, _p, _p, _p] + [_c_int] * 4 + [_p],
+    "sf_dcn_forward_f32": [_p] * 6 + [_c_int] * 15 + [_p],
+    "sf_epipolar_attn_bf16": [_p] * 5 + [_c_int] * 6 + [_p],
+    "sf_upsample_convex_f32": [_p, _p, _p] + [_c_int] * 4 + [_p],
+}
+
+_lib = None
+
+
+class SFError(RuntimeError):
+    pass
+
+
+def lib():
+    """Load (once) and return the ctypes handle; raises if the CUDA library has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise SFError("stereoformer_b200: %s not found -- build it with `python -m stereoformer_b200.build`; "
+                          "there is no CPU fallback" % LIB_PATH)
+        h = ctypes.CDLL(LIB_PATH)
+        h.sf_last_error.restype = ctypes.c_char_p
+        h.sf_last_error.argtypes = []
+        h.sf_abi_version.restype = _c_int
+        h.sf_device_sm_count.restype = _c_int
+        for name, args in SIGNATURES.items():
+            fn = getattr(h, name)
+            fn.argtypes = args
+            fn.restype = _c_int
+        _lib = h
+    return _lib
+
+
+def call(name, *args):
+    h = lib()
+    rc = getattr(h, name)(*args)
+    if rc != 0:
+        msg = h.sf_last_error().decode("utf-8", "replace")
+        if rc == 1:
+            raise ValueError("%s: %s" % (name, msg))
+        raise SFError("%s failed (code %d): %s" % (name, rc, msg))

@@ -1,0 +1,191 @@
+// Deformable convolution forward, DCNv2 (modulated) and DCNv1 (mask == null)  (SURVEY 8a row a10).
+//
+// Reference: deform/src/cuda/modulated_deform_conv_cuda.cu:19-121 (host), modulated_deform_im2col_cuda.cuh:25-54,
+// 128-194 (bilinear + im2col kernel); DCNv1 twin deform_conv_cuda.cu:19-120, deform_im2col_cuda.cuh:127-189.
+//
+//   out[b,o,y,x] = bias[o] + sum_{c,i,j} W[o,c,i,j] * mask[b,g,ij,y,x] * bilinear(in[b,c], y*s-p+i*dil+dy, x*s-p+j*dil+dx)
+//
+// The reference materialises a [Cin*kh*kw, M] column buffer in HBM, runs cuBLAS over it and then permutes
+// NHWC->NCHW.  Here it is one fused implicit-GEMM kernel (fp32-exact FFMA path): per CTA the sampling
+// descriptors (4 corner offsets + 4 bilinear weights + mask) of a pixel tile are computed once per deformable
+// group and kept in shared memory, channel chunks of the column tile are gathered straight into shared memory,
+// multiplied with a transposed weight tile from registers-tiled FFMAs, and the epilogue adds the bias and
+// writes NCHW directly.  No column buffer, no permute, no im2col_step loop (it never affected results:
+// deform/test.py:219-260).
+#include "common.cuh"
+#include "../../include/stereoformer_b200.h"
+
+namespace sf {
+
+constexpr int DCN_KC = 8;  // input channels per shared-memory chunk
+
+struct DcnParams {
+  const float* in;      // [B,Cin,H,W]
+  const float* weight;  // [Cout,Cin/G,kh,kw]
+  const float* bias;    // [Cout]
+  const float* offset;  // [B,dg*2*kh*kw,Ho,Wo]
+  const float* mask;    // [B,dg*kh*kw,Ho,Wo] or null (DCNv1)
+  float* out;           // [B,Cout,Ho,Wo]
+  int B, Cin, H, W, Cout, Ho, Wo;
+  int kh, kw, sh, sw, ph, pw, dh, dw, G, dg;
+};
+
+template <int TO, int TP>
+__global__ void __launch_bounds__((TO / 4) * (TP / 4))
+dcn_forward_kernel(const DcnParams p) {
+  constexpr int NT = (TO / 4) * (TP / 4);
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int T = p.kh * p.kw;
+  int4* d_off = reinterpret_cast<int4*>(smem_raw);                  // [T][TP]
+  float4* d_w = reinterpret_cast<float4*>(d_off + T * TP);          // [T][TP]
+  float* d_m = reinterpret_cast<float*>(d_w + T * TP);              // [T][TP]
+  float* col = d_m + T * TP;                                        // [KC*T][TP]
+  float* wsm = col + DCN_KC * T * TP;                               // [KC*T][TO]
+
+  const int M = p.Ho * p.Wo;
+  const int pix0 = blockIdx.x * TP;
+  const int b = blockIdx.y;
+  const int Cig = p.Cin / p.G, Cog = p.Cout / p.G;
+  const int otiles = (Cog + TO - 1) / TO;
+  const int g = blockIdx.z / otiles, o0 = (blockIdx.z % otiles) * TO;
+  const int cpdg = p.Cin / p.dg;
+  const int tid = threadIdx.x;
+  const int tx = tid % (TP / 4), ty = tid / (TP / 4);
+  const size_t HW = static_cast<size_t>(p.H) * p.W;
+
+  float acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+
+  int cur_dg = -1;
+  for (int c0 = 0; c0 < Cig;) {
+    const int cin0 = g * Cig + c0;
+    const int dgi = cin0 / cpdg;
+    const int nkc = min(min(DCN_KC, Cig - c0), (dgi + 1) * cpdg - cin0);
+    __syncthreads();  // previous chunk's GEMM has finished reading col / wsm / descriptors
+    if (dgi != cur_dg) {
+      cur_dg = dgi;
+      // sampling descriptors of this deformable group (modulated_deform_im2col_cuda.cuh:25-54,163-180)
+      for (int e = tid; e < T * TP; e += NT) {
+        const int px = e % TP, t = e / TP;
+        const int pix = pix0 + px;
+        int4 off = make_int4(0, 0, 0, 0);
+        float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
+        float m = 0.f;
+        if (pix < M) {
+          const int yo = pix / p.Wo, xo = pix % p.Wo;
+          const int i = t / p.kw, j = t % p.kw;
+          const size_t ob = ((static_cast<size_t>(b) * p.dg + dgi) * 2 * T) * M + pix;
+          const float oh = __ldg(p.offset + ob + static_cast<size_t>(2 * t) * M);
+          const float ow = __ldg(p.offset + ob + static_cast<size_t>(2 * t + 1) * M);
+          m = p.mask ? __ldg(p.mask + ((static_cast<size_t>(b) * p.dg + dgi) * T + t) * M + pix) : 1.f;
+          const float h_im = (float)(yo * p.sh - p.ph + i * p.dh) + oh;
+          const float w_im = (float)(xo * p.sw - p.pw + j * p.dw) + ow;
+          if (h_im > -1.f && w_im > -1.f && h_im < (float)p.H && w_im < (float)p.W) {
+            const int hl = (int)floorf(h_im), wl = (int)floorf(w_im);
+            const int hh_i = hl + 1, wh_i = wl + 1;
+            const float lh = h_im - (float)hl, lw = w_im - (float)wl;
+            const float hh = 1.f - lh, hw = 1.f - lw;
+            const bool t0 = hl >= 0, l0 = wl >= 0, b1 = hh_i <= p.H - 1, r1 = wh_i <= p.W - 1;
+            if (t0 && l0) { off.x = hl * p.W + wl; w.x = hh * hw; }
+            if (t0 && r1) { off.y = hl * p.W + wh_i; w.y = hh * lw; }
+            if (b1 && l0) { off.z = hh_i * p.W + wl; w.z = lh * hw; }
+            if (b1 && r1) { off.w = hh_i * p.W + wh_i; w.w = lh * lw; }
+          }
+        }
+        d_off[e] = off; d_w[e] = w; d_m[e] = m;
+      }
+      __syncthreads();
+    }
+    // column tile: col[(c*T+t)][px] = bilinear(in[b,cin0+c]) * mask
+    for (int e = tid; e < nkc * T * TP; e += NT) {
+      const int px = e % TP, kt = e / TP;
+      const int c = kt / T, t = kt % T;
+      const float* src = p.in + (static_cast<size_t>(b) * p.Cin + cin0 + c) * HW;
+      const int4 off = d_off[t * TP + px];
+      const float4 w = d_w[t * TP + px];
+      const float val = w.x * __ldg(src + off.x) + w.y * __ldg(src + off.y) + w.z * __ldg(src + off.z) +
+                        w.w * __ldg(src + off.w);
+      col[kt * TP + px] = val * d_m[t * TP + px];
+    }
+    // weight tile, transposed: wsm[k][o] = W[g*Cog+o0+o][c0+c][t]
+    for (int e = tid; e < nkc * T * TO; e += NT) {
+      const int k = e % (nkc * T), o = e / (nkc * T);
+      float v = 0.f;
+      if (o0 + o < Cog) v = __ldg(p.weight + (static_cast<size_t>(g * Cog + o0 + o) * Cig + c0) * T + k);
+      wsm[k * TO + o] = v;
+    }
+    __syncthreads();
+    const int nk = nkc * T;
+    for (int k = 0; k < nk; ++k) {
+      const float4 a = *reinterpret_cast<const float4*>(col + k * TP + tx * 4);
+      const float4 w = *reinterpret_cast<const float4*>(wsm + k * TO + ty * 4);
+      const float av[4] = {a.x, a.y, a.z, a.w}, wv[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(wv[i], av[j], acc[i][j]);
+    }
+    c0 += nkc;
+  }
+
+  // epilogue: + bias, NCHW store (addmm(bias, cols^T, W^T) + permute of the reference, .cu:108-118)
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int o = o0 + ty * 4 + i;
+    if (o >= Cog) continue;
+    const int oc = g * Cog + o;
+    const float bv = __ldg(p.bias + oc);
+    float* dst = p.out + (static_cast<size_t>(b) * p.Cout + oc) * M + pix0 + tx * 4;
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+      if (pix0 + tx * 4 + j < M) dst[j] = acc[i][j] + bv;
+  }
+}
+
+template <int TO, int TP>
+static int launch_dcn(const DcnParams& p, cudaStream_t s) {
+  const int T = p.kh * p.kw;
+  const size_t smem = static_cast<size_t>(T) * TP * (16 + 16 + 4) + static_cast<size_t>(DCN_KC) * T * (TP + TO) * 4;
+  SF_CHECK_ARG(smem <= 200 * 1024, "dcn_forward: kernel %dx%d too large for the shared-memory tile", p.kh, p.kw);
+  auto kern = dcn_forward_kernel<TO, TP>;
+  SF_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+  const int Cog = p.Cout / p.G;
+  dim3 grid(ceil_div(p.Ho * p.Wo, TP), p.B, p.G * ceil_div(Cog, TO));
+  SF_CHECK_ARG(grid.y <= 65535 && grid.z <= 65535, "dcn_forward: batch or group count too large");
+  kern<<<grid, (TO / 4) * (TP / 4), smem, s>>>(p);
+  SF_LAUNCH_CHECK();
+  return SF_OK;
+}
+
+}  // namespace sf
+
+extern "C" int sf_dcn_forward_f32(const float* input, const float* weight, const float* bias, const float* offset,
+                                  const float* mask, float* out, int B, int Cin, int H, int W, int Cout, int kh, int kw,
+                                  int stride_h, int stride_w, int pad_h, int pad_w, int dil_h, int dil_w, int group,
+                                  int deformable_group, void* stream) {
+  using namespace sf;
+  SF_CHECK_ARG(input && weight && bias && offset && out, "dcn_forward: null pointer");
+  SF_CHECK_ARG(B > 0 && Cin > 0 && H > 0 && W > 0 && Cout > 0 && kh > 0 && kw > 0, "dcn_forward: non-positive dimension");
+  SF_CHECK_ARG(stride_h > 0 && stride_w > 0 && dil_h > 0 && dil_w > 0 && pad_h >= 0 && pad_w >= 0,
+               "dcn_forward: bad stride / dilation / padding");
+  SF_CHECK_ARG(group > 0 && Cin % group == 0 && Cout % group == 0,
+               "channels(%d) and channels_out(%d) must divide group(%d)", Cin, Cout, group);
+  SF_CHECK_ARG(deformable_group > 0 && Cin % deformable_group == 0,
+               "channels(%d) must divide deformable_group(%d)", Cin, deformable_group);
+  DcnParams p;
+  p.in = input; p.weight = weight; p.bias = bias; p.offset = offset; p.mask = mask; p.out = out;
+  p.B = B; p.Cin = Cin; p.H = H; p.W = W; p.Cout = Cout;
+  p.kh = kh; p.kw = kw; p.sh = stride_h; p.sw = stride_w; p.ph = pad_h; p.pw = pad_w; p.dh = dil_h; p.dw = dil_w;
+  p.G = group; p.dg = deformable_group;
+  p.Ho = (H + 2 * pad_h - (dil_h * (kh - 1) + 1)) / stride_h + 1;  // modulated_deform_conv_cuda.cu:75-76
+  p.Wo = (W + 2 * pad_w - (dil_w * (kw - 1) + 1)) / stride_w + 1;
+  SF_CHECK_ARG(p.Ho > 0 && p.Wo > 0, "dcn_forward: empty output (%d x %d)", p.Ho, p.Wo);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const int Cog = Cout / group;
+  if (Cog <= 16) return launch_dcn<16, 128>(p, s);
+  if (Cog <= 32) return launch_dcn<32, 128>(p, s);
+  return launch_dcn<64, 64>(p, s);
+}

@@ -1,0 +1,157 @@
+// Disparity warp and the DLC-GRU guidance stage  (SURVEY 8a rows a7 and a6 (i),(iii),(iv)).
+//
+// Reference: utils/disparity_warper.py:48-106 (meshgrid, normalize_coords, disp_warp, LRwarp_error);
+// models/LocalCostVolume/Attempts/update.py:68-86 (BasicGuidanceNet up to the conv encoders).
+//
+// The reference normalises with (size-1) but samples with F.grid_sample's default align_corners=False, so the
+// source position is ((2*((x-d)/(W-1))-1+1)*W-1)/2, not x-d, and y maps to y*H/(H-1)-0.5: a true 2-row bilinear
+// gather.  That quirk is reproduced op by op (pixel_math.h); the normalised grid is bit-identical to the
+// reference's.  One thread per pixel, all image channels; loads are coalesced along x.
+#include "common.cuh"
+#include "pixel_math.h"
+#include "../../include/stereoformer_b200.h"
+
+namespace sf {
+
+struct Bilin {
+  int x0, y0;                  // north-west corner
+  float wnw, wne, wsw, wse;    // ATen weights
+  bool inx0, inx1, iny0, iny1; // corner in-bounds flags
+  float gx, gy, ix, iy;
+};
+
+// ATen grid_sampler_2d (bilinear), align_corners=False; border mode clips the source coordinate.
+__device__ __forceinline__ Bilin warp_setup(float x, float y, float d, int H, int W, bool border, int recip) {
+  Bilin r;
+  r.gx = sfm::warp_norm(sfm::fadd(x, -d), W, recip);
+  r.gy = sfm::warp_norm(sfm::fadd(y, 0.f), H, recip);
+  float ix = sfm::warp_unnorm(r.gx, W), iy = sfm::warp_unnorm(r.gy, H);
+  if (border) {
+    ix = fminf((float)(W - 1), fmaxf(ix, 0.f));
+    iy = fminf((float)(H - 1), fmaxf(iy, 0.f));
+  }
+  r.ix = ix; r.iy = iy;
+  const float fx = floorf(ix), fy = floorf(iy);
+  // out-of-range coordinates (zeros padding, huge disparities) are clamped before the int cast
+  r.x0 = (int)fminf(fmaxf(fx, -2.f), (float)W);
+  r.y0 = (int)fminf(fmaxf(fy, -2.f), (float)H);
+  const float ex = fx + 1.f, ey = fy + 1.f;
+  r.wnw = (ex - ix) * (ey - iy);
+  r.wne = (ix - fx) * (ey - iy);
+  r.wsw = (ex - ix) * (iy - fy);
+  r.wse = (ix - fx) * (iy - fy);
+  r.inx0 = r.x0 >= 0 && r.x0 < W; r.inx1 = r.x0 + 1 >= 0 && r.x0 + 1 < W;
+  r.iny0 = r.y0 >= 0 && r.y0 < H; r.iny1 = r.y0 + 1 >= 0 && r.y0 + 1 < H;
+  return r;
+}
+
+__device__ __forceinline__ float warp_sample(const float* __restrict__ plane, const Bilin& g, int W) {
+  float o = 0.f;
+  const float* r0 = plane + static_cast<size_t>(g.y0) * W + g.x0;
+  if (g.iny0 && g.inx0) o += __ldg(r0) * g.wnw;
+  if (g.iny0 && g.inx1) o += __ldg(r0 + 1) * g.wne;
+  if (g.iny1 && g.inx0) o += __ldg(r0 + W) * g.wsw;
+  if (g.iny1 && g.inx1) o += __ldg(r0 + W + 1) * g.wse;
+  return o;
+}
+
+// valid_mask of disp_warp (:102-105): zeros-padding sample of an all-ones image, <0.9999 -> 0, >0 -> 1.
+__device__ __forceinline__ float warp_mask(float x, float y, float d, int H, int W, int recip) {
+  const Bilin g = warp_setup(x, y, d, H, W, false, recip);
+  float o = 0.f;
+  if (g.iny0 && g.inx0) o += g.wnw;
+  if (g.iny0 && g.inx1) o += g.wne;
+  if (g.iny1 && g.inx0) o += g.wsw;
+  if (g.iny1 && g.inx1) o += g.wse;
+  if (o < 0.9999f) o = 0.f;
+  if (o > 0.f) o = 1.f;
+  return o;
+}
+
+__global__ void __launch_bounds__(256)
+disp_warp_kernel(const float* __restrict__ img, const float* __restrict__ disp, float* __restrict__ warped,
+                 float* __restrict__ mask, float* __restrict__ dbg_grid, float* __restrict__ dbg_src, int B, int C,
+                 int H, int W, int border, int recip, int* __restrict__ neg_flag) {
+  const size_t HW = static_cast<size_t>(H) * W, n = static_cast<size_t>(B) * HW;
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int x = i % W, y = (i / W) % H;
+    const size_t b = i / HW;
+    const float d = disp[i];
+    if (d < 0.f && neg_flag) *neg_flag = 1;  // reference asserts disp.min() >= 0 (disparity_warper.py:93)
+    const Bilin g = warp_setup((float)x, (float)y, d, H, W, border != 0, recip);
+    if (dbg_grid) { dbg_grid[2 * i] = g.gx; dbg_grid[2 * i + 1] = g.gy; }
+    if (dbg_src) { dbg_src[2 * i] = g.ix; dbg_src[2 * i + 1] = g.iy; }
+    const float mk = mask ? warp_mask((float)x, (float)y, d, H, W, recip) : 0.f;
+    for (int c = 0; c < C; ++c) {
+      const size_t o = (b * C + c) * HW + (i % HW);
+      warped[o] = warp_sample(img + (b * C + c) * HW, g, W);
+      if (mask) mask[o] = mk;
+    }
+  }
+}
+
+// BasicGuidanceNet.forward up to the encoders, one pass per pixel:
+//   error_map = disp_warp(right, disp) - left      (update.py:82-83)
+//   uncertainty[d] = softmax(cv)[d] * d * (d-disp) * (d-disp)   (update.py:71,86)
+__global__ void __launch_bounds__(256)
+guidance_kernel(const float* __restrict__ cv, const float* __restrict__ disp, const float* __restrict__ left,
+                const float* __restrict__ right, float* __restrict__ err, float* __restrict__ unc, int B, int D, int C,
+                int H, int W, int recip, int* __restrict__ neg_flag) {
+  const size_t HW = static_cast<size_t>(H) * W, n = static_cast<size_t>(B) * HW;
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int x = i % W, y = (i / W) % H;
+    const size_t b = i / HW, r = i % HW;
+    const float d = disp[i];
+    if (d < 0.f && neg_flag) *neg_flag = 1;
+    const Bilin g = warp_setup((float)x, (float)y, d, H, W, true, recip);
+    for (int c = 0; c < C; ++c) {
+      const size_t o = (b * C + c) * HW + r;
+      err[o] = warp_sample(right + (b * C + c) * HW, g, W) - left[o];
+    }
+    const float* src = cv + b * D * HW + r;
+    float m = -INFINITY;
+    for (int k = 0; k < D; ++k) m = fmaxf(m, __ldg(src + k * HW));
+    float s = 0.f;
+    for (int k = 0; k < D; ++k) s += __expf(__ldg(src + k * HW) - m);
+    const float inv = 1.0f / s;
+    float* dst = unc + b * D * HW + r;
+    for (int k = 0; k < D; ++k) {
+      const float p = __expf(__ldg(src + k * HW) - m) * inv;
+      const float e = sfm::fsub((float)k, d);
+      dst[k * HW] = sfm::fmul(sfm::fmul(sfm::fmul(p, (float)k), e), e);
+    }
+  }
+}
+
+}  // namespace sf
+
+extern "C" int sf_disp_warp_f32(const float* img, const float* disp, float* warped, float* mask, float* dbg_grid,
+                                float* dbg_src, int B, int C, int H, int W, int border, int div_mode, int* neg_flag,
+                                void* stream) {
+  using namespace sf;
+  SF_CHECK_ARG(img && disp && warped, "disp_warp: null pointer");
+  SF_CHECK_ARG(B > 0 && C > 0 && H > 0 && W > 0, "disp_warp: non-positive dimension");
+  size_t n = static_cast<size_t>(B) * H * W;
+  int grid = static_cast<int>(min(static_cast<size_t>(sm_count()) * 8, (n + 255) / 256));
+  disp_warp_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(img, disp, warped, mask, dbg_grid, dbg_src, B,
+                                                                      C, H, W, border, div_mode == SF_DIV_RECIP,
+                                                                      neg_flag);
+  SF_LAUNCH_CHECK();
+  return SF_OK;
+}
+
+extern "C" int sf_guidance_f32(const float* cv, const float* disp, const float* left, const float* right, float* err,
+                               float* unc, int B, int D, int C, int H, int W, int div_mode, int* neg_flag,
+                               void* stream) {
+  using namespace sf;
+  SF_CHECK_ARG(cv && disp && left && right && err && unc, "guidance: null pointer");
+  SF_CHECK_ARG(B > 0 && D > 0 && C > 0 && H > 0 && W > 0, "guidance: non-positive dimension");
+  size_t n = static_cast<size_t>(B) * H * W;
+  int grid = static_cast<int>(min(static_cast<size_t>(sm_count()) * 8, (n + 255) / 256));
+  guidance_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(cv, disp, left, right, err, unc, B, D, C, H, W,
+                                                                     div_mode == SF_DIV_RECIP, neg_flag);
+  SF_LAUNCH_CHECK();
+  return SF_OK;
+}

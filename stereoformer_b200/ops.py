@@ -1,0 +1,254 @@
+"""Functional operators: thin PyTorch wrappers over the C ABI (device memory + stream plumbing only).
+
+Every function takes CUDA tensors, launches hand-written sm_100a kernels from libsfb200.so on the
+current PyTorch stream and returns freshly allocated CUDA tensors.  CPU tensors raise
+``RuntimeError("Not implemented on the CPU")`` like the reference's DCN extension
+(deform/src/modulated_deform_conv.h:43); nothing here computes on the host.
+"""
+import ctypes
+
+import torch
+
+from . import _lib
+from ._lib import (SF_ALGO_AUTO, SF_ALGO_GENERIC, SF_ALGO_TMA, SF_DIV_RECIP, SF_DIV_TRUE, SF_WIN_ABSOLUTE,
+                   SF_WIN_FIXED, SF_WIN_OFFSETS, SF_WIN_VARIANCE)
+
+__all__ = ["corr_volume", "gwc_volume", "shift_volume", "soft_argmin", "local_window", "sample_volume", "disp_warp",
+           "guidance", "corr1d_pyramid", "corr1d_lookup", "dcn_forward", "epipolar_attention", "upsample_convex"]
+
+
+def _chk(t, name, dtype=torch.float32, dim=None):
+    if not torch.is_tensor(t):
+        raise TypeError("%s must be a tensor" % name)
+    if not t.is_cuda:
+        raise RuntimeError("Not implemented on the CPU (%s is a CPU tensor; stereoformer_b200 has no CPU path)" % name)
+    if t.dtype != dtype:
+        raise TypeError("%s must be %s, got %s" % (name, dtype, t.dtype))
+    if dim is not None and t.dim() != dim:
+        raise ValueError("%s must be %d-D, got shape %s" % (name, dim, tuple(t.shape)))
+    return t.contiguous()
+
+
+def _ptr(t):
+    return ctypes.c_void_p(t.data_ptr()) if t is not None else None
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def corr_volume(left, right, max_disp, groups=1, algo=SF_ALGO_AUTO):
+    """CostVolume('correlation') / build_gwc_volume.  Returns [B,D,H,W] (groups=1) or [B,G,D,H,W]."""
+    left, right = _chk(left, "left_feature", dim=4), _chk(right, "right_feature", dim=4)
+    if left.shape != right.shape:
+        raise ValueError("feature shapes differ: %s vs %s" % (tuple(left.shape), tuple(right.shape)))
+    B, C, H, W = left.shape
+    shape = (B, max_disp, H, W) if groups == 1 else (B, groups, max_disp, H, W)
+    out = torch.empty(shape, device=left.device, dtype=torch.float32)
+    with torch.cuda.device(left.device):
+        _lib.call("sf_corr_volume_f32", _ptr(left), _ptr(right), _ptr(out), B, C, H, W, int(max_disp), int(groups),
+                  int(algo), _stream())
+    return out
+
+
+def gwc_volume(left, right, max_disp, num_groups):
+    if left.shape[1] % num_groups != 0:
+        raise AssertionError("channels not divisible by num_groups")
+    return corr_volume(left, right, max_disp, groups=num_groups).view(left.shape[0], num_groups, max_disp,
+                                                                      left.shape[2], left.shape[3])
+
+
+def shift_volume(left, right, max_disp, concat=False):
+    """CostVolume('difference' | 'concat'): [B, C or 2C, D, H, W]."""
+    left, right = _chk(left, "left_feature", dim=4), _chk(right, "right_feature", dim=4)
+    B, C, H, W = left.shape
+    out = torch.empty((B, 2 * C if concat else C, max_disp, H, W), device=left.device, dtype=torch.float32)
+    with torch.cuda.device(left.device):
+        _lib.call("sf_shift_volume_f32", _ptr(left), _ptr(right), _ptr(out), B, C, H, W, int(max_disp), int(concat),
+                  _stream())
+    return out
+
+
+def soft_argmin(cv, match_similarity=True, with_prob=False):
+    cv = _chk(cv, "cost_volume", dim=4)
+    B, D, H, W = cv.shape
+    disp = torch.empty((B, H, W), device=cv.device, dtype=torch.float32)
+    prob = torch.empty_like(cv) if with_prob else None
+    with torch.cuda.device(cv.device):
+        _lib.call("sf_soft_argmin_f32", _ptr(cv), _ptr(disp), _ptr(prob), B, D, H, W, int(bool(match_similarity)),
+                  _stream())
+    return (disp, prob) if with_prob else disp
+
+
+def local_window(cv, disp=None, lo=None, up=None, mode=SF_WIN_FIXED, radius=0.0, gamma=1.0, n_points=10,
+                 consider_valid=False, div_mode=SF_DIV_TRUE, debug=False, return_disp0=False):
+    """Local disparity-window sampling + soft-max expectation -> [B,1,H,W].
+
+    debug=True additionally returns dict(cand, idx_floor, idx_ceil, local) for the bit-exact checks."""
+    cv = _chk(cv, "old_cost_volume", dim=4)
+    B, D, H, W = cv.shape
+    if disp is not None:
+        disp = _chk(disp, "cur_disparity")
+        if disp.numel() != B * H * W:
+            raise ValueError("cur_disparity must have B*H*W elements")
+    lo = _chk(lo, "lower bound") if lo is not None else None
+    up = _chk(up, "upper bound") if up is not None else None
+    out = torch.empty((B, 1, H, W), device=cv.device, dtype=torch.float32)
+    d0 = torch.empty((B, 1, H, W), device=cv.device, dtype=torch.float32) if return_disp0 else None
+    dbg = {}
+    if debug:
+        K = n_points + 1
+        dbg = dict(cand=torch.empty((B, K, H, W), device=cv.device, dtype=torch.float32),
+                   idx_floor=torch.empty((B, K, H, W), device=cv.device, dtype=torch.int32),
+                   idx_ceil=torch.empty((B, K, H, W), device=cv.device, dtype=torch.int32),
+                   local=torch.empty((B, K, H, W), device=cv.device, dtype=torch.float32))
+    with torch.cuda.device(cv.device):
+        _lib.call("sf_local_window_f32", _ptr(cv), _ptr(disp), _ptr(lo), _ptr(up), _ptr(out), _ptr(d0),
+                  _ptr(dbg.get("cand")), _ptr(dbg.get("idx_floor")), _ptr(dbg.get("idx_ceil")), _ptr(dbg.get("local")),
+                  B, D, H, W, int(mode), float(radius), float(gamma), int(n_points), int(bool(consider_valid)),
+                  int(div_mode), _stream())
+    res = (out,)
+    if return_disp0:
+        res += (d0,)
+    if debug:
+        res += (dbg,)
+    return res[0] if len(res) == 1 else res
+
+
+def sample_volume(old_volume, cand, return_indices=False):
+    """build_cost_volume_from_volume(old_volume, sampling_candidates) -> [B,K,H,W] (bit-exact)."""
+    cv, cand = _chk(old_volume, "old_volume", dim=4), _chk(cand, "sampling_candidates", dim=4)
+    B, D, H, W = cv.shape
+    K = cand.shape[1]
+    if cand.shape != (B, K, H, W):
+        raise ValueError("sampling_candidates shape %s does not match volume %s" % (tuple(cand.shape), tuple(cv.shape)))
+    out = torch.empty_like(cand)
+    jf = torch.empty(cand.shape, device=cv.device, dtype=torch.int32) if return_indices else None
+    ic = torch.empty(cand.shape, device=cv.device, dtype=torch.int32) if return_indices else None
+    with torch.cuda.device(cv.device):
+        _lib.call("sf_sample_volume_f32", _ptr(cv), _ptr(cand), _ptr(out), _ptr(jf), _ptr(ic), B, D, K, H, W, _stream())
+    return (out, jf, ic) if return_indices else out
+
+
+def disp_warp(img, disp, padding_mode="border", div_mode=SF_DIV_TRUE, check=True, with_mask=True, debug=False):
+    """disp_warp -> (warped, valid_mask).  check=True keeps the reference's ``assert disp.min() >= 0``
+    (one device->host read, like the reference); check=False is sync-free (CUDA-graph safe)."""
+    img, disp = _chk(img, "img", dim=4), _chk(disp, "disp")
+    B, C, H, W = img.shape
+    if disp.numel() != B * H * W:
+        raise ValueError("disp must be [B,1,H,W]")
+    if padding_mode not in ("border", "zeros"):
+        raise ValueError("padding_mode must be 'border' or 'zeros'")
+    warped = torch.empty_like(img)
+    mask = torch.empty_like(img) if with_mask else None
+    flag = torch.zeros(1, device=img.device, dtype=torch.int32) if check else None
+    grid = torch.empty((B, H, W, 2), device=img.device, dtype=torch.float32) if debug else None
+    src = torch.empty((B, H, W, 2), device=img.device, dtype=torch.float32) if debug else None
+    with torch.cuda.device(img.device):
+        _lib.call("sf_disp_warp_f32", _ptr(img), _ptr(disp), _ptr(warped), _ptr(mask), _ptr(grid), _ptr(src), B, C, H, W,
+                  int(padding_mode == "border"), int(div_mode), _ptr(flag), _stream())
+    if check and int(flag.item()) != 0:
+        raise AssertionError("disp.min() >= 0 violated")
+    if debug:
+        return warped, mask, dict(grid=grid, src=src)
+    return warped, mask
+
+
+def guidance(cv, disp, left, right, div_mode=SF_DIV_TRUE, flag=None):
+    """Fused BasicGuidanceNet prologue -> (error_map [B,C,H,W], uncertainty_volume [B,D,H,W])."""
+    cv, disp = _chk(cv, "old_cost_volume", dim=4), _chk(disp, "cur_disp")
+    left, right = _chk(left, "left_image", dim=4), _chk(right, "right_image", dim=4)
+    B, D, H, W = cv.shape
+    C = left.shape[1]
+    if left.shape != (B, C, H, W) or right.shape != left.shape:
+        raise ValueError("images must be [B,C,H,W] at the disparity resolution")
+    err = torch.empty_like(left)
+    unc = torch.empty_like(cv)
+    with torch.cuda.device(cv.device):
+        _lib.call("sf_guidance_f32", _ptr(cv), _ptr(disp), _ptr(left), _ptr(right), _ptr(err), _ptr(unc), B, D, C, H, W,
+                  int(div_mode), _ptr(flag), _stream())
+    return err, unc
+
+
+def corr1d_pyramid(f1, f2, num_levels=4, extra_level=True, algo=SF_ALGO_AUTO):
+    """CorrBlock1D pyramid: list of [B*H*W1,1,1,W2>>l]; extra_level keeps the reference's unused last level."""
+    f1, f2 = _chk(f1, "fmap1", dim=4), _chk(f2, "fmap2", dim=4)
+    B, C, H, W1 = f1.shape
+    W2 = f2.shape[3]
+    n_out = num_levels + (1 if extra_level else 0)
+    while n_out > 1 and (W2 >> (n_out - 1)) < 1:
+        n_out -= 1
+    lv = [torch.empty((B * H * W1, 1, 1, W2 >> l), device=f1.device, dtype=torch.float32) for l in range(n_out)]
+    arr = (ctypes.c_void_p * n_out)(*[t.data_ptr() for t in lv])
+    with torch.cuda.device(f1.device):
+        _lib.call("sf_corr1d_pyramid_f32", _ptr(f1), _ptr(f2), ctypes.cast(arr, ctypes.c_void_p), n_out, B, C, H, W1, W2,
+                  int(algo), _stream())
+    return lv
+
+
+def corr1d_lookup(pyramid, coords, radius=4, num_levels=4, div_mode=SF_DIV_TRUE, debug=False):
+    coords = _chk(coords, "coords", dim=4)
+    B, _, H, W1 = coords.shape
+    lv = [_chk(p, "pyramid level") for p in pyramid[:num_levels]]
+    ptrs = (ctypes.c_void_p * num_levels)(*[t.data_ptr() for t in lv])
+    widths = (ctypes.c_int * num_levels)(*[t.shape[-1] for t in lv])
+    ch = num_levels * (2 * radius + 1)
+    out = torch.empty((B, ch, H, W1), device=coords.device, dtype=torch.float32)
+    x0 = torch.empty_like(out) if debug else None
+    src = torch.empty_like(out) if debug else None
+    with torch.cuda.device(coords.device):
+        _lib.call("sf_corr1d_lookup_f32", ctypes.cast(ptrs, ctypes.c_void_p), ctypes.cast(widths, ctypes.c_void_p),
+                  num_levels, int(radius), _ptr(coords), _ptr(out), _ptr(x0), _ptr(src), B, H, W1, int(div_mode),
+                  _stream())
+    return (out, dict(x0=x0, src=src)) if debug else out
+
+
+def dcn_forward(inp, weight, bias, offset, mask, stride, padding, dilation, groups, deformable_groups):
+    """DCNv2 (mask given) / DCNv1 (mask None) forward -> [B,Cout,Ho,Wo]."""
+    inp, weight = _chk(inp, "input", dim=4), _chk(weight, "weight", dim=4)
+    bias, offset = _chk(bias, "bias"), _chk(offset, "offset", dim=4)
+    mask = _chk(mask, "mask", dim=4) if mask is not None else None
+    B, Cin, H, W = inp.shape
+    Cout, Cg, kh, kw = weight.shape
+    sh, sw = stride
+    ph, pw = padding
+    dh, dw = dilation
+    if Cin != Cg * groups:
+        raise RuntimeError("Input shape and kernel channels wont match: (%d vs %d)." % (Cin, Cg * groups))
+    Ho = (H + 2 * ph - (dh * (kh - 1) + 1)) // sh + 1
+    Wo = (W + 2 * pw - (dw * (kw - 1) + 1)) // sw + 1
+    if offset.shape != (B, deformable_groups * 2 * kh * kw, Ho, Wo):
+        raise RuntimeError("offset shape %s, expected %s" % (tuple(offset.shape),
+                                                             (B, deformable_groups * 2 * kh * kw, Ho, Wo)))
+    if mask is not None and mask.shape != (B, deformable_groups * kh * kw, Ho, Wo):
+        raise RuntimeError("mask shape %s, expected %s" % (tuple(mask.shape), (B, deformable_groups * kh * kw, Ho, Wo)))
+    out = torch.empty((B, Cout, Ho, Wo), device=inp.device, dtype=torch.float32)
+    with torch.cuda.device(inp.device):
+        _lib.call("sf_dcn_forward_f32", _ptr(inp), _ptr(weight), _ptr(bias), _ptr(offset), _ptr(mask), _ptr(out), B, Cin,
+                  H, W, Cout, kh, kw, sh, sw, ph, pw, dh, dw, int(groups), int(deformable_groups), _stream())
+    return out
+
+
+def epipolar_attention(q, k, v, band, return_scores=False, algo=SF_ALGO_AUTO):
+    """Band-restricted epipolar row cross-attention, bf16 [B,C,H,W] in/out (spec-derived)."""
+    q, k, v = (_chk(t, n, dtype=torch.bfloat16, dim=4) for t, n in ((q, "q"), (k, "k"), (v, "v")))
+    if not (q.shape == k.shape == v.shape):
+        raise ValueError("q, k, v must share one shape")
+    B, C, H, W = q.shape
+    out = torch.empty_like(q)
+    sc = torch.empty((B, band, H, W), device=q.device, dtype=torch.float32) if return_scores else None
+    with torch.cuda.device(q.device):
+        _lib.call("sf_epipolar_attn_bf16", _ptr(q), _ptr(k), _ptr(v), _ptr(out), _ptr(sc), B, C, H, W, int(band),
+                  int(algo), _stream())
+    return (out, sc) if return_scores else out
+
+
+def upsample_convex(disp, mask, factor=8):
+    disp, mask = _chk(disp, "disp", dim=4), _chk(mask, "mask", dim=4)
+    N, _, H, W = disp.shape
+    if mask.shape != (N, 9 * factor * factor, H, W):
+        raise ValueError("mask must be [N,%d,H,W]" % (9 * factor * factor))
+    out = torch.empty((N, 1, factor * H, factor * W), device=disp.device, dtype=torch.float32)
+    with torch.cuda.device(disp.device):
+        _lib.call("sf_upsample_convex_f32", _ptr(disp), _ptr(mask), _ptr(out), N, H, W, int(factor), _stream())
+    return out

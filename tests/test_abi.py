@@ -1,0 +1,61 @@
+"""The C-ABI shared library loads and exports every symbol include/stereoformer_b200.h declares (no compute)."""
+import ctypes
+import os
+import re
+
+import pytest
+
+from conftest import ROOT
+
+
+def declared():
+    txt = open(os.path.join(ROOT, "include", "stereoformer_b200.h")).read()
+    return re.findall(r"SF_API\s+[\w\s\*]+?\b(sf_\w+)\s*\(", txt)
+
+
+@pytest.fixture(scope="module")
+def so():
+    import __graft_entry__ as ge
+    ge.build()
+    from stereoformer_b200 import _lib
+    return _lib
+
+
+def test_header_symbols_exported(so):
+    names = declared()
+    assert len(names) >= 14
+    h = ctypes.CDLL(so.LIB_PATH)
+    for n in names:
+        assert hasattr(h, n), "missing export " + n
+
+
+def test_python_binding_covers_header(so):
+    names = set(declared()) - {"sf_last_error", "sf_abi_version", "sf_device_sm_count"}
+    assert names == set(so.SIGNATURES), names ^ set(so.SIGNATURES)
+    assert so.lib().sf_abi_version() == 1
+
+
+def test_header_arity_matches_binding(so):
+    txt = open(os.path.join(ROOT, "include", "stereoformer_b200.h")).read()
+    for name, args in so.SIGNATURES.items():
+        m = re.search(r"\b%s\s*\(([^;]*?)\)\s*;" % name, txt, re.S)
+        assert m, name
+        assert len([a for a in m.group(1).split(",") if a.strip()]) == len(args), name
+
+
+def test_cpu_tensors_fail_loudly(so):
+    import torch
+    import stereoformer_b200 as sf
+    with pytest.raises(RuntimeError, match="Not implemented on the CPU"):
+        sf.CostVolume(8)(torch.randn(1, 4, 2, 8), torch.randn(1, 4, 2, 8))
+    with pytest.raises(RuntimeError, match="Not implemented on the CPU"):
+        sf.ModulatedDeformConvPack(4, 4, 3, 1, 1)(torch.randn(1, 4, 5, 5))
+
+
+def test_product_never_imports_oracle():
+    pkg = os.path.join(ROOT, "stereoformer_b200")
+    for dp, _, fs in os.walk(pkg):
+        for f in fs:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                src = open(os.path.join(dp, f)).read()
+                assert "import oracle" not in src and "from oracle" not in src and "oracle/" not in src, f

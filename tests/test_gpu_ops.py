@@ -1,0 +1,249 @@
+"""GPU parity: warp, guidance, CorrBlock1D, DCN, epipolar attention, convex upsampling and the drop-in
+modules -- CUDA kernels (through the C ABI) vs the oracle / golden vectors."""
+import pytest
+import torch
+import torch.nn as nn
+
+from conftest import load_golden
+from oracle import dcn_c
+from oracle import stereo_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+def dev(t):
+    return t.cuda()
+
+
+@pytest.fixture(scope="module")
+def ops():
+    import stereoformer_b200.ops as ops
+    return ops
+
+
+# ------------------------------------------------------------------------------------------ a7 warp
+def test_disp_warp_golden(ops):
+    g = load_golden("disp_warp")
+    w, m, dbg = ops.disp_warp(dev(g["img"]), dev(g["disp"]), "border", div_mode=ops.SF_DIV_TRUE, debug=True)
+    assert torch.equal(dbg["grid"].cpu(), g["grid"])                     # normalised sampling grid: bit-exact
+    H, W = g["img"].shape[-2:]
+    ix, iy = O.warp_source_coords(g["grid"], H, W, border=True)
+    assert torch.equal(dbg["src"].cpu()[..., 0], ix) and torch.equal(dbg["src"].cpu()[..., 1], iy)
+    assert torch.allclose(w.cpu(), g["warped_border"], rtol=1e-4, atol=1e-5)
+    assert torch.equal(m.cpu(), g["mask_border"])
+    wz, mz = ops.disp_warp(dev(g["img"]), dev(g["disp"]), "zeros", div_mode=ops.SF_DIV_TRUE)
+    assert torch.allclose(wz.cpu(), g["warped_zeros"], rtol=1e-4, atol=1e-5)
+    assert torch.equal(mz.cpu(), g["mask_zeros"])
+
+
+@pytest.mark.parametrize("shape", [(8, 3, 68, 120), (1, 3, 248, 360), (2, 5, 7, 33)])
+def test_disp_warp_oracle(ops, shape):
+    torch.manual_seed(23)
+    B, C, H, W = shape
+    img, disp = torch.randn(B, C, H, W), torch.rand(B, 1, H, W) * W * 0.4
+    rw, rm = O.disp_warp(img, disp)
+    w, m = ops.disp_warp(dev(img), dev(disp), div_mode=ops.SF_DIV_TRUE)
+    assert torch.allclose(w.cpu(), rw, rtol=1e-4, atol=1e-4)
+    assert (m.cpu() != rm).float().mean() < 1e-4        # threshold 0.9999 may flip on a last-bit coordinate
+    # zero disparity is NOT the identity (align_corners quirk, SURVEY 8c iv)
+    w0, _ = ops.disp_warp(dev(img), torch.zeros(B, 1, H, W, device="cuda"), div_mode=ops.SF_DIV_TRUE)
+    r0, _ = O.disp_warp(img, torch.zeros(B, 1, H, W))
+    assert torch.allclose(w0.cpu(), r0, rtol=1e-4, atol=1e-4)
+    assert not torch.allclose(w0.cpu(), img, atol=1e-3)
+
+
+def test_disp_warp_matches_pytorch_cuda(ops):
+    """Against PyTorch's own CUDA kernels (what the reference executes on a GPU), reciprocal division."""
+    torch.manual_seed(29)
+    img, disp = torch.randn(2, 3, 20, 120, device="cuda"), torch.rand(2, 1, 20, 120, device="cuda") * 30
+    grid = O.warp_grid(disp, 20, 120)
+    _, _, dbg = ops.disp_warp(img, disp, div_mode=ops.SF_DIV_RECIP, debug=True)
+    assert torch.equal(dbg["grid"], grid)
+    rw, rm = O.disp_warp(img, disp)
+    w, m = ops.disp_warp(img, disp, div_mode=ops.SF_DIV_RECIP)
+    assert torch.allclose(w, rw, rtol=1e-4, atol=1e-4)
+    assert (m != rm).float().mean() < 1e-4
+
+
+def test_disp_warp_negative_raises(ops):
+    img, disp = torch.randn(1, 3, 4, 16, device="cuda"), torch.rand(1, 1, 4, 16, device="cuda")
+    disp[0, 0, 1, 3] = -0.5
+    with pytest.raises(AssertionError):
+        ops.disp_warp(img, disp)
+    ops.disp_warp(img, disp, check=False)      # sync-free path does not raise
+
+
+def test_guidance_oracle(ops):
+    g = load_golden("uncertainty")
+    torch.manual_seed(31)
+    B, D, H, W = g["cv"].shape
+    left, right = torch.randn(B, 3, H, W), torch.randn(B, 3, H, W)
+    e_ref, u_ref = O.guidance(g["cv"], g["cur"], left, right)
+    err, unc = ops.guidance(dev(g["cv"]), dev(g["cur"]), dev(left), dev(right), div_mode=ops.SF_DIV_TRUE)
+    assert torch.allclose(unc.cpu(), g["unc"], rtol=1e-4, atol=1e-5)
+    assert torch.allclose(unc.cpu(), u_ref, rtol=1e-4, atol=1e-5)
+    assert torch.allclose(err.cpu(), e_ref, rtol=1e-4, atol=1e-4)
+
+
+# ------------------------------------------------------------------------------------------ a8 / a9 CorrBlock1D
+def test_corr1d_golden(ops):
+    g = load_golden("corr1d")
+    pyr = ops.corr1d_pyramid(dev(g["f1"]), dev(g["f2"]), g["num_levels"])
+    assert len(pyr) == g["num_levels"] + 1
+    for i, p in enumerate(pyr):
+        assert p.shape == g["pyr%d" % i].shape
+        assert torch.allclose(p.cpu(), g["pyr%d" % i], rtol=1e-4, atol=1e-5)
+    # lookup on the golden pyramid isolates the lookup kernel
+    gp = [dev(g["pyr%d" % i]) for i in range(g["num_levels"])]
+    out, dbg = ops.corr1d_lookup(gp, dev(g["coords"]), g["radius"], g["num_levels"], div_mode=ops.SF_DIV_TRUE,
+                                 debug=True)
+    assert torch.allclose(out.cpu(), g["lookup"], rtol=1e-4, atol=1e-5)
+    B, _, H, W = g["coords"].shape
+    taps = 2 * g["radius"] + 1
+    for l in range(g["num_levels"]):
+        x0, _ = O.corr1d_lookup_coords(g["coords"][:, 0].reshape(-1), l, g["radius"], gp[l].shape[-1])
+        got = dbg["x0"][:, l * taps:(l + 1) * taps].permute(0, 2, 3, 1).reshape(-1, taps)
+        assert torch.equal(got.cpu(), x0)                               # lookup coordinates: bit-exact
+
+
+@pytest.mark.parametrize("shape", [(1, 256, 8, 240), (2, 32, 3, 100), (1, 20, 2, 37)])
+def test_corr1d_oracle(ops, shape):
+    torch.manual_seed(37)
+    B, C, H, W = shape
+    f1, f2 = torch.randn(B, C, H, W), torch.randn(B, C, H, W)
+    ref = O.corr1d_pyramid(f1, f2, 4)
+    pyr = ops.corr1d_pyramid(dev(f1), dev(f2), 4)
+    for p, r in zip(pyr, ref):
+        assert p.shape == r.shape
+        assert torch.allclose(p.cpu(), r, rtol=1e-4, atol=2e-5)
+    xs = torch.arange(W).float().view(1, 1, 1, W).repeat(B, 1, H, 1)
+    coords = torch.cat((xs - torch.rand(B, 1, H, W) * W / 4, torch.zeros(B, 1, H, W)), 1)
+    lref = O.corr1d_lookup(ref, coords, 4, 4)
+    out = ops.corr1d_lookup([dev(r) for r in ref], dev(coords), 4, 4, div_mode=ops.SF_DIV_TRUE)
+    assert torch.allclose(out.cpu(), lref, rtol=1e-4, atol=2e-5)
+    # KAT (SURVEY 8c v): integer coordinates at level 0 return V[x1, x1 + dx]
+    ci = torch.cat((xs, torch.zeros(B, 1, H, W)), 1)
+    o0 = ops.corr1d_lookup([dev(r) for r in ref], dev(ci), 4, 4, div_mode=ops.SF_DIV_TRUE).cpu()
+    v0 = ref[0].view(B, H, W, W)
+    for t, dx in enumerate(range(-4, 5)):
+        x2 = torch.arange(W) + dx
+        ok = (x2 >= 0) & (x2 < W)
+        want = torch.where(ok, v0[:, :, torch.arange(W), x2.clamp(0, W - 1)], torch.zeros(()))
+        assert torch.allclose(o0[:, t], want, rtol=1e-4, atol=2e-5)
+
+
+# ------------------------------------------------------------------------------------------ a10 DCN
+def test_dcn_reference_analytic_checks():
+    """deform/test.py:69-110, 142-181, 219-260 translated 1:1 to the drop-in DCN module."""
+    from stereoformer_b200 import DCN
+    from stereoformer_b200.dcn_modules import ModulatedDeformConv, DeformConv, ModulatedDeformConvPack
+    torch.manual_seed(3)
+    N, inC, inH, inW, outC = 2, 4, 4, 4, 4
+    conv = nn.Conv2d(inC, outC, 3, stride=1, padding=1, groups=2, bias=True).cuda()
+    md = ModulatedDeformConv(inC, outC, 3, 1, 1, 1, groups=2, deformable_groups=1, im2col_step=1).cuda()
+    md.weight.data.copy_(conv.weight.data)
+    md.bias.data.copy_(conv.bias.data)
+    x = torch.randn(N, inC, inH, inW).cuda()
+    off = torch.zeros(N, 18, inH, inW).cuda()
+    msk = torch.ones(N, 9, inH, inW).cuda()
+    with torch.no_grad():
+        assert (md(x, off, msk) - conv(x)).abs().max() < 1e-5          # zero offset == conv2d
+        d1 = DeformConv(inC, outC, 3, 1, 1, 1, groups=2, deformable_groups=1, im2col_step=1).cuda()
+        d1.weight.data.copy_(conv.weight.data)
+        d1.bias.data.copy_(conv.bias.data)
+        assert (d1(x, off) - conv(x)).abs().max() < 1e-5
+        # identity weights, mask 0.5 -> 2 * out == in
+        mi = ModulatedDeformConv(inC, inC, 3, 1, 1, 1, groups=inC, deformable_groups=1, im2col_step=1, bias=False).cuda()
+        mi.weight.data.zero_()
+        mi.weight.data[:, 0, 1, 1] = 1.0
+        mi.bias.data.zero_()
+        assert (2 * mi(x, off, msk * 0.5) - x).abs().max() < 1e-6
+        # im2col_step invariance + the divisibility error
+        offr = torch.randn(N, 18, inH, inW).cuda() * 2
+        mr = torch.sigmoid(torch.randn(N, 9, inH, inW).cuda())
+        md2 = ModulatedDeformConv(inC, outC, 3, 1, 1, 1, groups=2, deformable_groups=1, im2col_step=2).cuda()
+        md2.load_state_dict(md.state_dict())
+        assert torch.equal(md(x, offr, mr), md2(x, offr, mr))
+        with pytest.raises(RuntimeError, match="must divide im2col_step"):
+            DCN.modulated_deform_conv_forward(torch.cat([x, x[:1]]), md.weight, md.bias, torch.cat([offr, offr[:1]]),
+                                              torch.cat([mr, mr[:1]]), 3, 3, 1, 1, 1, 1, 1, 1, 2, 1, 2)
+        # a fresh Pack is 0.5 * conv2d + bias (zero-initialised offsets, mask = sigmoid(0))
+        pk = ModulatedDeformConvPack(inC, outC, 3, 1, 1).cuda()
+        ref = 0.5 * nn.functional.conv2d(x, pk.weight, None, 1, 1) + pk.bias.view(1, -1, 1, 1)
+        assert (pk(x) - ref).abs().max() < 1e-5
+    with pytest.raises(RuntimeError, match="Not implemented on the CPU"):
+        md.cpu()(x.cpu(), off.cpu(), msk.cpu())
+
+
+@pytest.mark.parametrize("cfg", [dict(B=2, Cin=16, Cout=16, H=17, W=30, G=1, dg=1, s=1, p=1, d=1),     # shipped shape
+                                 dict(B=2, Cin=64, Cout=128, H=12, W=20, G=1, dg=2, s=1, p=1, d=1),    # test.py:526
+                                 dict(B=1, Cin=24, Cout=40, H=9, W=11, G=2, dg=3, s=2, p=2, d=2),
+                                 dict(B=1, Cin=6, Cout=3, H=6, W=6, G=3, dg=3, s=1, p=0, d=1),
+                                 dict(B=1, Cin=128, Cout=128, H=8, W=10, G=1, dg=1, s=1, p=1, d=1)])
+def test_dcn_vs_c_oracle(ops, cfg):
+    torch.manual_seed(41)
+    B, Cin, Cout, H, W, G, dg, s, p, d = (cfg[k] for k in ("B", "Cin", "Cout", "H", "W", "G", "dg", "s", "p", "d"))
+    x = torch.randn(B, Cin, H, W)
+    w = torch.randn(Cout, Cin // G, 3, 3) / (3 * (Cin // G) ** 0.5)
+    b = torch.randn(Cout)
+    Ho = (H + 2 * p - (d * 2 + 1)) // s + 1
+    Wo = (W + 2 * p - (d * 2 + 1)) // s + 1
+    off = torch.randn(B, dg * 18, Ho, Wo) * 2
+    msk = torch.sigmoid(torch.randn(B, dg * 9, Ho, Wo))
+    ref = dcn_c.dcn_forward(x, w, b, off, msk, (s, s), (p, p), (d, d), G, dg)
+    out = ops.dcn_forward(dev(x), dev(w), dev(b), dev(off), dev(msk), (s, s), (p, p), (d, d), G, dg)
+    assert out.shape == ref.shape
+    assert torch.allclose(out.cpu(), ref, rtol=1e-4, atol=1e-4)
+    ref1 = dcn_c.dcn_forward(x, w, b, off, None, (s, s), (p, p), (d, d), G, dg)
+    out1 = ops.dcn_forward(dev(x), dev(w), dev(b), dev(off), None, (s, s), (p, p), (d, d), G, dg)
+    assert torch.allclose(out1.cpu(), ref1, rtol=1e-4, atol=1e-4)
+
+
+# ------------------------------------------------------------------------------------------ a11 attention (spec-derived)
+@pytest.mark.parametrize("shape,band", [((1, 128, 6, 312), 48), ((2, 32, 3, 40), 8), ((1, 256, 2, 100), 64),
+                                        ((1, 16, 2, 10), 24)])
+def test_epipolar_attention_oracle(ops, shape, band):
+    torch.manual_seed(43)
+    q, k, v = (torch.randn(*shape).bfloat16() for _ in range(3))
+    o_ref, s_ref = O.epipolar_attention(q, k, v, band)
+    out, sc = ops.epipolar_attention(dev(q), dev(k), dev(v), band, return_scores=True)
+    assert torch.allclose(out.float().cpu(), o_ref, rtol=2e-2, atol=2e-2)      # bf16 output
+    fin = torch.isfinite(s_ref)
+    assert torch.equal(torch.isfinite(sc.cpu()), fin)
+    assert torch.allclose(sc.cpu()[fin], s_ref[fin], rtol=1e-4, atol=1e-4)
+
+
+# ------------------------------------------------------------------------------------------ f1 upsampling
+def test_upsample_convex_golden(ops):
+    g = load_golden("upsample_convex8")
+    out = ops.upsample_convex(dev(g["disp"]), dev(g["mask"]), 8)
+    assert torch.allclose(out.cpu(), g["out"], rtol=1e-4, atol=1e-4)
+    torch.manual_seed(47)
+    d, m = torch.rand(2, 1, 9, 13) * 20, torch.randn(2, 9 * 16, 9, 13)
+    assert torch.allclose(ops.upsample_convex(dev(d), dev(m), 4).cpu(), O.upsample_convex(d, m, 4), rtol=1e-4, atol=1e-4)
+
+
+# ------------------------------------------------------------------------------------------ drop-in modules
+def test_dropin_modules_chain():
+    """The LowCNN LC hot-path chain (baseline.py:114-127) through the drop-in nn.Modules."""
+    import stereoformer_b200 as sf
+    torch.manual_seed(53)
+    fl, fr = torch.randn(1, 256, 32, 64), torch.randn(1, 256, 32, 64)      # BASELINE config 1
+    cv_ref = O.corr_volume(fl, fr, 24)
+    d_ref = O.soft_argmin(cv_ref)
+    cv = sf.CostVolume(24, "correlation")(dev(fl), dev(fr))
+    disp = sf.DisparityEstimation(24, True)(cv)
+    assert disp.shape == d_ref.shape and (disp.cpu() - d_ref).abs().max() < 1e-3
+    lc = sf.LocalCostVolume(radius=2, sample_points=20)
+    lc.div_mode = 0
+    out = lc(cv, disp.unsqueeze(1), True)
+    ref = O.local_cost_volume(cv.cpu(), disp.unsqueeze(1).cpu(), 2, 20, True)
+    assert out.shape == ref.shape and (out.cpu() - ref).abs().max() < 1e-3
+    blk = sf.CorrBlock1D(dev(fl[:, :, :4]), dev(fr[:, :, :4]), num_levels=4, radius=4)
+    assert len(blk.corr_pyramid) == 5 and blk.corr_pyramid[0].shape == (4 * 64, 1, 1, 64)
+    coords = torch.rand(1, 2, 4, 64, device="cuda") * 60
+    assert blk(coords).shape == (1, 36, 4, 64)
+    x = dev(fl).requires_grad_(True)
+    y = sf.CostVolume(24)(x, dev(fr))
+    with pytest.raises(NotImplementedError):
+        y.sum().backward()
