@@ -1,0 +1,302 @@
+#!/usr/bin/env python
+"""bench.py -- stereo pairs/s of the StereoFormer hot path on B200 (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+Workload (BASELINE.json configs[1], named in config.workload): the LocalCostVolume hot path of LowCNN at
+SceneFlow 544x960, maxdisp 192 -> 1/8 grid 68x120, 256 feature channels, D=24, batch 8 pairs per GPU
+(weak scaling: every rank processes its own 8 pairs).  One step = correlation cost volume (a1) +
+fused soft-argmin / local disparity-window sampling (a3+a4) over the batch; with N>1 the disparity maps are
+all-gathered over NCCL on a side stream (north_star: NCCL only gathers disparity maps).
+
+value : pairs/s, inputs resident in HBM, CUDA-event timed, max over ranks.
+e2e   : pairs/s through the public module API with HOST (pinned) feature buffers: H2D of both feature maps
+        and D2H of the refined disparity inside the timed region.
+roofline : the dominant kernel (corr_volume_tma_kernel) alone, algorithmic bytes / CUDA-event time vs the
+        measured HBM peak (MEASURED_PEAKS.json).
+cpu_baseline / --impl reference : the oracle's CPU port of the same chain on the host cores.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+B_PER_GPU, C, H8, W8, D = 8, 256, 68, 120, 24
+RADIUS, NPTS = 2, 20     # LowCNN baseline.py:38
+WORKLOAD = "LowCNN LocalCostVolume hot path (corr volume + soft-argmin + local window r=2 N=20), 544x960, maxdisp 192 " \
+           "(1/8 grid 68x120, C=256, D=24), batch 8 pairs per GPU"
+ALG_BYTES_CV = (2 * C + D) * H8 * W8 * 4          # per pair, SURVEY 8d
+ALG_BYTES_WIN = (D + 2) * H8 * W8 * 4
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def traffic_from_profile():
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(p):
+        try:
+            return json.load(open(p)).get("corr_volume_tma_kernel_bytes_per_launch")
+        except Exception:
+            pass
+    return None
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock + throttle reasons of one GPU through NVML while the timed region runs."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.max_mhz, self._stop_evt = index, [], set(), None, threading.Event()
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if self.nv is None:
+            return
+        nv = self.nv
+        names = {"hw_slowdown": getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8),
+                 "hw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40),
+                 "sw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20),
+                 "sw_power_cap": getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4)}
+        while not self._stop_evt.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for k, bit in names.items():
+                    if r & bit:
+                        self.reasons.add(k)
+            except Exception:
+                pass
+            time.sleep(0.002)
+
+    def finish(self):
+        self._stop_evt.set()
+        self.join(timeout=1.0)
+        s = sorted(self.samples)
+        return {"sm_mhz": (s[len(s) // 2] if s else None), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(s)}
+
+
+def make_features(device, seed):
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    fl = torch.randn(B_PER_GPU, C, H8, W8, generator=g)
+    fr = torch.randn(B_PER_GPU, C, H8, W8, generator=g)
+    return fl, fr
+
+
+def cpu_chain(fl, fr):
+    """The reference's CPU path for this chain, as restated by the oracle (checker, bench baseline only)."""
+    from oracle import stereo_oracle as O
+    cv = O.corr_volume(fl, fr, D)
+    d0 = O.soft_argmin(cv).unsqueeze(1)
+    return O.local_cost_volume(cv, d0, RADIUS, NPTS, True)
+
+
+def time_cpu(reps, fl, fr):
+    torch.set_num_threads(os.cpu_count() or 1)
+    cpu_chain(fl[:1], fr[:1])
+    best = float("inf")
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        cpu_chain(fl, fr)
+        best = min(best, time.perf_counter() - t0)
+    return best
+
+
+def run_reference(args, rank):
+    if rank != 0:
+        return
+    fl, fr = make_features("cpu", 1024)
+    torch.set_num_threads(os.cpu_count() or 1)
+    for _ in range(max(1, min(args.warmup, 2))):
+        cpu_chain(fl, fr)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        cpu_chain(fl, fr)
+    dt = time.perf_counter() - t0
+    v = args.steps * B_PER_GPU / dt
+    cores = torch.get_num_threads()
+    line = {"impl": "reference", "metric": "stereo pairs/s", "value": v, "unit": "pairs/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "arm": "oracle CPU port of the reference's PyTorch path (the reference is "
+                       "Python and cannot travel to the GPU box)"},
+            "cpu_baseline": {"value": v, "unit": "pairs/s", "cores": cores, "kind": "port",
+                             "sample": "%d steps x %d pairs, full chain" % (args.steps, B_PER_GPU)},
+            "e2e": {"value": v, "unit": "pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=300)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+
+    import torch.distributed as dist
+    import stereoformer_b200 as sf
+    from stereoformer_b200 import ops
+
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- inputs: 3 rotating feature sets per rank (each step reads 134 MB > L2; rotation rules out L2 reuse)
+    NSETS = 3
+    host = [make_features("cpu", 1024 + 97 * rank + i) for i in range(NSETS)]
+    sets = [(a.to(dev), b.to(dev)) for a, b in host]
+    gather_buf = torch.empty(world * B_PER_GPU, 1, H8, W8, device=dev) if world > 1 else None
+    side = torch.cuda.Stream(device=dev)
+
+    def step(i):
+        fl, fr = sets[i % NSETS]
+        cv = ops.corr_volume(fl, fr, D)
+        disp = ops.local_window(cv, None, mode=ops.SF_WIN_FIXED, radius=RADIUS, n_points=NPTS, consider_valid=True,
+                                div_mode=ops.SF_DIV_RECIP)
+        if world > 1:
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                disp.record_stream(side)
+                dist.all_gather_into_tensor(gather_buf, disp)
+        return disp
+
+    for i in range(args.warmup):
+        step(i)
+    barrier()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(args.steps):
+        step(i)
+    torch.cuda.current_stream().wait_stream(side)
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    clocks = sampler.finish()
+    t = torch.tensor([ms], device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    value = world * B_PER_GPU * args.steps / (ms * 1e-3)
+
+    # ---- dominant kernel alone (roofline)
+    for i in range(3):
+        ops.corr_volume(*sets[i % NSETS], D)
+    torch.cuda.synchronize()
+    nk = max(20, min(args.steps, 200))
+    e0.record()
+    for i in range(nk):
+        ops.corr_volume(*sets[i % NSETS], D)
+    e1.record()
+    torch.cuda.synchronize()
+    k_ms = e0.elapsed_time(e1) / nk
+    peak, peak_src = peaks()
+    achieved = B_PER_GPU * ALG_BYTES_CV / (k_ms * 1e-3) / 1e9
+    traffic = traffic_from_profile()
+
+    # ---- end to end through the public module API, host buffers
+    pin = [(a.pin_memory(), b.pin_memory()) for a, b in host]
+    out_host = torch.empty(B_PER_GPU, 1, H8, W8).pin_memory()
+    cvm, lc = sf.CostVolume(D, "correlation"), sf.LocalCostVolume(RADIUS, NPTS)
+    est = sf.DisparityEstimation(D)
+
+    def e2e_step(i):
+        a, b = pin[i % NSETS]
+        fl, fr = a.to(dev, non_blocking=True), b.to(dev, non_blocking=True)
+        cv = cvm(fl, fr)
+        d0 = est(cv).unsqueeze(1)
+        out_host.copy_(lc(cv, d0, True), non_blocking=True)
+
+    ne = max(3, min(args.steps, 30))
+    for i in range(3):
+        e2e_step(i)
+    barrier()
+    e0.record()
+    for i in range(ne):
+        e2e_step(i)
+    e1.record()
+    barrier()
+    t = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_v = world * B_PER_GPU * ne / (float(t.item()) * 1e-3)
+    h2d = 2 * B_PER_GPU * C * H8 * W8 * 4
+    d2h = B_PER_GPU * H8 * W8 * 4
+
+    # ---- parity spot check of what was just timed (oracle as checker only) + CPU baseline on rank 0
+    cpu_base = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        fl, fr = host[0]
+        got = step(0).cpu()
+        want = cpu_chain(fl[:2], fr[:2])
+        err = (got[:2] - want).abs()
+        assert err.median() < 1e-3, "bench parity check failed: median |disp err| %g" % err.median()
+        best = time_cpu(5, fl, fr)
+        cpu_base = {"value": B_PER_GPU / best, "unit": "pairs/s", "cores": torch.get_num_threads(), "kind": "port",
+                    "sample": "best of 5 passes over one batch of %d pairs (oracle CPU port, full chain)" % B_PER_GPU}
+
+    if rank == 0:
+        line = {"metric": "stereo pairs/s", "value": value, "unit": "pairs/s", "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": WORKLOAD, "pairs_per_gpu_per_step": B_PER_GPU, "parallelism": "pairs sharded "
+                           "across %d rank(s); NCCL all-gather of disparity on a side stream" % world,
+                           "l2": "each step reads 134 MB of features (> 126 MB L2) from one of 3 rotating sets"},
+                "roofline": {"kernel": "corr_volume_tma_kernel<24,1>", "bound": "hbm", "achieved": achieved, "peak": peak,
+                             "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                             "alg_bytes_per_launch": B_PER_GPU * ALG_BYTES_CV, "us_per_launch": k_ms * 1e3},
+                "cpu_baseline": cpu_base,
+                "e2e": {"value": e2e_v, "unit": "pairs/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                        "steps": ne},
+                "gpu_launches": 2 * args.steps, "clocks": clocks}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
