@@ -13,14 +13,14 @@
 //   * partial sums of the channel split are combined through shared memory in a fixed order (deterministic),
 //     scaled by 1/Cg and written as coalesced float4 rows.
 // Algorithmic bytes per row tile: (2*Cg + D) * W * 4.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "../../include/stereoformer_b200.h"
 
 namespace sf {
 
 constexpr int CV_NCW = 4;      // consumer warps
-constexpr int CV_CK = 4;       // channels per pipeline stage
-constexpr int CV_S = 8;        // pipeline stages
 constexpr int CV_XMAX = 128;   // pixels covered by one warp (32 lanes x 4)
 constexpr int CV_THREADS = (CV_NCW + 1) * 32;
 
@@ -34,25 +34,42 @@ struct CorrParams {
   int nch;        // channel chunks per tile
 };
 
-template <int DT, int NDB>
+// acc[dd][t] += L[t] * R[x0 + t - dd]: one channel of a lane's 4-pixel x DT-disparity register tile.
+template <int DT, int NR4>
+__device__ __forceinline__ void corr_fma(float (&acc)[DT][4], const float4& l4, const float4 (&r4)[NR4]) {
+  const float lv[4] = {l4.x, l4.y, l4.z, l4.w};
+  float r[4 * NR4];
+#pragma unroll
+  for (int j = 0; j < NR4; ++j) {
+    r[4 * j] = r4[j].x; r[4 * j + 1] = r4[j].y; r[4 * j + 2] = r4[j].z; r[4 * j + 3] = r4[j].w;
+  }
+#pragma unroll
+  for (int dd = 0; dd < DT; ++dd)
+#pragma unroll
+    for (int t = 0; t < 4; ++t) acc[dd][t] = fmaf(lv[t], r[DT + t - dd], acc[dd][t]);
+}
+
+// DT disparities per lane, NDB disparity blocks per CTA, CK channels per stage, S stages.
+template <int DT, int NDB, int CK, int S>
 __global__ void __launch_bounds__(CV_THREADS, 2)
 corr_volume_tma_kernel(const __grid_constant__ CUtensorMap mapL, const __grid_constant__ CUtensorMap mapR,
                        const CorrParams p) {
   constexpr int NCS = CV_NCW / NDB;  // warps splitting the channel chunks
   constexpr int DP = DT * NDB;       // left halo of the right-feature row
   constexpr int NR4 = DT / 4 + 1;    // float4s of the right row a lane needs per channel
+  constexpr int NSLOT = NCS > 1 ? 2 : 0;  // reduction slots of [DT][128]
 
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   const int XSL = p.XS, XSR = p.XS + DP;
-  const int stage_floats = CV_CK * (XSL + XSR);
+  const int stage_floats = CK * (XSL + XSR);
   float* stages = reinterpret_cast<float*>(smem_raw);
-  float* red = stages + CV_S * stage_floats;
-  uint64_t* full = reinterpret_cast<uint64_t*>(red + CV_NCW * DT * CV_XMAX);
-  uint64_t* empty = full + CV_S;
+  float* red = stages + S * stage_floats;
+  uint64_t* full = reinterpret_cast<uint64_t*>(red + NSLOT * DT * CV_XMAX);
+  uint64_t* empty = full + S;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
-    for (int s = 0; s < CV_S; ++s) {
+    for (int s = 0; s < S; ++s) {
       mbar_init(&full[s], 1);
       mbar_init(&empty[s], NDB);
     }
@@ -74,12 +91,12 @@ corr_volume_tma_kernel(const __grid_constant__ CUtensorMap mapL, const __grid_co
         int xs0 = seg * p.XS, row0 = bg * p.Cg;
         int xr0 = xs0 - dtile * DP - DP;
         for (int kk = 0; kk < p.nch; ++kk, ++it) {
-          int st = it % CV_S;
-          mbar_wait(&empty[st], ((it / CV_S) & 1) ^ 1);
+          int st = it % S;
+          mbar_wait(&empty[st], ((it / S) & 1) ^ 1);
           float* dst = stages + st * stage_floats;
           mbar_expect_tx(&full[st], bytes);
-          tma_load_3d(dst, &mapL, &full[st], xs0, y, row0 + kk * CV_CK);
-          tma_load_3d(dst + CV_CK * XSL, &mapR, &full[st], xr0, y, row0 + kk * CV_CK);
+          tma_load_3d(dst, &mapL, &full[st], xs0, y, row0 + kk * CK);
+          tma_load_3d(dst + CK * XSL, &mapR, &full[st], xr0, y, row0 + kk * CK);
         }
       }
     }
@@ -90,6 +107,9 @@ corr_volume_tma_kernel(const __grid_constant__ CUtensorMap mapL, const __grid_co
   const int db = warp % NDB, cs = warp / NDB;
   const int lx = (4 * lane < p.XS) ? 4 * lane : 0;  // lanes past the segment recompute lane 0, never store
   const int roff = lx + (NDB - 1 - db) * DT;
+  // The mbarrier test of a chunk is issued one chunk ahead (its ~90-cycle latency hides behind the FFMAs).
+  bool ready = false;
+  if (cs < p.nch && blockIdx.x < p.ntiles) ready = mbar_try_wait(&full[cs % S], (cs / S) & 1);
   int iter = 0;
   for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x, ++iter) {
     float acc[DT][4];
@@ -98,62 +118,107 @@ corr_volume_tma_kernel(const __grid_constant__ CUtensorMap mapL, const __grid_co
 
     for (int kk = cs; kk < p.nch; kk += NCS) {
       const int it = iter * p.nch + kk;
-      const int st = it % CV_S;
-      mbar_wait(&full[st], (it / CV_S) & 1);
+      const int st = it % S;
+      if (!ready) mbar_wait(&full[st], (it / S) & 1);
+      {  // probe the next chunk of this warp (this tile, or the first one of the next tile)
+        int itn = it + NCS;
+        bool have = kk + NCS < p.nch;
+        if (!have) {
+          itn = (iter + 1) * p.nch + cs;
+          have = (tile + static_cast<int>(gridDim.x) < p.ntiles) && cs < p.nch;
+        }
+        ready = have ? mbar_try_wait(&full[itn % S], (itn / S) & 1) : false;
+      }
       const float* Ls = stages + st * stage_floats + lx;
-      const float* Rs = stages + st * stage_floats + CV_CK * XSL + roff;
-      const int nv = min(CV_CK, p.Cg - kk * CV_CK);
+      const float* Rs = stages + st * stage_floats + CK * XSL + roff;
+      const int nv = min(CK, p.Cg - kk * CK);
+      if (nv == CK) {
+        // full chunk: branch-free, operands of channel c+1 are fetched while channel c is in the FMA pipe
+        float4 lq[2], rq[2][NR4];
+        lq[0] = *reinterpret_cast<const float4*>(Ls);
 #pragma unroll
-      for (int c = 0; c < CV_CK; ++c) {
-        if (c < nv) {
-          const float4 l4 = *reinterpret_cast<const float4*>(Ls + c * XSL);
-          const float lv[4] = {l4.x, l4.y, l4.z, l4.w};
-          float r[4 * NR4];
+        for (int j = 0; j < NR4; ++j) rq[0][j] = *reinterpret_cast<const float4*>(Rs + 4 * j);
 #pragma unroll
-          for (int j = 0; j < NR4; ++j) {
-            const float4 v = *reinterpret_cast<const float4*>(Rs + c * XSR + 4 * j);
-            r[4 * j] = v.x; r[4 * j + 1] = v.y; r[4 * j + 2] = v.z; r[4 * j + 3] = v.w;
+        for (int c = 0; c < CK; ++c) {
+          const int cur = c & 1, nxt = cur ^ 1;
+          if (c + 1 < CK) {
+            lq[nxt] = *reinterpret_cast<const float4*>(Ls + (c + 1) * XSL);
+#pragma unroll
+            for (int j = 0; j < NR4; ++j) rq[nxt][j] = *reinterpret_cast<const float4*>(Rs + (c + 1) * XSR + 4 * j);
           }
+          corr_fma<DT, NR4>(acc, lq[cur], rq[cur]);
+        }
+      } else {
+        for (int c = 0; c < nv; ++c) {
+          float4 l4 = *reinterpret_cast<const float4*>(Ls + c * XSL);
+          float4 r4[NR4];
 #pragma unroll
-          for (int dd = 0; dd < DT; ++dd)
-#pragma unroll
-            for (int t = 0; t < 4; ++t) acc[dd][t] = fmaf(lv[t], r[DT + t - dd], acc[dd][t]);
+          for (int j = 0; j < NR4; ++j) r4[j] = *reinterpret_cast<const float4*>(Rs + c * XSR + 4 * j);
+          corr_fma<DT, NR4>(acc, l4, r4);
         }
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(&empty[st]);
     }
 
-    // ---- combine the channel split (fixed order), scale, store
-    float* mine = red + ((cs * NDB + db) * DT) * CV_XMAX + 4 * lane;
-#pragma unroll
-    for (int dd = 0; dd < DT; ++dd)
-      *reinterpret_cast<float4*>(mine + dd * CV_XMAX) = make_float4(acc[dd][0], acc[dd][1], acc[dd][2], acc[dd][3]);
-    named_bar_sync(1, CV_NCW * 32);
-
+    // ---- combine the channel split in a fixed order (tree through shared memory), scale, store
     int seg = tile % p.nseg, t2 = tile / p.nseg;
     int y = t2 % p.H, t3 = t2 / p.H;
     int dtile = t3 % p.ndt, bg = t3 / p.ndt;
     const int x = seg * p.XS + 4 * lane;
     const bool xok = (4 * lane < p.XS) && (x < p.W);
     const float fc = static_cast<float>(p.Cg);
-    for (int j = warp; j < DP; j += CV_NCW) {
-      const int d = dtile * DP + j;
-      if (d >= p.D) break;
-      const int jb = j / DT, jd = j % DT;
-      float4 s = *reinterpret_cast<const float4*>(red + (jb * DT + jd) * CV_XMAX + 4 * lane);
-#pragma unroll
-      for (int q = 1; q < NCS; ++q) {
-        const float4 v = *reinterpret_cast<const float4*>(red + ((q * NDB + jb) * DT + jd) * CV_XMAX + 4 * lane);
-        s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
-      }
+    float* orow = p.out + ((static_cast<size_t>(bg) * p.D) * p.H + y) * p.W + x;
+    const size_t dstride = static_cast<size_t>(p.H) * p.W;
+    if (NCS == 1) {
       if (xok) {
-        s.x = __fdiv_rn(s.x, fc); s.y = __fdiv_rn(s.y, fc); s.z = __fdiv_rn(s.z, fc); s.w = __fdiv_rn(s.w, fc);
-        float* o = p.out + ((static_cast<size_t>(bg) * p.D + d) * p.H + y) * p.W + x;
-        stg_cs_f4(o, s);
+#pragma unroll
+        for (int dd = 0; dd < DT; ++dd) {
+          const int d = dtile * DP + db * DT + dd;
+          if (d < p.D)
+            stg_cs_f4(orow + d * dstride, make_float4(__fdiv_rn(acc[dd][0], fc), __fdiv_rn(acc[dd][1], fc),
+                                                      __fdiv_rn(acc[dd][2], fc), __fdiv_rn(acc[dd][3], fc)));
+        }
       }
+    } else {
+      // slot s holds [DT][128] partial sums.  NCS=4 (one disparity block): level one folds warps 2,3 into
+      // warps 0,1 (slots 0,1); NCS=2 (two blocks): warps 2,3 fold into warps 0,1 of the same block (slot = db).
+      float* slot = red + (NCS == 4 ? (cs & 1) : db) * DT * CV_XMAX + 4 * lane;
+      const bool upper = cs >= NCS / 2;
+      if (upper) {
+#pragma unroll
+        for (int dd = 0; dd < DT; ++dd)
+          *reinterpret_cast<float4*>(slot + dd * CV_XMAX) = make_float4(acc[dd][0], acc[dd][1], acc[dd][2], acc[dd][3]);
+      }
+      named_bar_sync(1, CV_NCW * 32);
+      if (!upper) {
+#pragma unroll
+        for (int dd = 0; dd < DT; ++dd) {
+          const float4 v = *reinterpret_cast<const float4*>(slot + dd * CV_XMAX);
+          *reinterpret_cast<float4*>(slot + dd * CV_XMAX) =
+              make_float4(acc[dd][0] + v.x, acc[dd][1] + v.y, acc[dd][2] + v.z, acc[dd][3] + v.w);
+        }
+      }
+      named_bar_sync(2, CV_NCW * 32);
+      // final: the NDB*DT output rows are dealt round-robin to the 4 warps
+      for (int j = warp; j < DP; j += CV_NCW) {
+        const int d = dtile * DP + j;
+        if (d >= p.D) break;
+        const int jb = j / DT, jd = j % DT;
+        float4 s4;
+        if (NCS == 4) {
+          const float4 u = *reinterpret_cast<const float4*>(red + jd * CV_XMAX + 4 * lane);
+          const float4 v = *reinterpret_cast<const float4*>(red + (DT + jd) * CV_XMAX + 4 * lane);
+          s4 = make_float4(u.x + v.x, u.y + v.y, u.z + v.z, u.w + v.w);
+        } else {
+          s4 = *reinterpret_cast<const float4*>(red + (jb * DT + jd) * CV_XMAX + 4 * lane);
+        }
+        if (xok)
+          stg_cs_f4(orow + d * dstride, make_float4(__fdiv_rn(s4.x, fc), __fdiv_rn(s4.y, fc), __fdiv_rn(s4.z, fc),
+                                                    __fdiv_rn(s4.w, fc)));
+      }
+      named_bar_sync(3, CV_NCW * 32);
     }
-    named_bar_sync(2, CV_NCW * 32);
   }
 }
 
@@ -208,37 +273,63 @@ __global__ void shift_volume_kernel(const float* __restrict__ L, const float* __
   }
 }
 
-template <int DT, int NDB>
-static int launch_corr_tma(const float* L, const float* R, float* out, int nBG, int Cg, int H, int W, int D,
-                           cudaStream_t stream) {
+template <int DT, int NDB, int CK, int S>
+static int launch_corr_tma_cfg(const float* L, const float* R, float* out, int nBG, int Cg, int H, int W, int D,
+                               cudaStream_t stream) {
   CorrParams p;
   p.out = out; p.Cg = Cg; p.H = H; p.W = W; p.D = D; p.nBG = nBG;
   constexpr int DP = DT * NDB;
+  constexpr int NCS = CV_NCW / NDB;
   int xcap = CV_XMAX;
   if (xcap + DP > 256) xcap = 256 - DP;  // TMA box limit for the haloed right row
   p.nseg = ceil_div(W, xcap);
   p.XS = ceil_div(ceil_div(W, p.nseg), 8) * 8;
   if (p.XS > xcap) { p.nseg += 1; p.XS = ceil_div(ceil_div(W, p.nseg), 8) * 8; }
   p.ndt = ceil_div(D, DP);
-  p.nch = ceil_div(Cg, CV_CK);
+  p.nch = ceil_div(Cg, CK);
   long long nt = 1LL * nBG * p.ndt * H * p.nseg;
   SF_CHECK_ARG(nt < (1LL << 30), "corr_volume: too many tiles");
   p.ntiles = static_cast<int>(nt);
 
   CUtensorMap mL, mR;
-  int rc = make_tmap_3d_f32(&mL, L, W, H, static_cast<uint64_t>(nBG) * Cg, p.XS, 1, CV_CK);
+  int rc = make_tmap_3d_f32(&mL, L, W, H, static_cast<uint64_t>(nBG) * Cg, p.XS, 1, CK);
   if (rc) return rc;
-  rc = make_tmap_3d_f32(&mR, R, W, H, static_cast<uint64_t>(nBG) * Cg, p.XS + DP, 1, CV_CK);
+  rc = make_tmap_3d_f32(&mR, R, W, H, static_cast<uint64_t>(nBG) * Cg, p.XS + DP, 1, CK);
   if (rc) return rc;
 
-  const int stage_floats = CV_CK * (2 * p.XS + DP);
-  const size_t smem = (static_cast<size_t>(CV_S) * stage_floats + CV_NCW * DT * CV_XMAX) * 4 + 2 * CV_S * 8 + 256;
-  auto kern = corr_volume_tma_kernel<DT, NDB>;
+  const int stage_floats = CK * (2 * p.XS + DP);
+  const int nslot = NCS > 1 ? 2 : 0;
+  const size_t smem = (static_cast<size_t>(S) * stage_floats + nslot * DT * CV_XMAX) * 4 + 2 * S * 8 + 256;
+  auto kern = corr_volume_tma_kernel<DT, NDB, CK, S>;
   SF_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
   int grid = min(p.ntiles, 2 * sm_count());
   kern<<<grid, CV_THREADS, smem, stream>>>(mL, mR, p);
   SF_LAUNCH_CHECK();
   return SF_OK;
+}
+
+// Pipeline shape (channels per stage x stages); SF_CV_VARIANT is a tuning hook for bench sweeps only.
+static int cv_variant() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("SF_CV_VARIANT");
+    v = e ? atoi(e) : 0;
+  }
+  return v;
+}
+
+template <int DT, int NDB>
+static int launch_corr_tma(const float* L, const float* R, float* out, int nBG, int Cg, int H, int W, int D,
+                           cudaStream_t stream) {
+  switch (cv_variant()) {
+    case 1: return launch_corr_tma_cfg<DT, NDB, 4, 8>(L, R, out, nBG, Cg, H, W, D, stream);
+    case 2: return launch_corr_tma_cfg<DT, NDB, 16, 6>(L, R, out, nBG, Cg, H, W, D, stream);
+    case 3: return launch_corr_tma_cfg<DT, NDB, 8, 4>(L, R, out, nBG, Cg, H, W, D, stream);
+    case 4: return launch_corr_tma_cfg<DT, NDB, 16, 4>(L, R, out, nBG, Cg, H, W, D, stream);
+    case 5: return launch_corr_tma_cfg<DT, NDB, 4, 16>(L, R, out, nBG, Cg, H, W, D, stream);
+    case 6: return launch_corr_tma_cfg<DT, NDB, 8, 10>(L, R, out, nBG, Cg, H, W, D, stream);
+    default: return launch_corr_tma_cfg<DT, NDB, 8, 8>(L, R, out, nBG, Cg, H, W, D, stream);
+  }
 }
 
 }  // namespace sf
