@@ -222,6 +222,175 @@ corr_volume_tma_kernel(const __grid_constant__ CUtensorMap mapL, const __grid_co
   }
 }
 
+// ------------------------------------------------------------------------------------------------------
+// v2: no producer warp.  Every channel-split group of warps owns a private ring of SW stages and refills a
+// slot itself (one elected lane issues the two TMA boxes) right after it has drained it, so a slow warp never
+// blocks the loads of the others (the shared in-order ring above couples all four warps to the slowest one).
+template <int DT, int NDB, int CK, int SW, int MINB>
+__global__ void __launch_bounds__(CV_NCW * 32, MINB)
+corr_volume_ring_kernel(const __grid_constant__ CUtensorMap mapL, const __grid_constant__ CUtensorMap mapR,
+                        const CorrParams p) {
+  constexpr int NCS = CV_NCW / NDB;
+  constexpr int DP = DT * NDB;
+  constexpr int NR4 = DT / 4 + 1;
+  constexpr int NSLOT = NCS > 1 ? 2 : 0;
+
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  const int XSL = p.XS, XSR = p.XS + DP;
+  const int stage_floats = CK * (XSL + XSR);
+  float* rings = reinterpret_cast<float*>(smem_raw);                 // [NCS][SW][stage]
+  float* red = rings + NCS * SW * stage_floats;
+  const int RP = p.XS;  // pitch of the reduction slots (lanes past the segment never touch them)
+  uint64_t* full = reinterpret_cast<uint64_t*>(red + NSLOT * DT * RP);   // [NCS][SW]
+  uint64_t* empty = full + NCS * SW;                                          // [NCS][SW] (used when NDB > 1)
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < NCS * SW; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], NDB);
+    }
+    fence_mbar_init();
+    tma_prefetch_desc(&mapL);
+    tma_prefetch_desc(&mapR);
+  }
+  __syncthreads();
+
+  const int db = warp % NDB, cs = warp / NDB;
+  const int lx = (4 * lane < p.XS) ? 4 * lane : 0;
+  const int roff = lx + (NDB - 1 - db) * DT;
+  float* ring = rings + cs * SW * stage_floats;
+  uint64_t* rfull = full + cs * SW;
+  uint64_t* rempty = empty + cs * SW;
+  const int npw = cs < p.nch ? (p.nch - cs + NCS - 1) / NCS : 0;     // chunks of a tile handled by this ring
+  const int ntl = (p.ntiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
+  const int total = npw * ntl;
+  const bool issuer = (db == 0) && (lane == 0);
+  const uint32_t bytes = stage_floats * 4;
+
+  // issue side state (only meaningful in the issuer lane)
+  int qi = 0, i_tile = blockIdx.x, i_j = 0;
+  auto issue = [&]() {
+    const int slot = qi % SW;
+    if (NDB > 1 && qi >= SW) mbar_wait(&rempty[slot], ((qi / SW) & 1) ^ 1);
+    int seg = i_tile % p.nseg, t2 = i_tile / p.nseg;
+    int y = t2 % p.H, t3 = t2 / p.H;
+    int dtile = t3 % p.ndt, bg = t3 / p.ndt;
+    const int xs0 = seg * p.XS, c0 = bg * p.Cg + (cs + i_j * NCS) * CK;
+    float* dst = ring + slot * stage_floats;
+    mbar_expect_tx(&rfull[slot], bytes);
+    tma_load_3d(dst, &mapL, &rfull[slot], xs0, y, c0);
+    tma_load_3d(dst + CK * XSL, &mapR, &rfull[slot], xs0 - dtile * DP - DP, y, c0);
+    ++qi;
+    if (++i_j == npw) { i_j = 0; i_tile += gridDim.x; }
+  };
+  if (issuer)
+    for (int i = 0; i < SW && i < total; ++i) issue();
+
+  int qc = 0;
+  for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
+    float acc[DT][4];
+#pragma unroll
+    for (int i = 0; i < DT; ++i) acc[i][0] = acc[i][1] = acc[i][2] = acc[i][3] = 0.f;
+
+    for (int j = 0; j < npw; ++j, ++qc) {
+      const int slot = qc % SW;
+      mbar_wait(&rfull[slot], (qc / SW) & 1);
+      const float* Ls = ring + slot * stage_floats + lx;
+      const float* Rs = ring + slot * stage_floats + CK * XSL + roff;
+      const int nv = min(CK, p.Cg - (cs + j * NCS) * CK);
+      if (nv == CK) {
+        float4 lq[2], rq[2][NR4];
+        lq[0] = *reinterpret_cast<const float4*>(Ls);
+#pragma unroll
+        for (int q = 0; q < NR4; ++q) rq[0][q] = *reinterpret_cast<const float4*>(Rs + 4 * q);
+#pragma unroll
+        for (int c = 0; c < CK; ++c) {
+          const int cur = c & 1, nxt = cur ^ 1;
+          if (c + 1 < CK) {
+            lq[nxt] = *reinterpret_cast<const float4*>(Ls + (c + 1) * XSL);
+#pragma unroll
+            for (int q = 0; q < NR4; ++q) rq[nxt][q] = *reinterpret_cast<const float4*>(Rs + (c + 1) * XSR + 4 * q);
+          }
+          corr_fma<DT, NR4>(acc, lq[cur], rq[cur]);
+        }
+      } else {
+        for (int c = 0; c < nv; ++c) {
+          float4 l4 = *reinterpret_cast<const float4*>(Ls + c * XSL);
+          float4 r4[NR4];
+#pragma unroll
+          for (int q = 0; q < NR4; ++q) r4[q] = *reinterpret_cast<const float4*>(Rs + c * XSR + 4 * q);
+          corr_fma<DT, NR4>(acc, l4, r4);
+        }
+      }
+      __syncwarp();
+      if (NDB > 1 && lane == 0) mbar_arrive(&rempty[slot]);
+      if (issuer && qi < total) {
+        fence_proxy_async();
+        issue();
+      }
+    }
+
+    // ---- combine the channel split in a fixed order (tree through shared memory), scale, store
+    int seg = tile % p.nseg, t2 = tile / p.nseg;
+    int y = t2 % p.H, t3 = t2 / p.H;
+    int dtile = t3 % p.ndt, bg = t3 / p.ndt;
+    const int x = seg * p.XS + 4 * lane;
+    const bool xok = (4 * lane < p.XS) && (x < p.W);
+    const float fc = static_cast<float>(p.Cg);
+    float* orow = p.out + ((static_cast<size_t>(bg) * p.D) * p.H + y) * p.W + x;
+    const size_t dstride = static_cast<size_t>(p.H) * p.W;
+    if (NCS == 1) {
+      if (xok) {
+#pragma unroll
+        for (int dd = 0; dd < DT; ++dd) {
+          const int d = dtile * DP + db * DT + dd;
+          if (d < p.D)
+            stg_cs_f4(orow + d * dstride, make_float4(__fdiv_rn(acc[dd][0], fc), __fdiv_rn(acc[dd][1], fc),
+                                                      __fdiv_rn(acc[dd][2], fc), __fdiv_rn(acc[dd][3], fc)));
+        }
+      }
+    } else {
+      float* slotp = red + (NCS == 4 ? (cs & 1) : db) * DT * RP + 4 * lane;
+      const bool lok = 4 * lane < p.XS;
+      const bool upper = cs >= NCS / 2;
+      if (upper && lok) {
+#pragma unroll
+        for (int dd = 0; dd < DT; ++dd)
+          *reinterpret_cast<float4*>(slotp + dd * RP) = make_float4(acc[dd][0], acc[dd][1], acc[dd][2], acc[dd][3]);
+      }
+      named_bar_sync(1, CV_NCW * 32);
+      if (!upper && lok) {
+#pragma unroll
+        for (int dd = 0; dd < DT; ++dd) {
+          const float4 v = *reinterpret_cast<const float4*>(slotp + dd * RP);
+          *reinterpret_cast<float4*>(slotp + dd * RP) =
+              make_float4(acc[dd][0] + v.x, acc[dd][1] + v.y, acc[dd][2] + v.z, acc[dd][3] + v.w);
+        }
+      }
+      named_bar_sync(2, CV_NCW * 32);
+      for (int j = warp; j < DP; j += CV_NCW) {
+        const int d = dtile * DP + j;
+        if (d >= p.D) break;
+        const int jb = j / DT, jd = j % DT;
+        float4 s4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (!xok) continue;
+        if (NCS == 4) {
+          const float4 u = *reinterpret_cast<const float4*>(red + jd * RP + 4 * lane);
+          const float4 v = *reinterpret_cast<const float4*>(red + (DT + jd) * RP + 4 * lane);
+          s4 = make_float4(u.x + v.x, u.y + v.y, u.z + v.z, u.w + v.w);
+        } else {
+          s4 = *reinterpret_cast<const float4*>(red + (jb * DT + jd) * RP + 4 * lane);
+        }
+        if (xok)
+          stg_cs_f4(orow + d * dstride, make_float4(__fdiv_rn(s4.x, fc), __fdiv_rn(s4.y, fc), __fdiv_rn(s4.z, fc),
+                                                    __fdiv_rn(s4.w, fc)));
+      }
+      named_bar_sync(3, CV_NCW * 32);
+    }
+  }
+}
+
 // Shape-agnostic path (W % 4 != 0 or unaligned pointers): one thread per output element.
 __global__ void corr_volume_generic_kernel(const float* __restrict__ L, const float* __restrict__ R,
                                            float* __restrict__ out, int nBG, int Cg, int H, int W, int D) {
@@ -308,6 +477,39 @@ static int launch_corr_tma_cfg(const float* L, const float* R, float* out, int n
   return SF_OK;
 }
 
+template <int DT, int NDB, int CK, int SW, int MINB = 2>
+static int launch_corr_ring_cfg(const float* L, const float* R, float* out, int nBG, int Cg, int H, int W, int D,
+                                cudaStream_t stream) {
+  CorrParams p;
+  p.out = out; p.Cg = Cg; p.H = H; p.W = W; p.D = D; p.nBG = nBG;
+  constexpr int DP = DT * NDB;
+  constexpr int NCS = CV_NCW / NDB;
+  int xcap = CV_XMAX;
+  if (xcap + DP > 256) xcap = 256 - DP;
+  p.nseg = ceil_div(W, xcap);
+  p.XS = ceil_div(ceil_div(W, p.nseg), 8) * 8;
+  if (p.XS > xcap) { p.nseg += 1; p.XS = ceil_div(ceil_div(W, p.nseg), 8) * 8; }
+  p.ndt = ceil_div(D, DP);
+  p.nch = ceil_div(Cg, CK);
+  long long nt = 1LL * nBG * p.ndt * H * p.nseg;
+  SF_CHECK_ARG(nt < (1LL << 30), "corr_volume: too many tiles");
+  p.ntiles = static_cast<int>(nt);
+  CUtensorMap mL, mR;
+  int rc = make_tmap_3d_f32(&mL, L, W, H, static_cast<uint64_t>(nBG) * Cg, p.XS, 1, CK);
+  if (rc) return rc;
+  rc = make_tmap_3d_f32(&mR, R, W, H, static_cast<uint64_t>(nBG) * Cg, p.XS + DP, 1, CK);
+  if (rc) return rc;
+  const int stage_floats = CK * (2 * p.XS + DP);
+  const int nslot = NCS > 1 ? 2 : 0;
+  const size_t smem = (static_cast<size_t>(NCS) * SW * stage_floats + nslot * DT * p.XS) * 4 + 2 * NCS * SW * 8 + 128;
+  auto kern = corr_volume_ring_kernel<DT, NDB, CK, SW, MINB>;
+  SF_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+  int grid = min(p.ntiles, MINB * sm_count());
+  kern<<<grid, CV_NCW * 32, smem, stream>>>(mL, mR, p);
+  SF_LAUNCH_CHECK();
+  return SF_OK;
+}
+
 // Pipeline shape (channels per stage x stages); SF_CV_VARIANT is a tuning hook for bench sweeps only.
 static int cv_variant() {
   static int v = -1;
@@ -321,15 +523,32 @@ static int cv_variant() {
 template <int DT, int NDB>
 static int launch_corr_tma(const float* L, const float* R, float* out, int nBG, int Cg, int H, int W, int D,
                            cudaStream_t stream) {
+  constexpr int NCS = CV_NCW / NDB;
   switch (cv_variant()) {
+    case 10: return launch_corr_ring_cfg<DT, NDB, 4, 20 / NCS>(L, R, out, nBG, Cg, H, W, D, stream);
+    case 11: return launch_corr_ring_cfg<DT, NDB, 8, 8 / NCS>(L, R, out, nBG, Cg, H, W, D, stream);
+    case 12: return launch_corr_ring_cfg<DT, NDB, 4, 16 / NCS>(L, R, out, nBG, Cg, H, W, D, stream);
+    case 13: return launch_corr_ring_cfg<DT, NDB, 8, 12 / NCS>(L, R, out, nBG, Cg, H, W, D, stream);
+    case 14: return launch_corr_ring_cfg<DT, NDB, 4, 12 / NCS, 3>(L, R, out, nBG, Cg, H, W, D, stream);
+    case 15: return launch_corr_ring_cfg<DT, NDB, 8, 8 / NCS, 3>(L, R, out, nBG, Cg, H, W, D, stream);
+    case 16: return launch_corr_ring_cfg<DT, NDB, 4, 8 / NCS, 3>(L, R, out, nBG, Cg, H, W, D, stream);
     case 1: return launch_corr_tma_cfg<DT, NDB, 4, 8>(L, R, out, nBG, Cg, H, W, D, stream);
     case 2: return launch_corr_tma_cfg<DT, NDB, 16, 6>(L, R, out, nBG, Cg, H, W, D, stream);
     case 3: return launch_corr_tma_cfg<DT, NDB, 8, 4>(L, R, out, nBG, Cg, H, W, D, stream);
     case 4: return launch_corr_tma_cfg<DT, NDB, 16, 4>(L, R, out, nBG, Cg, H, W, D, stream);
     case 5: return launch_corr_tma_cfg<DT, NDB, 4, 16>(L, R, out, nBG, Cg, H, W, D, stream);
     case 6: return launch_corr_tma_cfg<DT, NDB, 8, 10>(L, R, out, nBG, Cg, H, W, D, stream);
-    default: return launch_corr_tma_cfg<DT, NDB, 8, 8>(L, R, out, nBG, Cg, H, W, D, stream);
+    default: break;
   }
+  // measured on B200 (tools/time_cv.py): one disparity block -> private-ring kernel, 3 CTAs/SM once there are
+  // enough row tiles for >= 3 rounds, else 2 CTAs/SM with 8-channel stages; several blocks -> producer-warp kernel
+  if (NDB == 1) {
+    const long long approx_tiles = 1LL * nBG * H * ceil_div(W, CV_XMAX) * ceil_div(D, DT);
+    if (approx_tiles >= 9LL * sm_count())
+      return launch_corr_ring_cfg<DT, NDB, 4, 12 / NCS, 3>(L, R, out, nBG, Cg, H, W, D, stream);
+    return launch_corr_ring_cfg<DT, NDB, 8, 8 / NCS>(L, R, out, nBG, Cg, H, W, D, stream);
+  }
+  return launch_corr_tma_cfg<DT, NDB, 8, 8>(L, R, out, nBG, Cg, H, W, D, stream);
 }
 
 }  // namespace sf

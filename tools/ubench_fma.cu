@@ -42,6 +42,30 @@ __global__ void k(float* out, int iters, float a0) {
   out[blockIdx.x * blockDim.x + threadIdx.x] = s;
 }
 
+// MODE 2: same FMA count, every FFMA reads only two distinct registers besides the accumulator pattern a*a+c
+// (register-bank / operand-port probe); MODE 3: reports SM clock (clock64 vs globaltimer) under FMA load.
+__global__ void k2(float* out, int iters, float a0, long long* clk) {
+  float acc[96];
+#pragma unroll
+  for (int i = 0; i < 96; ++i) acc[i] = i;
+  float l[4] = {a0, a0 + 1, a0 + 2, a0 + 3};
+  long long c0 = clock64();
+  unsigned long long t0;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t0));
+  for (int it = 0; it < iters; ++it) {
+#pragma unroll
+    for (int i = 0; i < 96; ++i) acc[i] = fmaf(l[i & 3], l[i & 3], acc[i]);
+  }
+  long long c1 = clock64();
+  unsigned long long t1;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t1));
+  float s = 0;
+#pragma unroll
+  for (int i = 0; i < 96; ++i) s += acc[i];
+  out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+  if (threadIdx.x == 0 && blockIdx.x == 0) { clk[0] = c1 - c0; clk[1] = (long long)(t1 - t0); }
+}
+
 template <int MODE>
 void run(int warps_per_sm, const char* name) {
   float* out;
@@ -62,7 +86,25 @@ void run(int warps_per_sm, const char* name) {
   cudaFree(out);
 }
 
+void run2(int warps_per_sm) {
+  float* out; long long* clk; long long h[2];
+  cudaMalloc(&out, 148 * 1024 * 4); cudaMalloc(&clk, 16);
+  int iters = 40000;
+  cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+  k2<<<148, warps_per_sm * 32>>>(out, 100, 1.0f, clk);
+  cudaEventRecord(e0);
+  k2<<<148, warps_per_sm * 32>>>(out, iters, 1.0f, clk);
+  cudaEventRecord(e1); cudaEventSynchronize(e1);
+  float ms; cudaEventElapsedTime(&ms, e0, e1);
+  cudaMemcpy(h, clk, 16, cudaMemcpyDeviceToHost);
+  double fma = 148.0 * warps_per_sm * 32 * 96.0 * iters;
+  double mhz = (double)h[0] / (double)h[1] * 1e3;
+  printf("FFMA a*a+c warps/SM=%2d  %.1f TFLOP/s  SM clock under load %.0f MHz  -> %.1f FMA/clk/SM (measured clock)\n",
+         warps_per_sm, 2 * fma / ms / 1e9, mhz, fma / (ms * 1e-3) / 148 / (mhz * 1e6));
+}
+
 int main() {
+  for (int w : {4, 8, 16}) run2(w);
   for (int w : {4, 8, 16}) run<0>(w, "FFMA  ");
   for (int w : {4, 8, 16}) run<1>(w, "FFMA2 ");
   return 0;
