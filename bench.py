@@ -50,7 +50,7 @@ def traffic_from_profile():
     p = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(p):
         try:
-            return json.load(open(p)).get("corr_volume_tma_kernel_bytes_per_launch")
+            return json.load(open(p)).get("corr_volume_bytes_per_launch")
         except Exception:
             pass
     return None
@@ -286,7 +286,7 @@ def main():
                 "config": {"workload": WORKLOAD, "pairs_per_gpu_per_step": B_PER_GPU, "parallelism": "pairs sharded "
                            "across %d rank(s); NCCL all-gather of disparity on a side stream" % world,
                            "l2": "each step reads 134 MB of features (> 126 MB L2) from one of 3 rotating sets"},
-                "roofline": {"kernel": "corr_volume_tma_kernel<24,1>", "bound": "hbm", "achieved": achieved, "peak": peak,
+                "roofline": {"kernel": "corr_volume_ring_kernel<24,1,8,2,2>", "bound": "hbm", "achieved": achieved, "peak": peak,
                              "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                              "alg_bytes_per_launch": B_PER_GPU * ALG_BYTES_CV, "us_per_launch": k_ms * 1e3},
                 "cpu_baseline": cpu_base,

@@ -1,0 +1,67 @@
+"""Sharding of the hot path across the GPUs of one box (one process per GPU, torch.distributed).
+
+Two exchange-free partitions: by stereo pair (batch) and, for a single large pair, by epipolar row
+band.  The only collective on the inference path is the gather of the disparity maps (NCCL over NVLink on GPUs,
+gloo in the CPU tests).  Replaces the reference's single-process ``nn.DataParallel``
+(train_file/trainer_DLC_GRU.py:102-106).
+"""
+import torch
+import torch.distributed as dist
+
+
+def pair_shard(n_pairs, rank, world):
+    """Contiguous [start, stop) slice of the batch for ``rank``; the first ``n_pairs % world`` ranks get one more."""
+    base, rem = divmod(n_pairs, world)
+    start = rank * base + min(rank, rem)
+    return start, start + base + (1 if rank < rem else 0)
+
+
+def row_bands(height, world, align=1, halo=0):
+    """Row bands of a single pair: list of (y0, y1, y0_halo, y1_halo) per rank.
+
+    Bands are multiples of ``align`` rows (32 for the LowCNN trunk: 1/32 scale stages), the remainder goes to the
+    first ranks; ``halo`` rows (clipped to the image) are added on both sides for ops that are not row-local
+    (1 row at the 1/8 grid for disp_warp; the conv trunk's receptive field at full resolution)."""
+    blocks = -(-height // align)
+    out = []
+    b0 = 0
+    for r in range(world):
+        nb = blocks // world + (1 if r < blocks % world else 0)
+        y0, y1 = min(b0 * align, height), min((b0 + nb) * align, height)
+        out.append((y0, y1, max(0, y0 - halo), min(height, y1 + halo)))
+        b0 += nb
+    return out
+
+
+def _ragged_gather(t, sizes, dim, group):
+    """all_gather of tensors whose extent along ``dim`` differs per rank: pad to the largest, gather once, trim."""
+    world = len(sizes)
+    m = max(sizes)
+    shape = list(t.shape)
+    shape[dim] = m
+    pad = torch.zeros(shape, dtype=t.dtype, device=t.device)
+    pad.narrow(dim, 0, t.shape[dim]).copy_(t)
+    out = torch.empty([world] + shape, dtype=t.dtype, device=t.device)
+    dist.all_gather_into_tensor(out, pad.unsqueeze(0), group=group)
+    return torch.cat([out[r].narrow(dim, 0, sizes[r]) for r in range(world)], dim)
+
+
+def gather_disparity(disp_local, sizes=None, group=None):
+    """All-gather per-rank disparity maps [b_r,1,H,W] (b_r may differ per rank) -> [sum b_r,1,H,W] on every rank."""
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    if world == 1:
+        return disp_local
+    if sizes is None:
+        out = torch.empty((world * disp_local.shape[0],) + tuple(disp_local.shape[1:]), dtype=disp_local.dtype,
+                          device=disp_local.device)
+        dist.all_gather_into_tensor(out, disp_local.contiguous(), group=group)
+        return out
+    return _ragged_gather(disp_local, list(sizes), 0, group)
+
+
+def gather_row_bands(band_local, bands, group=None):
+    """All-gather row bands [B,1,h_r,W] (un-haloed interiors, in rank order) -> the full [B,1,H,W] map."""
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    if world == 1:
+        return band_local
+    return _ragged_gather(band_local, [y1 - y0 for (y0, y1, _, _) in bands], 2, group)
