@@ -21,7 +21,7 @@ extern "C" {
 
 /* algo selector of sf_corr_volume_f32 */
 #define SF_ALGO_AUTO 0
-#define SF_ALGO_TMA 1     /* persistent TMA + mbarrier kernel (needs W % 4 == 0, 16-B aligned pointers) */
+#define SF_ALGO_TMA 1     /* force the TMA (cost volume) / TMA + tcgen05 (attention) kernel; errors if the shape does not fit */
 #define SF_ALGO_GENERIC 2 /* shape-agnostic CUDA kernel (any W / alignment) */
 
 /* window modes of sf_local_window_f32 */

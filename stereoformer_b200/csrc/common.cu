@@ -47,7 +47,8 @@ static encode_tiled_fn get_encode() {
 }
 
 static int make_tmap_3d(CUtensorMap* out, CUtensorMapDataType dt, int esz, const void* base, uint64_t n0,
-                        uint64_t n1, uint64_t n2, uint32_t b0, uint32_t b1, uint32_t b2) {
+                        uint64_t n1, uint64_t n2, uint32_t b0, uint32_t b1, uint32_t b2,
+                        CUtensorMapSwizzle swz = CU_TENSOR_MAP_SWIZZLE_NONE) {
   encode_tiled_fn enc = get_encode();
   if (!enc) {
     set_error("cuTensorMapEncodeTiled driver entry point not available");
@@ -61,7 +62,7 @@ static int make_tmap_3d(CUtensorMap* out, CUtensorMapDataType dt, int esz, const
   cuuint32_t box[3] = {b0, b1, b2};
   cuuint32_t estr[3] = {1, 1, 1};
   CUresult r = enc(out, dt, 3, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                   CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                   swz, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     set_error("cuTensorMapEncodeTiled failed with CUresult %d (dims %llu,%llu,%llu box %u,%u,%u)", (int)r,
               (unsigned long long)n0, (unsigned long long)n1, (unsigned long long)n2, b0, b1, b2);
@@ -77,6 +78,13 @@ int make_tmap_3d_f32(CUtensorMap* out, const void* base, uint64_t n0, uint64_t n
 int make_tmap_3d_bf16(CUtensorMap* out, const void* base, uint64_t n0, uint64_t n1, uint64_t n2, uint32_t b0,
                       uint32_t b1, uint32_t b2) {
   return make_tmap_3d(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, base, n0, n1, n2, b0, b1, b2);
+}
+
+// bf16, 128-byte swizzle: the box's inner extent must be exactly 64 elements (128 B) -- the UMMA SW128 atom.
+int make_tmap_3d_bf16_sw128(CUtensorMap* out, const void* base, uint64_t n0, uint64_t n1, uint64_t n2, uint32_t b1,
+                            uint32_t b2) {
+  return make_tmap_3d(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, base, n0, n1, n2, 64, b1, b2,
+                      CU_TENSOR_MAP_SWIZZLE_128B);
 }
 
 }  // namespace sf

@@ -43,6 +43,9 @@ int make_tmap_3d_f32(CUtensorMap* out, const void* base, uint64_t n0, uint64_t n
 int make_tmap_3d_bf16(CUtensorMap* out, const void* base, uint64_t n0, uint64_t n1, uint64_t n2,
                       uint32_t b0, uint32_t b1, uint32_t b2);
 
+int make_tmap_3d_bf16_sw128(CUtensorMap* out, const void* base, uint64_t n0, uint64_t n1, uint64_t n2, uint32_t b1,
+                            uint32_t b2);
+
 static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 
 }  // namespace sf

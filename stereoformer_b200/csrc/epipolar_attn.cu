@@ -71,6 +71,10 @@ epipolar_attn_kernel(const __nv_bfloat16* __restrict__ Q, const __nv_bfloat16* _
   }
 }
 
+bool attn_tc_supported(const void* q, const void* k, const void* v, const void* out, int C, int W, int band);
+int launch_attn_tc(const void* q, const void* k, const void* v, void* out, int B, int C, int H, int W, int band,
+                   cudaStream_t stream);
+
 }  // namespace sf
 
 extern "C" int sf_epipolar_attn_bf16(const void* q, const void* k, const void* v, void* out, float* scores, int B,
@@ -79,7 +83,14 @@ extern "C" int sf_epipolar_attn_bf16(const void* q, const void* k, const void* v
   SF_CHECK_ARG(q && k && v && out, "epipolar_attn: null pointer");
   SF_CHECK_ARG(B > 0 && C > 0 && H > 0 && W > 0, "epipolar_attn: non-positive dimension");
   SF_CHECK_ARG(band >= 1 && band <= ATT_MAXBAND, "epipolar_attn: band must be in 1..%d, got %d", ATT_MAXBAND, band);
-  SF_CHECK_ARG(algo == SF_ALGO_AUTO || algo == SF_ALGO_GENERIC, "epipolar_attn: unknown algo %d", algo);
+  SF_CHECK_ARG(algo == SF_ALGO_AUTO || algo == SF_ALGO_GENERIC || algo == SF_ALGO_TMA, "epipolar_attn: unknown algo %d",
+               algo);
+  // tcgen05 path (SF_ALGO_TMA forces it): needs C % 64 == 0, C <= 256, W % 8 == 0, band <= 64, no score output
+  const bool tc_ok = attn_tc_supported(q, k, v, out, C, W, band) && scores == nullptr;
+  SF_CHECK_ARG(algo != SF_ALGO_TMA || tc_ok,
+               "epipolar_attn: tensor-core path needs C %% 64 == 0, C <= 256, W %% 8 == 0, band <= 64, scores == NULL");
+  if (algo != SF_ALGO_GENERIC && tc_ok)
+    return launch_attn_tc(q, k, v, out, B, C, H, W, band, static_cast<cudaStream_t>(stream));
   const __nv_bfloat16* Q = static_cast<const __nv_bfloat16*>(q);
   const __nv_bfloat16* K = static_cast<const __nv_bfloat16*>(k);
   const __nv_bfloat16* V = static_cast<const __nv_bfloat16*>(v);

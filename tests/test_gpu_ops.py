@@ -247,3 +247,19 @@ def test_dropin_modules_chain():
     y = sf.CostVolume(24)(x, dev(fr))
     with pytest.raises(NotImplementedError):
         y.sum().backward()
+
+
+@pytest.mark.parametrize("shape,band", [((1, 128, 6, 312), 48), ((2, 64, 3, 40), 8), ((1, 256, 2, 104), 64),
+                                        ((1, 192, 3, 264), 17), ((3, 128, 5, 128), 1), ((2, 128, 96, 312), 48)])
+def test_epipolar_attention_tcgen05(ops, shape, band):
+    """The tcgen05/TMEM kernel (forced with SF_ALGO_TMA) against the oracle and against the FFMA kernel."""
+    torch.manual_seed(59)
+    q, k, v = (torch.randn(*shape).bfloat16() for _ in range(3))
+    out = ops.epipolar_attention(dev(q), dev(k), dev(v), band, algo=ops.SF_ALGO_TMA)
+    gen = ops.epipolar_attention(dev(q), dev(k), dev(v), band, algo=ops.SF_ALGO_GENERIC)
+    assert torch.allclose(out.float(), gen.float(), rtol=2e-2, atol=2e-2)
+    if shape[2] <= 8:
+        o_ref, _ = O.epipolar_attention(q, k, v, band)
+        assert torch.allclose(out.float().cpu(), o_ref, rtol=2e-2, atol=2e-2)
+    with pytest.raises(ValueError):
+        ops.epipolar_attention(dev(q[:, :24]), dev(k[:, :24]), dev(v[:, :24]), band, algo=ops.SF_ALGO_TMA)
