@@ -154,6 +154,10 @@ __global__ void __launch_bounds__(256) corr1d_lookup_kernel(const LookupParams p
   }
 }
 
+bool corr1d_tc_supported(const float* f1, const float* f2, float* const* levels, int n_out, int W1, int W2);
+int launch_corr1d_tc(const float* f1, const float* f2, float* const* levels, int n_out, int B, int C, int H, int W1,
+                     int W2, cudaStream_t stream);
+
 }  // namespace sf
 
 extern "C" int sf_corr1d_pyramid_f32(const float* f1, const float* f2, float* const* levels, int n_out, int B, int C,
@@ -163,7 +167,14 @@ extern "C" int sf_corr1d_pyramid_f32(const float* f1, const float* f2, float* co
   SF_CHECK_ARG(B > 0 && C > 0 && H > 0 && W1 > 0 && W2 > 0, "corr1d_pyramid: non-positive dimension");
   SF_CHECK_ARG(n_out >= 1 && n_out <= C1_MAXLEV, "corr1d_pyramid: 1..%d pyramid tensors supported, got %d", C1_MAXLEV,
                n_out);
-  SF_CHECK_ARG(algo == SF_ALGO_AUTO || algo == SF_ALGO_GENERIC, "corr1d_pyramid: unknown algo %d", algo);
+  SF_CHECK_ARG(algo == SF_ALGO_AUTO || algo == SF_ALGO_GENERIC || algo == SF_ALGO_TMA, "corr1d_pyramid: unknown algo %d",
+               algo);
+  for (int l = 0; l < n_out; ++l) SF_CHECK_ARG(levels[l] && (W2 >> l) > 0, "corr1d_pyramid: level %d is empty or null", l);
+  // tcgen05 path (bf16 hi/mid split, fp32 accumulation): needs W1, W2 % 4 == 0 and 16-byte aligned pointers
+  const bool tc_ok = corr1d_tc_supported(f1, f2, levels, n_out, W1, W2);
+  SF_CHECK_ARG(algo != SF_ALGO_TMA || tc_ok, "corr1d_pyramid: tensor-core path needs W %% 4 == 0 and aligned pointers");
+  if (algo != SF_ALGO_GENERIC && tc_ok)
+    return launch_corr1d_tc(f1, f2, levels, n_out, B, C, H, W1, W2, static_cast<cudaStream_t>(stream));
   PyrPtrs out;
   int w = W2;
   for (int l = 0; l < C1_MAXLEV; ++l) {

