@@ -21,8 +21,9 @@ extern "C" {
 
 /* algo selector of sf_corr_volume_f32 */
 #define SF_ALGO_AUTO 0
-#define SF_ALGO_TMA 1     /* force the TMA (cost volume) / TMA + tcgen05 (attention) kernel; errors if the shape does not fit */
+#define SF_ALGO_TMA 1     /* force the TMA + FFMA (cost volume) / TMA + tcgen05 (attention) kernel; errors if the shape does not fit */
 #define SF_ALGO_GENERIC 2 /* shape-agnostic CUDA kernel (any W / alignment) */
+#define SF_ALGO_TC 3      /* cost volume on tcgen05 (bf16 hi/mid split, fp32 TMEM accumulation); errors if the shape does not fit */
 
 /* window modes of sf_local_window_f32 */
 #define SF_WIN_FIXED 0    /* fixed_local_cost_volume.py: bounds = disp -/+ radius                  */

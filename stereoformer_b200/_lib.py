@@ -9,7 +9,7 @@ import os
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libsfb200.so")
 
-SF_ALGO_AUTO, SF_ALGO_TMA, SF_ALGO_GENERIC = 0, 1, 2
+SF_ALGO_AUTO, SF_ALGO_TMA, SF_ALGO_GENERIC, SF_ALGO_TC = 0, 1, 2, 3
 SF_WIN_FIXED, SF_WIN_VARIANCE, SF_WIN_OFFSETS, SF_WIN_ABSOLUTE = 0, 1, 2, 3
 SF_DIV_TRUE, SF_DIV_RECIP = 0, 1
 

@@ -20,6 +20,11 @@
 
 namespace sf {
 
+// corr_volume_tc.cu
+bool corr_tc_supported(const float* L, const float* R, const float* out, int nBG, int Cg, int H, int W, int D);
+int launch_corr_tc(const float* L, const float* R, float* out, int nBG, int Cg, int H, int W, int D, int dbg,
+                   cudaStream_t stream);
+
 constexpr int CV_NCW = 4;      // consumer warps
 constexpr int CV_XMAX = 128;   // pixels covered by one warp (32 lanes x 4)
 constexpr int CV_THREADS = (CV_NCW + 1) * 32;
@@ -226,7 +231,7 @@ corr_volume_tma_kernel(const __grid_constant__ CUtensorMap mapL, const __grid_co
 // v2: no producer warp.  Every channel-split group of warps owns a private ring of SW stages and refills a
 // slot itself (one elected lane issues the two TMA boxes) right after it has drained it, so a slow warp never
 // blocks the loads of the others (the shared in-order ring above couples all four warps to the slowest one).
-template <int DT, int NDB, int CK, int SW, int MINB>
+template <int DT, int NDB, int CK, int SW, int MINB, int DBG = 0>
 __global__ void __launch_bounds__(CV_NCW * 32, MINB)
 corr_volume_ring_kernel(const __grid_constant__ CUtensorMap mapL, const __grid_constant__ CUtensorMap mapR,
                         const CorrParams p) {
@@ -278,9 +283,11 @@ corr_volume_ring_kernel(const __grid_constant__ CUtensorMap mapL, const __grid_c
     int dtile = t3 % p.ndt, bg = t3 / p.ndt;
     const int xs0 = seg * p.XS, c0 = bg * p.Cg + (cs + i_j * NCS) * CK;
     float* dst = ring + slot * stage_floats;
-    mbar_expect_tx(&rfull[slot], bytes);
-    tma_load_3d(dst, &mapL, &rfull[slot], xs0, y, c0);
-    tma_load_3d(dst + CK * XSL, &mapR, &rfull[slot], xs0 - dtile * DP - DP, y, c0);
+    if (DBG != 2) {
+      mbar_expect_tx(&rfull[slot], bytes);
+      tma_load_3d(dst, &mapL, &rfull[slot], xs0, y, c0);
+      tma_load_3d(dst + CK * XSL, &mapR, &rfull[slot], xs0 - dtile * DP - DP, y, c0);
+    }
     ++qi;
     if (++i_j == npw) { i_j = 0; i_tile += gridDim.x; }
   };
@@ -295,11 +302,13 @@ corr_volume_ring_kernel(const __grid_constant__ CUtensorMap mapL, const __grid_c
 
     for (int j = 0; j < npw; ++j, ++qc) {
       const int slot = qc % SW;
-      mbar_wait(&rfull[slot], (qc / SW) & 1);
+      if (DBG != 2) mbar_wait(&rfull[slot], (qc / SW) & 1);
       const float* Ls = ring + slot * stage_floats + lx;
       const float* Rs = ring + slot * stage_floats + CK * XSL + roff;
       const int nv = min(CK, p.Cg - (cs + j * NCS) * CK);
-      if (nv == CK) {
+      if (DBG == 1) {
+        acc[0][0] += Ls[0];
+      } else if (nv == CK) {
         float4 lq[2], rq[2][NR4];
         lq[0] = *reinterpret_cast<const float4*>(Ls);
 #pragma unroll
@@ -477,7 +486,7 @@ static int launch_corr_tma_cfg(const float* L, const float* R, float* out, int n
   return SF_OK;
 }
 
-template <int DT, int NDB, int CK, int SW, int MINB = 2>
+template <int DT, int NDB, int CK, int SW, int MINB = 2, int DBG = 0>
 static int launch_corr_ring_cfg(const float* L, const float* R, float* out, int nBG, int Cg, int H, int W, int D,
                                 cudaStream_t stream) {
   CorrParams p;
@@ -502,7 +511,7 @@ static int launch_corr_ring_cfg(const float* L, const float* R, float* out, int 
   const int stage_floats = CK * (2 * p.XS + DP);
   const int nslot = NCS > 1 ? 2 : 0;
   const size_t smem = (static_cast<size_t>(NCS) * SW * stage_floats + nslot * DT * p.XS) * 4 + 2 * NCS * SW * 8 + 128;
-  auto kern = corr_volume_ring_kernel<DT, NDB, CK, SW, MINB>;
+  auto kern = corr_volume_ring_kernel<DT, NDB, CK, SW, MINB, DBG>;
   SF_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
   int grid = min(p.ntiles, MINB * sm_count());
   kern<<<grid, CV_NCW * 32, smem, stream>>>(mL, mR, p);
@@ -532,6 +541,10 @@ static int launch_corr_tma(const float* L, const float* R, float* out, int nBG, 
     case 14: return launch_corr_ring_cfg<DT, NDB, 4, 12 / NCS, 3>(L, R, out, nBG, Cg, H, W, D, stream);
     case 15: return launch_corr_ring_cfg<DT, NDB, 8, 8 / NCS, 3>(L, R, out, nBG, Cg, H, W, D, stream);
     case 16: return launch_corr_ring_cfg<DT, NDB, 4, 8 / NCS, 3>(L, R, out, nBG, Cg, H, W, D, stream);
+    case 20: return launch_corr_ring_cfg<DT, NDB, 8, 8 / NCS, 2, 1>(L, R, out, nBG, Cg, H, W, D, stream);
+    case 21: return launch_corr_ring_cfg<DT, NDB, 8, 8 / NCS, 2, 2>(L, R, out, nBG, Cg, H, W, D, stream);
+    case 22: return launch_corr_ring_cfg<DT, NDB, 4, 16 / NCS, 2, 1>(L, R, out, nBG, Cg, H, W, D, stream);
+    case 23: return launch_corr_ring_cfg<DT, NDB, 4, 16 / NCS, 2, 2>(L, R, out, nBG, Cg, H, W, D, stream);
     case 1: return launch_corr_tma_cfg<DT, NDB, 4, 8>(L, R, out, nBG, Cg, H, W, D, stream);
     case 2: return launch_corr_tma_cfg<DT, NDB, 16, 6>(L, R, out, nBG, Cg, H, W, D, stream);
     case 3: return launch_corr_tma_cfg<DT, NDB, 8, 4>(L, R, out, nBG, Cg, H, W, D, stream);
@@ -564,6 +577,14 @@ extern "C" int sf_corr_volume_f32(const float* left, const float* right, float* 
   const bool tma_ok = (W % 4 == 0) && ((reinterpret_cast<uintptr_t>(left) | reinterpret_cast<uintptr_t>(right) |
                                         reinterpret_cast<uintptr_t>(out)) & 15) == 0;
   SF_CHECK_ARG(algo != SF_ALGO_TMA || tma_ok, "corr_volume: TMA path needs W %% 4 == 0 and 16-byte aligned pointers");
+  {
+    // tensor-core path: default whenever the channel count makes the 32-channel MMA chunks worthwhile
+    const int v = cv_variant();
+    const bool tc_ok = corr_tc_supported(left, right, out, nBG, Cg, H, W, D);
+    SF_CHECK_ARG(algo != SF_ALGO_TC || tc_ok, "corr_volume: shape / alignment does not fit the tcgen05 kernel");
+    if (algo == SF_ALGO_TC || (v >= 30 && v <= 49 && tc_ok) || (algo == SF_ALGO_AUTO && v == 0 && tc_ok && Cg >= 32))
+      return launch_corr_tc(left, right, out, nBG, Cg, H, W, D, v >= 30 ? v - 30 : 0, s);
+  }
   if (algo == SF_ALGO_GENERIC || !tma_ok) {
     size_t n = static_cast<size_t>(nBG) * D * H * W;
     int grid = static_cast<int>(min(static_cast<size_t>(sm_count()) * 16, (n + 255) / 256));

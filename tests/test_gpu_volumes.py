@@ -65,6 +65,35 @@ def test_corr_volume_oracle(ops, shape):
     assert close_rel(gen, ref)
 
 
+@pytest.mark.parametrize("shape", [(1, 256, 32, 64, 24),      # C1
+                                   (2, 256, 68, 120, 24),     # C2 (two pairs)
+                                   (1, 64, 9, 360, 48),       # C5 row shape: three x segments, D=48
+                                   (1, 32, 5, 312, 8), (1, 40, 3, 264, 16), (2, 10, 4, 48, 32), (1, 24, 3, 96, 64),
+                                   (1, 16, 2, 200, 100),      # wide halo: x segments of 96
+                                   (1, 7, 3, 20, 24), (1, 3, 1, 8, 30),   # ragged channel chunk, D > W
+                                   (1, 96, 2, 128, 129), (3, 33, 7, 132, 1)])
+def test_corr_volume_tensor_core(ops, shape):
+    """tcgen05 path (bf16 hi/mid split, fp32 TMEM accumulation) against the fp32 oracle at the same 1e-4 bound."""
+    B, C, H, W, D = shape
+    torch.manual_seed(1024)
+    L, R = torch.randn(B, C, H, W), torch.randn(B, C, H, W)
+    ref = O.corr_volume(L, R, D)
+    out = ops.corr_volume(dev(L), dev(R), D, algo=ops.SF_ALGO_TC)
+    assert close_rel(out, ref)
+    assert (out.cpu()[ref == 0] == 0).all()          # the x < d triangle is exactly zero
+    # large dynamic range: the split must track fp32, not bf16, accuracy
+    L2 = L * torch.logspace(-3, 3, C).view(1, C, 1, 1)
+    ref2 = O.corr_volume(L2, R, D)
+    assert close_rel(ops.corr_volume(dev(L2), dev(R), D, algo=ops.SF_ALGO_TC), ref2)
+
+
+def test_corr_volume_tensor_core_limits(ops):
+    x = torch.randn(1, 32, 2, 64, device="cuda")
+    with pytest.raises(ValueError):
+        ops.corr_volume(x, x, 140, algo=ops.SF_ALGO_TC)        # halo > 128 pixels
+    assert close_rel(ops.corr_volume(x, x, 140), O.corr_volume(x.cpu(), x.cpu(), 140))   # AUTO falls back
+
+
 def test_corr_volume_groups(ops):
     torch.manual_seed(3)
     L, R = torch.randn(2, 48, 6, 64), torch.randn(2, 48, 6, 64)
