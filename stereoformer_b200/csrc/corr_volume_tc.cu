@@ -4,11 +4,13 @@
 //   cv[b,g,d,y,x] = (1/Cg) * sum_{c in g} L[b,c,y,x] * R[b,c,y,x-d]   (0 for x < d).
 //
 // Per epipolar row this is the BAND of the product L^T R.  The FFMA kernel (corr_volume.cu) is co-limited by the
-// FP32 pipe (AI ~ 5.7 flop/B vs an FP32 ridge of ~8) and never overlaps loads and math well enough; here the
-// math moves to the tensor cores and the SM only converts and extracts:
+// FP32 pipe (AI ~ 5.7 flop/B vs an FP32 ridge of ~8); here the math moves to the tensor cores and the SM only
+// converts and extracts:
 //   * warp 0 streams 32-channel chunks of the left row segment and of the right row segment (with its left halo;
-//     TMA out-of-bounds zero fill = the reference's x<d zeros) into a shared-memory ring (cp.async.bulk.tensor);
-//   * 16 converter warps split every fp32 value into bf16 hi + bf16 mid (residual <= 2^-17 |x|) and write both
+//     TMA out-of-bounds zero fill = the reference's x<d zeros) into a shared-memory ring (cp.async.bulk.tensor).
+//     (Loading the rows straight into registers with ld.global instead was measured too: the LSU cannot keep
+//     more than ~32 KB per SM in flight, 3.0 TB/s; the TMA ring alone streams at 6.3 TB/s.)
+//   * 8 converter warps split every fp32 value into bf16 hi + bf16 mid (residual <= 2^-17 |x|) and write both
 //     halves into the canonical MN-major SWIZZLE_128B UMMA layout (double-buffered operand stage);
 //   * one thread issues hi*hi + hi*mid + mid*hi (3 tcgen05.mma per 16 channels) into a [128 x N] fp32 TMEM
 //     accumulator (double-buffered, 2 x 256 columns): acc[x][c] = <L[:,xs0+x], R[:,xs0-HL+c]>;
@@ -26,8 +28,8 @@
 
 namespace sf {
 
-constexpr int VT_KC = 32;                        // channels per stage
-constexpr int VT_NCONV = 16;                     // converter warps: warp w converts rows k = (w & 7) + 8 * {2h, 2h+1}, h = w >> 3
+constexpr int VT_KC = 32;                        // channels per operand stage
+constexpr int VT_NCONV = 8;                      // converter warps: warp w converts channel rows k = w mod 8 of every chunk
 constexpr int VT_WARP_MMA = 1 + VT_NCONV;
 constexpr int VT_THREADS = (1 + VT_NCONV + 1 + 4) * 32;
 constexpr int VT_BLK = VT_KC * 128;              // one MN block (64 elements) of an operand half: 4 KB
@@ -39,7 +41,7 @@ struct CorrTcParams {
   int Cg, H, W, D, nBG;
   int XS;          // pixels per x segment (multiple of 8, <= 128)
   int HL;          // left halo of the right row (multiple of 4, >= D-1)
-  int BW;          // XS + HL: width of the right-row box
+  int BW;          // XS + HL: width of the right-row box (<= 192)
   int N;           // MMA N: BW rounded up to 16
   int nbB;         // MN blocks of the B operand
   int nseg, ntiles, nch;
@@ -48,13 +50,15 @@ struct CorrTcParams {
   long long* ts;   // tuning only: per-role clock64 timeline of CTA 0 (NULL in production)
 };
 
-// fp32x4 -> bf16 hi x4 + bf16 mid x4
-__device__ __forceinline__ void split4(const float4 v, uint2& hi, uint2& mid) {
+// fp32x4 -> bf16 hi x4 + bf16 mid x4, stored into the two operand halves
+__device__ __forceinline__ void split_store(unsigned char* hi_p, unsigned char* mid_p, const float4 v) {
   const __nv_bfloat162 h01 = __floats2bfloat162_rn(v.x, v.y), h23 = __floats2bfloat162_rn(v.z, v.w);
   const __nv_bfloat162 m01 = __floats2bfloat162_rn(v.x - __low2float(h01), v.y - __high2float(h01));
   const __nv_bfloat162 m23 = __floats2bfloat162_rn(v.z - __low2float(h23), v.w - __high2float(h23));
-  hi = make_uint2(*reinterpret_cast<const uint32_t*>(&h01), *reinterpret_cast<const uint32_t*>(&h23));
-  mid = make_uint2(*reinterpret_cast<const uint32_t*>(&m01), *reinterpret_cast<const uint32_t*>(&m23));
+  *reinterpret_cast<uint2*>(hi_p) =
+      make_uint2(*reinterpret_cast<const uint32_t*>(&h01), *reinterpret_cast<const uint32_t*>(&h23));
+  *reinterpret_cast<uint2*>(mid_p) =
+      make_uint2(*reinterpret_cast<const uint32_t*>(&m01), *reinterpret_cast<const uint32_t*>(&m23));
 }
 
 // byte offset of MN element x (x % 4 == 0) in channel row kr (< 8) of an MN-major SW128 operand half
@@ -76,6 +80,7 @@ __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.comm
 __device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 
+
 // DBG (tuning only, bit mask): 1 = skip the conversion, 2 = skip the loads, 4 = skip the MMAs, 8 = skip the epilogue.
 template <int DBG>
 __global__ void __launch_bounds__(VT_THREADS, 1)
@@ -88,8 +93,8 @@ corr_volume_tc_kernel(const __grid_constant__ CUtensorMap mapL, const __grid_con
   float* sTile = reinterpret_cast<float*>(sOps + VT_NOPS * p.op_bytes);   // [D][XS] output tile
   uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<unsigned char*>(sTile) + p.tile_bytes);
   uint64_t* stg_full = bars;                        // [NS]  TMA -> converters
-  uint64_t* stg_empty = bars + VT_MAXNS;            // [NS]  converters -> TMA
-  uint64_t* op_full = bars + 2 * VT_MAXNS;          // [2]   converters -> MMA
+  uint64_t* stg_empty = bars + VT_MAXNS;            // [NS]  converters (8 warps) -> TMA
+  uint64_t* op_full = bars + 2 * VT_MAXNS;          // [2]   converters (8 warps) -> MMA
   uint64_t* op_empty = op_full + 2;                 // [2]   MMA commit -> converters
   uint64_t* acc_full = op_full + 4;                 // [2]   MMA commit -> epilogue
   uint64_t* acc_empty = op_full + 6;                // [2]   epilogue (4 warps) -> MMA
@@ -142,89 +147,55 @@ corr_volume_tc_kernel(const __grid_constant__ CUtensorMap mapL, const __grid_con
     }
   } else if (warp <= VT_NCONV) {
     // ================================================================= converters: fp32 -> bf16 hi/mid operands
-    const int cw = (warp - 1) & 7;                 // channel-row residue mod 8 (= the swizzle phase of the row)
-    const int i0 = ((warp - 1) >> 3) * 2;          // this warp's rows: cw + 8*i0, cw + 8*(i0+1)
+    const int cw = warp - 1;                       // this warp's channel rows of a chunk: cw + 8*i, i = 0..3
     const int nx4L = p.XS >> 2, nx4R = p.BW >> 2;
-    const bool okL = lane < nx4L, okR = lane < nx4R;
-    const int offM = op_offset(4 * lane, cw) + i0 * 1024;
-    // right-row tail (float4 columns >= 32): both rows share one pass when it has <= 16 columns
-    const int T = nx4R > 32 ? nx4R - 32 : 0;
-    const int PF = T == 0 ? 0 : (T <= 16 ? 2 : 1);
-    const int lpr = PF == 2 ? 16 : 32;
-    const int tsub = lane / lpr, tx4 = 32 + lane % lpr;
-    const bool okT = PF && (lane % lpr) < T;
-    const int offT = op_offset(4 * tx4, cw) + i0 * 1024;
-    const int kA = cw + 8 * i0, kB = kA + 8;
-    const float* Lp = reinterpret_cast<const float*>(sStage) + kA * p.XS + 4 * lane;
-    const float* Rp = reinterpret_cast<const float*>(sStage) + VT_KC * p.XS + kA * p.BW + 4 * lane;
-    const int stage_f = p.stage_bytes >> 2;
-    int s = 0, ph = 0, it = 0, nts = 0;
+    const int T = nx4R > 32 ? nx4R - 32 : 0;       // right-row float4 columns >= 32 (<= 16): two rows per pass
+    const int tsub = lane >> 4, tx4 = 32 + (lane & 15);
+    const int offM = op_offset(4 * lane, cw);
+    const int offT = op_offset(4 * tx4, cw) + tsub * 1024;
+    const bool stl = lane < nx4L, str = lane < nx4R, stt = (lane & 15) < T;
     const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    const int rowL = 8 * p.XS, rowR = 8 * p.BW;    // floats between this warp's consecutive rows
+    const float* Lp = reinterpret_cast<const float*>(sStage) + cw * p.XS + 4 * lane;
+    const float* Rp = reinterpret_cast<const float*>(sStage) + VT_KC * p.XS + cw * p.BW + 4 * lane;
+    const float* Tp = reinterpret_cast<const float*>(sStage) + VT_KC * p.XS + (cw + 8 * tsub) * p.BW + 4 * tx4;
+    const int stage_f = p.stage_bytes >> 2;
+    int s = 0, ph = 0, o = 0, pho = 1, nts = 0;
     for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
-      for (int kc = 0; kc < p.nch; ++kc, ++it) {
-        const int o = it & 1;
+      for (int kc = 0; kc < p.nch; ++kc) {
         if (!(DBG & 2)) mbar_wait(&stg_full[s], ph);
         if (threadIdx.x == 32) ts_mark(p, 1, nts);
-        mbar_wait(&op_empty[o], ((it >> 1) & 1) ^ 1);
+        mbar_wait(&op_empty[o], pho);
         if (threadIdx.x == 32) ts_mark(p, 1, nts);
         if (!(DBG & 1)) {
           const float* Ls = Lp + s * stage_f;
           const float* Rs = Rp + s * stage_f;
-          unsigned char* a_hi = sOps + o * p.op_bytes;
-          unsigned char* a_mid = a_hi + VT_A_HALF;
-          unsigned char* b_hi = a_hi + 2 * VT_A_HALF;
-          unsigned char* b_mid = b_hi + p.nbB * VT_BLK;
-          const int nv = p.Cg - kc * VT_KC;        // valid channels of this chunk (rows beyond are zeros)
-          const bool vA = kA < nv, vB = kB < nv;
-          // all six loads first (independent), then split + store
-          float4 l0 = zero4, l1 = zero4, r0 = zero4, r1 = zero4, t0 = zero4;
-          if (okL) {
-            if (vA) l0 = *reinterpret_cast<const float4*>(Ls);
-            if (vB) l1 = *reinterpret_cast<const float4*>(Ls + 8 * p.XS);
-          }
-          if (okR) {
-            if (vA) r0 = *reinterpret_cast<const float4*>(Rs);
-            if (vB) r1 = *reinterpret_cast<const float4*>(Rs + 8 * p.BW);
-          }
-          if (PF == 2) {
-            if (okT && (tsub ? vB : vA)) t0 = *reinterpret_cast<const float4*>(Rs + tsub * 8 * p.BW + 4 * (tx4 - lane));
-          }
-          uint2 h, m;
-          if (threadIdx.x == 32) ts_mark(p, 1, nts);
-          if (okL) {
-            split4(l0, h, m);
-            *reinterpret_cast<uint2*>(a_hi + offM) = h;
-            *reinterpret_cast<uint2*>(a_mid + offM) = m;
-            split4(l1, h, m);
-            *reinterpret_cast<uint2*>(a_hi + offM + 1024) = h;
-            *reinterpret_cast<uint2*>(a_mid + offM + 1024) = m;
-          }
-          if (okR) {
-            split4(r0, h, m);
-            *reinterpret_cast<uint2*>(b_hi + offM) = h;
-            *reinterpret_cast<uint2*>(b_mid + offM) = m;
-            split4(r1, h, m);
-            *reinterpret_cast<uint2*>(b_hi + offM + 1024) = h;
-            *reinterpret_cast<uint2*>(b_mid + offM + 1024) = m;
-          }
-          if (PF == 2) {
-            if (okT) {
-              split4(t0, h, m);
-              *reinterpret_cast<uint2*>(b_hi + offT + tsub * 1024) = h;
-              *reinterpret_cast<uint2*>(b_mid + offT + tsub * 1024) = m;
-            }
-          } else if (PF == 1) {
-            if (okT) {
+          const float* Ts = Tp + s * stage_f;
+          const int nv = p.Cg - kc * VT_KC - cw;   // row i is a real channel iff 8*i < nv
+          float4 l[4], r[4], t[2];
 #pragma unroll
-              for (int r = 0; r < 2; ++r) {
-                const float4 w = (r ? vB : vA) ? *reinterpret_cast<const float4*>(Rs + r * 8 * p.BW + 128) : zero4;
-                split4(w, h, m);
-                *reinterpret_cast<uint2*>(b_hi + offT + r * 1024) = h;
-                *reinterpret_cast<uint2*>(b_mid + offT + r * 1024) = m;
-              }
-            }
+          for (int i = 0; i < 4; ++i) {
+            l[i] = (stl && 8 * i < nv) ? *reinterpret_cast<const float4*>(Ls + i * rowL) : zero4;
+            r[i] = (str && 8 * i < nv) ? *reinterpret_cast<const float4*>(Rs + i * rowR) : zero4;
           }
-          if (threadIdx.x == 32) ts_mark(p, 1, nts);
+          t[0] = (stt && 8 * tsub < nv) ? *reinterpret_cast<const float4*>(Ts) : zero4;
+          t[1] = (stt && 8 * (tsub + 2) < nv) ? *reinterpret_cast<const float4*>(Ts + 2 * rowR) : zero4;
+          unsigned char* a_hi = sOps + o * p.op_bytes + offM;
+          unsigned char* b_hi = a_hi + 2 * VT_A_HALF;
+          const int bmid = p.nbB * VT_BLK;
+          if (stl) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) split_store(a_hi + i * 1024, a_hi + VT_A_HALF + i * 1024, l[i]);
+          }
+          if (str) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) split_store(b_hi + i * 1024, b_hi + bmid + i * 1024, r[i]);
+          }
+          if (stt) {
+            unsigned char* t_hi = b_hi + (offT - offM);
+            split_store(t_hi, t_hi + bmid, t[0]);
+            split_store(t_hi + 2048, t_hi + bmid + 2048, t[1]);
+          }
           fence_proxy_async_smem();
         }
         __syncwarp();
@@ -234,22 +205,21 @@ corr_volume_tc_kernel(const __grid_constant__ CUtensorMap mapL, const __grid_con
           mbar_arrive(&stg_empty[s]);
         }
         if (++s == p.NS) { s = 0; ph ^= 1; }
+        if (++o == VT_NOPS) { o = 0; pho ^= 1; }
       }
     }
-  }
-  else if (warp == VT_WARP_MMA) {
+  } else if (warp == VT_WARP_MMA) {
     // ================================================================= MMA issuer
     if (lane == 0) {
       const uint32_t idesc = make_idesc_bf16(128, p.N, 1, 1);
-      int it = 0, t = 0, nts = 0;
+      int o = 0, ph = 0, t = 0, nts = 0;
       for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x, ++t) {
         const int buf = t & 1;
         mbar_wait(&acc_empty[buf], ((t >> 1) & 1) ^ 1);
         tc_fence_after();
         const uint32_t acc = tmem + buf * 256;
-        for (int kc = 0; kc < p.nch; ++kc, ++it) {
-          const int o = it & 1;
-          mbar_wait(&op_full[o], (it >> 1) & 1);
+        for (int kc = 0; kc < p.nch; ++kc) {
+          mbar_wait(&op_full[o], ph);
           tc_fence_after();
           ts_mark(p, 2, nts);
           if (!(DBG & 4)) {
@@ -266,6 +236,7 @@ corr_volume_tc_kernel(const __grid_constant__ CUtensorMap mapL, const __grid_con
             }
           }
           umma_commit(&op_empty[o]);
+          if (++o == VT_NOPS) { o = 0; ph ^= 1; }
         }
         umma_commit(&acc_full[buf]);
       }
@@ -286,44 +257,45 @@ corr_volume_tc_kernel(const __grid_constant__ CUtensorMap mapL, const __grid_con
       const int buf = t & 1;
       mbar_wait(&acc_full[buf], (t >> 1) & 1);
       tc_fence_after();
-      if (q == 0 && lane == 0) ts_mark(p, 3, nts);
+      if (leader) ts_mark(p, 3, nts);
       if (leader && t > 0) bulk_wait_read0();        // the previous tile has left shared memory
       named_bar_sync(1, 128);
-      if (q == 0 && lane == 0) ts_mark(p, 3, nts);
       if (32 * q < XS && !(DBG & 8)) {
         const uint32_t trow = tmem + buf * 256 + (static_cast<uint32_t>(32 * q) << 16);
         for (int d0 = 0; d0 < p.D; d0 += 32) {
           // lane l, disparity d0+e needs column 32q + l + HL - d0 - e: a 63-column window starting at cs
           const int cs = max(0, 32 * q + p.HL - d0 - 31);
           const int ne = min(32, p.D - d0);
-          // register j of the window holds disparity d = dj0 - j for this lane
-          const int dj0 = xl + p.HL - cs;
+          const int dj0 = xl + p.HL - cs;           // register j of the window holds disparity dj0 - j
           float* tp = sTile + dj0 * XS + xl;
 #pragma unroll
           for (int hh = 0; hh < 2; ++hh) {
             uint32_t raw[32];
             tmem_ld32(trow + cs + 32 * hh, raw);
             tmem_ld_wait();
-            if (q == 0 && lane == 0) ts_mark(p, 3, nts);
             if (xl < XS) {
+              const unsigned ub = static_cast<unsigned>(ne);
+              const int e0 = dj0 - 32 * hh - d0;     // register j holds disparity d0 + (e0 - j)
+              float* tq = tp - 32 * hh * XS;
+              if (pow2) {
 #pragma unroll
-              for (int j = 0; j < 32; ++j) {
-                const int jj = 32 * hh + j;
-                const float a = __uint_as_float(raw[j]);
-                if (static_cast<unsigned>(dj0 - jj - d0) < static_cast<unsigned>(ne))
-                  tp[-jj * XS] = pow2 ? a * inv : __fdiv_rn(a, fc);
+                for (int j = 0; j < 32; ++j)
+                  if (static_cast<unsigned>(e0 - j) < ub) tq[-j * XS] = __uint_as_float(raw[j]) * inv;
+              } else {
+#pragma unroll
+                for (int j = 0; j < 32; ++j)
+                  if (static_cast<unsigned>(e0 - j) < ub) tq[-j * XS] = __fdiv_rn(__uint_as_float(raw[j]), fc);
               }
             }
           }
         }
       }
-      if (q == 0 && lane == 0) ts_mark(p, 3, nts);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&acc_empty[buf]);
       fence_proxy_async_smem();
       named_bar_sync(1, 128);
-      if (q == 0 && lane == 0) ts_mark(p, 3, nts);
+      if (leader) ts_mark(p, 3, nts);
       if (leader && !(DBG & 8)) {
         tma_store_3d(&mapO, sTile, seg * XS, y, bg * p.D);
         bulk_commit();
@@ -341,9 +313,10 @@ static bool corr_tc_plan(CorrTcParams& p, int nBG, int Cg, int H, int W, int D) 
   p.HL = ((D - 1 + 3) / 4) * 4;
   if (p.HL > 128 || D > 256 || 1LL * nBG * D >= (1LL << 31)) return false;
   p.nch = ceil_div(Cg, VT_KC);
-  // widest x segment whose staging ring (>= 2 stages), operand stages and output tile fit in shared memory
+  // widest x segment whose right-row window fits 48 float4 columns and whose staging ring (>= 2 stages), operand
+  // stages and output tile fit in shared memory
   for (int xcap = 128; xcap >= 32; xcap -= 32) {
-    if (xcap + p.HL > 256) continue;
+    if (xcap + p.HL > 192) continue;
     p.nseg = ceil_div(W, xcap);
     p.XS = ceil_div(ceil_div(W, p.nseg), 8) * 8;
     if (p.XS > xcap) { p.nseg += 1; p.XS = ceil_div(ceil_div(W, p.nseg), 8) * 8; }
@@ -355,9 +328,8 @@ static bool corr_tc_plan(CorrTcParams& p, int nBG, int Cg, int H, int W, int D) 
     p.ntiles = static_cast<int>(nt);
     p.stage_bytes = ceil_div(VT_KC * (p.XS + p.BW) * 4, 1024) * 1024;
     p.op_bytes = 2 * VT_A_HALF + 2 * p.nbB * VT_BLK;
-    p.tile_bytes = ceil_div(D * p.XS * 4, 128) * 128;
-    const int fixed = VT_NOPS * p.op_bytes + p.tile_bytes + 256;
-    p.NS = min(VT_MAXNS, (232448 - fixed) / p.stage_bytes);
+    p.tile_bytes = ceil_div(D * p.XS * 4, 1024) * 1024;
+    p.NS = min(VT_MAXNS, (232448 - VT_NOPS * p.op_bytes - p.tile_bytes - 256) / p.stage_bytes);
     if (p.NS >= 2) return true;
   }
   return false;
@@ -395,13 +367,12 @@ int launch_corr_tc(const float* L, const float* R, float* out, int nBG, int Cg, 
     return SF_OK;
   };
   switch (dbg) {
-    case 5: return go(corr_volume_tc_kernel<5>);     // loads + barrier protocol + epilogue
     case 13: return go(corr_volume_tc_kernel<13>);   // loads + barrier protocol only
     case 2: return go(corr_volume_tc_kernel<2>);     // everything but the loads
     case 14: return go(corr_volume_tc_kernel<14>);   // conversion only
     case 11: return go(corr_volume_tc_kernel<11>);   // MMA only
     case 8: return go(corr_volume_tc_kernel<8>);     // no epilogue
-    case 9: return go(corr_volume_tc_kernel<9>);     // loads + MMA (no conversion, no epilogue)
+    case 12: return go(corr_volume_tc_kernel<12>);   // loads + conversion
     default: return go(corr_volume_tc_kernel<0>);
   }
 }
