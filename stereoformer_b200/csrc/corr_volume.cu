@@ -582,7 +582,7 @@ extern "C" int sf_corr_volume_f32(const float* left, const float* right, float* 
     const int v = cv_variant();
     const bool tc_ok = corr_tc_supported(left, right, out, nBG, Cg, H, W, D);
     SF_CHECK_ARG(algo != SF_ALGO_TC || tc_ok, "corr_volume: shape / alignment does not fit the tcgen05 kernel");
-    if (algo == SF_ALGO_TC || (v >= 30 && v <= 49 && tc_ok) || (algo == SF_ALGO_AUTO && v == 0 && tc_ok && Cg >= 32))
+    if (algo == SF_ALGO_TC || (v >= 30 && v <= 99 && tc_ok) || (algo == SF_ALGO_AUTO && v == 0 && tc_ok && Cg >= 32))
       return launch_corr_tc(left, right, out, nBG, Cg, H, W, D, v >= 30 ? v - 30 : 0, s);
   }
   if (algo == SF_ALGO_GENERIC || !tma_ok) {

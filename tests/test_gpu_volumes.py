@@ -69,9 +69,9 @@ def test_corr_volume_oracle(ops, shape):
                                    (2, 256, 68, 120, 24),     # C2 (two pairs)
                                    (1, 64, 9, 360, 48),       # C5 row shape: three x segments, D=48
                                    (1, 32, 5, 312, 8), (1, 40, 3, 264, 16), (2, 10, 4, 48, 32), (1, 24, 3, 96, 64),
-                                   (1, 16, 2, 200, 100),      # wide halo: x segments of 96
+                                   (1, 48, 2, 200, 65),       # widest halo (64) + a clipped second segment
                                    (1, 7, 3, 20, 24), (1, 3, 1, 8, 30),   # ragged channel chunk, D > W
-                                   (1, 96, 2, 128, 129), (3, 33, 7, 132, 1)])
+                                   (2, 72, 2, 128, 40), (3, 33, 7, 132, 1)])
 def test_corr_volume_tensor_core(ops, shape):
     """tcgen05 path (bf16 hi/mid split, fp32 TMEM accumulation) against the fp32 oracle at the same 1e-4 bound."""
     B, C, H, W, D = shape
@@ -90,8 +90,8 @@ def test_corr_volume_tensor_core(ops, shape):
 def test_corr_volume_tensor_core_limits(ops):
     x = torch.randn(1, 32, 2, 64, device="cuda")
     with pytest.raises(ValueError):
-        ops.corr_volume(x, x, 140, algo=ops.SF_ALGO_TC)        # halo > 128 pixels
-    assert close_rel(ops.corr_volume(x, x, 140), O.corr_volume(x.cpu(), x.cpu(), 140))   # AUTO falls back
+        ops.corr_volume(x, x, 70, algo=ops.SF_ALGO_TC)         # halo > 64 pixels
+    assert close_rel(ops.corr_volume(x, x, 70), O.corr_volume(x.cpu(), x.cpu(), 70))   # AUTO falls back
 
 
 def test_corr_volume_groups(ops):
