@@ -9,10 +9,10 @@ SceneFlow 544x960, maxdisp 192 -> 1/8 grid 68x120, 256 feature channels, D=24, b
 fused soft-argmin / local disparity-window sampling (a3+a4) over the batch; with N>1 the disparity maps are
 all-gathered over NCCL on a side stream (north_star: NCCL only gathers disparity maps).
 
-value : pairs/s, inputs resident in HBM, CUDA-event timed, max over ranks.
+value : pairs/s, inputs resident in HBM, steps replayed from CUDA graphs, CUDA-event timed, max over ranks.
 e2e   : pairs/s through the public module API with HOST (pinned) feature buffers: H2D of both feature maps
         and D2H of the refined disparity inside the timed region.
-roofline : the dominant kernel (corr_volume_tma_kernel) alone, algorithmic bytes / CUDA-event time vs the
+roofline : the dominant kernel (corr_volume_tc_kernel) alone, algorithmic bytes / CUDA-event time vs the
         measured HBM peak (MEASURED_PEAKS.json).
 cpu_baseline / --impl reference : the oracle's CPU port of the same chain on the host cores.
 """
@@ -194,24 +194,43 @@ def main():
     def step(i):
         fl, fr = sets[i % NSETS]
         cv = ops.corr_volume(fl, fr, D)
-        disp = ops.local_window(cv, None, mode=ops.SF_WIN_FIXED, radius=RADIUS, n_points=NPTS, consider_valid=True,
+        return ops.local_window(cv, None, mode=ops.SF_WIN_FIXED, radius=RADIUS, n_points=NPTS, consider_valid=True,
                                 div_mode=ops.SF_DIV_RECIP)
+
+    # One CUDA graph per rotating feature set (a step = 2 kernel launches of this library); replaying graphs keeps
+    # the host launch path (ctypes + tensor-map encoding, ~25 us per step) off the device timeline.
+    cap = torch.cuda.Stream(device=dev)
+    graphs, gouts = [], []
+    with torch.cuda.stream(cap):
+        for i in range(NSETS):
+            step(i)
+        torch.cuda.synchronize()
+        for i in range(NSETS):
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, stream=cap):
+                o = step(i)
+            graphs.append(g)
+            gouts.append(o)
+    torch.cuda.synchronize()
+
+    def run_step(i):
+        graphs[i % NSETS].replay()
+        disp = gouts[i % NSETS]
         if world > 1:
             side.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(side):
-                disp.record_stream(side)
                 dist.all_gather_into_tensor(gather_buf, disp)
         return disp
 
     for i in range(args.warmup):
-        step(i)
+        run_step(i)
     barrier()
     sampler = ClockSampler(local_rank)
     sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for i in range(args.steps):
-        step(i)
+        run_step(i)
     torch.cuda.current_stream().wait_stream(side)
     e1.record()
     barrier()
@@ -223,17 +242,21 @@ def main():
     ms = float(t.item())
     value = world * B_PER_GPU * args.steps / (ms * 1e-3)
 
-    # ---- dominant kernel alone (roofline)
+    # ---- dominant kernel alone (roofline): graph of NSETS cost-volume launches, one per feature set
+    kg = torch.cuda.CUDAGraph()
+    with torch.cuda.stream(cap):
+        with torch.cuda.graph(kg, stream=cap):
+            kouts = [ops.corr_volume(*sets[i], D) for i in range(NSETS)]
     for i in range(3):
-        ops.corr_volume(*sets[i % NSETS], D)
+        kg.replay()
     torch.cuda.synchronize()
-    nk = max(20, min(args.steps, 200))
+    nk = max(7, min(args.steps, 200) // NSETS)
     e0.record()
     for i in range(nk):
-        ops.corr_volume(*sets[i % NSETS], D)
+        kg.replay()
     e1.record()
     torch.cuda.synchronize()
-    k_ms = e0.elapsed_time(e1) / nk
+    k_ms = e0.elapsed_time(e1) / (nk * NSETS)
     peak, peak_src = peaks()
     achieved = B_PER_GPU * ALG_BYTES_CV / (k_ms * 1e-3) / 1e9
     traffic = traffic_from_profile()
@@ -271,7 +294,7 @@ def main():
     cpu_base = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         fl, fr = host[0]
-        got = step(0).cpu()
+        got = run_step(0).cpu()
         want = cpu_chain(fl[:2], fr[:2])
         err = (got[:2] - want).abs()
         assert err.median() < 1e-3, "bench parity check failed: median |disp err| %g" % err.median()
@@ -285,8 +308,8 @@ def main():
                 "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": {"workload": WORKLOAD, "pairs_per_gpu_per_step": B_PER_GPU, "parallelism": "pairs sharded "
                            "across %d rank(s); NCCL all-gather of disparity on a side stream" % world,
-                           "l2": "each step reads 134 MB of features (> 126 MB L2) from one of 3 rotating sets"},
-                "roofline": {"kernel": "corr_volume_ring_kernel<24,1,8,2,2>", "bound": "hbm", "achieved": achieved, "peak": peak,
+                           "l2": "each step reads 134 MB of features (> 126 MB L2) from one of 3 rotating sets", "launch": "one CUDA graph per step (2 kernels)"},
+                "roofline": {"kernel": "corr_volume_tc_kernel (tcgen05, bf16 hi/mid split)", "bound": "hbm", "achieved": achieved, "peak": peak,
                              "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                              "alg_bytes_per_launch": B_PER_GPU * ALG_BYTES_CV, "us_per_launch": k_ms * 1e3},
                 "cpu_baseline": cpu_base,
