@@ -7,7 +7,7 @@
 // shared memory by one TMA box load per CTA (coalesced fallback copy when W % 4 != 0), so the data-dependent
 // floor/ceil gathers are bank-conflict-free shared-memory reads (bank = lane) instead of global gathers.
 // Candidates / indices / interpolation weights follow pixel_math.h and are bit-identical to the reference;
-// the soft-max over the N+1 samples is an online (running-max) soft-max in fp32.
+// the soft-max over the N+1 samples is a max-then-exponentials soft-max in fp32 (samples kept in registers).
 // Algorithmic bytes per pixel: (D + 2) * 4 (+8 with per-pixel bounds).
 #include "common.cuh"
 #include "pixel_math.h"
@@ -37,21 +37,22 @@ struct WindowParams {
 
 struct SoftStats { float m, s, e; };  // running max, sum exp, sum exp * d
 
+// Two passes over the staged column (max, then exponentials): the exponentials are independent, so the MUFU
+// pipe stays busy instead of waiting on the running-max rescale chain of an online soft-max.
 template <class F>
 __device__ __forceinline__ SoftStats softmax_stats(F cvat, int D) {
   SoftStats st; st.m = -INFINITY; st.s = 0.f; st.e = 0.f;
+  for (int d = 0; d < D; ++d) st.m = fmaxf(st.m, cvat(d));
   for (int d = 0; d < D; ++d) {
-    float v = cvat(d);
-    if (v > st.m) {
-      float sc = __expf(st.m - v);
-      st.s *= sc; st.e *= sc; st.m = v;
-    }
-    float ex = __expf(v - st.m);
+    const float ex = __expf(cvat(d) - st.m);
     st.s += ex; st.e = fmaf(ex, (float)d, st.e);
   }
   return st;
 }
 
+constexpr int WIN_MAXN = 32;   // samples kept in registers between the two soft-max passes (more: recomputed)
+
+template <bool DEBUG>
 __global__ void __launch_bounds__(WIN_TPB)
 local_window_kernel(const __grid_constant__ CUtensorMap mapCV, const WindowParams p) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -119,24 +120,34 @@ local_window_kernel(const __grid_constant__ CUtensorMap mapCV, const WindowParam
   }
   const sfm::Window w = sfm::make_window(lower, upper, D, N, p.consider_valid, p.mode == SF_WIN_VARIANCE, extra, p.recip);
 
-  // ---- N+1 samples, online soft-max, expectation of the candidates
-  float m = -INFINITY, s = 0.f, e = 0.f;
+  // ---- N+1 samples; soft-max over them (max first, then independent exponentials); expectation of the candidates
   const size_t dbg0 = (static_cast<size_t>(b) * (N + 1) * p.H + y) * p.W + x;
-  for (int k = 0; k <= N; ++k) {
-    const float cand = sfm::window_candidate(w, k, cur, p.consider_valid);
+  auto sample = [&](int k, float& cand) {
+    cand = sfm::window_candidate(w, k, cur, p.consider_valid);
     int jf, ic;
     sfm::window_index(cand, D, &jf, &ic);
     const float v = sfm::window_lerp(cvat(jf), cvat(ic), ic, cand);
-    if (p.dbg_cand) p.dbg_cand[dbg0 + k * HW] = cand;
-    if (p.dbg_idx_floor) p.dbg_idx_floor[dbg0 + k * HW] = jf;
-    if (p.dbg_idx_ceil) p.dbg_idx_ceil[dbg0 + k * HW] = ic;
-    if (p.dbg_local) p.dbg_local[dbg0 + k * HW] = v;
-    if (v > m) {
-      float sc = __expf(m - v);
-      s *= sc; e *= sc; m = v;
+    if (DEBUG) {
+      if (p.dbg_cand) p.dbg_cand[dbg0 + k * HW] = cand;
+      if (p.dbg_idx_floor) p.dbg_idx_floor[dbg0 + k * HW] = jf;
+      if (p.dbg_idx_ceil) p.dbg_idx_ceil[dbg0 + k * HW] = ic;
+      if (p.dbg_local) p.dbg_local[dbg0 + k * HW] = v;
     }
-    float ex = __expf(v - m);
-    s += ex; e = fmaf(ex, cand, e);
+    return v;
+  };
+  float m = -INFINITY, s = 0.f, e = 0.f;
+  if (N < WIN_MAXN) {
+    float vs[WIN_MAXN], cs[WIN_MAXN];
+#pragma unroll
+    for (int k = 0; k < WIN_MAXN; ++k)
+      if (k <= N) { vs[k] = sample(k, cs[k]); m = fmaxf(m, vs[k]); }
+#pragma unroll
+    for (int k = 0; k < WIN_MAXN; ++k)
+      if (k <= N) { const float ex = __expf(vs[k] - m); s += ex; e = fmaf(ex, cs[k], e); }
+  } else {
+    float cand;
+    for (int k = 0; k <= N; ++k) m = fmaxf(m, sample(k, cand));
+    for (int k = 0; k <= N; ++k) { const float v = sample(k, cand); const float ex = __expf(v - m); s += ex; e = fmaf(ex, cand, e); }
   }
   p.out[pix] = e / s;
 }
@@ -247,10 +258,12 @@ extern "C" int sf_local_window_f32(const float* cv, const float* disp, const flo
     if (rc) return rc;
   }
   const size_t smem = static_cast<size_t>(D) * WIN_TPB * 4;
-  SF_CUDA(cudaFuncSetAttribute(local_window_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+  const bool debug = dbg_cand || dbg_idx_floor || dbg_idx_ceil || dbg_local;
+  auto kern = debug ? local_window_kernel<true> : local_window_kernel<false>;
+  SF_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
   long long grid = 1LL * B * H * p.nseg;
   SF_CHECK_ARG(grid < (1LL << 31), "local_window: grid too large");
-  local_window_kernel<<<static_cast<int>(grid), WIN_TPB, smem, static_cast<cudaStream_t>(stream)>>>(map, p);
+  kern<<<static_cast<int>(grid), WIN_TPB, smem, static_cast<cudaStream_t>(stream)>>>(map, p);
   SF_LAUNCH_CHECK();
   return SF_OK;
 }
