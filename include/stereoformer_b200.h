@@ -12,6 +12,8 @@
 #ifndef STEREOFORMER_B200_H
 #define STEREOFORMER_B200_H
 
+#include <stddef.h>
+
 #ifdef __cplusplus
 extern "C" {
 #endif
@@ -101,6 +103,16 @@ SF_API int sf_dcn_forward_f32(const float* input, const float* weight, const flo
                               const float* mask, float* out, int B, int Cin, int H, int W, int Cout, int kh, int kw,
                               int stride_h, int stride_w, int pad_h, int pad_w, int dil_h, int dil_w, int group,
                               int deformable_group, void* stream);
+
+/* a10 on the tensor cores: same operator with a caller-provided scratch buffer for the bf16 hi/mid copy of the
+ * weights (sf_dcn_workspace_bytes bytes, 128-byte aligned; 0 = no tensor-core path for this shape).
+ * algo: SF_ALGO_AUTO (tcgen05 implicit GEMM when >= 32 channels per group on both sides, else the exact FFMA
+ * kernel), SF_ALGO_GENERIC (always the exact FFMA kernel), SF_ALGO_TC (force; errors if the shape does not fit). */
+SF_API size_t sf_dcn_workspace_bytes(int Cin, int Cout, int kh, int kw, int group);
+SF_API int sf_dcn_forward_ws_f32(const float* input, const float* weight, const float* bias, const float* offset,
+                                 const float* mask, float* out, int B, int Cin, int H, int W, int Cout, int kh, int kw,
+                                 int stride_h, int stride_w, int pad_h, int pad_w, int dil_h, int dil_w, int group,
+                                 int deformable_group, void* workspace, size_t workspace_bytes, int algo, void* stream);
 
 /* a11: epipolar row cross-attention (reference file is empty; SPEC-DERIVED from north_star).  q,k,v,out are
  * bf16 [B,C,H,W]; scores optional fp32 [B,band,H,W] (-inf outside the band). */

@@ -27,9 +27,13 @@ SIGNATURES = {
     "sf_corr1d_pyramid_f32": [_p, _p, _p] + [_c_int] * 7 + [_p],
     "sf_corr1d_lookup_f32": [_p, _p, _c_int, _c_int, _p, _p, _p, _p] + [_c_int] * 4 + [_p],
     "sf_dcn_forward_f32": [_p] * 6 + [_c_int] * 15 + [_p],
+    "sf_dcn_workspace_bytes": [_c_int] * 5,
+    "sf_dcn_forward_ws_f32": [_p] * 6 + [_c_int] * 15 + [_p, ctypes.c_size_t, _c_int, _p],
     "sf_epipolar_attn_bf16": [_p] * 5 + [_c_int] * 6 + [_p],
     "sf_upsample_convex_f32": [_p, _p, _p] + [_c_int] * 4 + [_p],
 }
+
+RESTYPES = {"sf_dcn_workspace_bytes": ctypes.c_size_t}   # everything else returns an int status code
 
 _lib = None
 
@@ -53,7 +57,7 @@ def lib():
         for name, args in SIGNATURES.items():
             fn = getattr(h, name)
             fn.argtypes = args
-            fn.restype = _c_int
+            fn.restype = RESTYPES.get(name, _c_int)
         _lib = h
     return _lib
 

@@ -13,6 +13,7 @@
 // writes NCHW directly.  No column buffer, no permute, no im2col_step loop (it never affected results:
 // deform/test.py:219-260).
 #include "common.cuh"
+#include "dcn_tc.cuh"
 #include "../../include/stereoformer_b200.h"
 
 namespace sf {
@@ -162,10 +163,10 @@ static int launch_dcn(const DcnParams& p, cudaStream_t s) {
 
 }  // namespace sf
 
-extern "C" int sf_dcn_forward_f32(const float* input, const float* weight, const float* bias, const float* offset,
-                                  const float* mask, float* out, int B, int Cin, int H, int W, int Cout, int kh, int kw,
-                                  int stride_h, int stride_w, int pad_h, int pad_w, int dil_h, int dil_w, int group,
-                                  int deformable_group, void* stream) {
+static int dcn_forward_impl(const float* input, const float* weight, const float* bias, const float* offset,
+                            const float* mask, float* out, int B, int Cin, int H, int W, int Cout, int kh, int kw,
+                            int stride_h, int stride_w, int pad_h, int pad_w, int dil_h, int dil_w, int group,
+                            int deformable_group, void* workspace, size_t workspace_bytes, int algo, void* stream) {
   using namespace sf;
   SF_CHECK_ARG(input && weight && bias && offset && out, "dcn_forward: null pointer");
   SF_CHECK_ARG(B > 0 && Cin > 0 && H > 0 && W > 0 && Cout > 0 && kh > 0 && kw > 0, "dcn_forward: non-positive dimension");
@@ -175,6 +176,7 @@ extern "C" int sf_dcn_forward_f32(const float* input, const float* weight, const
                "channels(%d) and channels_out(%d) must divide group(%d)", Cin, Cout, group);
   SF_CHECK_ARG(deformable_group > 0 && Cin % deformable_group == 0,
                "channels(%d) must divide deformable_group(%d)", Cin, deformable_group);
+  SF_CHECK_ARG(algo == SF_ALGO_AUTO || algo == SF_ALGO_GENERIC || algo == SF_ALGO_TC, "dcn_forward: unknown algo %d", algo);
   DcnParams p;
   p.in = input; p.weight = weight; p.bias = bias; p.offset = offset; p.mask = mask; p.out = out;
   p.B = B; p.Cin = Cin; p.H = H; p.W = W; p.Cout = Cout;
@@ -184,8 +186,44 @@ extern "C" int sf_dcn_forward_f32(const float* input, const float* weight, const
   p.Wo = (W + 2 * pad_w - (dil_w * (kw - 1) + 1)) / stride_w + 1;
   SF_CHECK_ARG(p.Ho > 0 && p.Wo > 0, "dcn_forward: empty output (%d x %d)", p.Ho, p.Wo);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  const int Cog = Cout / group;
+  const int Cog = Cout / group, Cig = Cin / group;
+  // tensor-core path: worthwhile once the GEMM is at least 32 x 32 channels per group (64->128, 128->128,
+  // 256->256); the 16-channel shipped-model shape is HBM/latency-bound and stays on the exact FFMA kernel
+  if (algo == SF_ALGO_TC || (algo == SF_ALGO_AUTO && Cig >= 32 && Cog >= 32)) {
+    DcnTcParams q;
+    q.in = input; q.bias = bias; q.offset = offset; q.mask = mask; q.out = out;
+    q.B = B; q.Cin = Cin; q.H = H; q.W = W; q.Cout = Cout; q.Ho = p.Ho; q.Wo = p.Wo;
+    q.kh = kh; q.kw = kw; q.sh = stride_h; q.sw = stride_w; q.ph = pad_h; q.pw = pad_w; q.dh = dil_h; q.dw = dil_w;
+    q.G = group; q.dg = deformable_group;
+    bool handled = false;
+    const int rc = launch_dcn_tc(q, weight, workspace, workspace_bytes, s, &handled);
+    if (rc) return rc;
+    if (handled) return SF_OK;
+    SF_CHECK_ARG(algo != SF_ALGO_TC, "dcn_forward: the tensor-core path needs %zu workspace bytes (got %zu) and <= 256 "
+                 "output channels per group", dcn_tc_workspace_bytes(Cin, Cout, kh, kw, group), workspace_bytes);
+  }
   if (Cog <= 16) return launch_dcn<16, 128>(p, s);
   if (Cog <= 32) return launch_dcn<32, 128>(p, s);
   return launch_dcn<64, 64>(p, s);
+}
+
+extern "C" int sf_dcn_forward_f32(const float* input, const float* weight, const float* bias, const float* offset,
+                                  const float* mask, float* out, int B, int Cin, int H, int W, int Cout, int kh, int kw,
+                                  int stride_h, int stride_w, int pad_h, int pad_w, int dil_h, int dil_w, int group,
+                                  int deformable_group, void* stream) {
+  return dcn_forward_impl(input, weight, bias, offset, mask, out, B, Cin, H, W, Cout, kh, kw, stride_h, stride_w, pad_h,
+                          pad_w, dil_h, dil_w, group, deformable_group, nullptr, 0, SF_ALGO_GENERIC, stream);
+}
+
+extern "C" size_t sf_dcn_workspace_bytes(int Cin, int Cout, int kh, int kw, int group) {
+  return sf::dcn_tc_workspace_bytes(Cin, Cout, kh, kw, group);
+}
+
+extern "C" int sf_dcn_forward_ws_f32(const float* input, const float* weight, const float* bias, const float* offset,
+                                     const float* mask, float* out, int B, int Cin, int H, int W, int Cout, int kh,
+                                     int kw, int stride_h, int stride_w, int pad_h, int pad_w, int dil_h, int dil_w,
+                                     int group, int deformable_group, void* workspace, size_t workspace_bytes, int algo,
+                                     void* stream) {
+  return dcn_forward_impl(input, weight, bias, offset, mask, out, B, Cin, H, W, Cout, kh, kw, stride_h, stride_w, pad_h,
+                          pad_w, dil_h, dil_w, group, deformable_group, workspace, workspace_bytes, algo, stream);
 }

@@ -1,0 +1,28 @@
+// Parameter block + launcher of the tcgen05 DCN kernel (dcn_tc.cu), shared with the C-ABI entry in dcn.cu.
+#pragma once
+#include <cuda_runtime.h>
+#include <stddef.h>
+
+namespace sf {
+
+struct DcnTcParams {
+  const float* in;      // [B,Cin,H,W]
+  const float* bias;    // [Cout]
+  const float* offset;  // [B,dg*2*T,Ho,Wo]
+  const float* mask;    // [B,dg*T,Ho,Wo] or null (DCNv1)
+  float* out;           // [B,Cout,Ho,Wo]
+  int B, Cin, H, W, Cout, Ho, Wo;
+  int kh, kw, sh, sw, ph, pw, dh, dw, G, dg;
+  int K, nchunk;        // Cig*T, ceil(K/64)
+  int N;                // MMA N: Cog rounded up to 16
+  int NST;              // stages (B in shared memory, A in tensor memory)
+  int nptile, ntiles;
+};
+
+size_t dcn_tc_workspace_bytes(int Cin, int Cout, int kh, int kw, int group);
+// Runs the tensor-core path when the shape fits and the workspace is large enough (*handled = true);
+// otherwise leaves *handled = false and launches nothing.
+int launch_dcn_tc(DcnTcParams p, const float* weight, void* workspace, size_t workspace_bytes, cudaStream_t stream,
+                  bool* handled);
+
+}  // namespace sf

@@ -203,8 +203,12 @@ def corr1d_lookup(pyramid, coords, radius=4, num_levels=4, div_mode=SF_DIV_TRUE,
     return (out, dict(x0=x0, src=src)) if debug else out
 
 
-def dcn_forward(inp, weight, bias, offset, mask, stride, padding, dilation, groups, deformable_groups):
-    """DCNv2 (mask given) / DCNv1 (mask None) forward -> [B,Cout,Ho,Wo]."""
+def dcn_forward(inp, weight, bias, offset, mask, stride, padding, dilation, groups, deformable_groups,
+                algo=SF_ALGO_AUTO):
+    """DCNv2 (mask given) / DCNv1 (mask None) forward -> [B,Cout,Ho,Wo].
+
+    algo: SF_ALGO_AUTO (tcgen05 implicit GEMM from 32 channels per group, exact FFMA kernel below),
+    SF_ALGO_GENERIC (exact FFMA kernel), SF_ALGO_TC (force the tensor-core path)."""
     inp, weight = _chk(inp, "input", dim=4), _chk(weight, "weight", dim=4)
     bias, offset = _chk(bias, "bias"), _chk(offset, "offset", dim=4)
     mask = _chk(mask, "mask", dim=4) if mask is not None else None
@@ -224,8 +228,11 @@ def dcn_forward(inp, weight, bias, offset, mask, stride, padding, dilation, grou
         raise RuntimeError("mask shape %s, expected %s" % (tuple(mask.shape), (B, deformable_groups * kh * kw, Ho, Wo)))
     out = torch.empty((B, Cout, Ho, Wo), device=inp.device, dtype=torch.float32)
     with torch.cuda.device(inp.device):
-        _lib.call("sf_dcn_forward_f32", _ptr(inp), _ptr(weight), _ptr(bias), _ptr(offset), _ptr(mask), _ptr(out), B, Cin,
-                  H, W, Cout, kh, kw, sh, sw, ph, pw, dh, dw, int(groups), int(deformable_groups), _stream())
+        nws = int(_lib.lib().sf_dcn_workspace_bytes(Cin, Cout, kh, kw, int(groups))) if algo != SF_ALGO_GENERIC else 0
+        ws = torch.empty(nws, device=inp.device, dtype=torch.uint8) if nws else None   # bf16 hi/mid weights (scratch)
+        _lib.call("sf_dcn_forward_ws_f32", _ptr(inp), _ptr(weight), _ptr(bias), _ptr(offset), _ptr(mask), _ptr(out), B,
+                  Cin, H, W, Cout, kh, kw, sh, sw, ph, pw, dh, dw, int(groups), int(deformable_groups), _ptr(ws),
+                  ctypes.c_size_t(nws), int(algo), _stream())
     return out
 
 

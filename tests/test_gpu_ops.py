@@ -209,6 +209,46 @@ def test_dcn_vs_c_oracle(ops, cfg):
     assert torch.allclose(out1.cpu(), ref1, rtol=1e-4, atol=1e-4)
 
 
+@pytest.mark.parametrize("cfg", [dict(B=2, Cin=64, Cout=128, H=12, W=20, G=1, dg=2, s=1, p=1, d=1),    # test.py:526
+                                 dict(B=1, Cin=48, Cout=80, H=13, W=21, G=2, dg=3, s=2, p=2, d=2),     # K, N padding
+                                 dict(B=1, Cin=128, Cout=128, H=19, W=23, G=1, dg=1, s=1, p=1, d=1),   # 437 pixels
+                                 dict(B=1, Cin=32, Cout=256, H=9, W=15, G=1, dg=4, s=1, p=0, d=1),     # N = 256
+                                 dict(B=3, Cin=8, Cout=8, H=6, W=40, G=1, dg=1, s=1, p=1, d=1)])       # tiny K (forced)
+def test_dcn_tensor_core(ops, cfg):
+    """tcgen05 implicit-GEMM path (bf16 hi/mid split, A operand in tensor memory) against the C oracle and the
+    exact FFMA kernel; tolerance 1e-4 of the output magnitude."""
+    torch.manual_seed(43)
+    B, Cin, Cout, H, W, G, dg, s, p, d = (cfg[k] for k in ("B", "Cin", "Cout", "H", "W", "G", "dg", "s", "p", "d"))
+    x = torch.randn(B, Cin, H, W)
+    w = torch.randn(Cout, Cin // G, 3, 3) / (3 * (Cin // G) ** 0.5)
+    b = torch.randn(Cout)
+    Ho = (H + 2 * p - (d * 2 + 1)) // s + 1
+    Wo = (W + 2 * p - (d * 2 + 1)) // s + 1
+    off = torch.randn(B, dg * 18, Ho, Wo) * 2
+    msk = torch.sigmoid(torch.randn(B, dg * 9, Ho, Wo))
+    for m in (msk, None):
+        ref = dcn_c.dcn_forward(x, w, b, off, m, (s, s), (p, p), (d, d), G, dg)
+        args = (dev(x), dev(w), dev(b), dev(off), dev(m) if m is not None else None, (s, s), (p, p), (d, d), G, dg)
+        tc = ops.dcn_forward(*args, algo=ops.SF_ALGO_TC)
+        ex = ops.dcn_forward(*args, algo=ops.SF_ALGO_GENERIC)
+        scale = ref.abs().max().item()
+        assert (tc.cpu() - ref).abs().max().item() <= 1e-4 * scale
+        assert (tc - ex).abs().max().item() <= 1e-4 * scale
+    # zero offsets + unit mask == plain convolution (deform/test.py:69-110) on the tensor-core path too
+    conv = torch.nn.functional.conv2d(x, w, b, stride=s, padding=p, dilation=d, groups=G)
+    z = ops.dcn_forward(dev(x), dev(w), dev(b), dev(torch.zeros_like(off)), dev(torch.ones_like(msk)), (s, s), (p, p),
+                        (d, d), G, dg, algo=ops.SF_ALGO_TC)
+    assert (z.cpu() - conv).abs().max().item() <= 1e-4 * conv.abs().max().item()
+
+
+def test_dcn_tensor_core_limits(ops):
+    x = torch.randn(1, 8, 5, 5, device="cuda")
+    w = torch.randn(4, 8, 3, 3, device="cuda")          # 4 output channels: no tensor-core shape
+    off = torch.zeros(1, 18, 5, 5, device="cuda")
+    with pytest.raises(ValueError):
+        ops.dcn_forward(x, w, torch.zeros(4, device="cuda"), off, None, (1, 1), (1, 1), (1, 1), 1, 1, algo=ops.SF_ALGO_TC)
+
+
 # ------------------------------------------------------------------------------------------ a11 attention (spec-derived)
 @pytest.mark.parametrize("shape,band", [((1, 128, 6, 312), 48), ((2, 32, 3, 40), 8), ((1, 256, 2, 100), 64),
                                         ((1, 16, 2, 10), 24)])
