@@ -191,16 +191,38 @@ def main():
     gather_buf = torch.empty(world * B_PER_GPU, 1, H8, W8, device=dev) if world > 1 else None
     side = torch.cuda.Stream(device=dev)
 
+    dbuf = [torch.empty(B_PER_GPU, 1, H8, W8, device=dev) for _ in range(NSETS)]
+
+    # N > 1: the disparity gather (north_star: the only exchange of the path).  Preferred: the window kernel stores
+    # its result straight into every rank's gather buffer through NVLink peer mappings (torch symmetric memory), so
+    # the gather is part of the step graph and costs no host call; fallback: an NCCL all-gather after each step.
+    pg, gather_mode = None, "none"
+    if world > 1:
+        try:
+            from stereoformer_b200.dist import PeerGather
+            pg = PeerGather(B_PER_GPU * H8 * W8, dev)
+            gather_mode = "P2P stores fused into the window kernel (NVLink peer mappings)"
+        except Exception as e:            # noqa: BLE001 -- any failure of the symmetric-memory plumbing
+            pg, gather_mode = None, "NCCL all_gather_into_tensor per step (symmetric memory unavailable: %s)" % type(e).__name__
+        flags = torch.tensor([1.0 if pg is not None else 0.0], device=dev)
+        dist.all_reduce(flags, op=dist.ReduceOp.MIN)
+        if float(flags.item()) < 1.0:
+            pg = None
+            if gather_mode.startswith("P2P"):
+                gather_mode = "NCCL all_gather_into_tensor per step (symmetric memory unavailable on a peer)"
+
     def step(i):
         fl, fr = sets[i % NSETS]
         cv = ops.corr_volume(fl, fr, D)
         return ops.local_window(cv, None, mode=ops.SF_WIN_FIXED, radius=RADIUS, n_points=NPTS, consider_valid=True,
-                                div_mode=ops.SF_DIV_RECIP)
+                                div_mode=ops.SF_DIV_RECIP, out=dbuf[i % NSETS],
+                                peers=pg.peer_ptrs if pg is not None else None,
+                                peer_offset=pg.offset() if pg is not None else 0)
 
     # One CUDA graph per rotating feature set (a step = 2 kernel launches of this library); replaying graphs keeps
     # the host launch path (ctypes + tensor-map encoding, ~25 us per step) off the device timeline.
     cap = torch.cuda.Stream(device=dev)
-    graphs, gouts = [], []
+    graphs = []
     with torch.cuda.stream(cap):
         for i in range(NSETS):
             step(i)
@@ -208,19 +230,18 @@ def main():
         for i in range(NSETS):
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g, stream=cap):
-                o = step(i)
+                step(i)
             graphs.append(g)
-            gouts.append(o)
     torch.cuda.synchronize()
 
     def run_step(i):
         graphs[i % NSETS].replay()
-        disp = gouts[i % NSETS]
-        if world > 1:
-            side.wait_stream(torch.cuda.current_stream())
-            with torch.cuda.stream(side):
-                dist.all_gather_into_tensor(gather_buf, disp)
-        return disp
+        if world > 1 and pg is None:
+            dist.all_gather_into_tensor(gather_buf, dbuf[i % NSETS])
+        return dbuf[i % NSETS]
+
+    def flush_gather(i):
+        pass
 
     for i in range(args.warmup):
         run_step(i)
@@ -231,7 +252,7 @@ def main():
     e0.record()
     for i in range(args.steps):
         run_step(i)
-    torch.cuda.current_stream().wait_stream(side)
+    flush_gather(args.steps - 1)
     e1.record()
     barrier()
     ms = e0.elapsed_time(e1)
@@ -241,6 +262,14 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms = float(t.item())
     value = world * B_PER_GPU * args.steps / (ms * 1e-3)
+
+    if pg is not None:
+        # the fused gather must have delivered every rank's last disparities into this rank's buffer
+        pg.sync()
+        last = (args.steps - 1) % NSETS
+        want = torch.empty(world * B_PER_GPU, 1, H8, W8, device=dev)
+        dist.all_gather_into_tensor(want, dbuf[last])
+        assert torch.equal(pg.buffer.view_as(want), want), "P2P disparity gather does not match the NCCL all-gather"
 
     # ---- dominant kernel alone (roofline): graph of NSETS cost-volume launches, one per feature set
     kg = torch.cuda.CUDAGraph()
@@ -307,7 +336,7 @@ def main():
                 "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": {"workload": WORKLOAD, "pairs_per_gpu_per_step": B_PER_GPU, "parallelism": "pairs sharded "
-                           "across %d rank(s); NCCL all-gather of disparity on a side stream" % world,
+                           "across %d rank(s); disparity gather: %s" % (world, gather_mode),
                            "l2": "each step reads 134 MB of features (> 126 MB L2) from one of 3 rotating sets", "launch": "one CUDA graph per step (2 kernels)"},
                 "roofline": {"kernel": "corr_volume_tc_kernel (tcgen05, bf16 hi/mid split)", "bound": "hbm", "achieved": achieved, "peak": peak,
                              "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,

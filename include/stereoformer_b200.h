@@ -68,6 +68,17 @@ SF_API int sf_local_window_f32(const float* cv, const float* disp, const float* 
                                float* dbg_local, int B, int D, int H, int W, int mode, float radius, float gamma,
                                int n_points, int consider_valid, int div_mode, void* stream);
 
+/* a4 + the multi-GPU disparity gather in one kernel: sf_local_window_f32 whose result is ALSO stored
+ * into every rank's gather buffer through NVLink peer mappings: h_peers is a HOST array of n_peers (<= SF_MAX_PEERS)
+ * device pointers (this rank's own buffer included, e.g. torch symmetric memory), element [peer_offset + b*H*W + y*W
+ * + x] of each receives the pixel.  Replaces the NCCL all-gather of trainer_DLC_GRU.py:102-106's DataParallel
+ * gather for the inference path; completion is ordered by the caller (stream sync + barrier) like any P2P store. */
+#define SF_MAX_PEERS 8
+SF_API int sf_local_window_gather_f32(const float* cv, const float* disp, const float* lo, const float* up, float* out,
+                                      int B, int D, int H, int W, int mode, float radius, float gamma, int n_points,
+                                      int consider_valid, int div_mode, float* const* h_peers, int n_peers,
+                                      long long peer_offset, void* stream);
+
 /* build_cost_volume_from_volume(old_volume, sampling_candidates)  fixed_local_cost_volume.py:61-80 (defined
  * identically in 5 reference files).  cand/out [B,K,H,W]; bit-exact; idx_* optional int32 [B,K,H,W]. */
 SF_API int sf_sample_volume_f32(const float* cv, const float* cand, float* out, int* idx_floor, int* idx_ceil, int B,

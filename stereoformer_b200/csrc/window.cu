@@ -33,6 +33,11 @@ struct WindowParams {
   float radius, gamma;
   int nseg;
   int use_tma;
+  // multi-GPU gather fused into the store: the result also goes to every rank's gather buffer through its
+  // NVLink peer mapping (peers[r] + peer_off + pixel index); n_peers == 0 outside sf_local_window_gather_f32
+  float* peers[SF_MAX_PEERS];
+  int n_peers;
+  long long peer_off;
 };
 
 struct SoftStats { float m, s, e; };  // running max, sum exp, sum exp * d
@@ -149,7 +154,9 @@ local_window_kernel(const __grid_constant__ CUtensorMap mapCV, const WindowParam
     for (int k = 0; k <= N; ++k) m = fmaxf(m, sample(k, cand));
     for (int k = 0; k <= N; ++k) { const float v = sample(k, cand); const float ex = __expf(v - m); s += ex; e = fmaf(ex, cand, e); }
   }
-  p.out[pix] = e / s;
+  const float res = e / s;
+  p.out[pix] = res;
+  for (int r = 0; r < p.n_peers; ++r) p.peers[r][p.peer_off + static_cast<long long>(pix)] = res;
 }
 
 // DisparityEstimation(.WithProb).forward  models/utils/estimation.py:14-62: no reuse -> straight coalesced loads.
@@ -232,10 +239,11 @@ extern "C" int sf_soft_argmin_f32(const float* cv, float* disp, float* prob, int
   return SF_OK;
 }
 
-extern "C" int sf_local_window_f32(const float* cv, const float* disp, const float* lo, const float* up, float* out,
-                                   float* disp0_out, float* dbg_cand, int* dbg_idx_floor, int* dbg_idx_ceil,
-                                   float* dbg_local, int B, int D, int H, int W, int mode, float radius, float gamma,
-                                   int n_points, int consider_valid, int div_mode, void* stream) {
+static int local_window_impl(const float* cv, const float* disp, const float* lo, const float* up, float* out,
+                             float* disp0_out, float* dbg_cand, int* dbg_idx_floor, int* dbg_idx_ceil,
+                             float* dbg_local, int B, int D, int H, int W, int mode, float radius, float gamma,
+                             int n_points, int consider_valid, int div_mode, float* const* h_peers, int n_peers,
+                             long long peer_offset, void* stream) {
   using namespace sf;
   SF_CHECK_ARG(cv && out, "local_window: null pointer");
   SF_CHECK_ARG(B > 0 && D > 0 && H > 0 && W > 0 && n_points > 0, "local_window: non-positive dimension");
@@ -249,6 +257,12 @@ extern "C" int sf_local_window_f32(const float* cv, const float* disp, const flo
   p.B = B; p.D = D; p.H = H; p.W = W; p.mode = mode; p.n_points = n_points;
   p.consider_valid = consider_valid ? 1 : 0; p.recip = div_mode == SF_DIV_RECIP;
   p.radius = radius; p.gamma = gamma;
+  SF_CHECK_ARG(n_peers >= 0 && n_peers <= SF_MAX_PEERS && (n_peers == 0 || h_peers) && peer_offset >= 0,
+               "local_window: bad peer list (at most %d peers)", SF_MAX_PEERS);
+  p.n_peers = n_peers;
+  p.peer_off = peer_offset;
+  for (int r = 0; r < SF_MAX_PEERS; ++r) p.peers[r] = r < n_peers ? h_peers[r] : nullptr;
+  for (int r = 0; r < n_peers; ++r) SF_CHECK_ARG(p.peers[r] != nullptr, "local_window: null peer pointer %d", r);
   p.nseg = ceil_div(W, WIN_TPB);
   p.use_tma = (W % 4 == 0) && D <= 256 && (reinterpret_cast<uintptr_t>(cv) & 15) == 0;
   CUtensorMap map;
@@ -266,6 +280,22 @@ extern "C" int sf_local_window_f32(const float* cv, const float* disp, const flo
   kern<<<static_cast<int>(grid), WIN_TPB, smem, static_cast<cudaStream_t>(stream)>>>(map, p);
   SF_LAUNCH_CHECK();
   return SF_OK;
+}
+
+extern "C" int sf_local_window_f32(const float* cv, const float* disp, const float* lo, const float* up, float* out,
+                                   float* disp0_out, float* dbg_cand, int* dbg_idx_floor, int* dbg_idx_ceil,
+                                   float* dbg_local, int B, int D, int H, int W, int mode, float radius, float gamma,
+                                   int n_points, int consider_valid, int div_mode, void* stream) {
+  return local_window_impl(cv, disp, lo, up, out, disp0_out, dbg_cand, dbg_idx_floor, dbg_idx_ceil, dbg_local, B, D, H, W,
+                           mode, radius, gamma, n_points, consider_valid, div_mode, nullptr, 0, 0, stream);
+}
+
+extern "C" int sf_local_window_gather_f32(const float* cv, const float* disp, const float* lo, const float* up, float* out,
+                                          int B, int D, int H, int W, int mode, float radius, float gamma, int n_points,
+                                          int consider_valid, int div_mode, float* const* h_peers, int n_peers,
+                                          long long peer_offset, void* stream) {
+  return local_window_impl(cv, disp, lo, up, out, nullptr, nullptr, nullptr, nullptr, nullptr, B, D, H, W, mode, radius,
+                           gamma, n_points, consider_valid, div_mode, h_peers, n_peers, peer_offset, stream);
 }
 
 extern "C" int sf_sample_volume_f32(const float* cv, const float* cand, float* out, int* idx_floor, int* idx_ceil,

@@ -65,3 +65,30 @@ def gather_row_bands(band_local, bands, group=None):
     if world == 1:
         return band_local
     return _ragged_gather(band_local, [y1 - y0 for (y0, y1, _, _) in bands], 2, group)
+
+
+class PeerGather:
+    """Gather buffer that every rank can write directly: torch symmetric memory (CUDA peer mappings over
+    NVLink / NVSwitch).  ``peer_ptrs`` are this process's device pointers to every rank's buffer (its own
+    included); kernels store their slice at ``offset(rank)`` of each of them (ops.local_window(..., peers=...)),
+    so the disparity gather costs no extra launch and no host call per step.  ``sync()`` orders the stores for
+    consumers on every rank (stream synchronise + barrier)."""
+
+    def __init__(self, numel_per_rank, device, group=None):
+        import torch.distributed._symmetric_memory as symm_mem
+        self.group = group if group is not None else dist.group.WORLD
+        self.world = dist.get_world_size(self.group)
+        self.rank = dist.get_rank(self.group)
+        self.numel_per_rank = int(numel_per_rank)
+        self.buffer = symm_mem.empty(self.world * self.numel_per_rank, dtype=torch.float32, device=device)
+        self.handle = symm_mem.rendezvous(self.buffer, self.group)
+        self.peer_ptrs = [int(p) for p in self.handle.buffer_ptrs]
+        if len(self.peer_ptrs) != self.world or any(p == 0 for p in self.peer_ptrs):
+            raise RuntimeError("symmetric memory rendezvous returned no peer mappings")
+
+    def offset(self, rank=None):
+        return (self.rank if rank is None else rank) * self.numel_per_rank
+
+    def sync(self):
+        torch.cuda.synchronize(self.buffer.device)
+        dist.barrier(group=self.group)

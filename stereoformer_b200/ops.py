@@ -81,10 +81,13 @@ def soft_argmin(cv, match_similarity=True, with_prob=False):
 
 
 def local_window(cv, disp=None, lo=None, up=None, mode=SF_WIN_FIXED, radius=0.0, gamma=1.0, n_points=10,
-                 consider_valid=False, div_mode=SF_DIV_TRUE, debug=False, return_disp0=False):
-    """Local disparity-window sampling + soft-max expectation -> [B,1,H,W].
+                 consider_valid=False, div_mode=SF_DIV_TRUE, debug=False, return_disp0=False, out=None, peers=None,
+                 peer_offset=0):
+    """Local disparity-window sampling + soft-max expectation -> [B,1,H,W] (written into ``out`` when given).
 
-    debug=True additionally returns dict(cand, idx_floor, idx_ceil, local) for the bit-exact checks."""
+    debug=True additionally returns dict(cand, idx_floor, idx_ceil, local) for the bit-exact checks.
+    peers: list of device pointers (ints) of every rank's gather buffer (NVLink peer mappings, see
+    dist.PeerGather); the result is also stored at element ``peer_offset`` + pixel index of each of them."""
     cv = _chk(cv, "old_cost_volume", dim=4)
     B, D, H, W = cv.shape
     if disp is not None:
@@ -93,7 +96,10 @@ def local_window(cv, disp=None, lo=None, up=None, mode=SF_WIN_FIXED, radius=0.0,
             raise ValueError("cur_disparity must have B*H*W elements")
     lo = _chk(lo, "lower bound") if lo is not None else None
     up = _chk(up, "upper bound") if up is not None else None
-    out = torch.empty((B, 1, H, W), device=cv.device, dtype=torch.float32)
+    if out is None:
+        out = torch.empty((B, 1, H, W), device=cv.device, dtype=torch.float32)
+    elif out.dtype != torch.float32 or out.numel() != B * H * W or not out.is_contiguous() or out.device != cv.device:
+        raise ValueError("out must be a contiguous fp32 CUDA tensor with B*H*W elements")
     d0 = torch.empty((B, 1, H, W), device=cv.device, dtype=torch.float32) if return_disp0 else None
     dbg = {}
     if debug:
@@ -102,6 +108,15 @@ def local_window(cv, disp=None, lo=None, up=None, mode=SF_WIN_FIXED, radius=0.0,
                    idx_floor=torch.empty((B, K, H, W), device=cv.device, dtype=torch.int32),
                    idx_ceil=torch.empty((B, K, H, W), device=cv.device, dtype=torch.int32),
                    local=torch.empty((B, K, H, W), device=cv.device, dtype=torch.float32))
+    if peers:
+        if debug or return_disp0:
+            raise ValueError("peers cannot be combined with debug / return_disp0")
+        arr = (ctypes.c_void_p * len(peers))(*[ctypes.c_void_p(int(q)) for q in peers])
+        with torch.cuda.device(cv.device):
+            _lib.call("sf_local_window_gather_f32", _ptr(cv), _ptr(disp), _ptr(lo), _ptr(up), _ptr(out), B, D, H, W,
+                      int(mode), float(radius), float(gamma), int(n_points), int(bool(consider_valid)), int(div_mode),
+                      arr, len(peers), ctypes.c_longlong(int(peer_offset)), _stream())
+        return out
     with torch.cuda.device(cv.device):
         _lib.call("sf_local_window_f32", _ptr(cv), _ptr(disp), _ptr(lo), _ptr(up), _ptr(out), _ptr(d0),
                   _ptr(dbg.get("cand")), _ptr(dbg.get("idx_floor")), _ptr(dbg.get("idx_ceil")), _ptr(dbg.get("local")),

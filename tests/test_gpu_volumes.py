@@ -264,3 +264,22 @@ def test_integer_candidates_return_volume_entries(ops):
     idx = torch.randint(0, 24, (2, 6, 5, 40), device="cuda")
     out = ops.sample_volume(cv, idx.float())
     assert torch.equal(out, torch.gather(cv, 1, idx))
+
+
+def test_window_fused_peer_gather_single_rank(ops):
+    """sf_local_window_gather_f32: the result is also stored at peer_offset of every buffer in the peer list
+    (here two local buffers stand in for the NVLink peer mappings of the multi-GPU bench)."""
+    torch.manual_seed(5)
+    B, D, H, W = 2, 24, 7, 40
+    cv = (torch.randn(B, D, H, W, device="cuda") * 3 - 2).abs()
+    ref = ops.local_window(cv, None, mode=ops.SF_WIN_FIXED, radius=2, n_points=20, consider_valid=True)
+    n = B * H * W
+    bufs = [torch.zeros(3 * n, device="cuda") for _ in range(2)]
+    out = ops.local_window(cv, None, mode=ops.SF_WIN_FIXED, radius=2, n_points=20, consider_valid=True,
+                           peers=[b.data_ptr() for b in bufs], peer_offset=n)
+    assert torch.equal(out, ref)
+    for b in bufs:
+        assert torch.equal(b[n:2 * n].view_as(ref), ref)
+        assert b[:n].abs().sum() == 0 and b[2 * n:].abs().sum() == 0
+    with pytest.raises(ValueError):
+        ops.local_window(cv, None, n_points=20, peers=[bufs[0].data_ptr()] * 9)
