@@ -57,7 +57,9 @@ __device__ __forceinline__ SoftStats softmax_stats(F cvat, int D) {
 
 constexpr int WIN_MAXN = 32;   // samples kept in registers between the two soft-max passes (more: recomputed)
 
-template <bool DEBUG>
+// NSAMP: number of window samples (n_points + 1) when it is one of the shipped values (21: LowCNN, 11: module
+// defaults), so the sample loop unrolls exactly; 0 = any count (predicated up to WIN_MAXN, recomputed beyond).
+template <bool DEBUG, int NSAMP>
 __global__ void __launch_bounds__(WIN_TPB)
 local_window_kernel(const __grid_constant__ CUtensorMap mapCV, const WindowParams p) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -141,7 +143,13 @@ local_window_kernel(const __grid_constant__ CUtensorMap mapCV, const WindowParam
     return v;
   };
   float m = -INFINITY, s = 0.f, e = 0.f;
-  if (N < WIN_MAXN) {
+  if (NSAMP > 0) {
+    float vs[NSAMP > 0 ? NSAMP : 1], cs[NSAMP > 0 ? NSAMP : 1];
+#pragma unroll
+    for (int k = 0; k < NSAMP; ++k) { vs[k] = sample(k, cs[k]); m = fmaxf(m, vs[k]); }
+#pragma unroll
+    for (int k = 0; k < NSAMP; ++k) { const float ex = __expf(vs[k] - m); s += ex; e = fmaf(ex, cs[k], e); }
+  } else if (N < WIN_MAXN) {
     float vs[WIN_MAXN], cs[WIN_MAXN];
 #pragma unroll
     for (int k = 0; k < WIN_MAXN; ++k)
@@ -273,7 +281,9 @@ static int local_window_impl(const float* cv, const float* disp, const float* lo
   }
   const size_t smem = static_cast<size_t>(D) * WIN_TPB * 4;
   const bool debug = dbg_cand || dbg_idx_floor || dbg_idx_ceil || dbg_local;
-  auto kern = debug ? local_window_kernel<true> : local_window_kernel<false>;
+  auto kern = debug ? local_window_kernel<true, 0>
+                    : (n_points == 20 ? local_window_kernel<false, 21>
+                                      : (n_points == 10 ? local_window_kernel<false, 11> : local_window_kernel<false, 0>));
   SF_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
   long long grid = 1LL * B * H * p.nseg;
   SF_CHECK_ARG(grid < (1LL << 31), "local_window: grid too large");
