@@ -80,6 +80,17 @@ int make_tmap_3d_bf16(CUtensorMap* out, const void* base, uint64_t n0, uint64_t 
   return make_tmap_3d(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, base, n0, n1, n2, b0, b1, b2);
 }
 
+// fp32 with an explicit shared-memory swizzle (0 / 32 / 64 / 128 bytes; the box's inner extent must then be exactly
+// that many bytes) -- used by the TMA-store epilogues whose staging tiles are written conflict-free by row.
+int make_tmap_3d_f32_swz(CUtensorMap* out, const void* base, uint64_t n0, uint64_t n1, uint64_t n2, uint32_t b0,
+                         uint32_t b1, uint32_t b2, int swizzle_bytes) {
+  CUtensorMapSwizzle swz = CU_TENSOR_MAP_SWIZZLE_NONE;
+  if (swizzle_bytes == 32) swz = CU_TENSOR_MAP_SWIZZLE_32B;
+  else if (swizzle_bytes == 64) swz = CU_TENSOR_MAP_SWIZZLE_64B;
+  else if (swizzle_bytes == 128) swz = CU_TENSOR_MAP_SWIZZLE_128B;
+  return make_tmap_3d(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, base, n0, n1, n2, b0, b1, b2, swz);
+}
+
 // bf16, 128-byte swizzle: the box's inner extent must be exactly 64 elements (128 B) -- the UMMA SW128 atom.
 int make_tmap_3d_bf16_sw128(CUtensorMap* out, const void* base, uint64_t n0, uint64_t n1, uint64_t n2, uint32_t b1,
                             uint32_t b2) {

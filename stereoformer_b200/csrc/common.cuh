@@ -40,6 +40,8 @@ int sm_count();
 // Requires n0 % 4 == 0 (16-byte global strides), b0 % 4 == 0, b0 <= 256, base 16-B aligned.
 int make_tmap_3d_f32(CUtensorMap* out, const void* base, uint64_t n0, uint64_t n1, uint64_t n2,
                      uint32_t b0, uint32_t b1, uint32_t b2);
+int make_tmap_3d_f32_swz(CUtensorMap* out, const void* base, uint64_t n0, uint64_t n1, uint64_t n2, uint32_t b0,
+                         uint32_t b1, uint32_t b2, int swizzle_bytes);
 int make_tmap_3d_bf16(CUtensorMap* out, const void* base, uint64_t n0, uint64_t n1, uint64_t n2,
                       uint32_t b0, uint32_t b1, uint32_t b2);
 

@@ -19,4 +19,4 @@ us = e0.elapsed_time(e1) / n * 1e3
 gb = 4 * C * H * W * 2 * B / (us * 1e-6) / 1e9
 fl = 4.0 * H * W * band * C * B / (us * 1e-6) / 1e12
 print("attn algo=%d shape=%s band=%d us=%.1f  %.0f GB/s (%.3f of HBM peak)  band-TFLOP/s=%.1f" %
-      (algo, (B, C, H, W), band, us, gb, gb / 6463, fl))
+      (algo, (B, C, H, W), band, us, gb, gb / 6549.8, fl))

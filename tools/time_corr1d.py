@@ -18,4 +18,4 @@ torch.cuda.synchronize()
 us = e0.elapsed_time(e1) / n * 1e3
 by = (2 * C * H * W + 1.9375 * H * W * W) * 4 * B
 print("corr1d algo=%d shape=%s us=%.1f  %.0f GB/s (%.3f of HBM peak)  %.1f TFLOP/s (fp32-equivalent)" %
-      (algo, (B, C, H, W), us, by / (us * 1e-6) / 1e9, by / (us * 1e-6) / 1e9 / 6463, 2.0 * H * W * W * C * B / (us * 1e-6) / 1e12))
+      (algo, (B, C, H, W), us, by / (us * 1e-6) / 1e9, by / (us * 1e-6) / 1e9 / 6549.8, 2.0 * H * W * W * C * B / (us * 1e-6) / 1e12))
