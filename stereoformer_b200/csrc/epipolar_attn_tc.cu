@@ -16,15 +16,22 @@
 
 #include "common.cuh"
 #include "tc_common.cuh"
+#include <cstdlib>
 #include "../../include/stereoformer_b200.h"
 
 namespace sf {
+
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 
 constexpr int AT_BOX = 8192;            // one TMA box: 64 rows x 128 B
 constexpr int AT_STAGE = 5 * AT_BOX;    // Q chunk (2 boxes) + K chunk (3 boxes) of 64 channels
 constexpr int AT_NSTAGE = 2;
 constexpr int AT_PBYTES = 3 * 16384;    // P: 3 key blocks x [128 rows][128 B]
-constexpr int AT_THREADS = 192;
+constexpr int AT_THREADS = 352;         // TMA warp, MMA warp, 8 soft-max/epilogue warps (two per TMEM lane quarter), TMA-store warp
 
 struct AttnParams {
   __nv_bfloat16* out;
@@ -32,35 +39,53 @@ struct AttnParams {
   int nqt;      // query tiles per row
   int ntiles;
   float scale_log2;  // log2(e) / sqrt(C)
+  int nS, nO;        // S and O accumulators in TMEM (192 and C columns each)
+  int defer;         // epilogue of tile t - 1 after the soft-max of tile t (needs nO == 2)
+  int o_col;         // TMEM column of the O accumulator
+  int tma_out;       // epilogue through a shared-memory tile + TMA store (C <= 128)
+  int dbg;           // tuning only: 1 skip soft-max/epilogue arithmetic, 2 skip the MMAs, 4 skip V loads' consumers
+  long long* ts;     // tuning only: per-role clock64 timeline of CTA 0 (NULL in production)
 };
+
+__device__ __forceinline__ void at_mark(const AttnParams& p, int role, int& n) {
+  if (p.ts != nullptr && blockIdx.x == 0 && n < 128) p.ts[role * 128 + n++] = clock64();
+}
 
 __global__ void __launch_bounds__(AT_THREADS, 1)
 epipolar_attn_tc_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CUtensorMap mapK,
-                        const __grid_constant__ CUtensorMap mapV, const AttnParams p) {
+                        const __grid_constant__ CUtensorMap mapV, const __grid_constant__ CUtensorMap mapO,
+                        const AttnParams p) {
   using namespace sftc;
   extern __shared__ __align__(1024) unsigned char smem[];
   const int NC = p.C / 64;                       // 64-channel chunks
   unsigned char* sStage = smem;                  // [AT_NSTAGE][AT_STAGE]
   unsigned char* sV = sStage + AT_NSTAGE * AT_STAGE;   // [3 key blocks][NC][64 rows][128 B]
   unsigned char* sP = sV + 3 * NC * AT_BOX;      // [3][128][128 B]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + AT_PBYTES);
+  unsigned char* sO = sP + AT_PBYTES;            // [NC][2 query halves][64 ch][128 B] output tile (tma_out only)
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sO + (p.tma_out ? 2 * NC * AT_BOX : 0));
   uint64_t* qk_full = bars;            // [2]
   uint64_t* qk_empty = bars + 2;       // [2]
   uint64_t* v_full = bars + 4;
   uint64_t* v_empty = bars + 5;
-  uint64_t* s_full = bars + 6;
-  uint64_t* p_full = bars + 7;
-  uint64_t* o_full = bars + 8;
-  uint64_t* o_empty = bars + 9;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 10);
+  uint64_t* s_full = bars + 6;         // [2]
+  uint64_t* s_empty = bars + 8;        // [2]
+  uint64_t* p_full = bars + 10;
+  uint64_t* o_full = bars + 11;        // [2]
+  uint64_t* o_empty = bars + 13;       // [2]
+  uint64_t* o_staged = bars + 15;      // output tile written to shared memory (256 arrivals)
+  uint64_t* so_free = bars + 16;       // output tile read by the TMA store
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 17);
+  float* sRed = reinterpret_cast<float*>(bars + 18);   // [2 halves][128 rows] row maxima, then the same for partial sums
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
     for (int s = 0; s < AT_NSTAGE; ++s) { mbar_init(&qk_full[s], 1); mbar_init(&qk_empty[s], 1); }
-    mbar_init(v_full, 1); mbar_init(v_empty, 1); mbar_init(s_full, 1); mbar_init(p_full, 128);
-    mbar_init(o_full, 1); mbar_init(o_empty, 128);
+    mbar_init(v_full, 1); mbar_init(v_empty, 1); mbar_init(p_full, 256);
+    for (int i = 0; i < 2; ++i) { mbar_init(&s_full[i], 1); mbar_init(&s_empty[i], 256); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&o_full[i], 1); mbar_init(&o_empty[i], 256); }
+    mbar_init(o_staged, 256); mbar_init(so_free, 1);
     fence_mbar_init();
-    tma_prefetch_desc(&mapQ); tma_prefetch_desc(&mapK); tma_prefetch_desc(&mapV);
+    tma_prefetch_desc(&mapQ); tma_prefetch_desc(&mapK); tma_prefetch_desc(&mapV); tma_prefetch_desc(&mapO);
   }
   if (warp == 1) tmem_alloc(tmem_slot, 512);
   tc_fence_before();
@@ -71,7 +96,7 @@ epipolar_attn_tc_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
   if (warp == 0) {
     // =========================================================== TMA producer
     if (lane == 0) {
-      int t = 0;
+      int t = 0, nts = 0;
       for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x, ++t) {
         const int qt = tile % p.nqt, r = tile / p.nqt;
         const int y = r % p.H, b = r / p.H;
@@ -79,6 +104,7 @@ epipolar_attn_tc_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
         for (int cc = 0; cc < NC; ++cc) {
           const int it = t * NC + cc, s = it % AT_NSTAGE;
           mbar_wait(&qk_empty[s], ((it / AT_NSTAGE) & 1) ^ 1);
+          at_mark(p, 0, nts);
           unsigned char* st = sStage + s * AT_STAGE;
           mbar_expect_tx(&qk_full[s], AT_STAGE);
           const int ch = b * p.C + cc * 64;
@@ -86,6 +112,7 @@ epipolar_attn_tc_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
           for (int j = 0; j < 3; ++j) tma_load_3d(st + (2 + j) * AT_BOX, &mapK, &qk_full[s], k0 + 64 * j, y, ch);
         }
         mbar_wait(v_empty, (t & 1) ^ 1);
+        at_mark(p, 0, nts);
         mbar_expect_tx(v_full, 3 * NC * AT_BOX);
         for (int kb = 0; kb < 3; ++kb)
           for (int cc = 0; cc < NC; ++cc)
@@ -97,78 +124,191 @@ epipolar_attn_tc_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
     if (lane == 0) {
       const uint32_t idesc_qk = make_idesc_bf16(128, 192, 1, 1);
       const uint32_t idesc_pv = make_idesc_bf16(128, p.C, 0, 0);
-      int t = 0;
-      for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x, ++t) {
-        for (int cc = 0; cc < NC; ++cc) {
-          const int it = t * NC + cc, s = it % AT_NSTAGE;
-          mbar_wait(&qk_full[s], (it / AT_NSTAGE) & 1);
-          tc_fence_after();
-          const uint32_t qa = smem_u32(sStage + s * AT_STAGE), ka = qa + 2 * AT_BOX;
+      const int ntl = (p.ntiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
+      // Two independent instruction streams, issued in whatever order their inputs arrive: S = Q^T K of tile qk_t
+      // (one 64-channel chunk at a time, into S accumulator qk_t % nS) and O = P V of tile pv_t.  Issuing them in a
+      // fixed order would stall the TMA stream: the V buffer is only released by P V, the Q/K stages only by Q^T K.
+      int it = 0, qk_t = 0, qk_cc = 0, pv_t = 0, nts = 0;
+      bool s_ok = false;
+      while (pv_t < ntl) {
+        if (qk_t < ntl) {
+          const int sb = qk_t % p.nS;
+          if (!s_ok) s_ok = mbar_test(&s_empty[sb], ((qk_t / p.nS) & 1) ^ 1);
+          const int s = it % AT_NSTAGE;
+          if (s_ok && mbar_test(&qk_full[s], (it / AT_NSTAGE) & 1)) {
+            tc_fence_after();
+            const uint32_t qa = smem_u32(sStage + s * AT_STAGE), ka = qa + 2 * AT_BOX;
+            if (!(p.dbg & 2))
 #pragma unroll
-          for (int j = 0; j < 4; ++j)
-            umma_bf16(tmem, make_smem_desc(qa + j * 2048, AT_BOX, 1024), make_smem_desc(ka + j * 2048, AT_BOX, 1024),
-                      idesc_qk, (cc | j) != 0);
-          umma_commit(&qk_empty[s]);
+            for (int j = 0; j < 4; ++j)
+              umma_bf16(tmem + sb * 192, make_smem_desc(qa + j * 2048, AT_BOX, 1024),
+                        make_smem_desc(ka + j * 2048, AT_BOX, 1024), idesc_qk, (qk_cc | j) != 0);
+            umma_commit(&qk_empty[s]);
+            at_mark(p, 1, nts);
+            ++it;
+            if (++qk_cc == NC) { umma_commit(&s_full[sb]); qk_cc = 0; ++qk_t; s_ok = false; }
+          }
         }
-        umma_commit(s_full);
-        mbar_wait(p_full, t & 1);
-        mbar_wait(v_full, t & 1);
-        mbar_wait(o_empty, (t & 1) ^ 1);
-        tc_fence_after();
-        const uint32_t pa = smem_u32(sP), va = smem_u32(sV);
-        for (int kb = 0; kb < 3; ++kb)
+        const int ob = pv_t % p.nO;
+        if (mbar_test(p_full, pv_t & 1) && mbar_test(v_full, pv_t & 1) &&
+            mbar_test(&o_empty[ob], ((pv_t / p.nO) & 1) ^ 1)) {
+          tc_fence_after();
+          const uint32_t pa = smem_u32(sP), va = smem_u32(sV);
+          if (!(p.dbg & 2))
+          for (int kb = 0; kb < 3; ++kb)
 #pragma unroll
-          for (int j = 0; j < 4; ++j)
-            umma_bf16(tmem + 256, make_smem_desc(pa + kb * 16384 + j * 32, 16, 1024),
-                      make_smem_desc(va + kb * NC * AT_BOX + j * 32, 16, 1024), idesc_pv, (kb | j) != 0);
-        umma_commit(v_empty);
-        umma_commit(o_full);
+            for (int j = 0; j < 4; ++j)
+              umma_bf16(tmem + p.o_col + ob * p.C, make_smem_desc(pa + kb * 16384 + j * 32, 16, 1024),
+                        make_smem_desc(va + kb * NC * AT_BOX + j * 32, 16, 1024), idesc_pv, (kb | j) != 0);
+          umma_commit(v_empty);
+          umma_commit(&o_full[ob]);
+          at_mark(p, 1, nts);
+          ++pv_t;
+        }
       }
     }
+  } else if (warp == 10) {
+    // =========================================================== TMA-store warp (output tiles, C <= 128)
+    if (lane == 0 && p.tma_out) {
+      int t = 0;
+      for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x, ++t) {
+        const int qt = tile % p.nqt, r = tile / p.nqt;
+        const int y = r % p.H, b = r / p.H;
+        mbar_wait(o_staged, t & 1);
+        for (int cc = 0; cc < NC; ++cc)
+          for (int qh = 0; qh < 2 && qt * 128 + 64 * qh < p.W; ++qh)
+            asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
+                         ::"l"(reinterpret_cast<uint64_t>(&mapO)), "r"(smem_u32(sO + (cc * 2 + qh) * AT_BOX)),
+                           "r"(qt * 128 + 64 * qh), "r"(y), "r"(b * p.C + cc * 64)
+                         : "memory");
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        mbar_arrive(so_free);
+      }
+      asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    }
   } else {
-    // =========================================================== soft-max + epilogue (128 threads, thread = query row)
-    const int quarter = warp & 3;
+    // =========================================================== soft-max + epilogue
+    // 256 threads: a query row is shared by two threads (warps w and w + 4 of the same TMEM lane quarter) which take
+    // alternate 32-key chunks of the band and half of the output channels each; row maxima and sums are exchanged
+    // through shared memory.  The epilogue of tile t - 1 runs after the soft-max of tile t, so that P V of tile t and
+    // Q^T K of tile t + 1 execute underneath it and these warps never wait for the tensor core.
+    const int quarter = warp & 3, half = (warp - 2) >> 2;
     const int row = quarter * 32 + lane;
     const uint32_t trow = tmem + (static_cast<uint32_t>(quarter * 32) << 16);
     const size_t HW = static_cast<size_t>(p.H) * p.W;
-    int t = 0;
-    for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x, ++t) {
-      const int qt = tile % p.nqt, r = tile / p.nqt;
+    float* sMax = sRed;          // [2 halves][128]
+    float* sSum = sRed + 256;    // [2 halves][128]
+    const int Ch = p.C >> 1;                               // channels of this half in the epilogue
+    int nts = 0;
+    const bool tsw = threadIdx.x == 64;
+
+    // epilogue of local tile te (global tile index etile): O rows from TMEM, normalise, bf16, store
+    auto epilogue = [&](int te, int etile, float mysum) {   // mysum: soft-max denominator of this row
+      const int qt = etile % p.nqt, r = etile / p.nqt;
       const int y = r % p.H, b = r / p.H;
+      const int q = qt * 128 + row;
+      const int ob = te % p.nO;
+      mbar_wait(&o_full[ob], (te / p.nO) & 1);
+      tc_fence_after();
+      if (tsw) at_mark(p, 2, nts);
+      const float inv = (mysum > 0.f) ? 1.0f / mysum : 0.f;
+      const uint32_t orow_t = trow + p.o_col + ob * p.C;
+      if (p.tma_out) {
+        // O rows -> [64 ch][64 q] bf16 boxes (SWIZZLE_128B, the layout of the input boxes) -> one TMA store per box
+        mbar_wait(so_free, (te & 1) ^ 1);
+        for (int c0 = half * Ch; c0 < (half + 1) * Ch && !(p.dbg & 1); c0 += 32) {
+          uint32_t v[32];
+          tmem_ld32(orow_t + c0, v);
+          tmem_ld_wait();
+          unsigned char* box = sO + ((c0 >> 6) * 2 + (row >> 6)) * AT_BOX + (row & 7) * 2;
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            const int c = (c0 & 63) + i;
+            *reinterpret_cast<__nv_bfloat16*>(box + c * 128 + ((((row & 63) >> 3) ^ (c & 7)) << 4)) =
+                __float2bfloat16(__uint_as_float(v[i]) * inv);
+          }
+        }
+        tc_fence_before();
+        mbar_arrive(&o_empty[ob]);
+        fence_proxy_async_smem();
+        mbar_arrive(o_staged);
+      } else {
+        __nv_bfloat16* orow = p.out + (static_cast<size_t>(b) * p.C) * HW + static_cast<size_t>(y) * p.W + q;
+        for (int c0 = half * Ch; c0 < (half + 1) * Ch; c0 += 32) {
+          uint32_t v[32];
+          tmem_ld32(orow_t + c0, v);
+          tmem_ld_wait();
+          if (q < p.W) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) orow[(c0 + i) * HW] = __float2bfloat16(__uint_as_float(v[i]) * inv);
+          }
+        }
+        tc_fence_before();
+        mbar_arrive(&o_empty[ob]);
+      }
+      if (tsw) at_mark(p, 2, nts);
+    };
+
+    int t = 0, prev_tile = 0;
+    float prev_sum = 0.f;
+    for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x, ++t) {
+      const int qt = tile % p.nqt;
       const int q = qt * 128 + row;
       // valid key columns of this row: j = row + 64 - d, d in [0, min(band, q + 1))
       const int nd = (q < p.W) ? min(p.band, q + 1) : 0;
       const int jhi = row + 64, jlo = jhi - nd + 1;       // inclusive range (empty when nd == 0)
-      mbar_wait(s_full, t & 1);
+      const int sb = t % p.nS;
+      const uint32_t srow = trow + sb * 192;
+      mbar_wait(&s_full[sb], (t / p.nS) & 1);
       tc_fence_after();
+      if (tsw) at_mark(p, 2, nts);
       // warp-uniform chunk range that any row of this warp can touch
       const int wlo = max(0, (quarter * 32 + 64 - p.band + 1) / 32), whi = (quarter * 32 + 31 + 64) / 32;
+      // valid keys of a 32-key chunk as a bit mask: one LOP3 per element instead of two compares
+      auto chunk_mask = [&](int cb) -> uint32_t {
+        const int lo = jlo - cb * 32, hi = jhi - cb * 32;          // valid bits [lo, hi]
+        if (hi < 0 || lo > 31 || lo > hi) return 0u;
+        const uint32_t ml = lo <= 0 ? 0xffffffffu : (0xffffffffu << lo);
+        const uint32_t mh = hi >= 31 ? 0xffffffffu : (0xffffffffu >> (31 - hi));
+        return ml & mh;
+      };
       float m = -INFINITY;
-      for (int cb = wlo; cb <= whi; ++cb) {
+      for (int cb = wlo + half; cb <= whi && !(p.dbg & 1); cb += 2) {
         uint32_t v[32];
-        tmem_ld32(trow + cb * 32, v);
+        tmem_ld32(srow + cb * 32, v);
+        const uint32_t vm = chunk_mask(cb);
         tmem_ld_wait();
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          const int j = cb * 32 + i;
-          if (j >= jlo && j <= jhi) m = fmaxf(m, __uint_as_float(v[i]));
-        }
+        for (int i = 0; i < 32; ++i)
+          if (vm & (1u << i)) m = fmaxf(m, __uint_as_float(v[i]));
       }
-      const float mb = (nd > 0) ? m * p.scale_log2 : 0.f;
+      sMax[half * 128 + row] = m;
+      named_bar_sync(2 + quarter, 64);                    // the two warps of this quarter
+      m = fmaxf(m, sMax[(half ^ 1) * 128 + row]);
+      const float scale = p.scale_log2;
+      const float mb = (nd > 0) ? m * scale : 0.f;
+      // P is single-buffered: P V of the previous tile must have read it
+      if (t > 0) mbar_wait(&o_full[(t - 1) % p.nO], ((t - 1) / p.nO) & 1);
+      if (tsw) at_mark(p, 2, nts);
       float sum = 0.f;
-      for (int cb = 0; cb < 6; ++cb) {
+      for (int cb = 0; cb < 6 && !(p.dbg & 1); ++cb) {
+        const bool live = cb >= wlo && cb <= whi;
+        if ((live ? ((cb - wlo) & 1) : (cb & 1)) != half) continue;
         uint32_t pk[16];
-        if (cb >= wlo && cb <= whi) {
+        if (live) {
           uint32_t v[32];
-          tmem_ld32(trow + cb * 32, v);
+          tmem_ld32(srow + cb * 32, v);
+          const uint32_t vm = chunk_mask(cb);
           tmem_ld_wait();
 #pragma unroll
           for (int i = 0; i < 32; i += 2) {
-            const int j = cb * 32 + i;
-            float e0 = (j >= jlo && j <= jhi) ? exp2f(fmaf(__uint_as_float(v[i]), p.scale_log2, -mb)) : 0.f;
-            float e1 = (j + 1 >= jlo && j + 1 <= jhi) ? exp2f(fmaf(__uint_as_float(v[i + 1]), p.scale_log2, -mb)) : 0.f;
+            // masked keys get exponent -inf -> weight exactly 0
+            const float x0 = fmaf(__uint_as_float(v[i]), scale, -mb), x1 = fmaf(__uint_as_float(v[i + 1]), scale, -mb);
+            const float e0 = ex2_approx((vm & (1u << i)) ? x0 : -INFINITY);
+            const float e1 = ex2_approx((vm & (2u << i)) ? x1 : -INFINITY);
+            sum += e0 + e1;
             __nv_bfloat162 h = __floats2bfloat162_rn(e0, e1);
-            sum += __low2float(h) + __high2float(h);
             pk[i >> 1] = *reinterpret_cast<uint32_t*>(&h);
           }
         } else {
@@ -184,27 +324,20 @@ epipolar_attn_tc_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
               make_uint4(pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
         }
       }
-      const float inv = (sum > 0.f) ? 1.0f / sum : 0.f;
+      sSum[half * 128 + row] = sum;
       fence_proxy_async_smem();
       tc_fence_before();
+      mbar_arrive(&s_empty[sb]);
       mbar_arrive(p_full);
-
-      // ---- epilogue: O rows from TMEM, normalise, bf16, store
-      mbar_wait(o_full, t & 1);
-      tc_fence_after();
-      __nv_bfloat16* orow = p.out + (static_cast<size_t>(b) * p.C) * HW + static_cast<size_t>(y) * p.W + q;
-      for (int c0 = 0; c0 < p.C; c0 += 32) {
-        uint32_t v[32];
-        tmem_ld32(trow + 256 + c0, v);
-        tmem_ld_wait();
-        if (q < p.W) {
-#pragma unroll
-          for (int i = 0; i < 32; ++i) orow[(c0 + i) * HW] = __float2bfloat16(__uint_as_float(v[i]) * inv);
-        }
-      }
-      tc_fence_before();
-      mbar_arrive(o_empty);
+      named_bar_sync(2 + quarter, 64);                    // (also orders the next tile's sMax write after this tile's read)
+      sum += sSum[(half ^ 1) * 128 + row];
+      if (tsw) at_mark(p, 2, nts);
+      if (!p.defer) epilogue(t, tile, sum);
+      else if (t > 0) epilogue(t - 1, prev_tile, prev_sum);
+      prev_tile = tile;
+      prev_sum = sum;
     }
+    if (p.defer && t > 0) epilogue(t - 1, prev_tile, prev_sum);
   }
   tc_fence_before();
   __syncthreads();
@@ -227,17 +360,33 @@ int launch_attn_tc(const void* q, const void* k, const void* v, void* out, int B
   SF_CHECK_ARG(nt < (1LL << 30), "epipolar_attn: too many tiles");
   p.ntiles = static_cast<int>(nt);
   p.scale_log2 = 1.4426950408889634f / sqrtf(static_cast<float>(C));
-  CUtensorMap mq, mk, mv;
+  // TMEM budget (512 columns): C = 64: 2 S + 2 O; C = 128: 2 S + 1 O (the early Q^T K keeps the TMA stream ahead,
+  // which measured faster than 1 S + 2 O with a deferred epilogue); C = 256: 1 S + 1 O
+  p.nS = C <= 128 ? 2 : 1;
+  p.nO = C == 64 ? 2 : 1;
+  p.defer = p.nO == 2;
+  p.o_col = C <= 128 ? 384 : 256;
+  p.tma_out = C <= 128 ? 1 : 0;
+  {
+    const char* d = getenv("SF_ATTN_DBG");
+    p.dbg = d ? atoi(d) : 0;
+    const char* f = getenv("SF_ATTN_DEFER");
+    if (f) p.defer = atoi(f);
+    const char* e = getenv("SF_ATTN_TS");   // tuning hook: device pointer of a [3][128] int64 timeline buffer
+    p.ts = e ? reinterpret_cast<long long*>(strtoull(e, nullptr, 16)) : nullptr;
+  }
+  CUtensorMap mq, mk, mv, mo;
   int rc;
   if ((rc = make_tmap_3d_bf16_sw128(&mq, q, W, H, static_cast<uint64_t>(B) * C, 1, 64))) return rc;
   if ((rc = make_tmap_3d_bf16_sw128(&mk, k, W, H, static_cast<uint64_t>(B) * C, 1, 64))) return rc;
   if ((rc = make_tmap_3d_bf16_sw128(&mv, v, W, H, static_cast<uint64_t>(B) * C, 1, 64))) return rc;
+  if ((rc = make_tmap_3d_bf16_sw128(&mo, out, W, H, static_cast<uint64_t>(B) * C, 1, 64))) return rc;
   const int NC = C / 64;
-  const size_t smem = AT_NSTAGE * AT_STAGE + 3 * NC * AT_BOX + AT_PBYTES + 128 + 1024;
+  const size_t smem = AT_NSTAGE * AT_STAGE + 3 * NC * AT_BOX + AT_PBYTES + (p.tma_out ? 2 * NC * AT_BOX : 0) + 2304;   // barriers + row maxima/sums
   SF_CUDA(cudaFuncSetAttribute(epipolar_attn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                static_cast<int>(smem)));
   const int grid = min(p.ntiles, sm_count());
-  epipolar_attn_tc_kernel<<<grid, AT_THREADS, smem, stream>>>(mq, mk, mv, p);
+  epipolar_attn_tc_kernel<<<grid, AT_THREADS, smem, stream>>>(mq, mk, mv, mo, p);
   SF_LAUNCH_CHECK();
   return SF_OK;
 }

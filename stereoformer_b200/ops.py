@@ -251,13 +251,16 @@ def dcn_forward(inp, weight, bias, offset, mask, stride, padding, dilation, grou
     return out
 
 
-def epipolar_attention(q, k, v, band, return_scores=False, algo=SF_ALGO_AUTO):
+def epipolar_attention(q, k, v, band, return_scores=False, algo=SF_ALGO_AUTO, out=None):
     """Band-restricted epipolar row cross-attention, bf16 [B,C,H,W] in/out (spec-derived)."""
     q, k, v = (_chk(t, n, dtype=torch.bfloat16, dim=4) for t, n in ((q, "q"), (k, "k"), (v, "v")))
     if not (q.shape == k.shape == v.shape):
         raise ValueError("q, k, v must share one shape")
     B, C, H, W = q.shape
-    out = torch.empty_like(q)
+    if out is None:
+        out = torch.empty_like(q)
+    elif out.shape != q.shape or out.dtype != q.dtype or not out.is_contiguous():
+        raise ValueError("out must be a contiguous bf16 tensor of q's shape")
     sc = torch.empty((B, band, H, W), device=q.device, dtype=torch.float32) if return_scores else None
     with torch.cuda.device(q.device):
         _lib.call("sf_epipolar_attn_bf16", _ptr(q), _ptr(k), _ptr(v), _ptr(out), _ptr(sc), B, C, H, W, int(band),

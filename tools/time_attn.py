@@ -8,13 +8,22 @@ sets = [[torch.randn(B, C, H, W, device="cuda").bfloat16() for _ in range(3)] fo
 for i in range(3):
     ops.epipolar_attention(*sets[i % 3], band, algo=algo)
 torch.cuda.synchronize()
-e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-n = 50
-e0.record()
-for i in range(n):
-    ops.epipolar_attention(*sets[i % 3], band, algo=algo)
-e1.record()
-torch.cuda.synchronize()
+# one CUDA graph of n launches over rotating inputs: the eager ctypes path is host-bound at these kernel times
+n = 30
+g = torch.cuda.CUDAGraph()
+st = torch.cuda.Stream()
+with torch.cuda.stream(st):
+    outs = [torch.empty_like(sets[0][0]) for _ in range(3)]
+    with torch.cuda.graph(g, stream=st):
+        for i in range(n):
+            ops.epipolar_attention(*sets[i % 3], band, algo=algo, out=outs[i % 3])
+    g.replay()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    g.replay()
+    e1.record()
+    torch.cuda.synchronize()
 us = e0.elapsed_time(e1) / n * 1e3
 gb = 4 * C * H * W * 2 * B / (us * 1e-6) / 1e9
 fl = 4.0 * H * W * band * C * B / (us * 1e-6) / 1e12
