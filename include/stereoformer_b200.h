@@ -32,6 +32,7 @@ extern "C" {
 #define SF_WIN_VARIANCE 1 /* variance_local_cost_volume.py: bounds = disp -/+ gamma * sigma        */
 #define SF_WIN_OFFSETS 2  /* Attempts/update.py:279-282: bounds = disp - lo, disp + up (tensors)   */
 #define SF_WIN_ABSOLUTE 3 /* pure_learning_method.py:112: lo/up ARE the bounds                     */
+#define SF_WIN_HEAD 4     /* as OFFSETS, lo = OffsetPredictionHead conv2 output [B,2,H,W] before relu2 (update.py:96-105): ReLU + chunk fused; up unused */
 
 /* scalar-division rounding (tensor / python scalar): PyTorch CPU divides, PyTorch CUDA multiplies
  * by the reciprocal.  Affects the last bit of sampling coordinates. */
@@ -134,6 +135,22 @@ SF_API int sf_epipolar_attn_bf16(const void* q, const void* k, const void* v, vo
  * disp [N,1,H,W], mask [N,9*F*F,H,W], out [N,1,F*H,F*W]. */
 SF_API int sf_upsample_convex_f32(const float* disp, const float* mask, float* out, int N, int H, int W, int factor,
                                   void* stream);
+/* same with the mask multiplied by mask_scale first: `mask = .25 * self.mask(hidden_state)` of
+ * Attempts/update.py:273 folded into the load (saves a read+write pass over the model's largest tensor). */
+SF_API int sf_upsample_convex_scaled_f32(const float* disp, const float* mask, float mask_scale, float* out, int N,
+                                         int H, int W, int factor, void* stream);
+
+/* f2: ConvGRU.forward gate arithmetic  models/LocalCostVolume/Attempts/update.py:36-49, around the three
+ * convolutions (which stay cuDNN).  b_pre / z_pre: conv_b / conv_z outputs BEFORE the sigmoid, [B,C,H,W] with batch
+ * stride *_bstride elements (>= C*H*W; lets both gates live in one [B,2C,H,W] tensor); prev_h [B,C,H,W] or NULL
+ * (= zeros, update.py:39); input [B,Cx,H,W].
+ *   sf_gru_reset_f32:  s_out [B,C+Cx,H,W] = cat(sigmoid(b_pre) * prev_h, input)              (update.py:45-46)
+ *   sf_gru_blend_f32:  h_out [B,C,H,W] = (1 - z) * prev_h + z * act(g_pre), z = sigmoid(z_pre),
+ *                      act = tanh, or softsign when softsign != 0                             (update.py:31-34,47-48) */
+SF_API int sf_gru_reset_f32(const float* b_pre, long long b_bstride, const float* prev_h, const float* input,
+                            float* s_out, int B, int C, int Cx, int H, int W, void* stream);
+SF_API int sf_gru_blend_f32(const float* z_pre, long long z_bstride, const float* g_pre, const float* prev_h,
+                            float* h_out, int B, int C, int H, int W, int softsign, void* stream);
 
 #ifdef __cplusplus
 }

@@ -170,6 +170,47 @@ def main():
     # ---- f1 convex upsampling -------------------------------------------------------------
     dlow, msk = torch.rand(1, 1, 3, 5) * 10, torch.randn(1, 576, 3, 5)
     save("upsample_convex8", disp=dlow, mask=msk, out=R["upsample_convex8"](dlow, msk))
+
+    # ---- f2 ConvGRU gates + one DLC-GRU step (update.py:16-49, 243-317) -------------------------------------
+    torch.manual_seed(77)
+    gru = upd.ConvGRU(nb_channel=8, softsign=False)
+    with torch.no_grad():                    # the reference zero-fills the biases; make them count
+        for c in (gru.conv_z, gru.conv_b, gru.conv_g):
+            c.bias.normal_(0, 0.5)
+    gin, gh = torch.randn(2, 8, 5, 12), torch.randn(2, 8, 5, 12)
+    cap = {}
+    hooks = [getattr(gru, n).register_forward_hook(lambda m, i, o, n=n: cap.update({n: o.detach().clone(),
+                                                                                    n + "_in": i[0].detach().clone()}))
+             for n in ("conv_z", "conv_b", "conv_g")]
+    with torch.no_grad():
+        gout = gru(gin, gh)
+    for h in hooks:
+        h.remove()
+    save("conv_gru", input=gin, prev_h=gh, z_pre=cap["conv_z"], b_pre=cap["conv_b"], s=cap["conv_g_in"],
+         g_pre=cap["conv_g"], h=gout, **{"sd_" + k: v for k, v in gru.state_dict().items() if "conv_" in k and
+                                         k.split(".")[0] in ("conv_z", "conv_b", "conv_g")})
+    gru_ss = upd.ConvGRU(nb_channel=8, softsign=True)
+    gru_ss.load_state_dict(gru.state_dict())
+    with torch.no_grad():
+        save("conv_gru_softsign", h=gru_ss(gin, gh))
+
+    torch.manual_seed(78)
+    step = upd.DisparityUpdateDLCWithMask(input_channels=24, hidden_dim=4, sample_points=20).eval()
+    with torch.no_grad():
+        for m in step.modules():
+            if isinstance(m, torch.nn.BatchNorm2d):
+                m.running_mean.normal_(0, 0.2); m.running_var.uniform_(0.5, 1.5)
+                m.weight.uniform_(0.5, 1.5); m.bias.normal_(0, 0.2)
+        step.offset.conv2.bias.fill_(1.0)    # keeps a good share of the bounds positive after relu2
+        lr, rr = torch.randn(2, 3, 6, 40), torch.randn(2, 3, 6, 40)
+        hid0 = torch.randn(2, 8, 6, 40)
+        d1, h1, m1 = step(cv, cur, lr, rr, hid0, True)
+        d2, h2, m2 = step(cv, d1, lr, rr, h1, False)
+    save("dlc_update_step", cv=cv, cur=cur, left=lr, right=rr, hidden0=hid0, disp1=d1, hidden1=h1,
+         mask1_head=m1[:, :18], disp2=d2, hidden2=h2, mask2_head=m2[:, :18],
+         **{"sd_" + k: (v[:18] if k.startswith("mask.2.") else v) for k, v in step.state_dict().items()
+            if "num_batches" not in k and not k.startswith(("gru.conv_zz", "gru.conv_bb", "gru.conv_gg"))})
+    # (only the first 18 of the 576 mask-head output filters are kept: the fixture checks mask[:, :18])
     print("golden vectors written to", os.path.normpath(OUT))
 
 

@@ -349,10 +349,70 @@ def epipolar_attention(q, k, v, band):
 
 
 # --------------------------------------------------------------------------- f1 ("next" row)
-def upsample_convex(disp, mask, factor=8):
-    """upsample_convex8, models/utils/upsample.py:22-38 (factor 8); RAFT upsample_flow uses 4."""
+def upsample_convex(disp, mask, factor=8, mask_scale=None):
+    """upsample_convex8, models/utils/upsample.py:22-38 (factor 8); RAFT upsample_flow uses 4.
+    mask_scale: the `.25 * self.mask(hidden_state)` of Attempts/update.py:273 applied first."""
     N, _, H, W = disp.shape
+    if mask_scale is not None:
+        mask = mask_scale * mask
     m = torch.softmax(mask.view(N, 1, 9, factor, factor, H, W), dim=2)
     u = F.unfold(factor * disp, [3, 3], padding=1).view(N, 1, 9, 1, 1, H, W)
     u = torch.sum(m * u, dim=2).permute(0, 1, 4, 2, 5, 3)
     return u.reshape(N, 1, factor * H, factor * W)
+
+
+# --------------------------------------------------------------------------- f2 ("next" row): ConvGRU + DLC step
+def gru_reset(b_pre, prev_h, inp):
+    """ConvGRU.forward, Attempts/update.py:43-46 after conv_b: s = cat(sigmoid(b_pre) * prev_h, input)."""
+    if prev_h is None:
+        prev_h = torch.zeros_like(b_pre)                                  # update.py:38-39
+    return torch.cat((torch.sigmoid(b_pre) * prev_h, inp), 1)
+
+
+def gru_blend(z_pre, g_pre, prev_h, softsign=False):
+    """ConvGRU.forward, Attempts/update.py:29-34,47-48: h = (1 - z) * prev_h + z * g."""
+    if prev_h is None:
+        prev_h = torch.zeros_like(g_pre)
+    z = torch.sigmoid(z_pre)
+    g = F.softsign(g_pre) if softsign else torch.tanh(g_pre)
+    return (1 - z) * prev_h + z * g
+
+
+def conv_gru(sd, prefix, inp, prev_h, softsign=False):
+    """ConvGRU.forward, Attempts/update.py:36-49, from a state dict (keys prefix + conv_z.weight ...)."""
+    h0 = torch.zeros(inp.size(0), sd[prefix + "conv_z.weight"].size(0), inp.size(2), inp.size(3),
+                     dtype=inp.dtype, device=inp.device) if prev_h is None else prev_h
+    x1 = torch.cat((inp, h0), 1)
+    z_pre = F.conv2d(x1, sd[prefix + "conv_z.weight"], sd[prefix + "conv_z.bias"], 1, 1)
+    b_pre = F.conv2d(x1, sd[prefix + "conv_b.weight"], sd[prefix + "conv_b.bias"], 1, 1)
+    s = gru_reset(b_pre, h0, inp)
+    g_pre = F.conv2d(s, sd[prefix + "conv_g.weight"], sd[prefix + "conv_g.bias"], 1, 1)
+    return gru_blend(z_pre, g_pre, h0, softsign)
+
+
+def head_window(old_volume, cur_disp, bounds_pre, n_points, consider_valid=True, recip=False):
+    """OffsetPredictionHead's relu2 + chunk (update.py:104-105, 275-277) followed by the window tail."""
+    lo, up = torch.chunk(torch.relu(bounds_pre), 2, dim=1)
+    return dlc_window(old_volume, cur_disp, lo, up, n_points, consider_valid, recip)
+
+
+def _conv_bn_relu(sd, prefix, x, eps=1e-5):
+    y = F.conv2d(x, sd[prefix + "0.weight"], None, 1, 1)
+    y = F.batch_norm(y, sd[prefix + "1.running_mean"], sd[prefix + "1.running_var"], sd[prefix + "1.weight"],
+                     sd[prefix + "1.bias"], False, 0.0, eps)
+    return F.relu(y)
+
+
+def dlc_update_step(sd, old_volume, cur_disp, left_r, right_r, hidden, n_points, consider_valid=True, recip=False):
+    """DisparityUpdateDLCWithMask.forward in eval mode, Attempts/update.py:263-317, from its state dict;
+    images already at the disparity resolution.  Returns (disp, hidden_state, mask) with mask = .25 * logits."""
+    err, unc = guidance(old_volume, cur_disp, left_r, right_r, recip=recip)
+    feat = torch.cat([_conv_bn_relu(sd, "encoder.disparity_error_encoder.", err),
+                      _conv_bn_relu(sd, "encoder.uncertain_encoder.", unc)], 1)
+    hidden = conv_gru(sd, "gru.", feat, hidden)
+    mask = F.conv2d(F.relu(F.conv2d(hidden, sd["mask.0.weight"], sd["mask.0.bias"], 1, 1)), sd["mask.2.weight"],
+                    sd["mask.2.bias"])
+    b_pre = F.conv2d(F.relu(F.conv2d(hidden, sd["offset.conv1.weight"], sd["offset.conv1.bias"], 1, 1)),
+                     sd["offset.conv2.weight"], sd["offset.conv2.bias"], 1, 1)
+    disp = head_window(old_volume, cur_disp, b_pre, n_points, consider_valid, recip)
+    return disp, hidden, .25 * mask

@@ -13,4 +13,7 @@ from .modules import (CorrBlock1D, CostVolume, DisparityEstimation, DisparityEst
 from .dcn_modules import (DeformConv, DeformConvPack, ModulatedDeformConv, ModulatedDeformConvPack,  # noqa: F401
                           ModulatedDeformNormal)
 
+from .update import (BasicGuidanceNet, ConvGRU, DisparityUpdateDLC, DisparityUpdateDLCWithMask,  # noqa: F401
+                     DlcGruRefiner, OffsetPredictionHead)
+
 __version__ = "0.1.0"

@@ -10,7 +10,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libsfb200.so")
 
 SF_ALGO_AUTO, SF_ALGO_TMA, SF_ALGO_GENERIC, SF_ALGO_TC = 0, 1, 2, 3
-SF_WIN_FIXED, SF_WIN_VARIANCE, SF_WIN_OFFSETS, SF_WIN_ABSOLUTE = 0, 1, 2, 3
+SF_WIN_FIXED, SF_WIN_VARIANCE, SF_WIN_OFFSETS, SF_WIN_ABSOLUTE, SF_WIN_HEAD = 0, 1, 2, 3, 4
 SF_DIV_TRUE, SF_DIV_RECIP = 0, 1
 
 _c_int, _c_float, _p = ctypes.c_int, ctypes.c_float, ctypes.c_void_p
@@ -32,6 +32,9 @@ SIGNATURES = {
     "sf_dcn_forward_ws_f32": [_p] * 6 + [_c_int] * 15 + [_p, ctypes.c_size_t, _c_int, _p],
     "sf_epipolar_attn_bf16": [_p] * 5 + [_c_int] * 6 + [_p],
     "sf_upsample_convex_f32": [_p, _p, _p] + [_c_int] * 4 + [_p],
+    "sf_upsample_convex_scaled_f32": [_p, _p, _c_float, _p] + [_c_int] * 4 + [_p],
+    "sf_gru_reset_f32": [_p, ctypes.c_longlong, _p, _p, _p] + [_c_int] * 5 + [_p],
+    "sf_gru_blend_f32": [_p, ctypes.c_longlong, _p, _p, _p] + [_c_int] * 5 + [_p],
 }
 
 RESTYPES = {"sf_dcn_workspace_bytes": ctypes.c_size_t}   # everything else returns an int status code

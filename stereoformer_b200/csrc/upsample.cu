@@ -13,7 +13,7 @@ namespace sf {
 template <int F>
 __global__ void __launch_bounds__(256)
 upsample_convex_kernel(const float* __restrict__ disp, const float* __restrict__ mask, float* __restrict__ out, int N,
-                       int H, int W) {
+                       int H, int W, float mask_scale) {
   // one thread per (low-resolution pixel, output sub-row i): F x 9 independent coalesced mask loads in flight per
   // thread, and a warp (32 consecutive x, same i) writes 32*F consecutive floats of one output row
   const size_t HW = static_cast<size_t>(H) * W, n = static_cast<size_t>(N) * HW * F;
@@ -37,6 +37,12 @@ upsample_convex_kernel(const float* __restrict__ disp, const float* __restrict__
     for (int j = 0; j < F; ++j)
 #pragma unroll
       for (int k = 0; k < 9; ++k) mv[j][k] = ldg_stream_f32(mp + static_cast<size_t>(k * F * F + j) * HW);
+    if (mask_scale != 1.0f) {                       // `.25 * self.mask(hidden)` of update.py:273 folded into the load
+#pragma unroll
+      for (int j = 0; j < F; ++j)
+#pragma unroll
+        for (int k = 0; k < 9; ++k) mv[j][k] = __fmul_rn(mask_scale, mv[j][k]);
+    }
     float res[F];
 #pragma unroll
     for (int j = 0; j < F; ++j) {
@@ -64,8 +70,8 @@ upsample_convex_kernel(const float* __restrict__ disp, const float* __restrict__
 
 }  // namespace sf
 
-extern "C" int sf_upsample_convex_f32(const float* disp, const float* mask, float* out, int N, int H, int W,
-                                      int factor, void* stream) {
+static int upsample_convex_impl(const float* disp, const float* mask, float mask_scale, float* out, int N, int H, int W,
+                                int factor, void* stream) {
   using namespace sf;
   SF_CHECK_ARG(disp && mask && out, "upsample_convex: null pointer");
   SF_CHECK_ARG(N > 0 && H > 0 && W > 0, "upsample_convex: non-positive dimension");
@@ -74,8 +80,18 @@ extern "C" int sf_upsample_convex_f32(const float* disp, const float* mask, floa
   size_t n = static_cast<size_t>(N) * H * W * factor;
   int grid = static_cast<int>(min(static_cast<size_t>(sm_count()) * 8, (n + 255) / 256));
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  if (factor == 8) upsample_convex_kernel<8><<<grid, 256, 0, s>>>(disp, mask, out, N, H, W);
-  else upsample_convex_kernel<4><<<grid, 256, 0, s>>>(disp, mask, out, N, H, W);
+  if (factor == 8) upsample_convex_kernel<8><<<grid, 256, 0, s>>>(disp, mask, out, N, H, W, mask_scale);
+  else upsample_convex_kernel<4><<<grid, 256, 0, s>>>(disp, mask, out, N, H, W, mask_scale);
   SF_LAUNCH_CHECK();
   return SF_OK;
+}
+
+extern "C" int sf_upsample_convex_f32(const float* disp, const float* mask, float* out, int N, int H, int W,
+                                      int factor, void* stream) {
+  return upsample_convex_impl(disp, mask, 1.0f, out, N, H, W, factor, stream);
+}
+
+extern "C" int sf_upsample_convex_scaled_f32(const float* disp, const float* mask, float mask_scale, float* out, int N,
+                                             int H, int W, int factor, void* stream) {
+  return upsample_convex_impl(disp, mask, mask_scale, out, N, H, W, factor, stream);
 }

@@ -121,6 +121,12 @@ local_window_kernel(const __grid_constant__ CUtensorMap mapCV, const WindowParam
   } else if (p.mode == SF_WIN_OFFSETS) {
     lower = sfm::fsub(cur, p.lo[pix]);
     upper = sfm::fadd(cur, p.up[pix]);
+  } else if (p.mode == SF_WIN_HEAD) {
+    // lo = the OffsetPredictionHead's last convolution output [B,2,H,W] BEFORE relu2 (update.py:96-105, 275-282):
+    // the ReLU and the channel chunk are folded into the load
+    const size_t hp = pix + static_cast<size_t>(b) * p.H * p.W;      // b * 2HW + y * W + x
+    lower = sfm::fsub(cur, fmaxf(p.lo[hp], 0.f));
+    upper = sfm::fadd(cur, fmaxf(p.lo[hp + static_cast<size_t>(p.H) * p.W], 0.f));
   } else {
     lower = p.lo[pix];
     upper = p.up[pix];
@@ -255,9 +261,10 @@ static int local_window_impl(const float* cv, const float* disp, const float* lo
   using namespace sf;
   SF_CHECK_ARG(cv && out, "local_window: null pointer");
   SF_CHECK_ARG(B > 0 && D > 0 && H > 0 && W > 0 && n_points > 0, "local_window: non-positive dimension");
-  SF_CHECK_ARG(mode >= SF_WIN_FIXED && mode <= SF_WIN_ABSOLUTE, "local_window: unknown mode %d", mode);
+  SF_CHECK_ARG(mode >= SF_WIN_FIXED && mode <= SF_WIN_HEAD, "local_window: unknown mode %d", mode);
   SF_CHECK_ARG((mode != SF_WIN_OFFSETS && mode != SF_WIN_ABSOLUTE) || (lo && up),
                "local_window: this mode needs the lo/up bound tensors");
+  SF_CHECK_ARG(mode != SF_WIN_HEAD || lo, "local_window: SF_WIN_HEAD needs the [B,2,H,W] head output in lo");
   SF_CHECK_ARG(static_cast<size_t>(D) * WIN_TPB * 4 <= 200 * 1024, "local_window: D=%d too large for the staged tile", D);
   WindowParams p;
   p.cv = cv; p.disp = disp; p.lo = lo; p.up = up; p.out = out; p.disp0_out = disp0_out;

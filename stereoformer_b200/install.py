@@ -13,6 +13,7 @@ import sys
 
 from . import DCN as _dcn
 from . import modules as _m
+from . import update as _u
 
 # reference module -> {attribute: replacement}
 PATCHES = {
@@ -26,7 +27,14 @@ PATCHES = {
         "Variance_Based_Local_Cost_Volume": _m.Variance_Based_Local_Cost_Volume,
         "build_cost_volume_from_volume": _m.build_cost_volume_from_volume},
     "models.LocalCostVolume.Attempts.update": {"build_cost_volume_from_volume": _m.build_cost_volume_from_volume,
-                                               "disp_warp": _m.disp_warp},
+                                               "disp_warp": _m.disp_warp, "ConvGRU": _u.ConvGRU,
+                                               "BasicGuidanceNet": _u.BasicGuidanceNet,
+                                               "OffsetPredictionHead": _u.OffsetPredictionHead,
+                                               "DisparityUpdateDLC": _u.DisparityUpdateDLC,
+                                               "DisparityUpdateDLCWithMask": _u.DisparityUpdateDLCWithMask},
+    # LowCNN binds the class at import time (baseline_dynamic_gru.py:11)
+    "models.LocalCostVolume.baseline_dynamic_gru": {"DisparityUpdateDLCWithMask": _u.DisparityUpdateDLCWithMask,
+                                                    "upsample_convex8": _m.upsample_convex8},
     "models.LocalCostVolume.Attempts.updatev2": {"build_cost_volume_from_volume": _m.build_cost_volume_from_volume,
                                                  "disp_warp": _m.disp_warp},
     "models.LocalCostVolume.Attempts.pure_learning_method": {

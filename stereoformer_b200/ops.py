@@ -11,10 +11,11 @@ import torch
 
 from . import _lib
 from ._lib import (SF_ALGO_AUTO, SF_ALGO_GENERIC, SF_ALGO_TC, SF_ALGO_TMA, SF_DIV_RECIP, SF_DIV_TRUE, SF_WIN_ABSOLUTE,
-                   SF_WIN_FIXED, SF_WIN_OFFSETS, SF_WIN_VARIANCE)
+                   SF_WIN_FIXED, SF_WIN_HEAD, SF_WIN_OFFSETS, SF_WIN_VARIANCE)
 
 __all__ = ["corr_volume", "gwc_volume", "shift_volume", "soft_argmin", "local_window", "sample_volume", "disp_warp",
-           "guidance", "corr1d_pyramid", "corr1d_lookup", "dcn_forward", "epipolar_attention", "upsample_convex"]
+           "guidance", "corr1d_pyramid", "corr1d_lookup", "dcn_forward", "epipolar_attention", "upsample_convex",
+           "gru_reset", "gru_blend"]
 
 
 def _chk(t, name, dtype=torch.float32, dim=None):
@@ -268,12 +269,66 @@ def epipolar_attention(q, k, v, band, return_scores=False, algo=SF_ALGO_AUTO, ou
     return (out, sc) if return_scores else out
 
 
-def upsample_convex(disp, mask, factor=8):
+def upsample_convex(disp, mask, factor=8, mask_scale=1.0, out=None):
+    """Convex upsampling; ``mask_scale`` multiplies the mask first (the `.25 *` of Attempts/update.py:273)."""
     disp, mask = _chk(disp, "disp", dim=4), _chk(mask, "mask", dim=4)
     N, _, H, W = disp.shape
     if mask.shape != (N, 9 * factor * factor, H, W):
         raise ValueError("mask must be [N,%d,H,W]" % (9 * factor * factor))
-    out = torch.empty((N, 1, factor * H, factor * W), device=disp.device, dtype=torch.float32)
+    if out is None:
+        out = torch.empty((N, 1, factor * H, factor * W), device=disp.device, dtype=torch.float32)
+    elif out.shape != (N, 1, factor * H, factor * W) or out.dtype != torch.float32 or not out.is_contiguous():
+        raise ValueError("out must be a contiguous fp32 [N,1,F*H,F*W] tensor")
     with torch.cuda.device(disp.device):
-        _lib.call("sf_upsample_convex_f32", _ptr(disp), _ptr(mask), _ptr(out), N, H, W, int(factor), _stream())
+        if mask_scale == 1.0:
+            _lib.call("sf_upsample_convex_f32", _ptr(disp), _ptr(mask), _ptr(out), N, H, W, int(factor), _stream())
+        else:
+            _lib.call("sf_upsample_convex_scaled_f32", _ptr(disp), _ptr(mask), float(mask_scale), _ptr(out), N, H, W,
+                      int(factor), _stream())
+    return out
+
+
+def _gate_view(t, name, B, C, H, W):
+    """A [B,C,H,W] gate pre-activation that may be a channel slice of a wider contiguous tensor -> (tensor, stride)."""
+    if not torch.is_tensor(t) or not t.is_cuda:
+        raise RuntimeError("Not implemented on the CPU (%s)" % name)
+    if t.dtype != torch.float32 or t.shape != (B, C, H, W):
+        raise ValueError("%s must be fp32 [%d,%d,%d,%d], got %s %s" % (name, B, C, H, W, t.dtype, tuple(t.shape)))
+    if t.stride()[1:] != (H * W, W, 1) or (B > 1 and t.stride(0) < C * H * W):
+        t = t.contiguous()
+    return t, (t.stride(0) if B > 1 else C * H * W)
+
+
+def gru_reset(b_pre, prev_h, inp, out=None):
+    """ConvGRU reset path: cat(sigmoid(b_pre) * prev_h, input) -> [B,C+Cx,H,W]  (Attempts/update.py:43-46)."""
+    inp = _chk(inp, "input", dim=4)
+    B, Cx, H, W = inp.shape
+    C = b_pre.shape[1]
+    b_pre, bs = _gate_view(b_pre, "b_pre", B, C, H, W)
+    if prev_h is not None:
+        prev_h = _chk(prev_h, "prev_h", dim=4)
+        if prev_h.shape != (B, C, H, W):
+            raise ValueError("prev_h must be [B,C,H,W]")
+    if out is None:
+        out = torch.empty((B, C + Cx, H, W), device=inp.device, dtype=torch.float32)
+    with torch.cuda.device(inp.device):
+        _lib.call("sf_gru_reset_f32", _ptr(b_pre), ctypes.c_longlong(bs), _ptr(prev_h), _ptr(inp), _ptr(out), B, C, Cx,
+                  H, W, _stream())
+    return out
+
+
+def gru_blend(z_pre, g_pre, prev_h, softsign=False, out=None):
+    """ConvGRU output: (1 - sigmoid(z_pre)) * prev_h + sigmoid(z_pre) * tanh(g_pre)  (Attempts/update.py:47-48)."""
+    g_pre = _chk(g_pre, "g_pre", dim=4)
+    B, C, H, W = g_pre.shape
+    z_pre, zs = _gate_view(z_pre, "z_pre", B, C, H, W)
+    if prev_h is not None:
+        prev_h = _chk(prev_h, "prev_h", dim=4)
+        if prev_h.shape != (B, C, H, W):
+            raise ValueError("prev_h must be [B,C,H,W]")
+    if out is None:
+        out = torch.empty_like(g_pre)
+    with torch.cuda.device(g_pre.device):
+        _lib.call("sf_gru_blend_f32", _ptr(z_pre), ctypes.c_longlong(zs), _ptr(g_pre), _ptr(prev_h), _ptr(out), B, C, H, W,
+                  int(bool(softsign)), _stream())
     return out

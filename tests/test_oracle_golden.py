@@ -107,3 +107,27 @@ def test_attention_is_spec_derived_unpinned():
     for d in range(4):
         ref[..., d:] += p[:, d:d + 1, :, d:] * v[..., : 12 - d]
     assert torch.allclose(o, ref, atol=1e-5)
+
+
+def _sd(g):
+    return {k[3:]: v for k, v in g.items() if k.startswith("sd_")}
+
+
+def test_conv_gru_gates():
+    """f2: the gate arithmetic around the three convolutions, pinned on the reference ConvGRU's own intermediate
+    tensors (forward hooks on conv_z / conv_b / conv_g)."""
+    g = load_golden("conv_gru")
+    assert eq(O.gru_reset(g["b_pre"], g["prev_h"], g["input"]), g["s"])
+    assert eq(O.gru_blend(g["z_pre"], g["g_pre"], g["prev_h"]), g["h"])
+    assert eq(O.conv_gru(_sd(g), "", g["input"], g["prev_h"]), g["h"])
+    assert eq(O.conv_gru(_sd(g), "", g["input"], g["prev_h"], softsign=True), load_golden("conv_gru_softsign")["h"])
+
+
+def test_dlc_update_step():
+    """f2: two chained DisparityUpdateDLCWithMask steps (consider_valid True then False) from the state dict."""
+    g = load_golden("dlc_update_step")
+    sd = _sd(g)
+    d1, h1, m1 = O.dlc_update_step(sd, g["cv"], g["cur"], g["left"], g["right"], g["hidden0"], 20, True)
+    assert eq(h1, g["hidden1"]) and eq(m1, g["mask1_head"]) and eq(d1, g["disp1"])
+    d2, h2, m2 = O.dlc_update_step(sd, g["cv"], d1, g["left"], g["right"], h1, 20, False)
+    assert eq(h2, g["hidden2"]) and eq(m2, g["mask2_head"]) and eq(d2, g["disp2"])
