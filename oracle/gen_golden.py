@@ -211,6 +211,36 @@ def main():
          **{"sd_" + k: (v[:18] if k.startswith("mask.2.") else v) for k, v in step.state_dict().items()
             if "num_batches" not in k and not k.startswith(("gru.conv_zz", "gru.conv_bb", "gru.conv_gg"))})
     # (only the first 18 of the 576 mask-head output filters are kept: the fixture checks mask[:, :18])
+
+    # ---- f4 on-disk formats: PFM bytes written / read by the reference's utils/file_io.py ------------------
+    import tempfile
+    from utils import file_io as fio
+    rng = np.random.RandomState(5)
+    grey = (rng.rand(5, 7).astype(np.float32) * 200)
+    color = rng.randn(4, 6, 3).astype(np.float32)
+    blobs = {}
+    with tempfile.TemporaryDirectory() as td:
+        for name, img, sc in (("grey", grey, 1), ("color", color, 2.5), ("grey1", grey[:, :, None], 1)):
+            fn = os.path.join(td, name + ".pfm")
+            fio.write_pfm(fn, img, sc)
+            blobs["pfm_" + name] = np.frombuffer(open(fn, "rb").read(), dtype=np.uint8)
+            back, bsc = fio._read_pfm(fn)
+            blobs["read_" + name] = np.ascontiguousarray(back)
+            blobs["scale_" + name] = bsc
+        big = os.path.join(td, "big.pfm")               # a big-endian file (positive scale)
+        with open(big, "wb") as f:
+            f.write(b"Pf\n7 5\n1.000000\n")
+            f.write(np.flipud(grey).astype(">f4").tobytes())
+        blobs["pfm_big"] = np.frombuffer(open(big, "rb").read(), dtype=np.uint8)
+        blobs["read_big"] = np.ascontiguousarray(fio._read_pfm(big)[0]).astype(np.float32)
+        from PIL import Image
+        k16 = (rng.rand(4, 9) * 40000).astype(np.uint16)
+        kp = os.path.join(td, "kitti.png")
+        Image.fromarray(k16).save(kp)
+        blobs["png_kitti"] = np.frombuffer(open(kp, "rb").read(), dtype=np.uint8)
+        blobs["read_kitti"] = fio.read_disp(kp)
+        blobs["read_subset"] = fio.read_disp(os.path.join(td, "grey.pfm"), subset=True)
+    save("file_io", grey=grey, color=color, **blobs)
     print("golden vectors written to", os.path.normpath(OUT))
 
 
