@@ -126,6 +126,16 @@ SF_API int sf_dcn_forward_ws_f32(const float* input, const float* weight, const 
                                  int stride_h, int stride_w, int pad_h, int pad_w, int dil_h, int dil_w, int group,
                                  int deformable_group, void* workspace, size_t workspace_bytes, int algo, void* stream);
 
+/* f3: DCN backward  deform/src/cuda/modulated_deform_conv_cuda.cu:124-280 (DCNv1: deform_conv_cuda.cu, mask = NULL).
+ * Every grad_* pointer may be NULL (that gradient is skipped); grad_input and grad_weight are zero-filled here and
+ * accumulated with atomics (as the reference's col2im does), grad_offset / grad_mask / grad_bias are plain stores.
+ * Kernels up to 36 taps (6x6). */
+SF_API int sf_dcn_backward_f32(const float* input, const float* weight, const float* offset, const float* mask,
+                               const float* grad_out, float* grad_input, float* grad_weight, float* grad_bias,
+                               float* grad_offset, float* grad_mask, int B, int Cin, int H, int W, int Cout, int kh,
+                               int kw, int stride_h, int stride_w, int pad_h, int pad_w, int dil_h, int dil_w,
+                               int group, int deformable_group, void* stream);
+
 /* a11: epipolar row cross-attention (reference file is empty; SPEC-DERIVED from north_star).  q,k,v,out are
  * bf16 [B,C,H,W]; scores optional fp32 [B,band,H,W] (-inf outside the band). */
 SF_API int sf_epipolar_attn_bf16(const void* q, const void* k, const void* v, void* out, float* scores, int B, int C,

@@ -1,7 +1,8 @@
 """Drop-in for the reference's pybind extension module ``DCN`` (deform/src/vision.cpp:5-12).
 
 Same six function names and positional signatures as the pybind module; the forward functions run
-the sm_100a fused implicit-GEMM kernel through the C ABI (``sf_dcn_forward_f32``).  Register it under
+the sm_100a fused implicit-GEMM kernel through the C ABI (``sf_dcn_forward_f32``), the backward functions
+``sf_dcn_backward_f32`` (no column buffer either way).  Register it under
 the name the reference imports with ``stereoformer_b200.install.install_dcn()`` (``import DCN`` in
 deform/functions/*_func.py:13 then resolves to this module).
 
@@ -62,10 +63,43 @@ def _not_built(name, why):
     return f
 
 
-modulated_deform_conv_backward = _not_built("modulated_deform_conv_backward",
-                                            "backward passes are the 'next' row of the scope table (SURVEY 8f-3)")
-deform_conv_backward = _not_built("deform_conv_backward",
-                                  "backward passes are the 'next' row of the scope table (SURVEY 8f-3)")
+def _check_grad(input, weight, grad_output, stride, pad, dil):
+    """modulated_deform_conv_cuda.cu:163-192: grad_output must match the forward's output shape."""
+    if not grad_output.is_cuda:
+        raise RuntimeError("grad_output must be a CUDA tensor")
+    kh, kw = weight.shape[2:]
+    ho = (input.shape[2] + 2 * pad[0] - (dil[0] * (kh - 1) + 1)) // stride[0] + 1
+    wo = (input.shape[3] + 2 * pad[1] - (dil[1] * (kw - 1) + 1)) // stride[1] + 1
+    if grad_output.shape[0] != input.shape[0]:
+        raise RuntimeError("Input shape and grad_out batch wont match: (%d vs %d)." % (input.shape[0], grad_output.shape[0]))
+    if grad_output.shape[1] != weight.shape[0]:
+        raise RuntimeError("Input shape and grad_out channels_out wont match: (%d vs %d)." % (weight.shape[0], grad_output.shape[1]))
+    if tuple(grad_output.shape[2:]) != (ho, wo):
+        raise RuntimeError("Input shape and grad_out shape wont match: (%d x %d vs %d x %d)." %
+                           (ho, wo, grad_output.shape[2], grad_output.shape[3]))
+
+
+def modulated_deform_conv_backward(input, weight, bias, offset, mask, grad_output, kernel_h, kernel_w, stride_h,
+                                   stride_w, pad_h, pad_w, dilation_h, dilation_w, group, deformable_group, im2col_step):
+    """deform/src/modulated_deform_conv.h:46-92 -> [grad_input, grad_offset, grad_mask, grad_weight, grad_bias]
+    (modulated_deform_conv_cuda.cu:277-279)."""
+    _checks(input, weight, bias, offset, kernel_h, kernel_w, group, im2col_step, mask)
+    _check_grad(input, weight, grad_output, (stride_h, stride_w), (pad_h, pad_w), (dilation_h, dilation_w))
+    return list(ops.dcn_backward(input, weight, offset, mask, grad_output.contiguous(), (stride_h, stride_w),
+                                 (pad_h, pad_w), (dilation_h, dilation_w), group, deformable_group))
+
+
+def deform_conv_backward(input, weight, bias, offset, grad_output, kernel_h, kernel_w, stride_h, stride_w, pad_h, pad_w,
+                         dilation_h, dilation_w, group, deformable_group, im2col_step):
+    """deform/src/deform_conv.h:45-88 -> [grad_input, grad_offset, grad_weight, grad_bias] (DCNv1)."""
+    _checks(input, weight, bias, offset, kernel_h, kernel_w, group, im2col_step)
+    _check_grad(input, weight, grad_output, (stride_h, stride_w), (pad_h, pad_w), (dilation_h, dilation_w))
+    g_in, g_off, _, g_w, g_b = ops.dcn_backward(input, weight, offset, None, grad_output.contiguous(),
+                                                (stride_h, stride_w), (pad_h, pad_w), (dilation_h, dilation_w), group,
+                                                deformable_group)
+    return [g_in, g_off, g_w, g_b]
+
+
 deform_psroi_pooling_forward = _not_built("deform_psroi_pooling_forward",
                                           "deformable PS-RoI pooling is out of scope (detection op, no stereo caller)")
 deform_psroi_pooling_backward = _not_built("deform_psroi_pooling_backward",

@@ -28,6 +28,7 @@ SIGNATURES = {
     "sf_corr1d_pyramid_f32": [_p, _p, _p] + [_c_int] * 7 + [_p],
     "sf_corr1d_lookup_f32": [_p, _p, _c_int, _c_int, _p, _p, _p, _p] + [_c_int] * 4 + [_p],
     "sf_dcn_forward_f32": [_p] * 6 + [_c_int] * 15 + [_p],
+    "sf_dcn_backward_f32": [_p] * 10 + [_c_int] * 15 + [_p],
     "sf_dcn_workspace_bytes": [_c_int] * 5,
     "sf_dcn_forward_ws_f32": [_p] * 6 + [_c_int] * 15 + [_p, ctypes.c_size_t, _c_int, _p],
     "sf_epipolar_attn_bf16": [_p] * 5 + [_c_int] * 6 + [_p],

@@ -2,13 +2,14 @@
 
 Same constructor / forward signatures and parameter names (``weight``, ``bias``, ``conv_offset_mask.*``,
 ``conv_offset.*``) so reference checkpoints load unchanged.  The forward runs the sm_100a kernel through
-``stereoformer_b200.DCN`` (the pybind drop-in); backward raises until SURVEY 8f-3 is built.
+``stereoformer_b200.DCN`` (the pybind drop-in), the backward ``sf_dcn_backward_f32``.
 """
 import math
 
 import torch
 from torch import nn
 from torch.autograd import Function
+from torch.autograd.function import once_differentiable
 from torch.nn import init
 from torch.nn.modules.utils import _pair
 
@@ -21,29 +22,49 @@ class ModulatedDeformConvFunction(Function):
     @staticmethod
     def forward(ctx, input, offset, mask, weight, bias, stride, padding, dilation, groups, deformable_groups,
                 im2col_step):
-        s, p, d = _pair(stride), _pair(padding), _pair(dilation)
-        k = _pair(weight.shape[2:4])
-        return DCN.modulated_deform_conv_forward(input, weight, bias, offset, mask, k[0], k[1], s[0], s[1], p[0], p[1],
-                                                 d[0], d[1], groups, deformable_groups, im2col_step)
+        ctx.stride, ctx.padding, ctx.dilation = _pair(stride), _pair(padding), _pair(dilation)
+        ctx.kernel_size = _pair(weight.shape[2:4])
+        ctx.groups, ctx.deformable_groups, ctx.im2col_step = groups, deformable_groups, im2col_step
+        s, p, d, k = ctx.stride, ctx.padding, ctx.dilation, ctx.kernel_size
+        output = DCN.modulated_deform_conv_forward(input, weight, bias, offset, mask, k[0], k[1], s[0], s[1], p[0],
+                                                   p[1], d[0], d[1], groups, deformable_groups, im2col_step)
+        ctx.save_for_backward(input, offset, mask, weight, bias)
+        return output
 
     @staticmethod
+    @once_differentiable
     def backward(ctx, grad_output):
-        return DCN.modulated_deform_conv_backward()
+        input, offset, mask, weight, bias = ctx.saved_tensors
+        s, p, d, k = ctx.stride, ctx.padding, ctx.dilation, ctx.kernel_size
+        grad_input, grad_offset, grad_mask, grad_weight, grad_bias = DCN.modulated_deform_conv_backward(
+            input, weight, bias, offset, mask, grad_output, k[0], k[1], s[0], s[1], p[0], p[1], d[0], d[1], ctx.groups,
+            ctx.deformable_groups, ctx.im2col_step)
+        return grad_input, grad_offset, grad_mask, grad_weight, grad_bias, None, None, None, None, None, None
 
 
 class DeformConvFunction(Function):
-    """deform/functions/deform_conv_func.py:15-55."""
+    """deform/functions/deform_conv_func.py:15-75."""
 
     @staticmethod
     def forward(ctx, input, offset, weight, bias, stride, padding, dilation, group, deformable_groups, im2col_step):
-        s, p, d = _pair(stride), _pair(padding), _pair(dilation)
-        k = _pair(weight.shape[2:4])
-        return DCN.deform_conv_forward(input, weight, bias, offset, k[0], k[1], s[0], s[1], p[0], p[1], d[0], d[1],
-                                       group, deformable_groups, im2col_step)
+        ctx.stride, ctx.padding, ctx.dilation = _pair(stride), _pair(padding), _pair(dilation)
+        ctx.kernel_size = _pair(weight.shape[2:4])
+        ctx.group, ctx.deformable_groups, ctx.im2col_step = group, deformable_groups, im2col_step
+        s, p, d, k = ctx.stride, ctx.padding, ctx.dilation, ctx.kernel_size
+        output = DCN.deform_conv_forward(input, weight, bias, offset, k[0], k[1], s[0], s[1], p[0], p[1], d[0], d[1],
+                                         group, deformable_groups, im2col_step)
+        ctx.save_for_backward(input, offset, weight, bias)
+        return output
 
     @staticmethod
+    @once_differentiable
     def backward(ctx, grad_output):
-        return DCN.deform_conv_backward()
+        input, offset, weight, bias = ctx.saved_tensors
+        s, p, d, k = ctx.stride, ctx.padding, ctx.dilation, ctx.kernel_size
+        grad_input, grad_offset, grad_weight, grad_bias = DCN.deform_conv_backward(
+            input, weight, bias, offset, grad_output, k[0], k[1], s[0], s[1], p[0], p[1], d[0], d[1], ctx.group,
+            ctx.deformable_groups, ctx.im2col_step)
+        return grad_input, grad_offset, grad_weight, grad_bias, None, None, None, None, None, None
 
 
 class _DeformBase(nn.Module):

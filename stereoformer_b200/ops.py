@@ -14,7 +14,7 @@ from ._lib import (SF_ALGO_AUTO, SF_ALGO_GENERIC, SF_ALGO_TC, SF_ALGO_TMA, SF_DI
                    SF_WIN_FIXED, SF_WIN_HEAD, SF_WIN_OFFSETS, SF_WIN_VARIANCE)
 
 __all__ = ["corr_volume", "gwc_volume", "shift_volume", "soft_argmin", "local_window", "sample_volume", "disp_warp",
-           "guidance", "corr1d_pyramid", "corr1d_lookup", "dcn_forward", "epipolar_attention", "upsample_convex",
+           "guidance", "corr1d_pyramid", "corr1d_lookup", "dcn_forward", "dcn_backward", "epipolar_attention", "upsample_convex",
            "gru_reset", "gru_blend"]
 
 
@@ -250,6 +250,42 @@ def dcn_forward(inp, weight, bias, offset, mask, stride, padding, dilation, grou
                   Cin, H, W, Cout, kh, kw, sh, sw, ph, pw, dh, dw, int(groups), int(deformable_groups), _ptr(ws),
                   ctypes.c_size_t(nws), int(algo), _stream())
     return out
+
+
+def dcn_backward(inp, weight, offset, mask, grad_out, stride, padding, dilation, groups, deformable_groups,
+                 needs=(True, True, True, True, True)):
+    """DCNv2 / DCNv1 (mask None) backward -> (grad_input, grad_offset, grad_mask, grad_weight, grad_bias), the order
+    of the reference's DCN.modulated_deform_conv_backward (modulated_deform_conv_cuda.cu:277-279); entries whose
+    ``needs`` flag is False (or grad_mask for DCNv1) are None."""
+    inp, weight = _chk(inp, "input", dim=4), _chk(weight, "weight", dim=4)
+    offset, grad_out = _chk(offset, "offset", dim=4), _chk(grad_out, "grad_output", dim=4)
+    mask = _chk(mask, "mask", dim=4) if mask is not None else None
+    B, Cin, H, W = inp.shape
+    Cout, Cg, kh, kw = weight.shape
+    sh, sw = stride
+    ph, pw = padding
+    dh, dw = dilation
+    Ho = (H + 2 * ph - (dh * (kh - 1) + 1)) // sh + 1
+    Wo = (W + 2 * pw - (dw * (kw - 1) + 1)) // sw + 1
+    if Cin != Cg * groups:
+        raise RuntimeError("Input shape and kernel channels wont match: (%d vs %d)." % (Cin, Cg * groups))
+    if grad_out.shape != (B, Cout, Ho, Wo):   # modulated_deform_conv_cuda.cu:185-192
+        raise RuntimeError("Input shape and grad_out shape wont match: (%s vs %s)." % ((B, Cout, Ho, Wo), tuple(grad_out.shape)))
+    if offset.shape != (B, deformable_groups * 2 * kh * kw, Ho, Wo):
+        raise RuntimeError("offset shape %s, expected %s" % (tuple(offset.shape),
+                                                             (B, deformable_groups * 2 * kh * kw, Ho, Wo)))
+    n_in, n_off, n_mask, n_w, n_b = needs
+    n_mask = n_mask and mask is not None
+    g_in = torch.empty_like(inp) if n_in else None
+    g_off = torch.empty_like(offset) if n_off else None
+    g_mask = torch.empty_like(mask) if n_mask else None
+    g_w = torch.empty_like(weight) if n_w else None
+    g_b = torch.empty(Cout, device=inp.device, dtype=torch.float32) if n_b else None
+    with torch.cuda.device(inp.device):
+        _lib.call("sf_dcn_backward_f32", _ptr(inp), _ptr(weight), _ptr(offset), _ptr(mask), _ptr(grad_out), _ptr(g_in),
+                  _ptr(g_w), _ptr(g_b), _ptr(g_off), _ptr(g_mask), B, Cin, H, W, Cout, kh, kw, sh, sw, ph, pw, dh, dw,
+                  int(groups), int(deformable_groups), _stream())
+    return g_in, g_off, g_mask, g_w, g_b
 
 
 def epipolar_attention(q, k, v, band, return_scores=False, algo=SF_ALGO_AUTO, out=None):

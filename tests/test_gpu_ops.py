@@ -295,7 +295,7 @@ def test_dropin_modules_chain():
     assert blk(coords).shape == (1, 36, 4, 64)
     x = dev(fl).requires_grad_(True)
     y = sf.CostVolume(24)(x, dev(fr))
-    with pytest.raises(NotImplementedError):
+    with pytest.raises(NotImplementedError):            # autograd for a1/a3/a4/a7 is not built (DCN's is)
         y.sum().backward()
 
 

@@ -36,3 +36,16 @@ for B, Cin, Cout, H, W, G, dg in shapes:
         by = (Cin + 27 * dg + Cout) * M * 4
         print("dcn %-8s B=%d %d->%d %dx%d G=%d dg=%d  %8.1f us  %6.1f TFLOP/s  %6.0f GB/s (algorithmic)" %
               (name, B, Cin, Cout, H, W, G, dg, us, fl / us / 1e6, by / us / 1e3))
+    # backward (f3): data (input / offset / mask) and weight gradients, event-timed eagerly (ms-scale kernels)
+    go = torch.randn(B, Cout, H, W, device="cuda")
+    for needs, name in (((True, True, True, False, False), "bwd data"), ((False, False, False, True, True), "bwd weight")):
+        fn = lambda: ops.dcn_backward(x, w, off, msk, go, (1, 1), (1, 1), (1, 1), G, dg, needs=needs)
+        fn(); torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(3):
+            fn()
+        e1.record(); torch.cuda.synchronize()
+        us = e0.elapsed_time(e1) / 3 * 1e3
+        print("dcn %-10s B=%d %d->%d %dx%d G=%d dg=%d  %8.1f us  %6.1f TFLOP/s" %
+              (name, B, Cin, Cout, H, W, G, dg, us, 2.0 * H * W * B * (Cin // G) * 9 * Cout / us / 1e6))
