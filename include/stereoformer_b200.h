@@ -126,6 +126,44 @@ SF_API int sf_dcn_forward_ws_f32(const float* input, const float* weight, const 
                                  int stride_h, int stride_w, int pad_h, int pad_w, int dil_h, int dil_w, int group,
                                  int deformable_group, void* workspace, size_t workspace_bytes, int algo, void* stream);
 
+/* f3: backward passes of the pure-PyTorch operators = the gradients autograd derives for the reference modules.
+ * Any grad_* output may be NULL (skipped).
+ *   sf_corr_volume_backward_f32   a1/a2  build_cost_volume.py:39-47, GWC_Cost_Volume.py:14-24 (groups as the forward)
+ *   sf_soft_argmin_backward_f32   a3     estimation.py:14-62
+ *   sf_local_window_backward_f32  a4/a6  fixed_local_cost_volume.py:18-80, Attempts/update.py:275-313; modes FIXED,
+ *                                        OFFSETS, ABSOLUTE, HEAD (grad_lo is then [B,2,H,W], ReLU backward included);
+ *                                        straight-through ceil/floor end in .long(): no gradient through indices
+ *   sf_sample_volume_backward_f32 build_cost_volume_from_volume alone (cand [B,K,H,W])
+ *   sf_disp_warp_backward_f32     a7     disparity_warper.py:83-106 (grad_img is zero-filled here, atomics) */
+SF_API int sf_corr_volume_backward_f32(const float* left, const float* right, const float* grad_cv, float* grad_left,
+                                       float* grad_right, int B, int C, int H, int W, int D, int groups, void* stream);
+SF_API int sf_soft_argmin_backward_f32(const float* cv, const float* grad_disp, float* grad_cv, int B, int D, int H,
+                                       int W, int match_similarity, void* stream);
+SF_API int sf_local_window_backward_f32(const float* cv, const float* disp, const float* lo, const float* up,
+                                        const float* grad_out, float* grad_cv, float* grad_disp, float* grad_lo,
+                                        float* grad_up, int B, int D, int H, int W, int mode, float radius,
+                                        int n_points, int consider_valid, int div_mode, void* stream);
+SF_API int sf_sample_volume_backward_f32(const float* cv, const float* cand, const float* grad_local, float* grad_cv,
+                                         float* grad_cand, int B, int D, int K, int H, int W, void* stream);
+SF_API int sf_disp_warp_backward_f32(const float* img, const float* disp, const float* grad_warped, float* grad_img,
+                                     float* grad_disp, int B, int C, int H, int W, int border, int div_mode,
+                                     void* stream);
+
+/* f3: backward of the f1 / f2 / a6-guidance kernels (what makes the DLC-GRU step trainable through the drop-ins).
+ * Any grad_* output may be NULL.  sf_upsample_convex_backward_f32 zero-fills grad_disp (atomics). */
+SF_API int sf_gru_reset_backward_f32(const float* b_pre, long long b_bstride, const float* prev_h, const float* grad_s,
+                                     float* grad_b_pre, float* grad_prev_h, float* grad_input, int B, int C, int Cx,
+                                     int H, int W, void* stream);
+SF_API int sf_gru_blend_backward_f32(const float* z_pre, long long z_bstride, const float* g_pre, const float* prev_h,
+                                     const float* grad_h, float* grad_z_pre, float* grad_g_pre, float* grad_prev_h,
+                                     int B, int C, int H, int W, int softsign, void* stream);
+SF_API int sf_guidance_backward_f32(const float* cv, const float* disp, const float* right, const float* grad_err,
+                                    const float* grad_unc, float* grad_cv, float* grad_disp, int B, int D, int C,
+                                    int H, int W, int div_mode, void* stream);
+SF_API int sf_upsample_convex_backward_f32(const float* disp, const float* mask, float mask_scale,
+                                           const float* grad_out, float* grad_disp, float* grad_mask, int N, int H,
+                                           int W, int factor, void* stream);
+
 /* f3: DCN backward  deform/src/cuda/modulated_deform_conv_cuda.cu:124-280 (DCNv1: deform_conv_cuda.cu, mask = NULL).
  * Every grad_* pointer may be NULL (that gradient is skipped); grad_input and grad_weight are zero-filled here and
  * accumulated with atomics (as the reference's col2im does), grad_offset / grad_mask / grad_bias are plain stores.

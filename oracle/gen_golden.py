@@ -220,9 +220,9 @@ def main():
     color = rng.randn(4, 6, 3).astype(np.float32)
     blobs = {}
     with tempfile.TemporaryDirectory() as td:
-        for name, img, sc in (("grey", grey, 1), ("color", color, 2.5), ("grey1", grey[:, :, None], 1)):
+        for name, pimg, sc in (("grey", grey, 1), ("color", color, 2.5), ("grey1", grey[:, :, None], 1)):
             fn = os.path.join(td, name + ".pfm")
-            fio.write_pfm(fn, img, sc)
+            fio.write_pfm(fn, pimg, sc)
             blobs["pfm_" + name] = np.frombuffer(open(fn, "rb").read(), dtype=np.uint8)
             back, bsc = fio._read_pfm(fn)
             blobs["read_" + name] = np.ascontiguousarray(back)
@@ -241,6 +241,34 @@ def main():
         blobs["read_kitti"] = fio.read_disp(kp)
         blobs["read_subset"] = fio.read_disp(os.path.join(td, "grey.pfm"), subset=True)
     save("file_io", grey=grey, color=color, **blobs)
+
+    # ---- f3 gradients: autograd through the UNMODIFIED reference modules on the inputs of the fixtures above ----
+    def grads(fn, *ts):
+        leaves = [t.clone().requires_grad_(True) for t in ts]
+        out = fn(*leaves)
+        out = out[0] if isinstance(out, tuple) else out
+        gen = torch.Generator().manual_seed(123)
+        go = torch.randn(out.shape, generator=gen)
+        return [go] + list(torch.autograd.grad(out, leaves, go, allow_unused=True))
+
+    gz = np.load(os.path.join(OUT, "corr_volume_small.npz"))
+    Lg, Rg, Dg = torch.from_numpy(gz["left"]), torch.from_numpy(gz["right"]), int(gz["D"])
+    blob = {}
+    for name, res in (
+            ("corr", grads(lambda l, r: R["CostVolume"](Dg, "correlation")(l, r), Lg, Rg)),
+            ("gwc", grads(lambda l, r: R["build_gwc_volume"](l, r, Dg, 4), Lg, Rg)),
+            ("argmin_sim", grads(lambda c: R["DisparityEstimation"](24, True)(c), cv)),
+            ("argmin_cost", grads(lambda c: R["DisparityEstimation"](24, False)(c), cv)),
+            ("win_valid1", grads(lambda c, d: flc.LocalCostVolume(2, 20)(c, d, True), cv, cur)),
+            ("win_valid0", grads(lambda c, d: flc.LocalCostVolume(2, 20)(c, d, False), cv, cur)),
+            ("sample", grads(lambda c, k: flc.build_cost_volume_from_volume(c, k), cv,
+                             torch.from_numpy(np.load(os.path.join(OUT, "sample_volume.npz"))["cand"]))),
+            ("warp_border", grads(lambda i, d: R["disp_warp"](i, d), img, dw)),
+            ("warp_zeros", grads(lambda i, d: R["disp_warp"](i, d, padding_mode="zeros"), img, dw))):
+        for k, t in enumerate(res):
+            if t is not None:
+                blob["%s_%d" % (name, k)] = t
+    save("gradients", **blob)
     print("golden vectors written to", os.path.normpath(OUT))
 
 

@@ -28,6 +28,15 @@ SIGNATURES = {
     "sf_corr1d_pyramid_f32": [_p, _p, _p] + [_c_int] * 7 + [_p],
     "sf_corr1d_lookup_f32": [_p, _p, _c_int, _c_int, _p, _p, _p, _p] + [_c_int] * 4 + [_p],
     "sf_dcn_forward_f32": [_p] * 6 + [_c_int] * 15 + [_p],
+    "sf_corr_volume_backward_f32": [_p] * 5 + [_c_int] * 6 + [_p],
+    "sf_soft_argmin_backward_f32": [_p] * 3 + [_c_int] * 5 + [_p],
+    "sf_local_window_backward_f32": [_p] * 9 + [_c_int] * 5 + [_c_float] + [_c_int] * 3 + [_p],
+    "sf_sample_volume_backward_f32": [_p] * 5 + [_c_int] * 5 + [_p],
+    "sf_disp_warp_backward_f32": [_p] * 5 + [_c_int] * 6 + [_p],
+    "sf_gru_reset_backward_f32": [_p, ctypes.c_longlong] + [_p] * 5 + [_c_int] * 5 + [_p],
+    "sf_gru_blend_backward_f32": [_p, ctypes.c_longlong] + [_p] * 6 + [_c_int] * 5 + [_p],
+    "sf_guidance_backward_f32": [_p] * 7 + [_c_int] * 6 + [_p],
+    "sf_upsample_convex_backward_f32": [_p, _p, _c_float, _p, _p, _p] + [_c_int] * 4 + [_p],
     "sf_dcn_backward_f32": [_p] * 10 + [_c_int] * 15 + [_p],
     "sf_dcn_workspace_bytes": [_c_int] * 5,
     "sf_dcn_forward_ws_f32": [_p] * 6 + [_c_int] * 15 + [_p, ctypes.c_size_t, _c_int, _p],

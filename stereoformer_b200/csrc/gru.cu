@@ -75,6 +75,43 @@ gru_blend_kernel(const float* __restrict__ z_pre, long long z_bstride, const flo
   }
 }
 
+// backward of the two kernels above (scalar; training only).  reset: gs [B,C+Cx,H,W] -> g_b_pre, g_prev_h, g_input
+__global__ void __launch_bounds__(256)
+gru_reset_bwd_kernel(const float* __restrict__ b_pre, long long b_bstride, const float* __restrict__ prev_h,
+                     const float* __restrict__ gs, float* __restrict__ g_b_pre, float* __restrict__ g_prev_h,
+                     float* __restrict__ g_input, long long CHW, long long XHW, long long n) {
+  const long long per = CHW + XHW;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long b = i / per, r = i - b * per;
+    const float g = gs[i];
+    if (r < CHW) {
+      const float sg = sigmoid_f(b_pre[b * b_bstride + r]);
+      const float h = prev_h ? prev_h[b * CHW + r] : 0.f;
+      if (g_b_pre) g_b_pre[b * CHW + r] = g * h * sg * (1.0f - sg);
+      if (g_prev_h) g_prev_h[b * CHW + r] = g * sg;
+    } else if (g_input) {
+      g_input[b * XHW + (r - CHW)] = g;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256)
+gru_blend_bwd_kernel(const float* __restrict__ z_pre, long long z_bstride, const float* __restrict__ g_pre,
+                     const float* __restrict__ prev_h, const float* __restrict__ go, float* __restrict__ g_z_pre,
+                     float* __restrict__ g_g_pre, float* __restrict__ g_prev_h, long long CHW, long long n, int softsign) {
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long b = i / CHW, r = i - b * CHW;
+    const float z = sigmoid_f(z_pre[b * z_bstride + r]);
+    const float x = g_pre[i], a = gate_act(x, softsign), h = prev_h ? prev_h[i] : 0.f, g = go[i];
+    const float da = softsign ? 1.0f / ((1.0f + fabsf(x)) * (1.0f + fabsf(x))) : 1.0f - a * a;
+    if (g_z_pre) g_z_pre[i] = g * (a - h) * z * (1.0f - z);
+    if (g_g_pre) g_g_pre[i] = g * z * da;
+    if (g_prev_h) g_prev_h[i] = g * (1.0f - z);
+  }
+}
+
 static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
 }  // namespace sf
@@ -111,6 +148,37 @@ extern "C" int sf_gru_blend_f32(const float* z_pre, long long z_bstride, const f
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   if (vec) gru_blend_kernel<4><<<grid, 256, 0, s>>>(z_pre, z_bstride, g_pre, prev_h, h_out, CHW, n, softsign);
   else gru_blend_kernel<1><<<grid, 256, 0, s>>>(z_pre, z_bstride, g_pre, prev_h, h_out, CHW, n, softsign);
+  SF_LAUNCH_CHECK();
+  return SF_OK;
+}
+
+extern "C" int sf_gru_reset_backward_f32(const float* b_pre, long long b_bstride, const float* prev_h,
+                                         const float* grad_s, float* grad_b_pre, float* grad_prev_h, float* grad_input,
+                                         int B, int C, int Cx, int H, int W, void* stream) {
+  using namespace sf;
+  SF_CHECK_ARG(b_pre && grad_s, "gru_reset_backward: null pointer");
+  SF_CHECK_ARG(B > 0 && C > 0 && Cx > 0 && H > 0 && W > 0, "gru_reset_backward: non-positive dimension");
+  const long long HW = 1LL * H * W, CHW = C * HW, XHW = Cx * HW, n = B * (CHW + XHW);
+  SF_CHECK_ARG(b_bstride >= CHW, "gru_reset_backward: batch stride %lld smaller than C*H*W", b_bstride);
+  const int grid = static_cast<int>(std::min<long long>(static_cast<long long>(sm_count()) * 8, (n + 255) / 256));
+  gru_reset_bwd_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(b_pre, b_bstride, prev_h, grad_s, grad_b_pre,
+                                                                          grad_prev_h, grad_input, CHW, XHW, n);
+  SF_LAUNCH_CHECK();
+  return SF_OK;
+}
+
+extern "C" int sf_gru_blend_backward_f32(const float* z_pre, long long z_bstride, const float* g_pre, const float* prev_h,
+                                         const float* grad_h, float* grad_z_pre, float* grad_g_pre, float* grad_prev_h,
+                                         int B, int C, int H, int W, int softsign, void* stream) {
+  using namespace sf;
+  SF_CHECK_ARG(z_pre && g_pre && grad_h, "gru_blend_backward: null pointer");
+  SF_CHECK_ARG(B > 0 && C > 0 && H > 0 && W > 0, "gru_blend_backward: non-positive dimension");
+  const long long CHW = 1LL * C * H * W, n = B * CHW;
+  SF_CHECK_ARG(z_bstride >= CHW, "gru_blend_backward: batch stride %lld smaller than C*H*W", z_bstride);
+  const int grid = static_cast<int>(std::min<long long>(static_cast<long long>(sm_count()) * 8, (n + 255) / 256));
+  gru_blend_bwd_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(z_pre, z_bstride, g_pre, prev_h, grad_h,
+                                                                          grad_z_pre, grad_g_pre, grad_prev_h, CHW, n,
+                                                                          softsign);
   SF_LAUNCH_CHECK();
   return SF_OK;
 }

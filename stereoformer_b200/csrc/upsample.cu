@@ -68,6 +68,56 @@ upsample_convex_kernel(const float* __restrict__ disp, const float* __restrict__
   }
 }
 
+// backward: out[F*y+i, F*x+j] = sum_k p_k * nb_k with p = softmax_k(scale * mask[k*F*F+i*F+j]), nb_k = F * disp(neighbour k)
+//   g_mask[k] = scale * g * p_k * (nb_k - out);   g_disp(neighbour k) += F * g * p_k   (atomics: 9 F^2 terms per pixel)
+template <int F>
+__global__ void __launch_bounds__(256)
+upsample_convex_bwd_kernel(const float* __restrict__ disp, const float* __restrict__ mask, const float* __restrict__ gout,
+                           float* __restrict__ gdisp, float* __restrict__ gmask, int N, int H, int W, float mask_scale) {
+  const size_t HW = static_cast<size_t>(H) * W, n = static_cast<size_t>(N) * HW * F;
+  for (size_t idx = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; idx < n;
+       idx += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int x = idx % W;
+    size_t r = idx / W;
+    const int i = r % F; r /= F;
+    const int y = r % H;
+    const size_t b = r / H;
+    const size_t pix = static_cast<size_t>(y) * W + x;
+    float nb[9], gnb[9];
+    bool in[9];
+#pragma unroll
+    for (int k = 0; k < 9; ++k) {
+      const int yy = y + k / 3 - 1, xx = x + k % 3 - 1;
+      in[k] = yy >= 0 && yy < H && xx >= 0 && xx < W;
+      nb[k] = in[k] ? (float)F * __ldg(disp + b * HW + yy * W + xx) : 0.f;
+      gnb[k] = 0.f;
+    }
+    const float* mp = mask + b * 9 * F * F * HW + static_cast<size_t>(i * F) * HW + pix;
+    float* gm = gmask ? gmask + b * 9 * F * F * HW + static_cast<size_t>(i * F) * HW + pix : nullptr;
+    const float* grow = gout + b * F * F * HW + (static_cast<size_t>(y) * F + i) * (W * F) + x * F;
+    for (int j = 0; j < F; ++j) {
+      float mv[9], m = -INFINITY;
+#pragma unroll
+      for (int k = 0; k < 9; ++k) { mv[k] = mask_scale * __ldg(mp + static_cast<size_t>(k * F * F + j) * HW); m = fmaxf(m, mv[k]); }
+      float s = 0.f, a = 0.f;
+#pragma unroll
+      for (int k = 0; k < 9; ++k) { mv[k] = __expf(mv[k] - m); s += mv[k]; a = fmaf(mv[k], nb[k], a); }
+      const float inv = 1.0f / s, o = a * inv, g = grow[j];
+#pragma unroll
+      for (int k = 0; k < 9; ++k) {
+        const float pk = mv[k] * inv;
+        if (gm) gm[static_cast<size_t>(k * F * F + j) * HW] = mask_scale * g * pk * (nb[k] - o);
+        gnb[k] = fmaf(g, pk, gnb[k]);
+      }
+    }
+    if (gdisp) {
+#pragma unroll
+      for (int k = 0; k < 9; ++k)
+        if (in[k]) atomicAdd(gdisp + b * HW + (y + k / 3 - 1) * W + (x + k % 3 - 1), (float)F * gnb[k]);
+    }
+  }
+}
+
 }  // namespace sf
 
 static int upsample_convex_impl(const float* disp, const float* mask, float mask_scale, float* out, int N, int H, int W,
@@ -94,4 +144,21 @@ extern "C" int sf_upsample_convex_f32(const float* disp, const float* mask, floa
 extern "C" int sf_upsample_convex_scaled_f32(const float* disp, const float* mask, float mask_scale, float* out, int N,
                                              int H, int W, int factor, void* stream) {
   return upsample_convex_impl(disp, mask, mask_scale, out, N, H, W, factor, stream);
+}
+
+extern "C" int sf_upsample_convex_backward_f32(const float* disp, const float* mask, float mask_scale,
+                                               const float* grad_out, float* grad_disp, float* grad_mask, int N, int H,
+                                               int W, int factor, void* stream) {
+  using namespace sf;
+  SF_CHECK_ARG(disp && mask && grad_out, "upsample_convex_backward: null pointer");
+  SF_CHECK_ARG(N > 0 && H > 0 && W > 0, "upsample_convex_backward: non-positive dimension");
+  SF_CHECK_ARG(factor == 8 || factor == 4, "upsample_convex_backward: factor must be 8 or 4, got %d", factor);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (grad_disp) SF_CUDA(cudaMemsetAsync(grad_disp, 0, sizeof(float) * static_cast<size_t>(N) * H * W, s));
+  size_t n = static_cast<size_t>(N) * H * W * factor;
+  int grid = static_cast<int>(min(static_cast<size_t>(sm_count()) * 8, (n + 255) / 256));
+  if (factor == 8) upsample_convex_bwd_kernel<8><<<grid, 256, 0, s>>>(disp, mask, grad_out, grad_disp, grad_mask, N, H, W, mask_scale);
+  else upsample_convex_bwd_kernel<4><<<grid, 256, 0, s>>>(disp, mask, grad_out, grad_disp, grad_mask, N, H, W, mask_scale);
+  SF_LAUNCH_CHECK();
+  return SF_OK;
 }

@@ -125,6 +125,105 @@ guidance_kernel(const float* __restrict__ cv, const float* __restrict__ disp, co
   }
 }
 
+// disp_warp backward = ATen grid_sampler_2d_backward (bilinear, align_corners=False) chained with the grid
+// arithmetic of disparity_warper.py:96-98: d ix / d disp = (W/2) * (-2/(W-1)), times 0 where border clipping is
+// active (clip_coordinates_set_grad: coordinates <= 0 or >= size-1).  The validity mask is a thresholded constant.
+__global__ void __launch_bounds__(256)
+disp_warp_bwd_kernel(const float* __restrict__ img, const float* __restrict__ disp, const float* __restrict__ gw,
+                     float* __restrict__ gimg, float* __restrict__ gdisp, int B, int C, int H, int W, int border,
+                     int recip) {
+  const size_t HW = static_cast<size_t>(H) * W, n = static_cast<size_t>(B) * HW;
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int x = i % W, y = (i / W) % H;
+    const size_t b = i / HW, r = i % HW;
+    const float d = disp[i];
+    const Bilin g = warp_setup((float)x, (float)y, d, H, W, border != 0, recip);
+    float mult = 1.f;
+    if (border) {
+      const float raw = sfm::warp_unnorm(g.gx, W);
+      if (raw <= 0.f || raw >= (float)(W - 1)) mult = 0.f;
+    }
+    const float wy_n = (float)(g.y0 + 1) - g.iy, wy_s = g.iy - (float)g.y0;   // (iy_s - iy), (iy - iy_n)
+    float gix = 0.f;
+    for (int c = 0; c < C; ++c) {
+      const size_t plane = (b * C + c) * HW;
+      const float go = gw[plane + r];
+      const float* r0 = img + plane + static_cast<size_t>(g.y0) * W + g.x0;
+      const float nw = (g.iny0 && g.inx0) ? __ldg(r0) : 0.f, ne = (g.iny0 && g.inx1) ? __ldg(r0 + 1) : 0.f;
+      const float sw = (g.iny1 && g.inx0) ? __ldg(r0 + W) : 0.f, se = (g.iny1 && g.inx1) ? __ldg(r0 + W + 1) : 0.f;
+      gix += go * ((ne - nw) * wy_n + (se - sw) * wy_s);
+      if (gimg) {
+        float* q0 = gimg + plane + static_cast<size_t>(g.y0) * W + g.x0;
+        if (g.iny0 && g.inx0) atomicAdd(q0, go * g.wnw);
+        if (g.iny0 && g.inx1) atomicAdd(q0 + 1, go * g.wne);
+        if (g.iny1 && g.inx0) atomicAdd(q0 + W, go * g.wsw);
+        if (g.iny1 && g.inx1) atomicAdd(q0 + W + 1, go * g.wse);
+      }
+    }
+    if (gdisp) gdisp[i] = -gix * mult * ((float)W / (float)(W - 1));
+  }
+}
+
+// guidance backward (BasicGuidanceNet prologue, update.py:68-86): with p = softmax(cv), u_d = p_d * d * (d - disp)^2,
+//   g_cv = p * (q - sum_d p_d q_d),  q_d = g_unc_d * d * (d - disp)^2          (soft-max backward)
+//   g_disp = -2 * sum_d g_unc_d * p_d * d * (d - disp)  +  warp term of error_map = warp(right, disp) - left
+// The images are network inputs: their gradients are not produced.
+__global__ void __launch_bounds__(256)
+guidance_bwd_kernel(const float* __restrict__ cv, const float* __restrict__ disp, const float* __restrict__ right,
+                    const float* __restrict__ gerr, const float* __restrict__ gunc, float* __restrict__ gcv,
+                    float* __restrict__ gdisp, int B, int D, int C, int H, int W, int recip) {
+  const size_t HW = static_cast<size_t>(H) * W, n = static_cast<size_t>(B) * HW;
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int x = i % W, y = (i / W) % H;
+    const size_t b = i / HW, r = i % HW;
+    const float d = disp[i];
+    float gd = 0.f;
+    if (gerr) {
+      const Bilin g = warp_setup((float)x, (float)y, d, H, W, true, recip);
+      const float raw = sfm::warp_unnorm(g.gx, W);
+      const float mult = (raw <= 0.f || raw >= (float)(W - 1)) ? 0.f : 1.f;
+      const float wy_n = (float)(g.y0 + 1) - g.iy, wy_s = g.iy - (float)g.y0;
+      float gix = 0.f;
+      for (int c = 0; c < C; ++c) {
+        const size_t plane = (b * C + c) * HW;
+        const float* r0 = right + plane + static_cast<size_t>(g.y0) * W + g.x0;
+        const float nw = (g.iny0 && g.inx0) ? __ldg(r0) : 0.f, ne = (g.iny0 && g.inx1) ? __ldg(r0 + 1) : 0.f;
+        const float sw = (g.iny1 && g.inx0) ? __ldg(r0 + W) : 0.f, se = (g.iny1 && g.inx1) ? __ldg(r0 + W + 1) : 0.f;
+        gix += gerr[plane + r] * ((ne - nw) * wy_n + (se - sw) * wy_s);
+      }
+      gd = -gix * mult * ((float)W / (float)(W - 1));
+    }
+    if (gunc) {
+      const float* src = cv + b * D * HW + r;
+      const float* gu = gunc + b * D * HW + r;
+      float m = -INFINITY;
+      for (int k = 0; k < D; ++k) m = fmaxf(m, __ldg(src + k * HW));
+      float s = 0.f;
+      for (int k = 0; k < D; ++k) s += __expf(__ldg(src + k * HW) - m);
+      const float inv = 1.0f / s;
+      float dot = 0.f;
+      for (int k = 0; k < D; ++k) {
+        const float pk = __expf(__ldg(src + k * HW) - m) * inv, e = (float)k - d, gk = __ldg(gu + k * HW);
+        dot = fmaf(pk, gk * (float)k * e * e, dot);
+        gd = fmaf(-2.0f * gk * pk, (float)k * e, gd);
+      }
+      if (gcv) {
+        float* dst = gcv + b * D * HW + r;
+        for (int k = 0; k < D; ++k) {
+          const float pk = __expf(__ldg(src + k * HW) - m) * inv, e = (float)k - d;
+          dst[k * HW] = pk * (__ldg(gu + k * HW) * (float)k * e * e - dot);
+        }
+      }
+    } else if (gcv) {
+      float* dst = gcv + b * D * HW + r;
+      for (int k = 0; k < D; ++k) dst[k * HW] = 0.f;
+    }
+    if (gdisp) gdisp[i] = gd;
+  }
+}
+
 }  // namespace sf
 
 extern "C" int sf_disp_warp_f32(const float* img, const float* disp, float* warped, float* mask, float* dbg_grid,
@@ -152,6 +251,37 @@ extern "C" int sf_guidance_f32(const float* cv, const float* disp, const float* 
   int grid = static_cast<int>(min(static_cast<size_t>(sm_count()) * 8, (n + 255) / 256));
   guidance_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(cv, disp, left, right, err, unc, B, D, C, H, W,
                                                                      div_mode == SF_DIV_RECIP, neg_flag);
+  SF_LAUNCH_CHECK();
+  return SF_OK;
+}
+
+extern "C" int sf_disp_warp_backward_f32(const float* img, const float* disp, const float* grad_warped, float* grad_img,
+                                         float* grad_disp, int B, int C, int H, int W, int border, int div_mode,
+                                         void* stream) {
+  using namespace sf;
+  SF_CHECK_ARG(img && disp && grad_warped, "disp_warp_backward: null pointer");
+  SF_CHECK_ARG(B > 0 && C > 0 && H > 1 && W > 1, "disp_warp_backward: needs H, W > 1");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (grad_img) SF_CUDA(cudaMemsetAsync(grad_img, 0, sizeof(float) * static_cast<size_t>(B) * C * H * W, s));
+  size_t n = static_cast<size_t>(B) * H * W;
+  int grid = static_cast<int>(min(static_cast<size_t>(sm_count()) * 8, (n + 255) / 256));
+  disp_warp_bwd_kernel<<<grid, 256, 0, s>>>(img, disp, grad_warped, grad_img, grad_disp, B, C, H, W, border,
+                                            div_mode == SF_DIV_RECIP);
+  SF_LAUNCH_CHECK();
+  return SF_OK;
+}
+
+extern "C" int sf_guidance_backward_f32(const float* cv, const float* disp, const float* right, const float* grad_err,
+                                        const float* grad_unc, float* grad_cv, float* grad_disp, int B, int D, int C,
+                                        int H, int W, int div_mode, void* stream) {
+  using namespace sf;
+  SF_CHECK_ARG(cv && disp && right, "guidance_backward: null pointer");
+  SF_CHECK_ARG(B > 0 && D > 0 && C > 0 && H > 1 && W > 1, "guidance_backward: needs H, W > 1");
+  size_t n = static_cast<size_t>(B) * H * W;
+  int grid = static_cast<int>(min(static_cast<size_t>(sm_count()) * 8, (n + 255) / 256));
+  guidance_bwd_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(cv, disp, right, grad_err, grad_unc, grad_cv,
+                                                                         grad_disp, B, D, C, H, W,
+                                                                         div_mode == SF_DIV_RECIP);
   SF_LAUNCH_CHECK();
   return SF_OK;
 }

@@ -2,12 +2,14 @@
 
 Same class / function names, constructor arguments, forward signatures and error behaviour as the
 reference's pure-PyTorch modules, so reference networks (LowCNN, RAFT_Stereo) use them as drop-ins
-(see install.py).  All of them are parameter-free, so checkpoints are unaffected.  Forward only:
-under autograd a backward call raises (backward passes are the 'next' row).
+(see install.py).  All of them are parameter-free, so checkpoints are unaffected.  Under autograd the
+correlation / group-wise volumes, soft-argmin, fixed and DLC windows, build_cost_volume_from_volume and disp_warp
+run their own backward kernels; the remaining operators are forward-only and raise on backward.
 """
 import torch
 import torch.nn as nn
 import torch.nn.functional as F
+from torch.autograd.function import once_differentiable
 
 from . import ops
 from ._lib import SF_DIV_RECIP, SF_DIV_TRUE, SF_WIN_ABSOLUTE, SF_WIN_FIXED, SF_WIN_OFFSETS, SF_WIN_VARIANCE
@@ -33,8 +35,36 @@ class _ForwardOnly(torch.autograd.Function):
                                   "SURVEY 8f-3)" % ctx.name)
 
 
-def _run(fn, name, *args):
+class _Differentiable(torch.autograd.Function):
+    """Runs ``fn(*args)`` on the CUDA kernels and ``bwd(args, grad, needs)`` (another kernel) for the backward."""
+
+    @staticmethod
+    def forward(ctx, fn, bwd, *args):
+        ctx.bwd = bwd
+        ctx.is_tensor = [torch.is_tensor(a) for a in args]
+        ctx.consts = [None if t else a for t, a in zip(ctx.is_tensor, args)]
+        ctx.save_for_backward(*[a for a in args if torch.is_tensor(a)])
+        with torch.no_grad():
+            out = fn(*args)
+        ctx.multi = getattr(bwd, "all_outputs", False)   # bwd wants the gradients of every output
+        if isinstance(out, tuple) and not ctx.multi:     # only the first output is differentiable (e.g. warp's mask)
+            ctx.mark_non_differentiable(*out[1:])
+        return out
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, grad, *more):
+        saved = iter(ctx.saved_tensors)
+        args = [next(saved) if t else c for t, c in zip(ctx.is_tensor, ctx.consts)]
+        g = (grad,) + more if ctx.multi else grad.contiguous()
+        grads = ctx.bwd(args, g, ctx.needs_input_grad[2:])
+        return (None, None) + tuple(grads)
+
+
+def _run(fn, name, *args, bwd=None):
     if torch.is_grad_enabled() and any(torch.is_tensor(a) and a.requires_grad for a in args):
+        if bwd is not None:
+            return _Differentiable.apply(fn, bwd, *args)
         return _ForwardOnly.apply(fn, name, *args)
     return fn(*args)
 
@@ -50,7 +80,8 @@ class CostVolume(nn.Module):
 
     def forward(self, left_feature, right_feature):
         if self.feature_similarity == 'correlation':
-            return _run(lambda l, r: ops.corr_volume(l, r, self.max_disp), "CostVolume", left_feature, right_feature)
+            return _run(lambda l, r: ops.corr_volume(l, r, self.max_disp), "CostVolume", left_feature, right_feature,
+                        bwd=lambda a, g, n: ops.corr_volume_backward(a[0], a[1], g, self.max_disp, 1, n))
         if self.feature_similarity == 'difference':
             return _run(lambda l, r: ops.shift_volume(l, r, self.max_disp, False), "CostVolume", left_feature,
                         right_feature)
@@ -62,12 +93,14 @@ class CostVolume(nn.Module):
 
 def build_gwc_volume(refimg_fea, targetimg_fea, maxdisp, num_groups):
     """models/CrossAttentionCostVolume/GWC_Cost_Volume.py:14-24 (dup models/utils/submodule.py:52-63)."""
-    return _run(lambda l, r: ops.gwc_volume(l, r, maxdisp, num_groups), "build_gwc_volume", refimg_fea, targetimg_fea)
+    return _run(lambda l, r: ops.gwc_volume(l, r, maxdisp, num_groups), "build_gwc_volume", refimg_fea, targetimg_fea,
+                bwd=lambda a, g, n: ops.corr_volume_backward(a[0], a[1], g, maxdisp, num_groups, n))
 
 
 def build_corr(img_left, img_right, max_disp=40):
     """models/utils/disp_residual.py:9-19 (same correlation volume)."""
-    return _run(lambda l, r: ops.corr_volume(l, r, max_disp), "build_corr", img_left, img_right)
+    return _run(lambda l, r: ops.corr_volume(l, r, max_disp), "build_corr", img_left, img_right,
+                bwd=lambda a, g, n: ops.corr_volume_backward(a[0], a[1], g, max_disp, 1, n))
 
 
 # ----------------------------------------------------------------------------- soft-argmin
@@ -81,7 +114,8 @@ class DisparityEstimation(nn.Module):
 
     def forward(self, cost_volume):
         assert cost_volume.dim() == 4
-        return _run(lambda cv: ops.soft_argmin(cv, self.match_similarity), "DisparityEstimation", cost_volume)
+        return _run(lambda cv: ops.soft_argmin(cv, self.match_similarity), "DisparityEstimation", cost_volume,
+                    bwd=lambda a, g, n: (ops.soft_argmin_backward(a[0], g, self.match_similarity),))
 
 
 class DisparityEstimationWithProb(DisparityEstimation):
@@ -96,7 +130,8 @@ class DisparityEstimationWithProb(DisparityEstimation):
 # ----------------------------------------------------------------------------- local windows
 def build_cost_volume_from_volume(old_volume, sampling_candidates):
     """fixed_local_cost_volume.py:61-80 (identical copies in variance_/pure_learning_/update*.py)."""
-    return _run(ops.sample_volume, "build_cost_volume_from_volume", old_volume, sampling_candidates)
+    return _run(ops.sample_volume, "build_cost_volume_from_volume", old_volume, sampling_candidates,
+                bwd=lambda a, g, n: ops.sample_volume_backward(a[0], a[1], g, n))
 
 
 class LocalCostVolume(nn.Module):
@@ -112,7 +147,10 @@ class LocalCostVolume(nn.Module):
         return _run(lambda cv, d: ops.local_window(cv, d, mode=SF_WIN_FIXED, radius=self.radius,
                                                    n_points=self.sample_points, consider_valid=consider_valid,
                                                    div_mode=self.div_mode),
-                    "LocalCostVolume", old_cost_volume, cur_disparity)
+                    "LocalCostVolume", old_cost_volume, cur_disparity,
+                    bwd=lambda a, g, n: ops.local_window_backward(
+                        a[0], a[1], None, None, g, SF_WIN_FIXED, self.radius, self.sample_points, consider_valid,
+                        self.div_mode, (n[0], n[1], False, False))[:2])
 
 
 class Variance_Based_Local_Cost_Volume(nn.Module):
@@ -137,24 +175,32 @@ def dlc_window(old_cost_volume, cur_disp, lower_offset, upper_offset, sample_poi
     cur_disp - lower_offset / cur_disp + upper_offset (absolute=True: the tensors are the bounds themselves,
     pure_learning_method.py:112)."""
     dm = DEFAULT_DIV_MODE if div_mode is None else div_mode
-    return _run(lambda cv, d, lo, up: ops.local_window(cv, d, lo, up,
-                                                       mode=SF_WIN_ABSOLUTE if absolute else SF_WIN_OFFSETS,
-                                                       n_points=sample_points, consider_valid=consider_valid,
-                                                       div_mode=dm),
-                "dlc_window", old_cost_volume, cur_disp, lower_offset, upper_offset)
+    mode = SF_WIN_ABSOLUTE if absolute else SF_WIN_OFFSETS
+    return _run(lambda cv, d, lo, up: ops.local_window(cv, d, lo, up, mode=mode, n_points=sample_points,
+                                                       consider_valid=consider_valid, div_mode=dm),
+                "dlc_window", old_cost_volume, cur_disp, lower_offset, upper_offset,
+                bwd=lambda a, g, n: ops.local_window_backward(a[0], a[1], a[2], a[3], g, mode, 0.0, sample_points,
+                                                              consider_valid, dm, n))
 
 
 def guidance_inputs(old_cost_volume, cur_disp, cur_left_image, cur_right_image, div_mode=None):
     """Fused front half of BasicGuidanceNet.forward (update.py:71-86) -> (error_map, uncertainty_volume)."""
     dm = DEFAULT_DIV_MODE if div_mode is None else div_mode
+
+    def bwd(a, g, n):                                    # g = (grad_error_map, grad_uncertainty_volume)
+        if n[2] or n[3]:
+            raise NotImplementedError("stereoformer_b200.guidance_inputs: no gradient w.r.t. the images (inputs)")
+        return ops.guidance_backward(a[0], a[1], a[3], g[0], g[1], dm, (n[0], n[1])) + (None, None)
+    bwd.all_outputs = True
     return _run(lambda cv, d, l, r: ops.guidance(cv, d, l, r, div_mode=dm), "guidance_inputs", old_cost_volume,
-                cur_disp, cur_left_image, cur_right_image)
+                cur_disp, cur_left_image, cur_right_image, bwd=bwd)
 
 
 # ----------------------------------------------------------------------------- warp
 def disp_warp(img, disp, padding_mode='border'):
     """utils/disparity_warper.py:83-106 -> (warped_img, valid_mask); asserts disp.min() >= 0."""
-    return _run(lambda i, d: ops.disp_warp(i, d, padding_mode, div_mode=DEFAULT_DIV_MODE), "disp_warp", img, disp)
+    return _run(lambda i, d: ops.disp_warp(i, d, padding_mode, div_mode=DEFAULT_DIV_MODE), "disp_warp", img, disp,
+                bwd=lambda a, g, n: ops.disp_warp_backward(a[0], a[1], g, padding_mode, DEFAULT_DIV_MODE, n))
 
 
 def LRwarp_error(imgL, disp, imgR):
@@ -208,4 +254,5 @@ class EpipolarCrossAttention(nn.Module):
 # ----------------------------------------------------------------------------- upsampling ("next" row)
 def upsample_convex8(disp, mask):
     """models/utils/upsample.py:22-38."""
-    return _run(lambda d, m: ops.upsample_convex(d, m, 8), "upsample_convex8", disp, mask)
+    return _run(lambda d, m: ops.upsample_convex(d, m, 8), "upsample_convex8", disp, mask,
+                bwd=lambda a, g, n: ops.upsample_convex_backward(a[0], a[1], g, 8, 1.0, n))

@@ -14,7 +14,9 @@ from ._lib import (SF_ALGO_AUTO, SF_ALGO_GENERIC, SF_ALGO_TC, SF_ALGO_TMA, SF_DI
                    SF_WIN_FIXED, SF_WIN_HEAD, SF_WIN_OFFSETS, SF_WIN_VARIANCE)
 
 __all__ = ["corr_volume", "gwc_volume", "shift_volume", "soft_argmin", "local_window", "sample_volume", "disp_warp",
-           "guidance", "corr1d_pyramid", "corr1d_lookup", "dcn_forward", "dcn_backward", "epipolar_attention", "upsample_convex",
+           "guidance", "corr1d_pyramid", "corr1d_lookup", "dcn_forward", "dcn_backward", "corr_volume_backward", "soft_argmin_backward",
+           "local_window_backward", "sample_volume_backward", "disp_warp_backward", "gru_reset_backward",
+           "gru_blend_backward", "guidance_backward", "upsample_convex_backward", "epipolar_attention", "upsample_convex",
            "gru_reset", "gru_blend"]
 
 
@@ -250,6 +252,134 @@ def dcn_forward(inp, weight, bias, offset, mask, stride, padding, dilation, grou
                   Cin, H, W, Cout, kh, kw, sh, sw, ph, pw, dh, dw, int(groups), int(deformable_groups), _ptr(ws),
                   ctypes.c_size_t(nws), int(algo), _stream())
     return out
+
+
+# ----------------------------------------------------------------------------- backward passes
+def corr_volume_backward(left, right, grad_cv, max_disp, groups=1, needs=(True, True)):
+    """Gradients of corr_volume / gwc_volume w.r.t. (left, right)."""
+    left, right = _chk(left, "left_feature", dim=4), _chk(right, "right_feature", dim=4)
+    grad_cv = _chk(grad_cv, "grad_cost_volume")
+    B, C, H, W = left.shape
+    if grad_cv.numel() != B * groups * max_disp * H * W:
+        raise ValueError("grad_cost_volume has %d elements, expected %d" % (grad_cv.numel(), B * groups * max_disp * H * W))
+    gl = torch.empty_like(left) if needs[0] else None
+    gr = torch.empty_like(right) if needs[1] else None
+    with torch.cuda.device(left.device):
+        _lib.call("sf_corr_volume_backward_f32", _ptr(left), _ptr(right), _ptr(grad_cv), _ptr(gl), _ptr(gr), B, C, H, W,
+                  int(max_disp), int(groups), _stream())
+    return gl, gr
+
+
+def soft_argmin_backward(cv, grad_disp, match_similarity=True):
+    cv, grad_disp = _chk(cv, "cost_volume", dim=4), _chk(grad_disp, "grad_disp")
+    B, D, H, W = cv.shape
+    if grad_disp.numel() != B * H * W:
+        raise ValueError("grad_disp must have B*H*W elements")
+    gcv = torch.empty_like(cv)
+    with torch.cuda.device(cv.device):
+        _lib.call("sf_soft_argmin_backward_f32", _ptr(cv), _ptr(grad_disp), _ptr(gcv), B, D, H, W,
+                  int(bool(match_similarity)), _stream())
+    return gcv
+
+
+def local_window_backward(cv, disp, lo, up, grad_out, mode=SF_WIN_FIXED, radius=0.0, n_points=10, consider_valid=False,
+                          div_mode=SF_DIV_TRUE, needs=(True, True, True, True)):
+    """Gradients of local_window w.r.t. (cv, disp, lo, up); modes FIXED / OFFSETS / ABSOLUTE / HEAD."""
+    cv, disp, grad_out = _chk(cv, "old_cost_volume", dim=4), _chk(disp, "cur_disparity"), _chk(grad_out, "grad_out")
+    B, D, H, W = cv.shape
+    if disp.numel() != B * H * W or grad_out.numel() != B * H * W:
+        raise ValueError("cur_disparity / grad_out must have B*H*W elements")
+    lo = _chk(lo, "lower bound") if lo is not None else None
+    up = _chk(up, "upper bound") if up is not None else None
+    gcv = torch.empty_like(cv) if needs[0] else None
+    gd = torch.empty_like(disp) if needs[1] else None
+    glo = torch.empty_like(lo) if (needs[2] and lo is not None) else None
+    gup = torch.empty_like(up) if (needs[3] and up is not None) else None
+    with torch.cuda.device(cv.device):
+        _lib.call("sf_local_window_backward_f32", _ptr(cv), _ptr(disp), _ptr(lo), _ptr(up), _ptr(grad_out), _ptr(gcv),
+                  _ptr(gd), _ptr(glo), _ptr(gup), B, D, H, W, int(mode), float(radius), int(n_points),
+                  int(bool(consider_valid)), int(div_mode), _stream())
+    return gcv, gd, glo, gup
+
+
+def sample_volume_backward(cv, cand, grad_local, needs=(True, True)):
+    cv, cand, grad_local = _chk(cv, "old_volume", dim=4), _chk(cand, "sampling_candidates", dim=4), _chk(grad_local, "grad", dim=4)
+    B, D, H, W = cv.shape
+    K = cand.shape[1]
+    gcv = torch.empty_like(cv) if needs[0] else None
+    gc = torch.empty_like(cand) if needs[1] else None
+    with torch.cuda.device(cv.device):
+        _lib.call("sf_sample_volume_backward_f32", _ptr(cv), _ptr(cand), _ptr(grad_local), _ptr(gcv), _ptr(gc), B, D, K,
+                  H, W, _stream())
+    return gcv, gc
+
+
+def disp_warp_backward(img, disp, grad_warped, padding_mode="border", div_mode=SF_DIV_TRUE, needs=(True, True)):
+    img, disp, grad_warped = _chk(img, "img", dim=4), _chk(disp, "disp"), _chk(grad_warped, "grad_warped", dim=4)
+    B, C, H, W = img.shape
+    gi = torch.empty_like(img) if needs[0] else None
+    gd = torch.empty_like(disp) if needs[1] else None
+    with torch.cuda.device(img.device):
+        _lib.call("sf_disp_warp_backward_f32", _ptr(img), _ptr(disp), _ptr(grad_warped), _ptr(gi), _ptr(gd), B, C, H, W,
+                  int(padding_mode == "border"), int(div_mode), _stream())
+    return gi, gd
+
+
+def gru_reset_backward(b_pre, prev_h, inp_shape, grad_s, needs=(True, True, True)):
+    """Gradients of gru_reset w.r.t. (b_pre, prev_h, input)."""
+    grad_s = _chk(grad_s, "grad_s", dim=4)
+    B, Cx, H, W = inp_shape
+    C = b_pre.shape[1]
+    b_pre, bs = _gate_view(b_pre, "b_pre", B, C, H, W)
+    prev_h = _chk(prev_h, "prev_h", dim=4) if prev_h is not None else None
+    dev = grad_s.device
+    gb = torch.empty((B, C, H, W), device=dev, dtype=torch.float32) if needs[0] else None
+    gh = torch.empty((B, C, H, W), device=dev, dtype=torch.float32) if (needs[1] and prev_h is not None) else None
+    gx = torch.empty((B, Cx, H, W), device=dev, dtype=torch.float32) if needs[2] else None
+    with torch.cuda.device(dev):
+        _lib.call("sf_gru_reset_backward_f32", _ptr(b_pre), ctypes.c_longlong(bs), _ptr(prev_h), _ptr(grad_s), _ptr(gb),
+                  _ptr(gh), _ptr(gx), B, C, Cx, H, W, _stream())
+    return gb, gh, gx
+
+
+def gru_blend_backward(z_pre, g_pre, prev_h, grad_h, softsign=False, needs=(True, True, True)):
+    """Gradients of gru_blend w.r.t. (z_pre, g_pre, prev_h)."""
+    g_pre, grad_h = _chk(g_pre, "g_pre", dim=4), _chk(grad_h, "grad_h", dim=4)
+    B, C, H, W = g_pre.shape
+    z_pre, zs = _gate_view(z_pre, "z_pre", B, C, H, W)
+    prev_h = _chk(prev_h, "prev_h", dim=4) if prev_h is not None else None
+    gz = torch.empty_like(g_pre) if needs[0] else None
+    gg = torch.empty_like(g_pre) if needs[1] else None
+    gh = torch.empty_like(g_pre) if (needs[2] and prev_h is not None) else None
+    with torch.cuda.device(g_pre.device):
+        _lib.call("sf_gru_blend_backward_f32", _ptr(z_pre), ctypes.c_longlong(zs), _ptr(g_pre), _ptr(prev_h), _ptr(grad_h),
+                  _ptr(gz), _ptr(gg), _ptr(gh), B, C, H, W, int(bool(softsign)), _stream())
+    return gz, gg, gh
+
+
+def guidance_backward(cv, disp, right, grad_err, grad_unc, div_mode=SF_DIV_TRUE, needs=(True, True)):
+    """Gradients of guidance w.r.t. (cv, disp); the images are inputs and get none."""
+    cv, disp, right = _chk(cv, "old_cost_volume", dim=4), _chk(disp, "cur_disp"), _chk(right, "right_image", dim=4)
+    grad_err = _chk(grad_err, "grad_err", dim=4) if grad_err is not None else None
+    grad_unc = _chk(grad_unc, "grad_unc", dim=4) if grad_unc is not None else None
+    B, D, H, W = cv.shape
+    gcv = torch.empty_like(cv) if needs[0] else None
+    gd = torch.empty_like(disp) if needs[1] else None
+    with torch.cuda.device(cv.device):
+        _lib.call("sf_guidance_backward_f32", _ptr(cv), _ptr(disp), _ptr(right), _ptr(grad_err), _ptr(grad_unc), _ptr(gcv),
+                  _ptr(gd), B, D, right.shape[1], H, W, int(div_mode), _stream())
+    return gcv, gd
+
+
+def upsample_convex_backward(disp, mask, grad_out, factor=8, mask_scale=1.0, needs=(True, True)):
+    disp, mask, grad_out = _chk(disp, "disp", dim=4), _chk(mask, "mask", dim=4), _chk(grad_out, "grad_out", dim=4)
+    N, _, H, W = disp.shape
+    gd = torch.empty_like(disp) if needs[0] else None
+    gm = torch.empty_like(mask) if needs[1] else None
+    with torch.cuda.device(disp.device):
+        _lib.call("sf_upsample_convex_backward_f32", _ptr(disp), _ptr(mask), float(mask_scale), _ptr(grad_out), _ptr(gd),
+                  _ptr(gm), N, H, W, int(factor), _stream())
+    return gd, gm
 
 
 def dcn_backward(inp, weight, offset, mask, grad_out, stride, padding, dilation, groups, deformable_groups,

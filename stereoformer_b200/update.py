@@ -50,9 +50,11 @@ class ConvGRU(nn.Module):
         # both gates read x1: one convolution with the two filter banks stacked
         zb = F.conv2d(x1, torch.cat((self.conv_z.weight, self.conv_b.weight), 0),
                       torch.cat((self.conv_z.bias, self.conv_b.bias), 0), 1, 1)
-        s = _m._run(lambda b, h, x: ops.gru_reset(b, h, x), "ConvGRU", zb[:, C:], prev_h, input)
+        s = _m._run(lambda b, h, x: ops.gru_reset(b, h, x), "ConvGRU", zb[:, C:], prev_h, input,
+                    bwd=lambda a, gs, n: ops.gru_reset_backward(a[0], a[1], a[2].shape, gs, n))
         g = self.conv_g(s)
-        return _m._run(lambda z, gg, h: ops.gru_blend(z, gg, h, self.softsign), "ConvGRU", zb[:, :C], g, prev_h)
+        return _m._run(lambda z, gg, h: ops.gru_blend(z, gg, h, self.softsign), "ConvGRU", zb[:, :C], g, prev_h,
+                       bwd=lambda a, gh, n: ops.gru_blend_backward(a[0], a[1], a[2], gh, self.softsign, n))
 
 
 class BasicGuidanceNet(nn.Module):
@@ -107,7 +109,10 @@ class OffsetPredictionHead(nn.Module):
 def _head_window(old_cost_volume, cur_disp, bounds_pre, sample_points, consider_valid):
     return _m._run(lambda cv, d, bp: ops.local_window(cv, d, lo=bp, mode=SF_WIN_HEAD, n_points=sample_points,
                                                       consider_valid=consider_valid, div_mode=_m.DEFAULT_DIV_MODE),
-                   "DisparityUpdateDLC", old_cost_volume, cur_disp, bounds_pre)
+                   "DisparityUpdateDLC", old_cost_volume, cur_disp, bounds_pre,
+                   bwd=lambda a, g, n: ops.local_window_backward(a[0], a[1], a[2], None, g, SF_WIN_HEAD, 0.0,
+                                                                 sample_points, consider_valid, _m.DEFAULT_DIV_MODE,
+                                                                 (n[0], n[1], n[2], False))[:3])
 
 
 class DisparityUpdateDLC(nn.Module):

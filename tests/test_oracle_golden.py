@@ -131,3 +131,38 @@ def test_dlc_update_step():
     assert eq(h1, g["hidden1"]) and eq(m1, g["mask1_head"]) and eq(d1, g["disp1"])
     d2, h2, m2 = O.dlc_update_step(sd, g["cv"], d1, g["left"], g["right"], h1, 20, False)
     assert eq(h2, g["hidden2"]) and eq(m2, g["mask2_head"]) and eq(d2, g["disp2"])
+
+
+# ------------------------------------------------------------------------------------------ f3 gradients
+def _grads(fn, g, name, *ts):
+    leaves = [t.clone().requires_grad_(True) for t in ts]
+    out = fn(*leaves)
+    out = out[0] if isinstance(out, tuple) else out
+    got = torch.autograd.grad(out, leaves, g[name + "_0"], allow_unused=True)
+    for k, a in enumerate(got):
+        ref = g.get("%s_%d" % (name, k + 1))
+        assert (a is None) == (ref is None), (name, k)
+        if a is not None:
+            assert torch.allclose(a, ref, rtol=1e-5, atol=1e-6), (name, k, (a - ref).abs().max())
+
+
+def test_oracle_autograd_matches_reference_autograd():
+    """The oracle restates the reference with the same differentiable torch ops; its autograd graph (straight-through
+    ceil/floor, clamps, constant masks, grid_sample) must give the gradients of the unmodified reference modules."""
+    g = load_golden("gradients")
+    cvs = load_golden("corr_volume_small")
+    L, R, D = cvs["left"], cvs["right"], cvs["D"]
+    _grads(lambda l, r: O.corr_volume(l, r, D), g, "corr", L, R)
+    _grads(lambda l, r: O.gwc_volume(l, r, D, 4), g, "gwc", L, R)
+    cv = load_golden("soft_argmin")["cv"]
+    _grads(lambda c: O.soft_argmin(c, True), g, "argmin_sim", cv)
+    _grads(lambda c: O.soft_argmin(c, False), g, "argmin_cost", cv)
+    for valid in (0, 1):
+        w = load_golden("local_window_valid%d" % valid)
+        _grads(lambda c, d: O.local_cost_volume(c, d, w["radius"], w["n_points"], bool(valid)), g,
+               "win_valid%d" % valid, w["cv"], w["cur"])
+    s = load_golden("sample_volume")
+    _grads(O.sample_volume, g, "sample", s["cv"], s["cand"])
+    wp = load_golden("disp_warp")
+    _grads(lambda i, d: O.disp_warp(i, d, "border"), g, "warp_border", wp["img"], wp["disp"])
+    _grads(lambda i, d: O.disp_warp(i, d, "zeros"), g, "warp_zeros", wp["img"], wp["disp"])
