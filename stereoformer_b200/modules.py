@@ -221,12 +221,13 @@ class CorrBlock1D:
         self.num_levels = num_levels
         self.radius = radius
         self.div_mode = DEFAULT_DIV_MODE
-        with torch.no_grad():
-            self.corr_pyramid = ops.corr1d_pyramid(fmap1, fmap2, num_levels, extra_level=True)
+        # forward-only: under autograd the pyramid carries a backward that raises instead of silently dropping gradients
+        self.corr_pyramid = list(_run(lambda a, b: tuple(ops.corr1d_pyramid(a, b, num_levels, extra_level=True)),
+                                      "CorrBlock1D", fmap1, fmap2))
 
     def __call__(self, coords):
-        return _run(lambda c: ops.corr1d_lookup(self.corr_pyramid, c, self.radius, self.num_levels, self.div_mode),
-                    "CorrBlock1D", coords)
+        return _run(lambda c, *pyr: ops.corr1d_lookup(list(pyr), c, self.radius, self.num_levels, self.div_mode),
+                    "CorrBlock1D", coords, *self.corr_pyramid)
 
     @staticmethod
     def corr(fmap1, fmap2):

@@ -295,8 +295,11 @@ def test_dropin_modules_chain():
     assert blk(coords).shape == (1, 36, 4, 64)
     x = dev(fl).requires_grad_(True)
     y = sf.CostVolume(24)(x, dev(fr))
-    with pytest.raises(NotImplementedError):            # autograd for a1/a3/a4/a7 is not built (DCN's is)
-        y.sum().backward()
+    y.sum().backward()                                  # backward kernels: tests/test_gpu_autograd.py
+    assert x.grad is not None and torch.isfinite(x.grad).all()
+    blk2 = sf.CorrBlock1D(dev(fl[:, :, :4]).requires_grad_(True), dev(fr[:, :, :4]), num_levels=4, radius=4)
+    with pytest.raises(NotImplementedError):            # CorrBlock1D stays forward-only
+        blk2(coords).sum().backward()
 
 
 @pytest.mark.parametrize("shape,band", [((1, 128, 6, 312), 48), ((2, 64, 3, 40), 8), ((1, 256, 2, 104), 64),

@@ -9,6 +9,8 @@ python bench.py --impl reference --steps 5 --warmup 1 > gpurun_out/bench_ref.jso
 python tools/time_cv.py > gpurun_out/time_cv.log 2>&1; cat gpurun_out/time_cv.log
 python tools/time_attn.py > gpurun_out/time_attn.log 2>&1; cat gpurun_out/time_attn.log
 python tools/time_corr1d.py > gpurun_out/time_corr1d.log 2>&1; cat gpurun_out/time_corr1d.log
+python tools/time_ops.py > gpurun_out/time_ops.log 2>&1; tail -20 gpurun_out/time_ops.log
+python tools/time_refiner.py 8 > gpurun_out/time_refiner.log 2>&1; tail -3 gpurun_out/time_refiner.log
 CMD="python bench.py --steps 20 --warmup 3 --no-cpu-baseline"
 $CMD > gpurun_out/plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_list.log 2>&1
