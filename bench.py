@@ -211,18 +211,49 @@ def main():
             if gather_mode.startswith("P2P"):
                 gather_mode = "NCCL all_gather_into_tensor per step (symmetric memory unavailable on a peer)"
 
-    def step(i):
+    def step(i, cv_out=None):
         fl, fr = sets[i % NSETS]
-        cv = ops.corr_volume(fl, fr, D)
+        cv = ops.corr_volume(fl, fr, D, out=cv_out)
+        return window(i, cv)
+
+    def window(i, cv):
         return ops.local_window(cv, None, mode=ops.SF_WIN_FIXED, radius=RADIUS, n_points=NPTS, consider_valid=True,
                                 div_mode=ops.SF_DIV_RECIP, out=dbuf[i % NSETS],
                                 peers=pg.peer_ptrs if pg is not None else None,
                                 peer_offset=pg.offset() if pg is not None else 0)
 
-    # One CUDA graph per rotating feature set (a step = 2 kernel launches of this library); replaying graphs keeps
-    # the host launch path (ctypes + tensor-map encoding, ~25 us per step) off the device timeline.
+    # CUDA graphs keep the host launch path (ctypes + tensor-map encoding, ~25 us per step) off the device timeline.
+    # A step = 2 kernel launches of this library.  `single[i]`: one step.  `pipe`: GSTEPS consecutive steps whose
+    # window kernel (5 us, plus the NVLink drain of its peer stores at N > 1) runs on a second captured stream
+    # underneath the NEXT step's cost-volume kernel -- the software pipelining any multi-batch caller gets from two
+    # streams; every step still does all of its work, the cost volumes are double-buffered.
+    GSTEPS = 4 * NSETS
+    NCV = 3                                                  # cost-volume buffers in flight
+    cvbuf = [torch.empty(B_PER_GPU, D, H8, W8, device=dev) for _ in range(NCV)]
     cap = torch.cuda.Stream(device=dev)
-    graphs = []
+    win = torch.cuda.Stream(device=dev)
+    single = []
+
+    def capture_pipe(nsteps):
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=cap):
+            done = [None] * NCV                              # window kernel that last read cvbuf[k]
+            for j in range(nsteps):
+                k = j % NCV
+                if done[k] is not None:
+                    cap.wait_event(done[k])                  # cvbuf[k] is free again
+                fl, fr = sets[j % NSETS]
+                ops.corr_volume(fl, fr, D, out=cvbuf[k])
+                ready = torch.cuda.Event()
+                ready.record(cap)
+                win.wait_event(ready)
+                with torch.cuda.stream(win):
+                    window(j, cvbuf[k])
+                    done[k] = torch.cuda.Event()
+                    done[k].record(win)
+            cap.wait_stream(win)
+        return g
+
     with torch.cuda.stream(cap):
         for i in range(NSETS):
             step(i)
@@ -231,28 +262,32 @@ def main():
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g, stream=cap):
                 step(i)
-            graphs.append(g)
+            single.append(g)
+        pipes = [(GSTEPS, capture_pipe(GSTEPS)), (NSETS, capture_pipe(NSETS))]
+    pipe = pipes[0][1]
     torch.cuda.synchronize()
 
-    def run_step(i):
-        graphs[i % NSETS].replay()
-        if world > 1 and pg is None:
-            dist.all_gather_into_tensor(gather_buf, dbuf[i % NSETS])
-        return dbuf[i % NSETS]
+    def run_steps(first, count):
+        """Steps first .. first+count-1: pipelined graphs while GSTEPS-aligned blocks remain, single steps otherwise."""
+        i, end = first, first + count
+        while i < end:
+            blk = [(n, g) for n, g in pipes if end - i >= n] if (i % NSETS == 0 and (pg is not None or world == 1)) else []
+            if blk:
+                blk[0][1].replay()
+                i += blk[0][0]
+            else:
+                single[i % NSETS].replay()
+                if world > 1 and pg is None:
+                    dist.all_gather_into_tensor(gather_buf, dbuf[i % NSETS])
+                i += 1
 
-    def flush_gather(i):
-        pass
-
-    for i in range(args.warmup):
-        run_step(i)
+    run_steps(0, max(args.warmup, GSTEPS))
     barrier()
     sampler = ClockSampler(local_rank)
     sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    for i in range(args.steps):
-        run_step(i)
-    flush_gather(args.steps - 1)
+    run_steps(0, args.steps)
     e1.record()
     barrier()
     ms = e0.elapsed_time(e1)
@@ -323,7 +358,9 @@ def main():
     cpu_base = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         fl, fr = host[0]
-        got = run_step(0).cpu()
+        pipe.replay()                                   # the pipelined path that was timed; dbuf[0] = feature set 0
+        torch.cuda.synchronize()
+        got = dbuf[0].cpu()
         want = cpu_chain(fl[:2], fr[:2])
         err = (got[:2] - want).abs()
         assert err.median() < 1e-3, "bench parity check failed: median |disp err| %g" % err.median()
@@ -337,7 +374,7 @@ def main():
                 "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": {"workload": WORKLOAD, "pairs_per_gpu_per_step": B_PER_GPU, "parallelism": "pairs sharded "
                            "across %d rank(s); disparity gather: %s" % (world, gather_mode),
-                           "l2": "each step reads 134 MB of features (> 126 MB L2) from one of 3 rotating sets", "launch": "one CUDA graph per step (2 kernels)"},
+                           "l2": "each step reads 134 MB of features (> 126 MB L2) from one of 3 rotating sets", "launch": "CUDA graphs of %d steps (2 kernels per step); the window kernel of step i overlaps the cost volume of step i+1 on a second captured stream" % GSTEPS},
                 "roofline": {"kernel": "corr_volume_tc_kernel (tcgen05, bf16 hi/mid split)", "bound": "hbm", "achieved": achieved, "peak": peak,
                              "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                              "alg_bytes_per_launch": B_PER_GPU * ALG_BYTES_CV, "us_per_launch": k_ms * 1e3},

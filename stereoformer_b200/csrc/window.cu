@@ -9,6 +9,7 @@
 // Candidates / indices / interpolation weights follow pixel_math.h and are bit-identical to the reference;
 // the soft-max over the N+1 samples is a max-then-exponentials soft-max in fp32 (samples kept in registers).
 // Algorithmic bytes per pixel: (D + 2) * 4 (+8 with per-pixel bounds).
+#include <cstdlib>
 #include "common.cuh"
 #include "pixel_math.h"
 #include "../../include/stereoformer_b200.h"
@@ -59,8 +60,8 @@ constexpr int WIN_MAXN = 32;   // samples kept in registers between the two soft
 
 // NSAMP: number of window samples (n_points + 1) when it is one of the shipped values (21: LowCNN, 11: module
 // defaults), so the sample loop unrolls exactly; 0 = any count (predicated up to WIN_MAXN, recomputed beyond).
-template <bool DEBUG, int NSAMP>
-__global__ void __launch_bounds__(WIN_TPB)
+template <bool DEBUG, int NSAMP, int TPB>
+__global__ void __launch_bounds__(TPB)
 local_window_kernel(const __grid_constant__ CUtensorMap mapCV, const WindowParams p) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   float* tile = reinterpret_cast<float*>(smem_raw);           // [D][128]
@@ -68,27 +69,27 @@ local_window_kernel(const __grid_constant__ CUtensorMap mapCV, const WindowParam
 
   const int seg = blockIdx.x % p.nseg, t = blockIdx.x / p.nseg;
   const int y = t % p.H, b = t / p.H;
-  const int x0 = seg * WIN_TPB, x = x0 + threadIdx.x;
+  const int x0 = seg * TPB, x = x0 + threadIdx.x;
   const size_t HW = static_cast<size_t>(p.H) * p.W;
 
   if (p.use_tma) {
     if (threadIdx.x == 0) {
       mbar_init(&bar, 1);
       fence_mbar_init();
-      mbar_expect_tx(&bar, p.D * WIN_TPB * 4);
+      mbar_expect_tx(&bar, p.D * TPB * 4);
       tma_load_3d(tile, &mapCV, &bar, x0, y, b * p.D);
     }
     __syncthreads();
     mbar_wait(&bar, 0);
   } else {
     const float* src = p.cv + (static_cast<size_t>(b) * p.D * p.H + y) * p.W;
-    for (int d = 0; d < p.D; ++d) tile[d * WIN_TPB + threadIdx.x] = (x < p.W) ? src[d * HW + x] : 0.f;
+    for (int d = 0; d < p.D; ++d) tile[d * TPB + threadIdx.x] = (x < p.W) ? src[d * HW + x] : 0.f;
     __syncthreads();
   }
   if (x >= p.W) return;
 
   const float* col = tile + threadIdx.x;
-  auto cvat = [&](int d) { return col[d * WIN_TPB]; };
+  auto cvat = [&](int d) { return col[d * TPB]; };
   const size_t pix = (static_cast<size_t>(b) * p.H + y) * p.W + x;
   const int D = p.D, N = p.n_points;
 
@@ -278,23 +279,32 @@ static int local_window_impl(const float* cv, const float* disp, const float* lo
   p.peer_off = peer_offset;
   for (int r = 0; r < SF_MAX_PEERS; ++r) p.peers[r] = r < n_peers ? h_peers[r] : nullptr;
   for (int r = 0; r < n_peers; ++r) SF_CHECK_ARG(p.peers[r] != nullptr, "local_window: null peer pointer %d", r);
-  p.nseg = ceil_div(W, WIN_TPB);
+  // CTA width: 128 pixels, or 32 when the row is short enough that single-warp CTAs waste fewer lanes; single-warp CTAs
+  // (3 KB of shared memory at D = 24) also fit next to a resident persistent kernel, so a caller that pipelines the
+  // window under the next batch's cost volume (bench.py) gets real overlap
+  static const int env_tpb = []() { const char* e = getenv("SF_WIN_TPB"); return e ? atoi(e) : 0; }();
+  const bool debug = dbg_cand || dbg_idx_floor || dbg_idx_ceil || dbg_local;
+  const int tpb = (env_tpb == 32 || env_tpb == 128) ? env_tpb : ((!debug && W <= 256) ? 32 : 128);
+  p.nseg = ceil_div(W, tpb);
   p.use_tma = (W % 4 == 0) && D <= 256 && (reinterpret_cast<uintptr_t>(cv) & 15) == 0;
   CUtensorMap map;
   memset(&map, 0, sizeof(map));
   if (p.use_tma) {
-    int rc = make_tmap_3d_f32(&map, cv, W, H, static_cast<uint64_t>(B) * D, WIN_TPB, 1, D);
+    int rc = make_tmap_3d_f32(&map, cv, W, H, static_cast<uint64_t>(B) * D, tpb, 1, D);
     if (rc) return rc;
   }
-  const size_t smem = static_cast<size_t>(D) * WIN_TPB * 4;
-  const bool debug = dbg_cand || dbg_idx_floor || dbg_idx_ceil || dbg_local;
-  auto kern = debug ? local_window_kernel<true, 0>
-                    : (n_points == 20 ? local_window_kernel<false, 21>
-                                      : (n_points == 10 ? local_window_kernel<false, 11> : local_window_kernel<false, 0>));
+  const size_t smem = static_cast<size_t>(D) * tpb * 4;
+  using KernT = void (*)(const CUtensorMap, const WindowParams);
+  KernT kern;
+  if (debug) kern = local_window_kernel<true, 0, 128>;
+  else if (tpb == 128) kern = n_points == 20 ? local_window_kernel<false, 21, 128>
+                                             : (n_points == 10 ? local_window_kernel<false, 11, 128> : local_window_kernel<false, 0, 128>);
+  else kern = n_points == 20 ? local_window_kernel<false, 21, 32>
+                             : (n_points == 10 ? local_window_kernel<false, 11, 32> : local_window_kernel<false, 0, 32>);
   SF_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
   long long grid = 1LL * B * H * p.nseg;
   SF_CHECK_ARG(grid < (1LL << 31), "local_window: grid too large");
-  kern<<<static_cast<int>(grid), WIN_TPB, smem, static_cast<cudaStream_t>(stream)>>>(map, p);
+  kern<<<static_cast<int>(grid), tpb, smem, static_cast<cudaStream_t>(stream)>>>(map, p);
   SF_LAUNCH_CHECK();
   return SF_OK;
 }

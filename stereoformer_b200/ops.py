@@ -40,14 +40,18 @@ def _stream():
     return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
-def corr_volume(left, right, max_disp, groups=1, algo=SF_ALGO_AUTO):
-    """CostVolume('correlation') / build_gwc_volume.  Returns [B,D,H,W] (groups=1) or [B,G,D,H,W]."""
+def corr_volume(left, right, max_disp, groups=1, algo=SF_ALGO_AUTO, out=None):
+    """CostVolume('correlation') / build_gwc_volume.  Returns [B,D,H,W] (groups=1) or [B,G,D,H,W]
+    (written into ``out`` when given)."""
     left, right = _chk(left, "left_feature", dim=4), _chk(right, "right_feature", dim=4)
     if left.shape != right.shape:
         raise ValueError("feature shapes differ: %s vs %s" % (tuple(left.shape), tuple(right.shape)))
     B, C, H, W = left.shape
     shape = (B, max_disp, H, W) if groups == 1 else (B, groups, max_disp, H, W)
-    out = torch.empty(shape, device=left.device, dtype=torch.float32)
+    if out is None:
+        out = torch.empty(shape, device=left.device, dtype=torch.float32)
+    elif tuple(out.shape) != shape or out.dtype != torch.float32 or not out.is_contiguous() or out.device != left.device:
+        raise ValueError("out must be a contiguous fp32 CUDA tensor of shape %s" % (shape,))
     with torch.cuda.device(left.device):
         _lib.call("sf_corr_volume_f32", _ptr(left), _ptr(right), _ptr(out), B, C, H, W, int(max_disp), int(groups),
                   int(algo), _stream())
