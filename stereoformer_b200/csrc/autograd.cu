@@ -52,6 +52,82 @@ corr_volume_bwd_kernel(const float* __restrict__ L, const float* __restrict__ R,
   }
 }
 
+// Register-tiled form (W % 4 == 0, Cg % 4 == 0): a thread owns 4 consecutive x of 4 channels.  gS[d][x] = G[d][x] and
+// the skewed copy gK[d][x] = G[d][x+d] are read as aligned float4 and reused by the 4 channels; the R / L rows of a
+// 32-channel chunk are staged in shared memory 4-way interleaved (Rt[c][x % 4][x / 4]) so that the sliding 4-wide
+// register windows take their ONE new element per disparity with a conflict-free scalar load (consecutive lanes own
+// consecutive x / 4).  L1 wavefronts per FMA drop 4x against the one-output-per-thread form.
+constexpr int CB_CH = 32;
+__global__ void __launch_bounds__(256)
+corr_volume_bwd4_kernel(const float* __restrict__ L, const float* __restrict__ R, const float* __restrict__ G,
+                        float* __restrict__ gL, float* __restrict__ gR, int C, int H, int W, int D, int groups) {
+  extern __shared__ __align__(16) float gS[];                         // [D][W], gK [D][W], Rt [CH][4][W4], Lt [CH][4][W4]
+  const int W4 = W >> 2;
+  float* gK = gS + D * W;
+  float* Rt = gK + D * W;
+  float* Lt = Rt + CB_CH * W;
+  const int y = blockIdx.x, b = blockIdx.y, g = blockIdx.z;
+  const int Cg = C / groups;
+  const size_t HW = static_cast<size_t>(H) * W;
+  const float* Grow = G + ((static_cast<size_t>(b) * groups + g) * D * H + y) * W;
+  for (int d = threadIdx.x >> 5; d < D; d += 8)
+    for (int x = threadIdx.x & 31; x < W; x += 32) {
+      gS[d * W + x] = __ldg(Grow + static_cast<size_t>(d) * HW + x);
+      gK[d * W + x] = (x + d < W) ? __ldg(Grow + static_cast<size_t>(d) * HW + x + d) : 0.f;
+    }
+  const float inv = 1.0f / (float)Cg;
+  for (int cc = 0; cc < Cg; cc += CB_CH) {
+    const int nch = min(CB_CH, Cg - cc);
+    __syncthreads();
+    for (int c = threadIdx.x >> 5; c < nch; c += 8) {                 // one warp per channel row: no divisions
+      const size_t src = ((static_cast<size_t>(b) * C + g * Cg + cc + c) * H + y) * W;
+      for (int x = threadIdx.x & 31; x < W; x += 32) {
+        Rt[(c * 4 + (x & 3)) * W4 + (x >> 2)] = __ldg(R + src + x);
+        Lt[(c * 4 + (x & 3)) * W4 + (x >> 2)] = __ldg(L + src + x);
+      }
+    }
+    __syncthreads();
+    // items: (channel quad cq, x quad xq); a warp takes one channel quad and sweeps xq in steps of 32
+    for (int cq = threadIdx.x >> 5; cq < (nch >> 2); cq += 8)
+    for (int xq = threadIdx.x & 31; xq < W4; xq += 32) {
+      const int c0 = cq * 4, x0 = xq * 4;
+      float rw[4][4], lw[4][4], al[4][4], ar[4][4];
+#pragma unroll
+      for (int c = 0; c < 4; ++c)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          rw[c][i] = Rt[((c0 + c) * 4 + i) * W4 + xq];
+          lw[c][i] = Lt[((c0 + c) * 4 + i) * W4 + xq];
+          al[c][i] = 0.f; ar[c][i] = 0.f;
+        }
+#pragma unroll 4
+      for (int d = 0; d < D; ++d) {
+        const float4 ga = *reinterpret_cast<const float4*>(gS + d * W + x0);
+        const float4 gb = *reinterpret_cast<const float4*>(gK + d * W + x0);
+        const int xr = x0 - d - 1, xl = x0 + d + 4;
+        const int ro = (xr & 3) * W4 + (xr >> 2), lo = (xl & 3) * W4 + (xl >> 2);
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          al[c][0] = fmaf(ga.x, rw[c][0], al[c][0]); al[c][1] = fmaf(ga.y, rw[c][1], al[c][1]);
+          al[c][2] = fmaf(ga.z, rw[c][2], al[c][2]); al[c][3] = fmaf(ga.w, rw[c][3], al[c][3]);
+          ar[c][0] = fmaf(gb.x, lw[c][0], ar[c][0]); ar[c][1] = fmaf(gb.y, lw[c][1], ar[c][1]);
+          ar[c][2] = fmaf(gb.z, lw[c][2], ar[c][2]); ar[c][3] = fmaf(gb.w, lw[c][3], ar[c][3]);
+          rw[c][3] = rw[c][2]; rw[c][2] = rw[c][1]; rw[c][1] = rw[c][0];
+          rw[c][0] = xr >= 0 ? Rt[(c0 + c) * W + ro] : 0.f;
+          lw[c][0] = lw[c][1]; lw[c][1] = lw[c][2]; lw[c][2] = lw[c][3];
+          lw[c][3] = xl < W ? Lt[(c0 + c) * W + lo] : 0.f;
+        }
+      }
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        const size_t row = ((static_cast<size_t>(b) * C + g * Cg + cc + c0 + c) * H + y) * W + x0;
+        if (gL) *reinterpret_cast<float4*>(gL + row) = make_float4(al[c][0] * inv, al[c][1] * inv, al[c][2] * inv, al[c][3] * inv);
+        if (gR) *reinterpret_cast<float4*>(gR + row) = make_float4(ar[c][0] * inv, ar[c][1] * inv, ar[c][2] * inv, ar[c][3] * inv);
+      }
+    }
+  }
+}
+
 // ------------------------------------------------------------------------------------------------ a3
 __global__ void __launch_bounds__(256)
 soft_argmin_bwd_kernel(const float* __restrict__ cv, const float* __restrict__ gdisp, float* __restrict__ gcv, int B,
@@ -215,8 +291,18 @@ extern "C" int sf_corr_volume_backward_f32(const float* left, const float* right
   if (!grad_left && !grad_right) return SF_OK;
   const size_t smem = static_cast<size_t>(D) * W * sizeof(float);
   const int use_smem = smem <= 160 * 1024;
-  if (use_smem) SF_CUDA(cudaFuncSetAttribute(corr_volume_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
   dim3 grid(H, B, groups);
+  const bool al16 = ((reinterpret_cast<uintptr_t>(left) | reinterpret_cast<uintptr_t>(right) |
+                      reinterpret_cast<uintptr_t>(grad_left) | reinterpret_cast<uintptr_t>(grad_right)) & 15) == 0;
+  const size_t smem4 = 2 * smem + 2 * static_cast<size_t>(CB_CH) * W * sizeof(float);
+  if (W % 4 == 0 && (C / groups) % 4 == 0 && al16 && smem4 <= 100 * 1024) {
+    SF_CUDA(cudaFuncSetAttribute(corr_volume_bwd4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem4)));
+    corr_volume_bwd4_kernel<<<grid, 256, smem4, static_cast<cudaStream_t>(stream)>>>(left, right, grad_cv, grad_left,
+                                                                                       grad_right, C, H, W, D, groups);
+    SF_LAUNCH_CHECK();
+    return SF_OK;
+  }
+  if (use_smem) SF_CUDA(cudaFuncSetAttribute(corr_volume_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
   corr_volume_bwd_kernel<<<grid, 256, use_smem ? smem : 0, static_cast<cudaStream_t>(stream)>>>(
       left, right, grad_cv, grad_left, grad_right, C, H, W, D, groups, use_smem);
   SF_LAUNCH_CHECK();

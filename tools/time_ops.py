@@ -37,3 +37,26 @@ timeit("local_window variance", lambda: ops.local_window(cv, disp, mode=ops.SF_W
 timeit("soft_argmin", lambda: ops.soft_argmin(cv), (D + 1) * px * 4)
 timeit("disp_warp", lambda: ops.disp_warp(img, disp, check=False), (3 * 3 + 1) * px * 4)
 timeit("upsample_convex8", lambda: ops.upsample_convex(disp, mask, 8), (576 + 1 + 64) * px * 4)
+
+# ---- f2 / f3 kernels at the same shape (C2: B=8, 68x120, D=24, features 256 ch, hidden 64)
+C = 64
+zb = torch.randn(B, 2 * C, H, W, device="cuda")
+gp, h0, xin = (torch.randn(B, C, H, W, device="cuda") for _ in range(3))
+timeit("gru_reset", lambda: ops.gru_reset(zb[:, C:], h0, xin), 5 * C * px * 4)
+timeit("gru_blend", lambda: ops.gru_blend(zb[:, :C], gp, h0), 4 * C * px * 4)
+pre = torch.randn(B, 2, H, W, device="cuda") * 3
+timeit("local_window head-fused (DLC)", lambda: ops.local_window(cv, disp, lo=pre, mode=ops.SF_WIN_HEAD, n_points=20,
+                                                                  consider_valid=True), (D + 4) * px * 4)
+left = torch.randn(B, 3, H, W, device="cuda")
+timeit("guidance", lambda: ops.guidance(cv, disp, left, img), (2 * D + 10) * px * 4)
+fl, fr = torch.randn(B, 256, H, W, device="cuda"), torch.randn(B, 256, H, W, device="cuda")
+gcv, gd = torch.randn(B, D, H, W, device="cuda"), torch.randn(B, 1, H, W, device="cuda")
+timeit("corr_volume backward", lambda: ops.corr_volume_backward(fl, fr, gcv, D), (4 * 256 + D) * px * 4, nl=3, reps=5)
+timeit("soft_argmin backward", lambda: ops.soft_argmin_backward(cv, gd), (2 * D + 1) * px * 4)
+timeit("local_window backward (fixed)", lambda: ops.local_window_backward(cv, disp, None, None, gd, ops.SF_WIN_FIXED, 2.0,
+                                                                           20, True), (2 * D + 3) * px * 4)
+timeit("local_window backward (head)", lambda: ops.local_window_backward(cv, disp, pre, None, gd, ops.SF_WIN_HEAD, 0.0, 20,
+                                                                          True), (2 * D + 7) * px * 4)
+timeit("disp_warp backward", lambda: ops.disp_warp_backward(img, disp, img), (3 * 3 * 2 + 2) * px * 4)
+gfull = torch.randn(B, 1, 8 * H, 8 * W, device="cuda")
+timeit("upsample_convex8 backward", lambda: ops.upsample_convex_backward(disp, mask, gfull, 8), (2 * 576 + 2 + 64) * px * 4)
