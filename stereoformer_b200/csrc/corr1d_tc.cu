@@ -278,13 +278,11 @@ corr1d_pyramid_tc_kernel(const __grid_constant__ Corr1dMaps maps, const Corr1dTc
         tmem_ld32(trow + cb * 32, raw);
         tmem_ld_wait();
         float v[32];
-        if (p.pow2) {
+        // / sqrt(C) as a multiply by the reciprocal: bit-identical when sqrt(C) is a power of two (C = 256), within
+        // 1 ulp otherwise (far below the 2^-16 of the bf16 split); an IEEE division here is 240 slow-path divides per
+        // thread per tile on single-warp-per-scheduler epilogue warps
 #pragma unroll
-          for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(raw[i]) * p.inv_sqrt_c;
-        } else {
-#pragma unroll
-          for (int i = 0; i < 32; ++i) v[i] = __fdiv_rn(__uint_as_float(raw[i]), p.sqrt_c);
-        }
+        for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(raw[i]) * p.inv_sqrt_c;
         // staging set of this block; its previous TMA stores (two blocks ago) must have finished reading it
         unsigned char* S = sEpi + (blk & 1) * CT_EPI_BYTES;
         if (leader) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
