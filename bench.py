@@ -333,6 +333,15 @@ def main():
     e1.record()
     torch.cuda.synchronize()
     k_ms = e0.elapsed_time(e1) / (nk * NSETS)
+    # the same step without any overlap (one serial 2-kernel graph per step): the denominator for the kernel's share of
+    # the step, comparable with an ncu launch list (which serialises kernels)
+    ns = 3 * NSETS
+    e0.record()
+    for i in range(ns):
+        single[i % NSETS].replay()
+    e1.record()
+    torch.cuda.synchronize()
+    serial_ms = e0.elapsed_time(e1) / ns
     peak, peak_src = peaks()
     achieved = B_PER_GPU * ALG_BYTES_CV / (k_ms * 1e-3) / 1e9
     traffic = traffic_from_profile()
@@ -389,7 +398,8 @@ def main():
                            "l2": "each step reads 134 MB of features (> 126 MB L2) from one of 3 rotating sets", "launch": "CUDA graphs of %d steps (2 kernels per step); consecutive steps overlap on captured streams (window kernel of step i and the tail of its cost volume under the cost volume of step i+1)" % GSTEPS},
                 "roofline": {"kernel": "corr_volume_tc_kernel (tcgen05, bf16 hi/mid split)", "bound": "hbm", "achieved": achieved, "peak": peak,
                              "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
-                             "alg_bytes_per_launch": B_PER_GPU * ALG_BYTES_CV, "us_per_launch": k_ms * 1e3},
+                             "alg_bytes_per_launch": B_PER_GPU * ALG_BYTES_CV, "us_per_launch": k_ms * 1e3,
+                             "serial_step_us": serial_ms * 1e3, "share_of_serial_step": k_ms / serial_ms},
                 "cpu_baseline": cpu_base,
                 "e2e": {"value": e2e_v, "unit": "pairs/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                         "steps": ne},
