@@ -273,15 +273,22 @@ epipolar_attn_tc_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
         const uint32_t mh = hi >= 31 ? 0xffffffffu : (0xffffffffu >> (31 - hi));
         return ml & mh;
       };
+      // this thread's (at most two) live chunks are read from TMEM ONCE, both loads in flight together, and kept in
+      // registers for both soft-max passes; S is released to the next Q^T K right away
+      const int cba = wlo + half, cbb = cba + 2;
+      const bool hasA = cba <= whi && !(p.dbg & 1), hasB = cbb <= whi && !(p.dbg & 1);
+      uint32_t va[32], vb[32];
+      if (hasA) tmem_ld32(srow + cba * 32, va);
+      if (hasB) tmem_ld32(srow + cbb * 32, vb);
+      const uint32_t vma = hasA ? chunk_mask(cba) : 0u, vmb = hasB ? chunk_mask(cbb) : 0u;
+      tmem_ld_wait();
+      tc_fence_before();
+      mbar_arrive(&s_empty[sb]);
       float m = -INFINITY;
-      for (int cb = wlo + half; cb <= whi && !(p.dbg & 1); cb += 2) {
-        uint32_t v[32];
-        tmem_ld32(srow + cb * 32, v);
-        const uint32_t vm = chunk_mask(cb);
-        tmem_ld_wait();
 #pragma unroll
-        for (int i = 0; i < 32; ++i)
-          if (vm & (1u << i)) m = fmaxf(m, __uint_as_float(v[i]));
+      for (int i = 0; i < 32; ++i) {
+        if (vma & (1u << i)) m = fmaxf(m, __uint_as_float(va[i]));
+        if (vmb & (1u << i)) m = fmaxf(m, __uint_as_float(vb[i]));
       }
       sMax[half * 128 + row] = m;
       named_bar_sync(2 + quarter, 64);                    // the two warps of this quarter
@@ -292,30 +299,8 @@ epipolar_attn_tc_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
       if (t > 0) mbar_wait(&o_full[(t - 1) % p.nO], ((t - 1) / p.nO) & 1);
       if (tsw) at_mark(p, 2, nts);
       float sum = 0.f;
-      for (int cb = 0; cb < 6 && !(p.dbg & 1); ++cb) {
-        const bool live = cb >= wlo && cb <= whi;
-        if ((live ? ((cb - wlo) & 1) : (cb & 1)) != half) continue;
-        uint32_t pk[16];
-        if (live) {
-          uint32_t v[32];
-          tmem_ld32(srow + cb * 32, v);
-          const uint32_t vm = chunk_mask(cb);
-          tmem_ld_wait();
-#pragma unroll
-          for (int i = 0; i < 32; i += 2) {
-            // masked keys get exponent -inf -> weight exactly 0
-            const float x0 = fmaf(__uint_as_float(v[i]), scale, -mb), x1 = fmaf(__uint_as_float(v[i + 1]), scale, -mb);
-            const float e0 = ex2_approx((vm & (1u << i)) ? x0 : -INFINITY);
-            const float e1 = ex2_approx((vm & (2u << i)) ? x1 : -INFINITY);
-            sum += e0 + e1;
-            __nv_bfloat162 h = __floats2bfloat162_rn(e0, e1);
-            pk[i >> 1] = *reinterpret_cast<uint32_t*>(&h);
-          }
-        } else {
-#pragma unroll
-          for (int i = 0; i < 16; ++i) pk[i] = 0u;
-        }
-        // 32 keys = 4 chunks of 16 B in key block cb/2, chunk index (cb&1)*4 + c
+      // 32 keys = 4 chunks of 16 B in key block cb/2, chunk index (cb&1)*4 + c
+      auto store_p = [&](int cb, const uint32_t* pk) {
         unsigned char* prow = sP + (cb >> 1) * 16384 + (row >> 3) * 1024 + (row & 7) * 128;
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
@@ -323,11 +308,32 @@ epipolar_attn_tc_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
           *reinterpret_cast<uint4*>(prow + ((chunk ^ (row & 7)) << 4)) =
               make_uint4(pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
         }
+      };
+      auto emit = [&](int cb, const uint32_t* v, uint32_t vm) {
+        uint32_t pk[16];
+#pragma unroll
+        for (int i = 0; i < 32; i += 2) {
+          // masked keys get exponent -inf -> weight exactly 0
+          const float x0 = fmaf(__uint_as_float(v[i]), scale, -mb), x1 = fmaf(__uint_as_float(v[i + 1]), scale, -mb);
+          const float e0 = ex2_approx((vm & (1u << i)) ? x0 : -INFINITY);
+          const float e1 = ex2_approx((vm & (2u << i)) ? x1 : -INFINITY);
+          sum += e0 + e1;
+          __nv_bfloat162 h = __floats2bfloat162_rn(e0, e1);
+          pk[i >> 1] = *reinterpret_cast<uint32_t*>(&h);
+        }
+        store_p(cb, pk);
+      };
+      if (hasA) emit(cba, va, vma);
+      if (hasB) emit(cbb, vb, vmb);
+      if (!(p.dbg & 1)) {
+        uint32_t zero[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) zero[i] = 0u;
+        for (int cb = half; cb < 6; cb += 2)               // key chunks outside the band of this warp: P = 0
+          if (cb < wlo || cb > whi) store_p(cb, zero);
       }
       sSum[half * 128 + row] = sum;
       fence_proxy_async_smem();
-      tc_fence_before();
-      mbar_arrive(&s_empty[sb]);
       mbar_arrive(p_full);
       named_bar_sync(2 + quarter, 64);                    // (also orders the next tile's sMax write after this tile's read)
       sum += sSum[(half ^ 1) * 128 + row];
