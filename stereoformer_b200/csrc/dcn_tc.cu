@@ -36,15 +36,18 @@ constexpr int DT_TA_BASE = 256;           // TMEM columns of the A stages: [NST]
 constexpr int DT_MAXST = 4;
 
 
-// fp32 weights [Cout][K] -> bf16 hi / mid [2][Cout][Kpad] (zero padded along K)
+// fp32 weights [Cout][Cig][T] -> bf16 hi / mid [2][Cout][Kpad] (zero padded along K) with the reduction index PERMUTED to
+// k' = t * Cig + c (tap-major): a gather thread's 32 consecutive k' then share one tap, i.e. one sampling descriptor, and
+// walk consecutive input planes
 __global__ void dcn_split_weights_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ ws, int Cout, int K,
-                                         int Kpad) {
+                                         int Kpad, int Cig, int T) {
   const size_t n = static_cast<size_t>(Cout) * Kpad;
   for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n;
        i += static_cast<size_t>(gridDim.x) * blockDim.x) {
     const int k = static_cast<int>(i % Kpad);
     const size_t o = i / Kpad;
-    const float v = k < K ? w[o * K + k] : 0.f;
+    const int t = k / Cig, c = k - t * Cig;
+    const float v = k < K ? w[o * K + static_cast<size_t>(c) * T + t] : 0.f;
     const __nv_bfloat16 h = __float2bfloat16_rn(v);
     ws[i] = h;
     ws[n + i] = __float2bfloat16_rn(v - __bfloat162float(h));
@@ -151,9 +154,15 @@ dcn_tc_kernel(const __grid_constant__ CUtensorMap mapW, const DcnTcParams p) {
       for (int ch = 0; ch < p.nchunk; ++ch) {
         mbar_wait(&st_empty[s], ph);
         tc_fence_after();
-        // this thread's 32 K values of the chunk: k = k0 .. k0+31, k = c*T + t
+        // this thread's 32 K values of the chunk: k' = k0 .. k0+31 with k' = t*Cig + c (tap-major, see the weight split):
+        // the sampling descriptor is reloaded only when the tap or the deformable group changes
         const int k0 = ch * DT_KC + 32 * kh2;
-        int c = k0 / T, t = k0 - c * T;
+        int t = k0 / Cig, c = k0 - t * Cig;
+        int dgi = (g * Cig + c) / cpdg, bound = (dgi + 1) * cpdg - g * Cig;   // channel (within the group) where dgi steps
+        const float* src = in_g + static_cast<size_t>(c) * HW;
+        int4 off = make_int4(0, 0, 0, 0);
+        float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
+        bool fresh = true;
         uint32_t ahi[16], amid[16];
 #pragma unroll
         for (int u = 0; u < 16; ++u) {
@@ -163,15 +172,18 @@ dcn_tc_kernel(const __grid_constant__ CUtensorMap mapW, const DcnTcParams p) {
             const int k = k0 + 2 * u + e;
             float val = 0.f;
             if (k < p.K) {                                  // warp-uniform
-              const int dgi = (g * Cig + c) / cpdg;
-              const int di = (dgi * T + t) * 128 + px;
-              const int4 off = d_off[di];
-              const float4 w = d_w[di];
-              const float* src = in_g + static_cast<size_t>(c) * HW;
+              if (fresh) {
+                const int di = (dgi * T + t) * 128 + px;
+                off = d_off[di];
+                w = d_w[di];
+                fresh = false;
+              }
               val = w.x * __ldg(src + off.x) + w.y * __ldg(src + off.y) + w.z * __ldg(src + off.z) + w.w * __ldg(src + off.w);
             }
             v[e] = val;
-            if (++t == T) { t = 0; ++c; }
+            ++c; src += HW;
+            if (c == Cig) { c = 0; ++t; src = in_g; dgi = (g * Cig) / cpdg; bound = (dgi + 1) * cpdg - g * Cig; fresh = true; }
+            else if (c == bound) { ++dgi; bound += cpdg; fresh = true; }
           }
           const __nv_bfloat162 h = __floats2bfloat162_rn(v[0], v[1]);
           const __nv_bfloat162 m = __floats2bfloat162_rn(v[0] - __low2float(h), v[1] - __high2float(h));
@@ -289,7 +301,7 @@ int launch_dcn_tc(DcnTcParams p, const float* weight, void* workspace, size_t wo
   {
     const size_t n = static_cast<size_t>(p.Cout) * Kpad;
     const int grid = static_cast<int>(min(static_cast<size_t>(sm_count()) * 8, (n + 255) / 256));
-    dcn_split_weights_kernel<<<grid, 256, 0, stream>>>(weight, ws, p.Cout, p.K, Kpad);
+    dcn_split_weights_kernel<<<grid, 256, 0, stream>>>(weight, ws, p.Cout, p.K, Kpad, p.Cin / p.G, p.kh * p.kw);
     SF_LAUNCH_CHECK();
   }
   CUtensorMap mW;

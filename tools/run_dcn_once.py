@@ -1,0 +1,14 @@
+"""Dev tool: one tcgen05 DCN forward at 128->128 @ 248x360 (for ncu captures)."""
+import os, sys, torch
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from stereoformer_b200 import ops
+B, Cin, Cout, H, W = 1, 128, 128, 248, 360
+torch.manual_seed(0)
+x = torch.randn(B, Cin, H, W, device="cuda")
+w = torch.randn(Cout, Cin, 3, 3, device="cuda") * 0.05
+b = torch.randn(Cout, device="cuda")
+off = torch.randn(B, 18, H, W, device="cuda") * 2
+msk = torch.sigmoid(torch.randn(B, 9, H, W, device="cuda"))
+for _ in range(3):
+    ops.dcn_forward(x, w, b, off, msk, (1, 1), (1, 1), (1, 1), 1, 1, algo=ops.SF_ALGO_TC)
+torch.cuda.synchronize()
