@@ -8,9 +8,9 @@
 //   col[k][pix] = mask * bilinear(in[b, g*Cig+c], sampling point of tap t at pix)
 //
 // Work tile: 128 output pixels (M, one TMEM lane each) x all Cog output channels of one group (N <= 256).
-//   * 8 gather warps (two per TMEM lane quarter, thread = pixel): sampling descriptors (4 clamped corner offsets +
+//   * 16 gather warps (four per TMEM lane quarter, thread = pixel; measured against 8: more gathers in flight): sampling descriptors (4 clamped corner offsets +
 //     4 bilinear weights with the mask folded in) once per tile and deformable group in shared memory; per 64-wide
-//     K chunk every thread gathers its 32 column values, splits them into bf16 hi + bf16 mid and stores them with
+//     K chunk every thread gathers its 16 column values, splits them into bf16 hi + bf16 mid and stores them with
 //     tcgen05.st (A operand, K-major, two K-consecutive bf16 per 32-bit column);
 //   * warp 0 streams the pre-split weights (bf16 hi/mid, [Cout][Kpad], prepared once per call into the caller's
 //     workspace by dcn_split_weights_kernel) with TMA boxes [64 k][N rows], SWIZZLE_128B = K-major B operand;
@@ -29,7 +29,8 @@
 namespace sf {
 
 constexpr int DT_KC = 64;                 // K values per chunk (one 128-byte swizzle row of bf16)
-constexpr int DT_NG = 8;                  // gather warps (warps 1..8)
+constexpr int DT_NG = 16;                 // gather warps (warps 1..16): four per TMEM lane quarter
+constexpr int DT_KPT = DT_KC / (DT_NG / 4);  // K values per gather thread and chunk
 constexpr int DT_WARP_MMA = 1 + DT_NG;
 constexpr int DT_THREADS = (DT_WARP_MMA + 1 + 4) * 32;
 constexpr int DT_TA_BASE = 256;           // TMEM columns of the A stages: [NST][hi 32 | mid 32]
@@ -111,7 +112,7 @@ dcn_tc_kernel(const __grid_constant__ CUtensorMap mapW, const DcnTcParams p) {
     const int gtid = (warp - 1) * 32 + lane;             // 0..255 within the gather group
     const size_t HW = static_cast<size_t>(p.H) * p.W;
     const int cpdg = p.Cin / p.dg;
-    const uint32_t ta = tmem + DT_TA_BASE + 16 * kh2 + (static_cast<uint32_t>(32 * qa) << 16);
+    const uint32_t ta = tmem + DT_TA_BASE + (DT_KPT / 2) * kh2 + (static_cast<uint32_t>(32 * qa) << 16);
     int s = 0, ph = 1;
     for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
       const int pt = tile % p.nptile, t2 = tile / p.nptile;
@@ -156,16 +157,16 @@ dcn_tc_kernel(const __grid_constant__ CUtensorMap mapW, const DcnTcParams p) {
         tc_fence_after();
         // this thread's 32 K values of the chunk: k' = k0 .. k0+31 with k' = t*Cig + c (tap-major, see the weight split):
         // the sampling descriptor is reloaded only when the tap or the deformable group changes
-        const int k0 = ch * DT_KC + 32 * kh2;
+        const int k0 = ch * DT_KC + DT_KPT * kh2;
         int t = k0 / Cig, c = k0 - t * Cig;
         int dgi = (g * Cig + c) / cpdg, bound = (dgi + 1) * cpdg - g * Cig;   // channel (within the group) where dgi steps
         const float* src = in_g + static_cast<size_t>(c) * HW;
         int4 off = make_int4(0, 0, 0, 0);
         float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
         bool fresh = true;
-        uint32_t ahi[16], amid[16];
+        uint32_t ahi[DT_KPT / 2], amid[DT_KPT / 2];
 #pragma unroll
-        for (int u = 0; u < 16; ++u) {
+        for (int u = 0; u < DT_KPT / 2; ++u) {
           float v[2];
 #pragma unroll
           for (int e = 0; e < 2; ++e) {
@@ -190,8 +191,9 @@ dcn_tc_kernel(const __grid_constant__ CUtensorMap mapW, const DcnTcParams p) {
           ahi[u] = *reinterpret_cast<const uint32_t*>(&h);
           amid[u] = *reinterpret_cast<const uint32_t*>(&m);
         }
-        tmem_st16(ta + s * 64, ahi);
-        tmem_st16(ta + s * 64 + 32, amid);
+        static_assert(DT_KPT == 16, "gather threads store 8 packed columns per half");
+        tmem_st8(ta + s * 64, ahi);
+        tmem_st8(ta + s * 64 + 32, amid);
         tmem_st_wait();
         tc_fence_before();
         __syncwarp();
