@@ -19,6 +19,7 @@
 namespace sf {
 
 constexpr int DCN_KC = 8;  // input channels per shared-memory chunk
+constexpr int DCN_NT = 512; // threads per CTA
 
 struct DcnParams {
   const float* in;      // [B,Cin,H,W]
@@ -31,10 +32,13 @@ struct DcnParams {
   int kh, kw, sh, sw, ph, pw, dh, dw, G, dg;
 };
 
+// NT threads gather (the gathers are latency-bound: the more in flight the better); the first (TO/4)*(TP/4) of them
+// also run the register-tiled GEMM.
 template <int TO, int TP>
-__global__ void __launch_bounds__((TO / 4) * (TP / 4))
+__global__ void __launch_bounds__(DCN_NT)
 dcn_forward_kernel(const DcnParams p) {
-  constexpr int NT = (TO / 4) * (TP / 4);
+  constexpr int NT = DCN_NT, NGEMM = (TO / 4) * (TP / 4);
+  static_assert(NGEMM <= NT, "GEMM tile needs more threads than the CTA has");
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int T = p.kh * p.kw;
   int4* d_off = reinterpret_cast<int4*>(smem_raw);                  // [T][TP]
@@ -120,6 +124,7 @@ dcn_forward_kernel(const DcnParams p) {
     }
     __syncthreads();
     const int nk = nkc * T;
+    if (tid < NGEMM)
     for (int k = 0; k < nk; ++k) {
       const float4 a = *reinterpret_cast<const float4*>(col + k * TP + tx * 4);
       const float4 w = *reinterpret_cast<const float4*>(wsm + k * TO + ty * 4);
@@ -133,6 +138,7 @@ dcn_forward_kernel(const DcnParams p) {
   }
 
   // epilogue: + bias, NCHW store (addmm(bias, cols^T, W^T) + permute of the reference, .cu:108-118)
+  if (tid >= NGEMM) return;
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
     const int o = o0 + ty * 4 + i;
@@ -156,7 +162,7 @@ static int launch_dcn(const DcnParams& p, cudaStream_t s) {
   const int Cog = p.Cout / p.G;
   dim3 grid(ceil_div(p.Ho * p.Wo, TP), p.B, p.G * ceil_div(Cog, TO));
   SF_CHECK_ARG(grid.y <= 65535 && grid.z <= 65535, "dcn_forward: batch or group count too large");
-  kern<<<grid, (TO / 4) * (TP / 4), smem, s>>>(p);
+  kern<<<grid, DCN_NT, smem, s>>>(p);
   SF_LAUNCH_CHECK();
   return SF_OK;
 }
