@@ -26,7 +26,8 @@
 namespace sf {
 
 constexpr int BW_TP = 64;     // pixels per tile
-constexpr int BW_NT = 256;    // threads per CTA
+constexpr int BW_NT = 640;    // data kernel: all threads gather / scatter (latency-bound), the first 144 run the GEMM
+constexpr int BW_NTW = 256;   // weight kernel (GEMM-bound: more threads measured slower)
 constexpr int BW_OB = 256;    // output channels per shared-memory block
 constexpr int BW_NK = 36;     // (channel, tap) pairs per chunk: a 4 x 9 register tile per thread in the weight kernel
 
@@ -148,7 +149,7 @@ dcn_bwd_data_kernel(const DcnBwdParams p) {
         wS[o * NKP + k] = __ldg(p.weight + (static_cast<size_t>(g * Cog + o0 + o) * Cig + (c0 - g * Cig)) * T + k);
       }
       __syncthreads();
-      if (ty * 4 < nk) {
+      if (ty * 4 < nk && tid < 16 * 9) {
         for (int o = 0; o < no; ++o) {
           const float4 gv = *reinterpret_cast<const float4*>(gS + o * BW_TP + tx * 4);
           const float4 wv = *reinterpret_cast<const float4*>(wS + o * NKP + ty * 4);
@@ -160,7 +161,7 @@ dcn_bwd_data_kernel(const DcnBwdParams p) {
         }
       }
     }
-    if (ty * 4 < nk) {
+    if (ty * 4 < nk && tid < 16 * 9) {
 #pragma unroll
       for (int i = 0; i < 4; ++i)
         if (ty * 4 + i < nk)
@@ -211,7 +212,7 @@ dcn_bwd_data_kernel(const DcnBwdParams p) {
 }
 
 // ---------------------------------------------------------------------------------------------- weight gradient
-__global__ void __launch_bounds__(BW_NT)
+__global__ void __launch_bounds__(BW_NTW)
 dcn_bwd_weight_kernel(const DcnBwdParams p) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int T = p.kh * p.kw, M = p.Ho * p.Wo;
@@ -241,13 +242,13 @@ dcn_bwd_weight_kernel(const DcnBwdParams p) {
   for (long long tile = blockIdx.y; tile < ntiles; tile += gridDim.y) {
     const int b = static_cast<int>(tile / tiles_per_b), pix0 = static_cast<int>(tile % tiles_per_b) * BW_TP;
     __syncthreads();
-    for (int e = tid; e < T * BW_TP; e += BW_NT) ds[e] = make_desc(p, b, dgi, e / BW_TP, pix0 + e % BW_TP, M);
-    for (int e = tid; e < no * BW_TP; e += BW_NT) {
+    for (int e = tid; e < T * BW_TP; e += BW_NTW) ds[e] = make_desc(p, b, dgi, e / BW_TP, pix0 + e % BW_TP, M);
+    for (int e = tid; e < no * BW_TP; e += BW_NTW) {
       const int px = e % BW_TP, o = e / BW_TP;
       gS[px * OP + o] = (pix0 + px < M) ? __ldg(p.gout + (static_cast<size_t>(b) * p.Cout + g * Cog + o0 + o) * M + pix0 + px) : 0.f;
     }
     __syncthreads();
-    for (int e = tid; e < nk * BW_TP; e += BW_NT) {
+    for (int e = tid; e < nk * BW_TP; e += BW_NTW) {
       const int px = e % BW_TP, k = e / BW_TP;
       const int c = k / T, t = k % T;
       const Desc d = ds[t * BW_TP + px];
@@ -262,7 +263,7 @@ dcn_bwd_weight_kernel(const DcnBwdParams p) {
       colS[px * KP + k] = val;
     }
     __syncthreads();
-    if (to * 4 < no && tk * 9 < nk) {
+    if (tid < 256 && to * 4 < no && tk * 9 < nk) {
       for (int px = 0; px < BW_TP; ++px) {
         const float4 gv = *reinterpret_cast<const float4*>(gS + px * OP + to * 4);
         const float ga[4] = {gv.x, gv.y, gv.z, gv.w};
@@ -277,6 +278,7 @@ dcn_bwd_weight_kernel(const DcnBwdParams p) {
     }
   }
   // one atomicAdd per element per CTA (the reference accumulates with addmm over im2col steps, .cu:268)
+  if (tid >= 256) return;
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
     const int o = to * 4 + i;
@@ -363,7 +365,7 @@ extern "C" int sf_dcn_backward_f32(const float* input, const float* weight, cons
     p.nsplit = static_cast<int>(split);
     SF_CHECK_ARG(oblocks <= 65535, "dcn_backward: too many output-channel blocks");
     dim3 grid(nchunks, p.nsplit, oblocks);
-    dcn_bwd_weight_kernel<<<grid, BW_NT, smem, s>>>(p);
+    dcn_bwd_weight_kernel<<<grid, BW_NTW, smem, s>>>(p);
     SF_LAUNCH_CHECK();
   }
   if (grad_bias) {
