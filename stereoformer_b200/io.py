@@ -20,70 +20,74 @@ def read_img(filename):
     return np.array(Image.open(filename).convert('RGB')).astype(np.float32)
 
 
+_PFM_KINDS = {b'PF': 3, b'Pf': 1}          # header tag -> channels
+
+
+def _pfm_header(buf):
+    """Parse the three text lines of a PFM header -> (channels, width, height, scale, payload offset)."""
+    pos, fields = 0, []
+    for _ in range(3):
+        end = buf.index(b'\n', pos)
+        fields.append(buf[pos:end + 1])
+        pos = end + 1
+    tag = fields[0].rstrip()
+    if tag not in _PFM_KINDS:
+        raise Exception('Not a PFM file.')
+    dims = re.match(r'^(\d+)\s(\d+)\s$', fields[1].decode("ascii"))
+    if dims is None:
+        raise Exception('Malformed PFM header.')
+    return _PFM_KINDS[tag], int(dims.group(1)), int(dims.group(2)), float(fields[2].decode("ascii").rstrip()), pos
+
+
 def _read_pfm(file):
-    """utils/file_io.py:34-69 -> (data, scale); rows bottom-to-top in the file, returned top-to-bottom."""
-    with open(file, 'rb') as f:
-        header = f.readline().rstrip().decode("ascii")
-        if header == 'PF':
-            color = True
-        elif header == 'Pf':
-            color = False
-        else:
-            raise Exception('Not a PFM file.')
-        dim = re.match(r'^(\d+)\s(\d+)\s$', f.readline().decode("ascii"))
-        if not dim:
-            raise Exception('Malformed PFM header.')
-        width, height = (int(v) for v in dim.groups())
-        scale = float(f.readline().decode("ascii").rstrip())
-        endian = '<' if scale < 0 else '>'
-        data = np.frombuffer(f.read(), dtype=endian + 'f4')
-    shape = (height, width, 3) if color else (height, width)
-    return np.flipud(np.reshape(data, shape)), abs(scale)
+    """utils/file_io.py:34-69 -> (data, scale).  The file stores rows bottom-to-top; a negative scale marks
+    little-endian floats.  Returned array: top-to-bottom, [H,W] or [H,W,3], in the file's byte order."""
+    with open(file, 'rb') as fh:
+        buf = fh.read()
+    channels, width, height, scale, start = _pfm_header(buf)
+    dtype = np.dtype('<f4' if scale < 0 else '>f4')
+    shape = (height, width) if channels == 1 else (height, width, channels)
+    data = np.frombuffer(buf, dtype=dtype, offset=start).reshape(shape)
+    return data[::-1], abs(scale)
 
 
 read_pfm = _read_pfm
 
 
 def write_pfm(file, image, scale=1):
-    """utils/file_io.py:72-98 (also utils/common.py:67-96): byte-identical output."""
+    """utils/file_io.py:72-98 (also utils/common.py:67-96): byte-identical files."""
     if image.dtype.name != 'float32':
         raise Exception('Image dtype must be float32.')
-    image = np.flipud(image)
-    if len(image.shape) == 3 and image.shape[2] == 3:
-        color = True
-    elif len(image.shape) == 2 or len(image.shape) == 3 and image.shape[2] == 1:
-        color = False
+    if image.ndim == 3 and image.shape[2] == 3:
+        tag = b'PF'
+    elif image.ndim == 2 or (image.ndim == 3 and image.shape[2] == 1):
+        tag = b'Pf'
     else:
         raise Exception('Image must have H x W x 3, H x W x 1 or H x W dimensions.')
-    endian = image.dtype.byteorder
-    if endian == '<' or endian == '=' and sys.byteorder == 'little':
-        scale = -scale
-    with open(file, 'wb') as f:
-        f.write(b'PF\n' if color else b'Pf\n')
-        f.write(b'%d %d\n' % (image.shape[1], image.shape[0]))
-        f.write(b'%f\n' % scale)
-        f.write(np.ascontiguousarray(image).tobytes())
+    little = image.dtype.byteorder == '<' or (image.dtype.byteorder == '=' and sys.byteorder == 'little')
+    header = b'%s\n%d %d\n%f\n' % (tag, image.shape[1], image.shape[0], -scale if little else scale)
+    with open(file, 'wb') as fh:
+        fh.write(header)
+        fh.write(np.ascontiguousarray(image[::-1]).tobytes())      # bottom row first
 
 
 def _read_kitti_disp(filename):
-    """utils/file_io.py:101-104: 16-bit PNG / 256."""
+    """utils/file_io.py:101-104: KITTI stores disparity * 256 in a 16-bit PNG."""
     from PIL import Image
-    return np.array(Image.open(filename)).astype(np.float32) / 256.
+    return np.asarray(Image.open(filename), dtype=np.float32) / 256.
+
+
+_DISP_READERS = (('pfm', lambda f, subset: (-1.0 if subset else 1.0) * np.ascontiguousarray(_read_pfm(f)[0])),
+                 ('png', lambda f, subset: _read_kitti_disp(f)),
+                 ('npy', lambda f, subset: np.load(f)))
 
 
 def read_disp(filename, subset=False):
-    """utils/file_io.py:17-31 -> [H,W] float32."""
-    if filename.endswith('pfm'):
-        disp = np.ascontiguousarray(_read_pfm(filename)[0])
-        if subset:
-            disp = -disp
-    elif filename.endswith('png'):
-        disp = _read_kitti_disp(filename)
-    elif filename.endswith('npy'):
-        disp = np.load(filename)
-    else:
-        raise Exception('Invalid disparity file format!')
-    return disp
+    """utils/file_io.py:17-31 -> [H,W] float32.  SceneFlow `subset` ground truth is stored negated."""
+    for suffix, reader in _DISP_READERS:
+        if filename.endswith(suffix):
+            return reader(filename, subset)
+    raise Exception('Invalid disparity file format!')
 
 
 def read_text_lines(filepath):
@@ -92,30 +96,26 @@ def read_text_lines(filepath):
         return [line.rstrip() for line in f.readlines()]
 
 
+def _pseudo_gt_path(disp_path):
+    """dataloader/SceneflowLoader.py:90-99: pseudo ground truth exists for the KITTI layouts only."""
+    for key in ('disp_occ_0', 'disp_occ'):                 # KITTI 2015 first ('disp_occ' is a prefix of it)
+        if key in disp_path:
+            return disp_path.replace(key, key + '_pseudo_gt')
+    raise NotImplementedError
+
+
 def load_samples(data_dir, list_file, save_filename=False, load_pseudo_gt=False):
     """The sample list of StereoDataset.__init__, dataloader/SceneflowLoader.py:73-102: one dict per line of
     `left right [disp]` with keys left / right / disp / pseudo_disp (/ left_name)."""
     samples = []
     for line in read_text_lines(list_file):
-        splits = line.split()
-        left_img, right_img = splits[:2]
-        gt_disp = None if len(splits) == 2 else splits[2]
-        sample = dict()
+        names = line.split()
+        disp = os.path.join(data_dir, names[2]) if len(names) > 2 else None
+        entry = {'left': os.path.join(data_dir, names[0]), 'right': os.path.join(data_dir, names[1]), 'disp': disp,
+                 'pseudo_disp': _pseudo_gt_path(disp) if (load_pseudo_gt and disp is not None) else None}
         if save_filename:
-            sample['left_name'] = left_img.split('/', 1)[1]
-        sample['left'] = os.path.join(data_dir, left_img)
-        sample['right'] = os.path.join(data_dir, right_img)
-        sample['disp'] = os.path.join(data_dir, gt_disp) if gt_disp is not None else None
-        if load_pseudo_gt and sample['disp'] is not None:
-            if 'disp_occ_0' in sample['disp']:
-                sample['pseudo_disp'] = sample['disp'].replace('disp_occ_0', 'disp_occ_0_pseudo_gt')
-            elif 'disp_occ' in sample['disp']:
-                sample['pseudo_disp'] = sample['disp'].replace('disp_occ', 'disp_occ_pseudo_gt')
-            else:
-                raise NotImplementedError
-        else:
-            sample['pseudo_disp'] = None
-        samples.append(sample)
+            entry['left_name'] = names[0].split('/', 1)[1]
+        samples.append(entry)
     return samples
 
 
