@@ -92,10 +92,25 @@ SF_API int sf_disp_warp_f32(const float* img, const float* disp, float* warped, 
                             float* dbg_src, int B, int C, int H, int W, int border, int div_mode, int* neg_flag,
                             void* stream);
 
+/* a7 on a row band (partition 2: one large pair split by epipolar row bands).  The output covers rows
+ * [y0, y0 + rows) of an image of full_height rows; img holds rows [src_y0, src_y0 + src_rows) and must include the
+ * 1-row halo the align_corners quirk needs (rows y0-1 .. y0+rows, clipped to the image; SF_ERR_ARG otherwise).
+ * Coordinates are computed from the global row index and height: the band equals the same rows of the whole-image
+ * call bit for bit.  disp/warped/mask/dbg_* are [B,*,rows,W]. */
+SF_API int sf_disp_warp_band_f32(const float* img, const float* disp, float* warped, float* mask, float* dbg_grid,
+                                 float* dbg_src, int B, int C, int rows, int W, int full_height, int y0, int src_y0,
+                                 int src_rows, int border, int div_mode, int* neg_flag, void* stream);
+
 /* a6 (i),(iii),(iv): BasicGuidanceNet.forward up to the conv encoders  Attempts/update.py:68-86.
  * left/right [B,C,H,W] already at the disparity resolution; err [B,C,H,W]; unc [B,D,H,W]. */
 SF_API int sf_guidance_f32(const float* cv, const float* disp, const float* left, const float* right, float* err,
                            float* unc, int B, int D, int C, int H, int W, int div_mode, int* neg_flag, void* stream);
+
+/* The same on a row band: cv/disp/left/err/unc hold the band's rows, right holds [src_y0, src_y0 + src_rows)
+ * (1-row halo as for sf_disp_warp_band_f32). */
+SF_API int sf_guidance_band_f32(const float* cv, const float* disp, const float* left, const float* right, float* err,
+                                float* unc, int B, int D, int C, int rows, int W, int full_height, int y0, int src_y0,
+                                int src_rows, int div_mode, int* neg_flag, void* stream);
 
 /* a8: CorrBlock1D.__init__ / corr  models/IterativeLocalCostVolume/corr/corr.py:55-76,103-111.
  * levels: HOST array of n_out device pointers, level l is [B*H*W1, W2 >> l]. */

@@ -25,6 +25,8 @@ SIGNATURES = {
     "sf_sample_volume_f32": [_p] * 5 + [_c_int] * 5 + [_p],
     "sf_disp_warp_f32": [_p] * 6 + [_c_int] * 6 + [_p, _p],
     "sf_guidance_f32": [_p] * 6 + [_c_int] * 6 + [_p, _p],
+    "sf_disp_warp_band_f32": [_p] * 6 + [_c_int] * 10 + [_p, _p],
+    "sf_guidance_band_f32": [_p] * 6 + [_c_int] * 10 + [_p, _p],
     "sf_corr1d_pyramid_f32": [_p, _p, _p] + [_c_int] * 7 + [_p],
     "sf_corr1d_lookup_f32": [_p, _p, _c_int, _c_int, _p, _p, _p, _p] + [_c_int] * 4 + [_p],
     "sf_dcn_forward_f32": [_p] * 6 + [_c_int] * 15 + [_p],

@@ -45,9 +45,10 @@ __device__ __forceinline__ Bilin warp_setup(float x, float y, float d, int H, in
   return r;
 }
 
-__device__ __forceinline__ float warp_sample(const float* __restrict__ plane, const Bilin& g, int W) {
+// ys0 = global index of the first source row the plane holds (0 for a whole image, the halo start for a row band).
+__device__ __forceinline__ float warp_sample(const float* __restrict__ plane, const Bilin& g, int W, int ys0 = 0) {
   float o = 0.f;
-  const float* r0 = plane + static_cast<size_t>(g.y0) * W + g.x0;
+  const float* r0 = plane + (static_cast<ptrdiff_t>(g.y0) - ys0) * W + g.x0;
   if (g.iny0 && g.inx0) o += __ldg(r0) * g.wnw;
   if (g.iny0 && g.inx1) o += __ldg(r0 + 1) * g.wne;
   if (g.iny1 && g.inx0) o += __ldg(r0 + W) * g.wsw;
@@ -68,24 +69,32 @@ __device__ __forceinline__ float warp_mask(float x, float y, float d, int H, int
   return o;
 }
 
+// Row-band form (partition 2): the output covers rows [band.y0, band.y0 + H) of an image of band.hfull rows,
+// the source planes hold rows [band.ys0, band.ys0 + band.srows).  The sampling coordinates are computed from the
+// GLOBAL row index and height (y_src = y*Hfull/(Hfull-1) - 0.5 depends on both), so a band reproduces the rows of
+// the whole-image call bit for bit.  A whole image is the band {H, 0, 0, H}.
+struct RowBand { int hfull, y0, ys0, srows; };
+
 __global__ void __launch_bounds__(256)
 disp_warp_kernel(const float* __restrict__ img, const float* __restrict__ disp, float* __restrict__ warped,
                  float* __restrict__ mask, float* __restrict__ dbg_grid, float* __restrict__ dbg_src, int B, int C,
-                 int H, int W, int border, int recip, int* __restrict__ neg_flag) {
+                 int H, int W, int border, int recip, int* __restrict__ neg_flag, RowBand band) {
   const size_t HW = static_cast<size_t>(H) * W, n = static_cast<size_t>(B) * HW;
+  const size_t SHW = static_cast<size_t>(band.srows) * W;
   for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n;
        i += static_cast<size_t>(gridDim.x) * blockDim.x) {
     const int x = i % W, y = (i / W) % H;
     const size_t b = i / HW;
     const float d = disp[i];
     if (d < 0.f && neg_flag) *neg_flag = 1;  // reference asserts disp.min() >= 0 (disparity_warper.py:93)
-    const Bilin g = warp_setup((float)x, (float)y, d, H, W, border != 0, recip);
+    const float yg = (float)(y + band.y0);
+    const Bilin g = warp_setup((float)x, yg, d, band.hfull, W, border != 0, recip);
     if (dbg_grid) { dbg_grid[2 * i] = g.gx; dbg_grid[2 * i + 1] = g.gy; }
     if (dbg_src) { dbg_src[2 * i] = g.ix; dbg_src[2 * i + 1] = g.iy; }
-    const float mk = mask ? warp_mask((float)x, (float)y, d, H, W, recip) : 0.f;
+    const float mk = mask ? warp_mask((float)x, yg, d, band.hfull, W, recip) : 0.f;
     for (int c = 0; c < C; ++c) {
       const size_t o = (b * C + c) * HW + (i % HW);
-      warped[o] = warp_sample(img + (b * C + c) * HW, g, W);
+      warped[o] = warp_sample(img + (b * C + c) * SHW, g, W, band.ys0);
       if (mask) mask[o] = mk;
     }
   }
@@ -97,18 +106,19 @@ disp_warp_kernel(const float* __restrict__ img, const float* __restrict__ disp, 
 __global__ void __launch_bounds__(256)
 guidance_kernel(const float* __restrict__ cv, const float* __restrict__ disp, const float* __restrict__ left,
                 const float* __restrict__ right, float* __restrict__ err, float* __restrict__ unc, int B, int D, int C,
-                int H, int W, int recip, int* __restrict__ neg_flag) {
+                int H, int W, int recip, int* __restrict__ neg_flag, RowBand band) {
   const size_t HW = static_cast<size_t>(H) * W, n = static_cast<size_t>(B) * HW;
+  const size_t SHW = static_cast<size_t>(band.srows) * W;
   for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n;
        i += static_cast<size_t>(gridDim.x) * blockDim.x) {
     const int x = i % W, y = (i / W) % H;
     const size_t b = i / HW, r = i % HW;
     const float d = disp[i];
     if (d < 0.f && neg_flag) *neg_flag = 1;
-    const Bilin g = warp_setup((float)x, (float)y, d, H, W, true, recip);
+    const Bilin g = warp_setup((float)x, (float)(y + band.y0), d, band.hfull, W, true, recip);
     for (int c = 0; c < C; ++c) {
       const size_t o = (b * C + c) * HW + r;
-      err[o] = warp_sample(right + (b * C + c) * HW, g, W) - left[o];
+      err[o] = warp_sample(right + (b * C + c) * SHW, g, W, band.ys0) - left[o];
     }
     const float* src = cv + b * D * HW + r;
     float m = -INFINITY;
@@ -226,17 +236,54 @@ guidance_bwd_kernel(const float* __restrict__ cv, const float* __restrict__ disp
 
 }  // namespace sf
 
+// A band's source rows must cover every row the 2-row bilinear gather can touch: y-1 .. y+1, clipped to the image.
+static int check_band(const char* what, int rows, int hfull, int y0, int ys0, int srows) {
+  SF_CHECK_ARG(hfull > 0 && rows > 0 && srows > 0 && y0 >= 0 && ys0 >= 0, "row band: non-positive dimension");
+  SF_CHECK_ARG(y0 + rows <= hfull && ys0 + srows <= hfull, "row band: band exceeds the image");
+  const int need0 = y0 > 0 ? y0 - 1 : 0, need1 = y0 + rows < hfull ? y0 + rows + 1 : hfull;
+  if (ys0 > need0 || ys0 + srows < need1) {
+    sf::set_error("%s: the source rows must include a 1-row halo on both sides of the band", what);
+    return SF_ERR_ARG;
+  }
+  return SF_OK;
+}
+
+extern "C" int sf_disp_warp_band_f32(const float* img, const float* disp, float* warped, float* mask, float* dbg_grid,
+                                     float* dbg_src, int B, int C, int rows, int W, int full_height, int y0,
+                                     int src_y0, int src_rows, int border, int div_mode, int* neg_flag,
+                                     void* stream) {
+  using namespace sf;
+  SF_CHECK_ARG(img && disp && warped, "disp_warp: null pointer");
+  SF_CHECK_ARG(B > 0 && C > 0 && rows > 0 && W > 0, "disp_warp: non-positive dimension");
+  if (int rc = check_band("disp_warp", rows, full_height, y0, src_y0, src_rows)) return rc;
+  size_t n = static_cast<size_t>(B) * rows * W;
+  int grid = static_cast<int>(min(static_cast<size_t>(sm_count()) * 8, (n + 255) / 256));
+  disp_warp_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      img, disp, warped, mask, dbg_grid, dbg_src, B, C, rows, W, border, div_mode == SF_DIV_RECIP, neg_flag,
+      RowBand{full_height, y0, src_y0, src_rows});
+  SF_LAUNCH_CHECK();
+  return SF_OK;
+}
+
 extern "C" int sf_disp_warp_f32(const float* img, const float* disp, float* warped, float* mask, float* dbg_grid,
                                 float* dbg_src, int B, int C, int H, int W, int border, int div_mode, int* neg_flag,
                                 void* stream) {
+  return sf_disp_warp_band_f32(img, disp, warped, mask, dbg_grid, dbg_src, B, C, H, W, H, 0, 0, H, border, div_mode,
+                               neg_flag, stream);
+}
+
+extern "C" int sf_guidance_band_f32(const float* cv, const float* disp, const float* left, const float* right,
+                                    float* err, float* unc, int B, int D, int C, int rows, int W, int full_height,
+                                    int y0, int src_y0, int src_rows, int div_mode, int* neg_flag, void* stream) {
   using namespace sf;
-  SF_CHECK_ARG(img && disp && warped, "disp_warp: null pointer");
-  SF_CHECK_ARG(B > 0 && C > 0 && H > 0 && W > 0, "disp_warp: non-positive dimension");
-  size_t n = static_cast<size_t>(B) * H * W;
+  SF_CHECK_ARG(cv && disp && left && right && err && unc, "guidance: null pointer");
+  SF_CHECK_ARG(B > 0 && D > 0 && C > 0 && rows > 0 && W > 0, "guidance: non-positive dimension");
+  if (int rc = check_band("guidance", rows, full_height, y0, src_y0, src_rows)) return rc;
+  size_t n = static_cast<size_t>(B) * rows * W;
   int grid = static_cast<int>(min(static_cast<size_t>(sm_count()) * 8, (n + 255) / 256));
-  disp_warp_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(img, disp, warped, mask, dbg_grid, dbg_src, B,
-                                                                      C, H, W, border, div_mode == SF_DIV_RECIP,
-                                                                      neg_flag);
+  guidance_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      cv, disp, left, right, err, unc, B, D, C, rows, W, div_mode == SF_DIV_RECIP, neg_flag,
+      RowBand{full_height, y0, src_y0, src_rows});
   SF_LAUNCH_CHECK();
   return SF_OK;
 }
@@ -244,15 +291,7 @@ extern "C" int sf_disp_warp_f32(const float* img, const float* disp, float* warp
 extern "C" int sf_guidance_f32(const float* cv, const float* disp, const float* left, const float* right, float* err,
                                float* unc, int B, int D, int C, int H, int W, int div_mode, int* neg_flag,
                                void* stream) {
-  using namespace sf;
-  SF_CHECK_ARG(cv && disp && left && right && err && unc, "guidance: null pointer");
-  SF_CHECK_ARG(B > 0 && D > 0 && C > 0 && H > 0 && W > 0, "guidance: non-positive dimension");
-  size_t n = static_cast<size_t>(B) * H * W;
-  int grid = static_cast<int>(min(static_cast<size_t>(sm_count()) * 8, (n + 255) / 256));
-  guidance_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(cv, disp, left, right, err, unc, B, D, C, H, W,
-                                                                     div_mode == SF_DIV_RECIP, neg_flag);
-  SF_LAUNCH_CHECK();
-  return SF_OK;
+  return sf_guidance_band_f32(cv, disp, left, right, err, unc, B, D, C, H, W, H, 0, 0, H, div_mode, neg_flag, stream);
 }
 
 extern "C" int sf_disp_warp_backward_f32(const float* img, const float* disp, const float* grad_warped, float* grad_img,

@@ -176,6 +176,52 @@ def disp_warp(img, disp, padding_mode="border", div_mode=SF_DIV_TRUE, check=True
     return warped, mask
 
 
+def disp_warp_band(img_src, disp, full_height, y0, src_y0, padding_mode="border", div_mode=SF_DIV_TRUE, check=True,
+                   with_mask=True, debug=False):
+    """disp_warp on the row band [y0, y0 + rows) of an image of ``full_height`` rows (partition 2).
+
+    ``img_src`` [B,C,src_rows,W] holds rows [src_y0, src_y0 + src_rows) and must include a 1-row halo; ``disp``
+    [B,1,rows,W].  Equals the same rows of the whole-image call bit for bit."""
+    img_src, disp = _chk(img_src, "img", dim=4), _chk(disp, "disp", dim=4)
+    B, C, S, W = img_src.shape
+    rows = disp.shape[2]
+    if disp.shape != (B, 1, rows, W):
+        raise ValueError("disp must be [B,1,rows,W]")
+    if padding_mode not in ("border", "zeros"):
+        raise ValueError("padding_mode must be 'border' or 'zeros'")
+    dev = img_src.device
+    warped = torch.empty((B, C, rows, W), device=dev, dtype=torch.float32)
+    mask = torch.empty_like(warped) if with_mask else None
+    flag = torch.zeros(1, device=dev, dtype=torch.int32) if check else None
+    grid = torch.empty((B, rows, W, 2), device=dev, dtype=torch.float32) if debug else None
+    src = torch.empty((B, rows, W, 2), device=dev, dtype=torch.float32) if debug else None
+    with torch.cuda.device(dev):
+        _lib.call("sf_disp_warp_band_f32", _ptr(img_src), _ptr(disp), _ptr(warped), _ptr(mask), _ptr(grid), _ptr(src),
+                  B, C, rows, W, int(full_height), int(y0), int(src_y0), S, int(padding_mode == "border"),
+                  int(div_mode), _ptr(flag), _stream())
+    if check and int(flag.item()) != 0:
+        raise AssertionError("disp.min() >= 0 violated")
+    if debug:
+        return warped, mask, dict(grid=grid, src=src)
+    return warped, mask
+
+
+def guidance_band(cv, disp, left, right_src, full_height, y0, src_y0, div_mode=SF_DIV_TRUE, flag=None):
+    """guidance() on a row band: cv/disp/left hold the band's rows, ``right_src`` rows [src_y0, ...) with a 1-row halo."""
+    cv, disp = _chk(cv, "old_cost_volume", dim=4), _chk(disp, "cur_disp")
+    left, right_src = _chk(left, "left_image", dim=4), _chk(right_src, "right_image", dim=4)
+    B, D, rows, W = cv.shape
+    C, S = left.shape[1], right_src.shape[2]
+    if left.shape != (B, C, rows, W) or right_src.shape != (B, C, S, W) or disp.numel() != B * rows * W:
+        raise ValueError("band tensors must be [B,*,rows,W]; right_src [B,C,src_rows,W]")
+    err = torch.empty_like(left)
+    unc = torch.empty_like(cv)
+    with torch.cuda.device(cv.device):
+        _lib.call("sf_guidance_band_f32", _ptr(cv), _ptr(disp), _ptr(left), _ptr(right_src), _ptr(err), _ptr(unc), B,
+                  D, C, rows, W, int(full_height), int(y0), int(src_y0), S, int(div_mode), _ptr(flag), _stream())
+    return err, unc
+
+
 def guidance(cv, disp, left, right, div_mode=SF_DIV_TRUE, flag=None):
     """Fused BasicGuidanceNet prologue -> (error_map [B,C,H,W], uncertainty_volume [B,D,H,W])."""
     cv, disp = _chk(cv, "old_cost_volume", dim=4), _chk(disp, "cur_disp")

@@ -58,3 +58,29 @@ def test_gather_world2_gloo():
     port = s.getsockname()[1]
     s.close()
     mp.spawn(_worker, args=(2, port), nprocs=2, join=True)
+
+
+def test_row_band_host_logic():
+    from stereoformer_b200 import bands as sfb
+    H = 248
+    for world in (2, 4, 8):
+        bs = [sfb.RowBand.of_rank(H, world, r, halo=3) for r in range(world)]
+        assert bs[0].ys0 == 0 and bs[-1].ys1 == H and sum(b.rows for b in bs) == H
+        full = torch.arange(H * 5, dtype=torch.float32).view(1, 1, H, 5)
+        for b in bs:
+            assert b.covers(3) and not (b.covers(4) and 0 < b.y0 and b.y1 < H)
+            assert torch.equal(b.crop(b.source(full)), b.interior(full))
+            s = b.scaled(8)
+            assert (s.height, s.y0, s.y1, s.ys0, s.ys1) == (H * 8, b.y0 * 8, b.y1 * 8, b.ys0 * 8, b.ys1 * 8)
+        assert torch.equal(torch.cat([b.interior(full) for b in bs], 2), full)
+    import pytest
+    with pytest.raises(ValueError):
+        sfb.RowBand(10, 4, 4)
+    with pytest.raises(ValueError):
+        sfb.RowBand(10, 4, 8, 5, 8)
+    off = torch.zeros(1, 18, 4, 4)
+    off[0, 4, 1, 1] = -2.25          # a dy channel
+    off[0, 5, 1, 1] = 9.0            # a dx channel: does not widen the row halo
+    assert sfb.dcn_halo_rows(off, 3, 1, 1) == 1 + 3 + 1
+    with pytest.raises(ValueError):
+        sfb.dcn_halo_rows(off, 3, 0, 1)

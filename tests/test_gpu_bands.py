@@ -1,0 +1,159 @@
+"""GPU parity of the row-band partition (SURVEY 8e partition 2, BASELINE config 5: 1984x2880 -> 248x360 grid,
+D = 48, 2/4/8 bands): every band, computed from the rows one rank would hold, equals the same rows of the
+whole-image call -- bit for bit for the row-local operators and the warp, <= 5e-5 for the DCN -- and the
+whole-image calls are themselves checked against the oracle on this shape."""
+import pytest
+import torch
+
+from oracle import dcn_c
+from oracle import stereo_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+H5, W5, D5 = 248, 360, 48            # config 5 at the 1/8 grid
+
+
+@pytest.fixture(scope="module")
+def mods():
+    import stereoformer_b200.bands as bands
+    import stereoformer_b200.dist as sfd
+    import stereoformer_b200.ops as ops
+    return ops, bands, sfd
+
+
+def _bands(bands, sfd, height, world, halo):
+    return [bands.RowBand(height, *b) for b in sfd.row_bands(height, world, halo=halo)]
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+@pytest.mark.parametrize("algo", ["tc", "exact"])
+def test_lcv_bands_bit_exact(mods, world, algo):
+    ops, bands, sfd = mods
+    torch.manual_seed(5)
+    C = 64
+    left, right = torch.randn(1, C, H5, W5, device="cuda"), torch.randn(1, C, H5, W5, device="cuda")
+    a = ops.SF_ALGO_TC if algo == "tc" else ops.SF_ALGO_TMA
+    cv, disp = bands.lcv_band(left, right, D5, algo=a)
+    parts_cv, parts_d = [], []
+    for b in _bands(bands, sfd, H5, world, 0):
+        c, d = bands.lcv_band(b.interior(left), b.interior(right), D5, algo=a)
+        parts_cv.append(c)
+        parts_d.append(d)
+    assert torch.equal(torch.cat(parts_cv, 2), cv)
+    assert torch.equal(torch.cat(parts_d, 2), disp)
+
+
+def test_lcv_whole_image_matches_oracle_c5(mods):
+    ops, bands, _ = mods
+    torch.manual_seed(6)
+    C, H = 32, 40                                      # C5 row shape, fewer rows so the oracle finishes in seconds
+    left, right = torch.randn(1, C, H, W5), torch.randn(1, C, H, W5)
+    rcv = O.corr_volume(left, right, D5)
+    cv, disp = bands.lcv_band(left.cuda(), right.cuda(), D5, div_mode=ops.SF_DIV_TRUE)
+    s = rcv.pow(2).mean().sqrt()
+    assert ((cv.cpu() - rcv).abs() <= 1e-4 * torch.clamp(rcv.abs(), min=s)).all()
+    d0 = O.soft_argmin(rcv)
+    rd = O.local_cost_volume(rcv, d0.reshape(1, 1, H, W5), 2, 20)
+    assert (disp.cpu() - rd).abs().max() < 1e-3        # px
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+@pytest.mark.parametrize("padding_mode", ["border", "zeros"])
+def test_disp_warp_bands_bit_exact(mods, world, padding_mode):
+    ops, bands, sfd = mods
+    torch.manual_seed(7)
+    img = torch.randn(1, 3, H5, W5, device="cuda")
+    disp = torch.rand(1, 1, H5, W5, device="cuda") * 60
+    w, m, dbg = ops.disp_warp(img, disp, padding_mode, debug=True)
+    pw, pm, pg, ps = [], [], [], []
+    for b in _bands(bands, sfd, H5, world, 1):
+        bw, bm, bd = bands.disp_warp_band(b.source(img), b.interior(disp), b, padding_mode, debug=True)
+        pw.append(bw); pm.append(bm); pg.append(bd["grid"]); ps.append(bd["src"])
+    assert torch.equal(torch.cat(pg, 1), dbg["grid"])          # sampling coordinates: bit-exact
+    assert torch.equal(torch.cat(ps, 1), dbg["src"])
+    assert torch.equal(torch.cat(pw, 2), w)
+    assert torch.equal(torch.cat(pm, 2), m)
+
+
+def test_disp_warp_band_needs_halo(mods):
+    ops, bands, _ = mods
+    img = torch.randn(1, 3, 10, 16, device="cuda")
+    disp = torch.zeros(1, 1, 10, 16, device="cuda")
+    with pytest.raises((ValueError, RuntimeError), match="halo"):
+        ops.disp_warp_band(img, disp, 20, 5, 5)                                              # no row above the band
+    b = bands.RowBand(20, 5, 15, 4, 16)
+    bands.disp_warp_band(torch.randn(1, 3, 12, 16, device="cuda"), disp, b)                 # 1-row halo: accepted
+    with pytest.raises(ValueError):
+        bands.RowBand(20, 5, 15, 6, 16)
+
+
+@pytest.mark.parametrize("world", [2, 8])
+def test_guidance_bands_bit_exact(mods, world):
+    ops, bands, sfd = mods
+    torch.manual_seed(8)
+    H = 64
+    cv = torch.randn(1, D5, H, W5, device="cuda")
+    disp = torch.rand(1, 1, H, W5, device="cuda") * (D5 - 1)
+    left, right = torch.randn(1, 3, H, W5, device="cuda"), torch.randn(1, 3, H, W5, device="cuda")
+    err, unc = ops.guidance(cv, disp, left, right)
+    pe, pu = [], []
+    for b in _bands(bands, sfd, H, world, 1):
+        e, u = bands.guidance_band(b.interior(cv), b.interior(disp), b.interior(left), b.source(right), b)
+        pe.append(e); pu.append(u)
+    assert torch.equal(torch.cat(pe, 2), err)
+    assert torch.equal(torch.cat(pu, 2), unc)
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_upsample_bands_bit_exact(mods, world):
+    ops, bands, sfd = mods
+    torch.manual_seed(9)
+    H, W = 32, 48
+    disp = torch.rand(1, 1, H, W, device="cuda") * 40
+    mask = torch.randn(1, 576, H, W, device="cuda")
+    up = ops.upsample_convex(disp, mask)
+    parts = [bands.upsample_convex_band(b.source(disp), b.source(mask), b) for b in _bands(bands, sfd, H, world, 1)]
+    assert torch.equal(torch.cat(parts, 2), up)
+    with pytest.raises(ValueError, match="halo"):
+        b = bands.RowBand(H, 8, 16)
+        bands.upsample_convex_band(b.source(disp), b.source(mask), b)
+
+
+@pytest.mark.parametrize("cfg", [dict(cin=16, cout=16, dg=1, world=4, H=H5, W=W5, scale=2.0),      # shipped 16->16 @C5
+                                 dict(cin=64, cout=64, dg=2, world=2, H=64, W=96, scale=3.0)])      # tcgen05 path
+def test_dcn_bands(mods, cfg):
+    ops, bands, sfd = mods
+    torch.manual_seed(10)
+    H, W, cin, cout, dg = cfg["H"], cfg["W"], cfg["cin"], cfg["cout"], cfg["dg"]
+    x = torch.randn(1, cin, H, W, device="cuda")
+    wt = torch.randn(cout, cin, 3, 3, device="cuda") * 0.1
+    bias = torch.randn(cout, device="cuda")
+    off = torch.randn(1, dg * 18, H, W, device="cuda") * cfg["scale"]
+    msk = torch.sigmoid(torch.randn(1, dg * 9, H, W, device="cuda"))
+    full = ops.dcn_forward(x, wt, bias, off, msk, (1, 1), (1, 1), (1, 1), 1, dg)
+    halo = bands.dcn_halo_rows(off, 3, 1, 1)
+    assert halo == 1 + int(torch.ceil(off[:, 0::2].abs().max()).item()) + 1
+    parts = []
+    for b in _bands(bands, sfd, H, cfg["world"], halo):
+        parts.append(bands.dcn_band(b.source(x), wt, bias, b.source(off), b.source(msk), b, deformable_groups=dg))
+    got = torch.cat(parts, 2)
+    # the local row index differs from the global one by an integer, so y + dy rounds differently in fp32
+    # (ulp(248) = 1.5e-5 px of sampling coordinate): 5e-5 for the exact FFMA kernel, 2e-4 with the bf16 hi/mid split
+    tol = 5e-5 if cin < 32 else 2e-4
+    s = full.pow(2).mean().sqrt()
+    assert ((got - full).abs() <= tol * torch.clamp(full.abs(), min=s)).all()
+    # a halo smaller than the offsets reach is refused, with the rows needed in the message
+    b = _bands(bands, sfd, H, cfg["world"], 1)[1]
+    with pytest.raises(ValueError, match="rows beyond the band"):
+        bands.dcn_band(b.source(x), wt, bias, b.source(off), b.source(msk), b, deformable_groups=dg)
+
+
+def test_dcn_whole_image_matches_oracle_c5_rows(mods):
+    ops, _, _ = mods
+    torch.manual_seed(11)
+    H, W = 24, W5
+    x, wt, bias = torch.randn(1, 16, H, W), torch.randn(16, 16, 3, 3) * 0.1, torch.randn(16)
+    off, msk = torch.randn(1, 18, H, W) * 2, torch.sigmoid(torch.randn(1, 9, H, W))
+    ref = dcn_c.dcn_forward(x, wt, bias, off, msk, (1, 1), (1, 1), (1, 1), 1, 1)
+    got = ops.dcn_forward(x.cuda(), wt.cuda(), bias.cuda(), off.cuda(), msk.cuda(), (1, 1), (1, 1), (1, 1), 1, 1)
+    assert torch.allclose(got.cpu(), ref, rtol=1e-5, atol=1e-5)
