@@ -203,6 +203,16 @@ SF_API int sf_upsample_convex_f32(const float* disp, const float* mask, float* o
 SF_API int sf_upsample_convex_scaled_f32(const float* disp, const float* mask, float mask_scale, float* out, int N,
                                          int H, int W, int factor, void* stream);
 
+/* f1 on a row band, with the multi-GPU gather of the full-resolution rows fused into the store (SURVEY 8e partition
+ * 2).  disp [N,1,H,W] / mask [N,9*F*F,H,W] hold H SOURCE rows (band + halo, >= 1 row unless at the image border);
+ * only the low-resolution rows [y_first, y_first + rows) are computed; out is [N,1,rows*F,W*F].  Every result is also
+ * stored to each of the n_peers (<= SF_MAX_PEERS, may be 0) device pointers of the HOST array h_peers at element
+ * peer_offset + n*peer_batch_stride + (row-major index inside the band): with whole-map buffers [N,1,Hfull*F,W*F]
+ * that is peer_offset = y0*F*W*F, peer_batch_stride = Hfull*F*W*F.  Completion is ordered by the caller. */
+SF_API int sf_upsample_convex_gather_f32(const float* disp, const float* mask, float mask_scale, float* out, int N,
+                                         int H, int W, int factor, int y_first, int rows, float* const* h_peers,
+                                         int n_peers, long long peer_offset, long long peer_batch_stride, void* stream);
+
 /* f2: ConvGRU.forward gate arithmetic  models/LocalCostVolume/Attempts/update.py:36-49, around the three
  * convolutions (which stay cuDNN).  b_pre / z_pre: conv_b / conv_z outputs BEFORE the sigmoid, [B,C,H,W] with batch
  * stride *_bstride elements (>= C*H*W; lets both gates live in one [B,2C,H,W] tensor); prev_h [B,C,H,W] or NULL

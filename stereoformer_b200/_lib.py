@@ -45,6 +45,8 @@ SIGNATURES = {
     "sf_epipolar_attn_bf16": [_p] * 5 + [_c_int] * 6 + [_p],
     "sf_upsample_convex_f32": [_p, _p, _p] + [_c_int] * 4 + [_p],
     "sf_upsample_convex_scaled_f32": [_p, _p, _c_float, _p] + [_c_int] * 4 + [_p],
+    "sf_upsample_convex_gather_f32": [_p, _p, _c_float, _p] + [_c_int] * 6 + [_p, _c_int, ctypes.c_longlong,
+                                                                              ctypes.c_longlong, _p],
     "sf_gru_reset_f32": [_p, ctypes.c_longlong, _p, _p, _p] + [_c_int] * 5 + [_p],
     "sf_gru_blend_f32": [_p, ctypes.c_longlong, _p, _p, _p] + [_c_int] * 5 + [_p],
 }

@@ -98,13 +98,23 @@ def guidance_band(cv_rows, disp_rows, left_rows, right_src, band, **kw):
     return ops.guidance_band(cv_rows, disp_rows, left_rows, right_src, band.height, band.y0, band.ys0, **kw)
 
 
-def upsample_convex_band(disp_src, mask_src, band, factor=8, mask_scale=1.0):
+def upsample_convex_band(disp_src, mask_src, band, factor=8, mask_scale=1.0, gather=None):
     """Convex upsampling of a band: disparity and mask on the source rows (1-row halo); returns the band's
-    ``rows*factor`` output rows."""
+    ``rows*factor`` output rows (the halo rows are not computed).  ``gather``: a ``dist.PeerGather`` over whole-map
+    buffers [N,1,height*factor,W*factor]; the band's rows are then also stored into every rank's buffer by the same
+    kernel (NVLink peer stores), which replaces the all-gather of the full-resolution map."""
     if not band.covers(1):
         raise ValueError("convex upsampling needs a 1-row halo")
-    up = ops.upsample_convex(disp_src, mask_src, factor=factor, mask_scale=mask_scale)
-    return band.scaled(factor).crop(up).contiguous()
+    if disp_src.shape[2] != band.ys1 - band.ys0:
+        raise ValueError("disp_src does not match the band's source rows")
+    N, W = disp_src.shape[0], disp_src.shape[3]
+    peers, off, bstride = None, 0, band.height * factor * W * factor
+    if gather is not None:
+        if gather.numel_total < N * bstride:
+            raise ValueError("gather buffer must hold [N,1,height*factor,W*factor] floats")
+        peers, off = gather.peer_ptrs, band.y0 * factor * W * factor
+    return ops.upsample_convex_rows(disp_src, mask_src, band.halo_top(), band.rows, factor=factor,
+                                    mask_scale=mask_scale, peers=peers, peer_offset=off, peer_batch_stride=bstride)
 
 
 def dcn_halo_rows(offset, kernel_h, padding_h, dilation_h):

@@ -10,20 +10,30 @@
 
 namespace sf {
 
+// Row-band + multi-GPU form (SURVEY 8e partition 2): disp / mask hold H source rows (band + halo), only the low-
+// resolution rows [y_first, y_first + rows) are computed, out is [N,1,rows*F,W*F].  The gather of the band's
+// full-resolution rows is fused into the store: every result also goes to each rank's whole-map buffer through its
+// NVLink peer mapping, element peers.off + b*peers.bstride + (row-major index inside the band).
+struct UpPeers {
+  float* p[SF_MAX_PEERS];
+  int n;
+  long long off, bstride;
+};
+
 template <int F>
 __global__ void __launch_bounds__(256)
 upsample_convex_kernel(const float* __restrict__ disp, const float* __restrict__ mask, float* __restrict__ out, int N,
-                       int H, int W, float mask_scale) {
+                       int H, int W, float mask_scale, int y_first, int rows, UpPeers peers) {
   // one thread per (low-resolution pixel, output sub-row i): F x 9 independent coalesced mask loads in flight per
   // thread, and a warp (32 consecutive x, same i) writes 32*F consecutive floats of one output row
-  const size_t HW = static_cast<size_t>(H) * W, n = static_cast<size_t>(N) * HW * F;
+  const size_t HW = static_cast<size_t>(H) * W, n = static_cast<size_t>(N) * rows * W * F;
   for (size_t idx = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; idx < n;
        idx += static_cast<size_t>(gridDim.x) * blockDim.x) {
     const int x = idx % W;
     size_t r = idx / W;
     const int i = r % F; r /= F;
-    const int y = r % H;
-    const size_t b = r / H;
+    const int yl = r % rows, y = y_first + yl;
+    const size_t b = r / rows;
     const size_t pix = static_cast<size_t>(y) * W + x;
     float nb[9];
 #pragma unroll
@@ -57,13 +67,20 @@ upsample_convex_kernel(const float* __restrict__ disp, const float* __restrict__
       }
       res[j] = a / s;
     }
-    float* row = out + b * F * F * HW + (static_cast<size_t>(y) * F + i) * (W * F) + x * F;
+    const size_t local = (static_cast<size_t>(yl) * F + i) * (W * F) + x * F;
+    float* row = out + b * F * F * rows * W + local;
     if (F % 4 == 0) {
 #pragma unroll
       for (int j = 0; j < F; j += 4) stg_cs_f4(row + j, make_float4(res[j], res[j + 1], res[j + 2], res[j + 3]));
     } else {
 #pragma unroll
       for (int j = 0; j < F; ++j) row[j] = res[j];
+    }
+    for (int q = 0; q < peers.n; ++q) {
+      float* prow = peers.p[q] + peers.off + static_cast<long long>(b) * peers.bstride + local;
+#pragma unroll
+      for (int j = 0; j < F; j += 4)
+        *reinterpret_cast<float4*>(prow + j) = make_float4(res[j], res[j + 1], res[j + 2], res[j + 3]);
     }
   }
 }
@@ -121,19 +138,46 @@ upsample_convex_bwd_kernel(const float* __restrict__ disp, const float* __restri
 }  // namespace sf
 
 static int upsample_convex_impl(const float* disp, const float* mask, float mask_scale, float* out, int N, int H, int W,
-                                int factor, void* stream) {
+                                int factor, void* stream, int y_first = 0, int rows = -1,
+                                float* const* h_peers = nullptr, int n_peers = 0, long long peer_offset = 0,
+                                long long peer_batch_stride = 0) {
   using namespace sf;
+  if (rows < 0) rows = H;
   SF_CHECK_ARG(disp && mask && out, "upsample_convex: null pointer");
   SF_CHECK_ARG(N > 0 && H > 0 && W > 0, "upsample_convex: non-positive dimension");
   SF_CHECK_ARG(factor == 8 || factor == 4, "upsample_convex: factor must be 8 or 4, got %d", factor);
   SF_CHECK_ARG((reinterpret_cast<uintptr_t>(out) & 15) == 0, "upsample_convex: out must be 16-byte aligned");
-  size_t n = static_cast<size_t>(N) * H * W * factor;
+  SF_CHECK_ARG(y_first >= 0 && rows > 0 && y_first + rows <= H, "upsample_convex: rows [%d, %d) outside the %d source rows",
+               y_first, y_first + rows, H);
+  SF_CHECK_ARG(n_peers >= 0 && n_peers <= SF_MAX_PEERS && (n_peers == 0 || h_peers) && peer_offset >= 0 &&
+                   peer_batch_stride >= 0, "upsample_convex: bad peer list (at most %d peers)", SF_MAX_PEERS);
+  UpPeers peers;
+  peers.n = n_peers;
+  peers.off = peer_offset;
+  peers.bstride = peer_batch_stride;
+  for (int r = 0; r < SF_MAX_PEERS; ++r) peers.p[r] = r < n_peers ? h_peers[r] : nullptr;
+  for (int r = 0; r < n_peers; ++r) {
+    SF_CHECK_ARG(peers.p[r] != nullptr, "upsample_convex: null peer pointer %d", r);
+    SF_CHECK_ARG(((reinterpret_cast<uintptr_t>(peers.p[r]) + 4 * static_cast<uintptr_t>(peer_offset)) & 15) == 0 &&
+                     (peer_batch_stride & 3) == 0, "upsample_convex: peer buffers must be 16-byte aligned");
+  }
+  size_t n = static_cast<size_t>(N) * rows * W * factor;
   int grid = static_cast<int>(min(static_cast<size_t>(sm_count()) * 8, (n + 255) / 256));
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  if (factor == 8) upsample_convex_kernel<8><<<grid, 256, 0, s>>>(disp, mask, out, N, H, W, mask_scale);
-  else upsample_convex_kernel<4><<<grid, 256, 0, s>>>(disp, mask, out, N, H, W, mask_scale);
+  if (factor == 8)
+    upsample_convex_kernel<8><<<grid, 256, 0, s>>>(disp, mask, out, N, H, W, mask_scale, y_first, rows, peers);
+  else
+    upsample_convex_kernel<4><<<grid, 256, 0, s>>>(disp, mask, out, N, H, W, mask_scale, y_first, rows, peers);
   SF_LAUNCH_CHECK();
   return SF_OK;
+}
+
+extern "C" int sf_upsample_convex_gather_f32(const float* disp, const float* mask, float mask_scale, float* out, int N,
+                                             int H, int W, int factor, int y_first, int rows, float* const* h_peers,
+                                             int n_peers, long long peer_offset, long long peer_batch_stride,
+                                             void* stream) {
+  return upsample_convex_impl(disp, mask, mask_scale, out, N, H, W, factor, stream, y_first, rows, h_peers, n_peers,
+                              peer_offset, peer_batch_stride);
 }
 
 extern "C" int sf_upsample_convex_f32(const float* disp, const float* mask, float* out, int N, int H, int W,

@@ -80,6 +80,7 @@ class PeerGather:
         self.world = dist.get_world_size(self.group)
         self.rank = dist.get_rank(self.group)
         self.numel_per_rank = int(numel_per_rank)
+        self.numel_total = self.world * self.numel_per_rank
         self.buffer = symm_mem.empty(self.world * self.numel_per_rank, dtype=torch.float32, device=device)
         self.handle = symm_mem.rendezvous(self.buffer, self.group)
         self.peer_ptrs = [int(p) for p in self.handle.buffer_ptrs]

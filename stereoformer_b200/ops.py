@@ -504,6 +504,26 @@ def upsample_convex(disp, mask, factor=8, mask_scale=1.0, out=None):
     return out
 
 
+def upsample_convex_rows(disp_src, mask_src, y_first, rows, factor=8, mask_scale=1.0, peers=None, peer_offset=0,
+                         peer_batch_stride=0):
+    """Convex upsampling of the low-resolution rows [y_first, y_first + rows) of tensors that hold a band's SOURCE
+    rows (band + halo) -> [N,1,rows*F,W*F].  peers: device pointers of every rank's whole-map buffer (NVLink peer
+    mappings, dist.PeerGather); each result is also stored at element ``peer_offset`` + n*``peer_batch_stride`` +
+    its row-major index inside the band of each of them, so the gather needs no collective."""
+    disp_src, mask_src = _chk(disp_src, "disp", dim=4), _chk(mask_src, "mask", dim=4)
+    N, _, H, W = disp_src.shape
+    if mask_src.shape != (N, 9 * factor * factor, H, W):
+        raise ValueError("mask must be [N,%d,H,W]" % (9 * factor * factor))
+    out = torch.empty((N, 1, factor * rows, factor * W), device=disp_src.device, dtype=torch.float32)
+    peers = list(peers or [])
+    arr = (ctypes.c_void_p * max(len(peers), 1))(*[ctypes.c_void_p(int(q)) for q in peers])
+    with torch.cuda.device(disp_src.device):
+        _lib.call("sf_upsample_convex_gather_f32", _ptr(disp_src), _ptr(mask_src), float(mask_scale), _ptr(out), N, H,
+                  W, int(factor), int(y_first), int(rows), arr if peers else None, len(peers),
+                  ctypes.c_longlong(int(peer_offset)), ctypes.c_longlong(int(peer_batch_stride)), _stream())
+    return out
+
+
 def _gate_view(t, name, B, C, H, W):
     """A [B,C,H,W] gate pre-activation that may be a channel slice of a wider contiguous tensor -> (tensor, stride)."""
     if not torch.is_tensor(t) or not t.is_cuda:

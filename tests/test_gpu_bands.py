@@ -117,6 +117,19 @@ def test_upsample_bands_bit_exact(mods, world):
     with pytest.raises(ValueError, match="halo"):
         b = bands.RowBand(H, 8, 16)
         bands.upsample_convex_band(b.source(disp), b.source(mask), b)
+    # the fused gather: every band stores its rows into the "peer" whole-map buffers (here two local buffers)
+    N = 2
+    disp2, mask2 = torch.rand(N, 1, H, W, device="cuda") * 40, torch.randn(N, 576, H, W, device="cuda")
+    up2 = ops.upsample_convex(disp2, mask2)
+    bufs = [torch.full((N, 1, 8 * H, 8 * W), float("nan"), device="cuda") for _ in range(2)]
+    for b in _bands(bands, sfd, H, world, 1):
+        got = ops.upsample_convex_rows(b.source(disp2), b.source(mask2), b.halo_top(), b.rows,
+                                       peers=[t.data_ptr() for t in bufs], peer_offset=b.y0 * 8 * W * 8,
+                                       peer_batch_stride=H * 8 * W * 8)
+        assert torch.equal(got, up2[:, :, b.y0 * 8:b.y1 * 8])
+    assert torch.equal(bufs[0], up2) and torch.equal(bufs[1], up2)
+    with pytest.raises(ValueError, match="outside"):
+        ops.upsample_convex_rows(disp2, mask2, H - 2, 4)
 
 
 @pytest.mark.parametrize("cfg", [dict(cin=16, cout=16, dg=1, world=4, H=H5, W=W5, scale=2.0),      # shipped 16->16 @C5

@@ -5,7 +5,8 @@ epipolar row bands (SURVEY 8e partition 2).  Launch: python tools/run_bands.py (
 Every rank builds the same seeded whole-image tensors, keeps only the rows a band-partitioned trunk would hand it
 (its band + halo) and runs, per step: cost volume + fused soft-argmin / local window (no halo), the guidance stage
 (warp with a 1-row halo), the shipped 16->16 DCN (data-dependent halo) and convex x8 upsampling (1-row halo); the
-band's full-resolution disparity rows are gathered with one NCCL all-gather.  Rank 0 checks the gathered map against
+band's full-resolution disparity rows reach every rank through peer stores fused into the upsampling kernel
+(--nccl: one NCCL all-gather per step instead).  Rank 0 checks the gathered map against
 the whole-image computation on its own GPU and prints one JSON line (strong scaling: the pair is fixed)."""
 import json
 import os
@@ -31,14 +32,6 @@ def whole_image_inputs(dev):
     return t
 
 
-def step(t, band, halo_dcn):
-    """One pass over a band.  t holds: left_f/right_f/left_i on the band's rows, everything else on its source rows."""
-    cv, disp = sfb.lcv_band(t["left_f"], t["right_f"], D)
-    err, unc = sfb.guidance_band(cv, disp, t["left_i"], t["right_i"], band)
-    y = sfb.dcn_band(t["x"], t["wt"], t["bias"], t["off"], t["msk"], band, halo=halo_dcn)
-    return disp, err, unc, y
-
-
 def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -54,32 +47,84 @@ def main():
     mine = {k: (band.interior(v) if k in ("left_f", "right_f", "left_i") else
                 v if k in ("wt", "bias") else band.source(v)) for k, v in full.items()}
 
-    # the band's disparity needs its halo rows for the 3x3 neighbourhood of the upsampling: a rank computes the
-    # (row-local) window on band + 1 row; here the extra rows come from the same kernels run on the source rows
+    # the upsampling reads the 3x3 neighbourhood of the low-resolution disparity: the (row-local) window is computed on
+    # band + 1 row, the other outputs are cropped from it
+    b1 = sfb.RowBand(H, band.y0, band.y1, max(band.y0 - 1, 0), min(band.y1 + 1, H))
+    lf1, rf1, um1 = b1.source(full["left_f"]), b1.source(full["right_f"]), b1.source(full["up_mask"])
+    even = all(b[1] - b[0] == bands[0][1] - bands[0][0] for b in bands)
+    up_full = torch.empty((1, 1, H * 8, W * 8), device=dev)
+    # gather of the full-resolution rows: fused into the upsampling kernel's store (NVLink peer mappings); NCCL
+    # all-gather only when symmetric memory is unavailable or --nccl is given
+    pg, gather_mode = None, "none"
+    if world > 1:
+        gather_mode = "NCCL all_gather per step"
+        if "--nccl" not in sys.argv:
+            try:
+                pg = sfd.PeerGather(-(-(H * 8 * W * 8) // world), dev)
+            except Exception as e:          # noqa: BLE001
+                pg, gather_mode = None, "NCCL all_gather per step (symmetric memory unavailable: %s)" % type(e).__name__
+        flags = torch.tensor([1.0 if pg is not None else 0.0], device=dev)
+        dist.all_reduce(flags, op=dist.ReduceOp.MIN)
+        if float(flags.item()) < 1.0:
+            pg = None
+        else:
+            gather_mode = "P2P stores fused into the upsampling kernel (NVLink peer mappings)"
+
     def band_pass():
-        disp, err, unc, y = step(mine, band, halo)
-        b1 = sfb.RowBand(H, band.y0, band.y1, max(band.y0 - 1, 0), min(band.y1 + 1, H))
-        lf, rf = b1.source(full["left_f"]), b1.source(full["right_f"])
-        _, disp_src = sfb.lcv_band(lf, rf, D)
-        up = sfb.upsample_convex_band(disp_src, b1.source(full["up_mask"]), b1)
+        cv1, disp1 = sfb.lcv_band(lf1, rf1, D)
+        cv, disp = b1.crop(cv1).contiguous(), b1.crop(disp1).contiguous()
+        err, unc = sfb.guidance_band(cv, disp, mine["left_i"], mine["right_i"], band)
+        y = sfb.dcn_band(mine["x"], mine["wt"], mine["bias"], mine["off"], mine["msk"], band, halo=halo)
+        up = sfb.upsample_convex_band(disp1, um1, b1, gather=pg)
         return disp, err, unc, y, up
 
+    side = torch.cuda.Stream()
+    with torch.cuda.stream(side):
+        for _ in range(3):
+            out = band_pass()
+        side.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, stream=side):
+            out = band_pass()
+    torch.cuda.synchronize()
+    disp, err, unc, y, up = out
+    up_bands = [(a * 8, b * 8, c * 8, d * 8) for a, b, c, d in bands]
+
+    def gather():
+        if world == 1:
+            return up
+        if pg is not None:
+            return pg.buffer[:H * 8 * W * 8].view(1, 1, H * 8, W * 8)
+        if even:
+            dist.all_gather_into_tensor(up_full, up)          # B = 1: rank-major rows are the whole map
+            return up_full
+        return sfd.gather_row_bands(up, up_bands)
+
     for _ in range(3):
-        out = band_pass()
+        graph.replay()
+        got = gather()
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    steps = 20
+    e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+    steps = 50
     e0.record()
     for _ in range(steps):
-        disp, err, unc, y, up = band_pass()
-        up_full = sfd.gather_row_bands(up, [(a * 8, b * 8, c * 8, d * 8) for a, b, c, d in bands]) if world > 1 else up
+        graph.replay()
     e1.record()
+    for _ in range(steps):
+        graph.replay()
+        got = gather()
+    e2.record()
     torch.cuda.synchronize()
-    ms = torch.tensor([e0.elapsed_time(e1) / steps], device=dev)
+    if pg is not None:
+        pg.sync()
+    up_full = got
+    ms_kernels = torch.tensor([e0.elapsed_time(e1) / steps], device=dev)
+    ms = torch.tensor([e1.elapsed_time(e2) / steps], device=dev)
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        dist.all_reduce(ms_kernels, op=dist.ReduceOp.MAX)
         y_full = sfd.gather_row_bands(y, bands)
         disp_full = sfd.gather_row_bands(disp, bands)
         err_full = sfd.gather_row_bands(err, bands)
@@ -94,6 +139,8 @@ def main():
         res = dict(config="C5 1984x2880 (248x360 grid, C=256, D=48), one pair, %d row band(s), DCN halo %d rows"
                           % (world, halo),
                    n_gpus=world, ms_per_pair=float(ms.item()), pairs_per_s=1000.0 / float(ms.item()),
+                   ms_per_pair_without_gather=float(ms_kernels.item()),
+                   launch="one CUDA graph per band pass", gather=gather_mode,
                    scaling="strong",
                    disparity_bit_exact=bool(torch.equal(disp_full, d_ref)),
                    warp_error_bit_exact=bool(torch.equal(err_full, e_ref)),
