@@ -189,6 +189,19 @@ SF_API int sf_dcn_backward_f32(const float* input, const float* weight, const fl
                                int kw, int stride_h, int stride_w, int pad_h, int pad_w, int dil_h, int dil_w,
                                int group, int deformable_group, void* stream);
 
+/* a10 / f3 in double precision: the reference dispatches its DCN over float and double
+ * (modulated_deform_conv_cuda.cu:93) and its gradient tests run in double (deform/test.py:376-403).  Same arguments
+ * as sf_dcn_forward_f32 / sf_dcn_backward_f32 with double pointers; direct (unfused) kernels, a verification dtype. */
+SF_API int sf_dcn_forward_f64(const double* input, const double* weight, const double* bias, const double* offset,
+                              const double* mask, double* out, int B, int Cin, int H, int W, int Cout, int kh, int kw,
+                              int stride_h, int stride_w, int pad_h, int pad_w, int dil_h, int dil_w, int group,
+                              int deformable_group, void* stream);
+SF_API int sf_dcn_backward_f64(const double* input, const double* weight, const double* offset, const double* mask,
+                               const double* grad_out, double* grad_input, double* grad_weight, double* grad_bias,
+                               double* grad_offset, double* grad_mask, int B, int Cin, int H, int W, int Cout, int kh,
+                               int kw, int stride_h, int stride_w, int pad_h, int pad_w, int dil_h, int dil_w,
+                               int group, int deformable_group, void* stream);
+
 /* a11: epipolar row cross-attention (reference file is empty; SPEC-DERIVED from north_star).  q,k,v,out are
  * bf16 [B,C,H,W]; scores optional fp32 [B,band,H,W] (-inf outside the band). */
 SF_API int sf_epipolar_attn_bf16(const void* q, const void* k, const void* v, void* out, float* scores, int B, int C,
@@ -212,6 +225,14 @@ SF_API int sf_upsample_convex_scaled_f32(const float* disp, const float* mask, f
 SF_API int sf_upsample_convex_gather_f32(const float* disp, const float* mask, float mask_scale, float* out, int N,
                                          int H, int W, int factor, int y_first, int rows, float* const* h_peers,
                                          int n_peers, long long peer_offset, long long peer_batch_stride, void* stream);
+
+/* f1: upsample_simple8(disp, mode='bilinear')  models/utils/upsample.py:40-43 (the LocalCostVolume baseline's output
+ * when no mask head is used, baseline.py:138): factor * F.interpolate(disp, bilinear, align_corners=True).
+ * disp [N,1,H,W] -> out [N,1,factor*H,factor*W]; ATen's index / weight arithmetic op for op, no FMA contraction.
+ * The backward is a deterministic gather (no atomics). */
+SF_API int sf_upsample_simple_f32(const float* disp, float* out, int N, int H, int W, int factor, void* stream);
+SF_API int sf_upsample_simple_backward_f32(const float* grad_out, float* grad_disp, int N, int H, int W, int factor,
+                                           void* stream);
 
 /* f2: ConvGRU.forward gate arithmetic  models/LocalCostVolume/Attempts/update.py:36-49, around the three
  * convolutions (which stay cuDNN).  b_pre / z_pre: conv_b / conv_z outputs BEFORE the sigmoid, [B,C,H,W] with batch

@@ -52,7 +52,12 @@ def import_reference():
                 normalize_coords=normalize_coords)
 
 
+ONLY = set(a for a in sys.argv[1:] if not a.startswith("-"))   # `gen_golden.py NAME ...` rewrites only those files
+
+
 def save(name, **arrs):
+    if ONLY and name not in ONLY:
+        return
     os.makedirs(OUT, exist_ok=True)
     np.savez_compressed(os.path.join(OUT, name + ".npz"),
                         **{k: (v.detach().cpu().numpy() if torch.is_tensor(v) else np.asarray(v))
@@ -269,6 +274,14 @@ def main():
             if t is not None:
                 blob["%s_%d" % (name, k)] = t
     save("gradients", **blob)
+
+    # ---- f1 upsample_simple8 (models/utils/upsample.py:40-43) with its gradient; own seed: added after the others
+    from models.utils.upsample import upsample_simple8
+    torch.manual_seed(79)
+    ds = (torch.rand(2, 1, 5, 9) * 20).requires_grad_(True)
+    us = upsample_simple8(ds)
+    gs = torch.randn(us.shape)
+    save("upsample_simple8", disp=ds, out=us, grad_out=gs, grad_disp=torch.autograd.grad(us, ds, gs)[0])
     print("golden vectors written to", os.path.normpath(OUT))
 
 

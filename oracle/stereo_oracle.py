@@ -361,6 +361,29 @@ def upsample_convex(disp, mask, factor=8, mask_scale=None):
     return u.reshape(N, 1, factor * H, factor * W)
 
 
+def upsample_simple(disp, factor=8):
+    """upsample_simple8, models/utils/upsample.py:40-43: factor * F.interpolate(bilinear, align_corners=True), with
+    ATen's index / weight arithmetic written out (aten/src/ATen/native/UpSample.h: area_pixel_compute_scale,
+    guard_index_and_lambda; cpu/UpSampleKernel.cpp: interpolate over the outer dimension first).  Indices and weights
+    are ATen's; the accumulation order of ATen's vectorised CPU loop is not reproduced, so values agree with the
+    reference to 2 ulp (pinned at 1e-4 px in tests/test_oracle_golden.py), not bit for bit."""
+    N, C, H, W = disp.shape
+
+    def axis(n_in, n_out):
+        scale = (torch.tensor(float(n_in - 1)) / torch.tensor(float(n_out - 1))) if n_out > 1 else torch.tensor(0.0)
+        src = scale * torch.arange(n_out, dtype=torch.float32)
+        i0 = torch.clamp(src.floor().long(), max=n_in - 1)
+        l1 = torch.clamp(src - i0.float(), 0.0, 1.0)
+        i1 = i0 + (i0 < n_in - 1).long()
+        return i0, i1, 1.0 - l1, l1
+
+    y0, y1, ly0, ly1 = axis(H, H * factor)
+    x0, x1, lx0, lx1 = axis(W, W * factor)
+    top = disp[:, :, y0][..., x0] * lx0 + disp[:, :, y0][..., x1] * lx1
+    bot = disp[:, :, y1][..., x0] * lx0 + disp[:, :, y1][..., x1] * lx1
+    return factor * (top * ly0.view(-1, 1) + bot * ly1.view(-1, 1))
+
+
 # --------------------------------------------------------------------------- f2 ("next" row): ConvGRU + DLC step
 def gru_reset(b_pre, prev_h, inp):
     """ConvGRU.forward, Attempts/update.py:43-46 after conv_b: s = cat(sigmoid(b_pre) * prev_h, input)."""

@@ -25,8 +25,8 @@ def _checks(input, weight, bias, offset, kernel_h, kernel_w, group, im2col_step,
         raise RuntimeError("input tensor has to be contiguous")
     if not weight.is_contiguous():
         raise RuntimeError("weight tensor has to be contiguous")
-    if input.dtype != torch.float32:
-        raise RuntimeError("stereoformer_b200 DCN: only float32 is implemented (got %s)" % input.dtype)
+    if input.dtype not in (torch.float32, torch.float64):   # AT_DISPATCH_FLOATING_TYPES, modulated_deform_conv_cuda.cu:93
+        raise RuntimeError("stereoformer_b200 DCN: float32 and float64 are implemented (got %s)" % input.dtype)
     batch, channels = input.shape[0], input.shape[1]
     step = min(batch, im2col_step)
     if batch % step != 0:  # modulated_deform_conv_cuda.cu:58-60 (im2col_step otherwise never changes results)

@@ -40,11 +40,15 @@ SIGNATURES = {
     "sf_guidance_backward_f32": [_p] * 7 + [_c_int] * 6 + [_p],
     "sf_upsample_convex_backward_f32": [_p, _p, _c_float, _p, _p, _p] + [_c_int] * 4 + [_p],
     "sf_dcn_backward_f32": [_p] * 10 + [_c_int] * 15 + [_p],
+    "sf_dcn_forward_f64": [_p] * 6 + [_c_int] * 15 + [_p],
+    "sf_dcn_backward_f64": [_p] * 10 + [_c_int] * 15 + [_p],
     "sf_dcn_workspace_bytes": [_c_int] * 5,
     "sf_dcn_forward_ws_f32": [_p] * 6 + [_c_int] * 15 + [_p, ctypes.c_size_t, _c_int, _p],
     "sf_epipolar_attn_bf16": [_p] * 5 + [_c_int] * 6 + [_p],
     "sf_upsample_convex_f32": [_p, _p, _p] + [_c_int] * 4 + [_p],
     "sf_upsample_convex_scaled_f32": [_p, _p, _c_float, _p] + [_c_int] * 4 + [_p],
+    "sf_upsample_simple_f32": [_p, _p] + [_c_int] * 4 + [_p],
+    "sf_upsample_simple_backward_f32": [_p, _p] + [_c_int] * 4 + [_p],
     "sf_upsample_convex_gather_f32": [_p, _p, _c_float, _p] + [_c_int] * 6 + [_p, _c_int, ctypes.c_longlong,
                                                                               ctypes.c_longlong, _p],
     "sf_gru_reset_f32": [_p, ctypes.c_longlong, _p, _p, _p] + [_c_int] * 5 + [_p],

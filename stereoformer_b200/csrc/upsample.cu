@@ -20,7 +20,7 @@ struct UpPeers {
   long long off, bstride;
 };
 
-template <int F>
+template <int F, bool GATHER>
 __global__ void __launch_bounds__(256)
 upsample_convex_kernel(const float* __restrict__ disp, const float* __restrict__ mask, float* __restrict__ out, int N,
                        int H, int W, float mask_scale, int y_first, int rows, UpPeers peers) {
@@ -76,7 +76,7 @@ upsample_convex_kernel(const float* __restrict__ disp, const float* __restrict__
 #pragma unroll
       for (int j = 0; j < F; ++j) row[j] = res[j];
     }
-    for (int q = 0; q < peers.n; ++q) {
+    for (int q = 0; GATHER && q < peers.n; ++q) {
       float* prow = peers.p[q] + peers.off + static_cast<long long>(b) * peers.bstride + local;
 #pragma unroll
       for (int j = 0; j < F; j += 4)
@@ -135,6 +135,107 @@ upsample_convex_bwd_kernel(const float* __restrict__ disp, const float* __restri
   }
 }
 
+// upsample_simple8 (models/utils/upsample.py:40-43): F * F.interpolate(disp, size = F*(H, W), mode='bilinear',
+// align_corners=True).  ATen's arithmetic (UpSample.h area_pixel_compute_scale / guard_index_and_lambda,
+// UpSampleKernel.cpp interpolate<2>): scale = (in-1)/(out-1) in fp32, src = scale*dst, i0 = min(floor(src), in-1),
+// l1 = clamp(src - i0, 0, 1), l0 = 1 - l1, i1 = i0 + (i0 < in-1); out = lh0*(lw0*a + lw1*b) + lh1*(lw0*c + lw1*d),
+// evaluated without FMA contraction.  One thread per 4 consecutive output pixels (one float4 store); the 4 source
+// values a thread needs are L1/L2 hits (the input is F*F times smaller than the output): write-bound.
+struct Lerp1 { int i0, i1; float l0, l1; };
+
+__device__ __forceinline__ Lerp1 simple_index(float scale, int dst, int in) {
+  Lerp1 r;
+  const float src = __fmul_rn(scale, (float)dst);
+  r.i0 = min((int)floorf(src), in - 1);
+  r.l1 = fminf(fmaxf(__fsub_rn(src, (float)r.i0), 0.f), 1.f);
+  r.l0 = __fsub_rn(1.f, r.l1);
+  r.i1 = r.i0 + (r.i0 < in - 1 ? 1 : 0);
+  return r;
+}
+
+__global__ void __launch_bounds__(128)
+upsample_simple_kernel(const float* __restrict__ disp, float* __restrict__ out, int nrows, int H, int W, int F,
+                       float sh, float sw) {
+  // a block walks output rows (n*Ho + yo); a thread keeps its float4 column and that column's x weights across rows
+  const int Ho = H * F, Wo = W * F, Wq = Wo >> 2;
+  const int xq = blockIdx.y * blockDim.x + threadIdx.x;
+  if (xq >= Wq) return;
+  Lerp1 lx[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) lx[j] = simple_index(sw, 4 * xq + j, W);
+  for (int row = blockIdx.x; row < nrows; row += gridDim.x) {
+    const int yo = row % Ho, b = row / Ho;
+    const Lerp1 ly = simple_index(sh, yo, H);
+    const float* r0 = disp + (static_cast<size_t>(b) * H + ly.i0) * W;
+    const float* r1 = disp + (static_cast<size_t>(b) * H + ly.i1) * W;
+    float res[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float top = __fadd_rn(__fmul_rn(lx[j].l0, __ldg(r0 + lx[j].i0)), __fmul_rn(lx[j].l1, __ldg(r0 + lx[j].i1)));
+      const float bot = __fadd_rn(__fmul_rn(lx[j].l0, __ldg(r1 + lx[j].i0)), __fmul_rn(lx[j].l1, __ldg(r1 + lx[j].i1)));
+      res[j] = __fmul_rn((float)F, __fadd_rn(__fmul_rn(ly.l0, top), __fmul_rn(ly.l1, bot)));
+    }
+    stg_cs_f4(out + static_cast<size_t>(row) * Wo + 4 * xq, make_float4(res[0], res[1], res[2], res[3]));
+  }
+}
+
+// backward of the above: every output pixel adds F * g * (lh, lw weights) to its <= 4 sources.  Gather form: one thread
+// per LOW-resolution pixel sums the output pixels whose footprint touches it (rows/columns within F of it), so the
+// result is deterministic and needs no atomics.
+__global__ void __launch_bounds__(256)
+upsample_simple_bwd_kernel(const float* __restrict__ gout, float* __restrict__ gdisp, int N, int H, int W, int F,
+                           float sh, float sw) {
+  const int Ho = H * F, Wo = W * F;
+  const size_t n = static_cast<size_t>(N) * H * W;
+  for (size_t idx = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; idx < n;
+       idx += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int x = idx % W, y = (idx / W) % H;
+    const size_t b = idx / (static_cast<size_t>(H) * W);
+    // output rows whose i0 or i1 can equal y: src in (y-1, y+1)  ->  dst in ((y-1)/sh, (y+1)/sh); scanned generously
+    const int yo0 = max(0, (int)floorf((float)(y - 1) / sh) - 1), yo1 = min(Ho - 1, (int)ceilf((float)(y + 1) / sh) + 1);
+    const int xo0 = max(0, (int)floorf((float)(x - 1) / sw) - 1), xo1 = min(Wo - 1, (int)ceilf((float)(x + 1) / sw) + 1);
+    constexpr int SPAN = 24;                       // column weights once per pixel (2F + 5 <= 21 candidates at F = 8)
+    float wxs[SPAN];
+    const bool cached = xo1 - xo0 < SPAN;
+    if (cached) {
+#pragma unroll
+      for (int k = 0; k < SPAN; ++k) {
+        const int xo = min(xo0 + k, xo1);
+        const Lerp1 lx = simple_index(sw, xo, W);
+        float wx = 0.f;
+        if (lx.i0 == x) wx += lx.l0;
+        if (lx.i1 == x) wx += lx.l1;
+        wxs[k] = xo0 + k <= xo1 ? wx : 0.f;
+      }
+    }
+    float acc = 0.f;
+    for (int yo = yo0; yo <= yo1; ++yo) {
+      const Lerp1 ly = simple_index(sh, yo, H);
+      float wy = 0.f;
+      if (ly.i0 == y) wy += ly.l0;
+      if (ly.i1 == y) wy += ly.l1;
+      if (wy == 0.f) continue;
+      const float* grow = gout + (b * Ho + yo) * Wo;
+      float racc = 0.f;
+      if (cached) {
+#pragma unroll
+        for (int k = 0; k < SPAN; ++k)
+          if (wxs[k] != 0.f) racc = fmaf(wxs[k], __ldg(grow + xo0 + k), racc);
+      } else {
+        for (int xo = xo0; xo <= xo1; ++xo) {
+          const Lerp1 lx = simple_index(sw, xo, W);
+          float wx = 0.f;
+          if (lx.i0 == x) wx += lx.l0;
+          if (lx.i1 == x) wx += lx.l1;
+          if (wx != 0.f) racc = fmaf(wx, __ldg(grow + xo), racc);
+        }
+      }
+      acc = fmaf(wy, racc, acc);
+    }
+    gdisp[idx] = (float)F * acc;
+  }
+}
+
 }  // namespace sf
 
 static int upsample_convex_impl(const float* disp, const float* mask, float mask_scale, float* out, int N, int H, int W,
@@ -164,10 +265,11 @@ static int upsample_convex_impl(const float* disp, const float* mask, float mask
   size_t n = static_cast<size_t>(N) * rows * W * factor;
   int grid = static_cast<int>(min(static_cast<size_t>(sm_count()) * 8, (n + 255) / 256));
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  if (factor == 8)
-    upsample_convex_kernel<8><<<grid, 256, 0, s>>>(disp, mask, out, N, H, W, mask_scale, y_first, rows, peers);
-  else
-    upsample_convex_kernel<4><<<grid, 256, 0, s>>>(disp, mask, out, N, H, W, mask_scale, y_first, rows, peers);
+#define SF_UP_LAUNCH(F, G) \
+  upsample_convex_kernel<F, G><<<grid, 256, 0, s>>>(disp, mask, out, N, H, W, mask_scale, y_first, rows, peers)
+  if (factor == 8) { if (n_peers) SF_UP_LAUNCH(8, true); else SF_UP_LAUNCH(8, false); }
+  else { if (n_peers) SF_UP_LAUNCH(4, true); else SF_UP_LAUNCH(4, false); }
+#undef SF_UP_LAUNCH
   SF_LAUNCH_CHECK();
   return SF_OK;
 }
@@ -203,6 +305,46 @@ extern "C" int sf_upsample_convex_backward_f32(const float* disp, const float* m
   int grid = static_cast<int>(min(static_cast<size_t>(sm_count()) * 8, (n + 255) / 256));
   if (factor == 8) upsample_convex_bwd_kernel<8><<<grid, 256, 0, s>>>(disp, mask, grad_out, grad_disp, grad_mask, N, H, W, mask_scale);
   else upsample_convex_bwd_kernel<4><<<grid, 256, 0, s>>>(disp, mask, grad_out, grad_disp, grad_mask, N, H, W, mask_scale);
+  SF_LAUNCH_CHECK();
+  return SF_OK;
+}
+
+static int simple_scales(int H, int W, int factor, float* sh, float* sw) {
+  SF_CHECK_ARG(H > 0 && W > 0 && factor >= 1 && (W * factor) % 4 == 0,
+               "upsample_simple: need positive sizes and an output width that is a multiple of 4");
+  // area_pixel_compute_scale<float>(in, out, align_corners=true): (in-1)/(out-1), 0 when out == 1
+  *sh = H * factor > 1 ? static_cast<float>(H - 1) / static_cast<float>(H * factor - 1) : 0.f;
+  *sw = W * factor > 1 ? static_cast<float>(W - 1) / static_cast<float>(W * factor - 1) : 0.f;
+  return SF_OK;
+}
+
+extern "C" int sf_upsample_simple_f32(const float* disp, float* out, int N, int H, int W, int factor, void* stream) {
+  using namespace sf;
+  SF_CHECK_ARG(disp && out && N > 0, "upsample_simple: null pointer / empty batch");
+  SF_CHECK_ARG((reinterpret_cast<uintptr_t>(out) & 15) == 0, "upsample_simple: out must be 16-byte aligned");
+  float sh, sw;
+  if (int rc = simple_scales(H, W, factor, &sh, &sw)) return rc;
+  const long long rows = 1LL * N * H * factor;
+  SF_CHECK_ARG(rows < (1LL << 31), "upsample_simple: too many output rows");
+  const int ychunks = (W * factor / 4 + 127) / 128;
+  dim3 grid(static_cast<unsigned>(min(rows, static_cast<long long>(sm_count()) * 16 / ychunks + 1)), ychunks);
+  upsample_simple_kernel<<<grid, 128, 0, static_cast<cudaStream_t>(stream)>>>(disp, out, static_cast<int>(rows), H, W,
+                                                                              factor, sh, sw);
+  SF_LAUNCH_CHECK();
+  return SF_OK;
+}
+
+extern "C" int sf_upsample_simple_backward_f32(const float* grad_out, float* grad_disp, int N, int H, int W, int factor,
+                                               void* stream) {
+  using namespace sf;
+  SF_CHECK_ARG(grad_out && grad_disp && N > 0, "upsample_simple_backward: null pointer / empty batch");
+  SF_CHECK_ARG(H > 1 && W > 1, "upsample_simple_backward: needs H, W > 1");
+  float sh, sw;
+  if (int rc = simple_scales(H, W, factor, &sh, &sw)) return rc;
+  size_t n = static_cast<size_t>(N) * H * W;
+  int grid = static_cast<int>(min(static_cast<size_t>(sm_count()) * 8, (n + 255) / 256));
+  upsample_simple_bwd_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(grad_out, grad_disp, N, H, W, factor,
+                                                                                 sh, sw);
   SF_LAUNCH_CHECK();
   return SF_OK;
 }

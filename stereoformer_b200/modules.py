@@ -257,3 +257,12 @@ def upsample_convex8(disp, mask):
     """models/utils/upsample.py:22-38."""
     return _run(lambda d, m: ops.upsample_convex(d, m, 8), "upsample_convex8", disp, mask,
                 bwd=lambda a, g, n: ops.upsample_convex_backward(a[0], a[1], g, 8, 1.0, n))
+
+
+def upsample_simple8(disp, mode='bilinear'):
+    """models/utils/upsample.py:40-43: 8 * F.interpolate(disp, size=8x, mode=mode, align_corners=True)."""
+    if mode != 'bilinear':
+        raise NotImplementedError("upsample_simple8: only mode='bilinear' (the reference's default and only use, "
+                                  "baseline.py:138) is built")
+    return _run(lambda d: ops.upsample_simple(d, 8), "upsample_simple8", disp,
+                bwd=lambda a, g, n: (ops.upsample_simple_backward(g, 8),))

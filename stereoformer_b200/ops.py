@@ -277,9 +277,10 @@ def dcn_forward(inp, weight, bias, offset, mask, stride, padding, dilation, grou
 
     algo: SF_ALGO_AUTO (tcgen05 implicit GEMM from 32 channels per group, exact FFMA kernel below),
     SF_ALGO_GENERIC (exact FFMA kernel), SF_ALGO_TC (force the tensor-core path)."""
-    inp, weight = _chk(inp, "input", dim=4), _chk(weight, "weight", dim=4)
-    bias, offset = _chk(bias, "bias"), _chk(offset, "offset", dim=4)
-    mask = _chk(mask, "mask", dim=4) if mask is not None else None
+    dt = inp.dtype if torch.is_tensor(inp) and inp.dtype == torch.float64 else torch.float32   # fp64: verification dtype
+    inp, weight = _chk(inp, "input", dt, dim=4), _chk(weight, "weight", dt, dim=4)
+    bias, offset = _chk(bias, "bias", dt), _chk(offset, "offset", dt, dim=4)
+    mask = _chk(mask, "mask", dt, dim=4) if mask is not None else None
     B, Cin, H, W = inp.shape
     Cout, Cg, kh, kw = weight.shape
     sh, sw = stride
@@ -294,7 +295,12 @@ def dcn_forward(inp, weight, bias, offset, mask, stride, padding, dilation, grou
                                                              (B, deformable_groups * 2 * kh * kw, Ho, Wo)))
     if mask is not None and mask.shape != (B, deformable_groups * kh * kw, Ho, Wo):
         raise RuntimeError("mask shape %s, expected %s" % (tuple(mask.shape), (B, deformable_groups * kh * kw, Ho, Wo)))
-    out = torch.empty((B, Cout, Ho, Wo), device=inp.device, dtype=torch.float32)
+    out = torch.empty((B, Cout, Ho, Wo), device=inp.device, dtype=dt)
+    if dt == torch.float64:
+        with torch.cuda.device(inp.device):
+            _lib.call("sf_dcn_forward_f64", _ptr(inp), _ptr(weight), _ptr(bias), _ptr(offset), _ptr(mask), _ptr(out), B,
+                      Cin, H, W, Cout, kh, kw, sh, sw, ph, pw, dh, dw, int(groups), int(deformable_groups), _stream())
+        return out
     with torch.cuda.device(inp.device):
         nws = int(_lib.lib().sf_dcn_workspace_bytes(Cin, Cout, kh, kw, int(groups))) if algo != SF_ALGO_GENERIC else 0
         ws = torch.empty(nws, device=inp.device, dtype=torch.uint8) if nws else None   # bf16 hi/mid weights (scratch)
@@ -437,9 +443,10 @@ def dcn_backward(inp, weight, offset, mask, grad_out, stride, padding, dilation,
     """DCNv2 / DCNv1 (mask None) backward -> (grad_input, grad_offset, grad_mask, grad_weight, grad_bias), the order
     of the reference's DCN.modulated_deform_conv_backward (modulated_deform_conv_cuda.cu:277-279); entries whose
     ``needs`` flag is False (or grad_mask for DCNv1) are None."""
-    inp, weight = _chk(inp, "input", dim=4), _chk(weight, "weight", dim=4)
-    offset, grad_out = _chk(offset, "offset", dim=4), _chk(grad_out, "grad_output", dim=4)
-    mask = _chk(mask, "mask", dim=4) if mask is not None else None
+    dt = inp.dtype if torch.is_tensor(inp) and inp.dtype == torch.float64 else torch.float32
+    inp, weight = _chk(inp, "input", dt, dim=4), _chk(weight, "weight", dt, dim=4)
+    offset, grad_out = _chk(offset, "offset", dt, dim=4), _chk(grad_out, "grad_output", dt, dim=4)
+    mask = _chk(mask, "mask", dt, dim=4) if mask is not None else None
     B, Cin, H, W = inp.shape
     Cout, Cg, kh, kw = weight.shape
     sh, sw = stride
@@ -460,9 +467,9 @@ def dcn_backward(inp, weight, offset, mask, grad_out, stride, padding, dilation,
     g_off = torch.empty_like(offset) if n_off else None
     g_mask = torch.empty_like(mask) if n_mask else None
     g_w = torch.empty_like(weight) if n_w else None
-    g_b = torch.empty(Cout, device=inp.device, dtype=torch.float32) if n_b else None
+    g_b = torch.empty(Cout, device=inp.device, dtype=dt) if n_b else None
     with torch.cuda.device(inp.device):
-        _lib.call("sf_dcn_backward_f32", _ptr(inp), _ptr(weight), _ptr(offset), _ptr(mask), _ptr(grad_out), _ptr(g_in),
+        _lib.call("sf_dcn_backward_f64" if dt == torch.float64 else "sf_dcn_backward_f32", _ptr(inp), _ptr(weight), _ptr(offset), _ptr(mask), _ptr(grad_out), _ptr(g_in),
                   _ptr(g_w), _ptr(g_b), _ptr(g_off), _ptr(g_mask), B, Cin, H, W, Cout, kh, kw, sh, sw, ph, pw, dh, dw,
                   int(groups), int(deformable_groups), _stream())
     return g_in, g_off, g_mask, g_w, g_b
@@ -502,6 +509,26 @@ def upsample_convex(disp, mask, factor=8, mask_scale=1.0, out=None):
             _lib.call("sf_upsample_convex_scaled_f32", _ptr(disp), _ptr(mask), float(mask_scale), _ptr(out), N, H, W,
                       int(factor), _stream())
     return out
+
+
+def upsample_simple(disp, factor=8):
+    """upsample_simple8: factor * bilinear(align_corners=True) resize by ``factor`` -> [N,1,F*H,F*W]."""
+    disp = _chk(disp, "disp", dim=4)
+    N, C, H, W = disp.shape
+    out = torch.empty((N, C, factor * H, factor * W), device=disp.device, dtype=torch.float32)
+    with torch.cuda.device(disp.device):
+        _lib.call("sf_upsample_simple_f32", _ptr(disp), _ptr(out), N * C, H, W, int(factor), _stream())
+    return out
+
+
+def upsample_simple_backward(grad_out, factor=8):
+    grad_out = _chk(grad_out, "grad_out", dim=4)
+    N, C, Ho, Wo = grad_out.shape
+    gd = torch.empty((N, C, Ho // factor, Wo // factor), device=grad_out.device, dtype=torch.float32)
+    with torch.cuda.device(grad_out.device):
+        _lib.call("sf_upsample_simple_backward_f32", _ptr(grad_out), _ptr(gd), N * C, Ho // factor, Wo // factor,
+                  int(factor), _stream())
+    return gd
 
 
 def upsample_convex_rows(disp_src, mask_src, y_first, rows, factor=8, mask_scale=1.0, peers=None, peer_offset=0,

@@ -126,8 +126,9 @@ def test_pack_module_trains_one_step():
 
 
 def test_gradcheck_like_reference():
-    """deform/test.py:304-349 runs torch.autograd.gradcheck in double on the CUDA op; this build is float32-only, so
-    the same check is a central-difference probe of a few offset / mask / input entries with float32 tolerances."""
+    """The float32 kernels under the same kind of check as deform/test.py:304-349: a central-difference probe of a few
+    offset / mask / input entries with float32 tolerances (the double-precision gradcheck itself is
+    test_reference_gradcheck_double below)."""
     import stereoformer_b200.ops as ops
     c = CFGS[0]
     x, w, b, off, msk, go = (t.cuda() for t in _inputs(c, True, seed=5))
@@ -151,3 +152,52 @@ def test_gradcheck_like_reference():
             # offsets: the bilinear surface is piecewise linear, a kink inside +-eps breaks the difference quotient
             tol = 0.15 if which == "off" else 2e-2
             assert abs(num - g[idx].item()) < tol * max(1.0, abs(num)), (which, idx, num, g[idx].item())
+
+
+# ------------------------------------------------------------------------------------------ double precision
+@pytest.mark.parametrize("cfg", CFGS[:4] + CFGS[7:])
+@pytest.mark.parametrize("v2", [True, False])
+def test_dcn_f64_forward_backward_vs_oracle(cfg, v2):
+    """The reference dispatches float and double (modulated_deform_conv_cuda.cu:93): sf_dcn_forward_f64 /
+    sf_dcn_backward_f64 against autograd through the oracle's float64 dense restatement (1e-10)."""
+    from oracle import stereo_oracle as O
+    from stereoformer_b200 import DCN
+    x, w, b, off, msk, go = (t.double() if t is not None else None for t in _inputs(cfg, v2))
+    k, s, p, d = cfg["k"], cfg["s"], cfg["p"], cfg["d"]
+    leaves = [t.clone().requires_grad_(True) for t in (x, off, w, b)] + ([msk.clone().requires_grad_(True)] if v2 else [])
+    ref_out = O.dcn_forward(leaves[0], leaves[2], leaves[3], leaves[1], leaves[4] if v2 else None, (s, s), (p, p), (d, d),
+                            cfg["G"], cfg["dg"])
+    ref = torch.autograd.grad(ref_out, leaves, go)
+    cu = lambda t: t.cuda()
+    if v2:
+        out = DCN.modulated_deform_conv_forward(cu(x), cu(w), cu(b), cu(off), cu(msk), k, k, s, s, p, p, d, d, cfg["G"],
+                                                cfg["dg"], 64)
+        g_in, g_off, g_m, g_w, g_b = DCN.modulated_deform_conv_backward(cu(x), cu(w), cu(b), cu(off), cu(msk), cu(go), k,
+                                                                       k, s, s, p, p, d, d, cfg["G"], cfg["dg"], 64)
+        assert (g_m.cpu() - ref[4]).abs().max() < 1e-10
+    else:
+        out = DCN.deform_conv_forward(cu(x), cu(w), cu(b), cu(off), k, k, s, s, p, p, d, d, cfg["G"], cfg["dg"], 64)
+        g_in, g_off, g_w, g_b = DCN.deform_conv_backward(cu(x), cu(w), cu(b), cu(off), cu(go), k, k, s, s, p, p, d, d,
+                                                         cfg["G"], cfg["dg"], 64)
+    assert out.dtype == torch.float64 and (out.cpu() - ref_out.detach()).abs().max() < 1e-10
+    for n, a, r in zip(("input", "offset", "weight", "bias"), (g_in, g_off, g_w, g_b), ref):
+        assert a.dtype == torch.float64 and (a.cpu() - r).abs().max() < 1e-9, n
+
+
+def test_reference_gradcheck_double():
+    """deform/test.py:376-403 (check_gradient_dconv) and :405-434 (check_gradient_mdconv) as the reference runs them:
+    torch.autograd.gradcheck on the autograd Functions with the reference's shapes (N,inC,inH,inW = 2,4,4,4; outC 4;
+    3x3; groups 2; seed 3; deform/test.py:15-21) and tolerances (eps 1e-3, atol 1e-3, rtol 1e-2), in double."""
+    from torch.autograd import gradcheck
+    from stereoformer_b200.dcn_modules import DeformConvFunction, ModulatedDeformConvFunction
+    torch.manual_seed(3)
+    N, inC, inH, inW, outC, kH, kW, groups, dgs = 2, 4, 4, 4, 4, 3, 3, 2, 1
+    inp = (torch.rand(N, inC, inH, inW).double().cuda() * 0.01).requires_grad_(True)
+    offset = (torch.randn(N, dgs * 2 * kW * kH, inH, inW).double().cuda() * 2).requires_grad_(True)
+    weight = torch.randn(outC, inC // groups, kH, kW).double().cuda().requires_grad_(True)
+    bias = torch.rand(outC).double().cuda().requires_grad_(True)
+    assert gradcheck(DeformConvFunction.apply, (inp, offset, weight, bias, 1, 1, 1, groups, dgs, 1),
+                     eps=1e-3, atol=1e-3, rtol=1e-2, raise_exception=True, nondet_tol=1e-12)
+    mask = torch.sigmoid(torch.rand(N, dgs * kW * kH, inH, inW).double().cuda()).requires_grad_(True)
+    assert gradcheck(ModulatedDeformConvFunction.apply, (inp, offset, mask, weight, bias, 1, 1, 1, groups, dgs, 1),
+                     eps=1e-3, atol=1e-3, rtol=1e-2, raise_exception=True, nondet_tol=1e-12)

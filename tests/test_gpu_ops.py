@@ -273,6 +273,32 @@ def test_upsample_convex_golden(ops):
     assert torch.allclose(ops.upsample_convex(dev(d), dev(m), 4).cpu(), O.upsample_convex(d, m, 4), rtol=1e-4, atol=1e-4)
 
 
+@pytest.mark.parametrize("shape", [(2, 1, 5, 9), (1, 1, 68, 120), (1, 1, 2, 3)])
+def test_upsample_simple8(ops, shape):
+    """upsample_simple8 (models/utils/upsample.py:40-43): golden vector of the reference, the oracle, and PyTorch's
+    own CUDA kernel on the same device (1e-4 px; values reach 8*disp)."""
+    import torch.nn.functional as F
+    import stereoformer_b200 as sf
+    g = load_golden("upsample_simple8")
+    out = sf.upsample_simple8(dev(g["disp"].detach()))
+    assert out.shape == g["out"].shape and (out.cpu() - g["out"]).abs().max() < 1e-4
+    dg = dev(g["disp"].detach()).requires_grad_(True)
+    gd = torch.autograd.grad(sf.upsample_simple8(dg), dg, dev(g["grad_out"]))[0]
+    assert torch.allclose(gd.cpu(), g["grad_disp"], rtol=1e-5, atol=1e-4)
+    torch.manual_seed(48)
+    d = torch.rand(*shape) * 24
+    got = ops.upsample_simple(dev(d), 8)
+    assert (got.cpu() - O.upsample_simple(d, 8)).abs().max() < 1e-4
+    Hh, Ww = shape[2] * 8, shape[3] * 8
+    assert (got - 8 * F.interpolate(dev(d), size=(Hh, Ww), mode="bilinear", align_corners=True)).abs().max() < 1e-4
+    go = torch.randn(shape[0], 1, Hh, Ww)
+    d2 = d.clone().requires_grad_(True)
+    ref_g = torch.autograd.grad(O.upsample_simple(d2, 8), d2, go)[0]
+    assert torch.allclose(ops.upsample_simple_backward(dev(go), 8).cpu(), ref_g, rtol=1e-5, atol=1e-4)
+    with pytest.raises(NotImplementedError):
+        sf.upsample_simple8(dev(d), mode="nearest")
+
+
 # ------------------------------------------------------------------------------------------ drop-in modules
 def test_dropin_modules_chain():
     """The LowCNN LC hot-path chain (baseline.py:114-127) through the drop-in nn.Modules."""

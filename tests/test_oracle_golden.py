@@ -91,6 +91,15 @@ def test_corr1d():
     assert eq(O.corr1d_lookup(pyr, g["coords"], g["radius"], g["num_levels"]), g["lookup"])
 
 
+def test_upsample_simple8():
+    g = load_golden("upsample_simple8")
+    out = O.upsample_simple(g["disp"], 8)
+    assert (out - g["out"]).abs().max() < 1e-4                     # px, values up to 160 (2 ulp)
+    d = g["disp"].clone().requires_grad_(True)
+    gd = torch.autograd.grad(O.upsample_simple(d, 8), d, g["grad_out"])[0]
+    assert torch.allclose(gd, g["grad_disp"], rtol=1e-5, atol=1e-4)
+
+
 def test_upsample_convex8():
     g = load_golden("upsample_convex8")
     assert eq(O.upsample_convex(g["disp"], g["mask"], 8), g["out"])

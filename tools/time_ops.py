@@ -37,6 +37,7 @@ timeit("local_window variance", lambda: ops.local_window(cv, disp, mode=ops.SF_W
 timeit("soft_argmin", lambda: ops.soft_argmin(cv), (D + 1) * px * 4)
 timeit("disp_warp", lambda: ops.disp_warp(img, disp, check=False), (3 * 3 + 1) * px * 4)
 timeit("upsample_convex8", lambda: ops.upsample_convex(disp, mask, 8), (576 + 1 + 64) * px * 4)
+timeit("upsample_simple8", lambda: ops.upsample_simple(disp, 8), (1 + 64) * px * 4)
 
 # ---- f2 / f3 kernels at the same shape (C2: B=8, 68x120, D=24, features 256 ch, hidden 64)
 C = 64
@@ -59,4 +60,5 @@ timeit("local_window backward (head)", lambda: ops.local_window_backward(cv, dis
                                                                           True), (2 * D + 7) * px * 4)
 timeit("disp_warp backward", lambda: ops.disp_warp_backward(img, disp, img), (3 * 3 * 2 + 2) * px * 4)
 gfull = torch.randn(B, 1, 8 * H, 8 * W, device="cuda")
+timeit("upsample_simple8 backward", lambda: ops.upsample_simple_backward(gfull, 8), (1 + 64) * px * 4)
 timeit("upsample_convex8 backward", lambda: ops.upsample_convex_backward(disp, mask, gfull, 8), (2 * 576 + 2 + 64) * px * 4)
