@@ -12,6 +12,7 @@
 // multiplied with a transposed weight tile from registers-tiled FFMAs, and the epilogue adds the bias and
 // writes NCHW directly.  No column buffer, no permute, no im2col_step loop (it never affected results:
 // deform/test.py:219-260).
+#include <cstdlib>
 #include "common.cuh"
 #include "dcn_tc.cuh"
 #include "../../include/stereoformer_b200.h"
@@ -167,6 +168,135 @@ static int launch_dcn(const DcnParams& p, cudaStream_t s) {
   return SF_OK;
 }
 
+
+// ---------------------------------------------------------------------------------------------- small channel counts
+// The shipped model's DCN is 16 -> 16 channels (pure_learning_method.py:52, resnet.py:57): 0.3 GFLOP and 15 MB at
+// C2 x 8, but 37 M bilinear corner gathers.  Through L1 a warp-level gather with learned offsets touches ~20 sectors,
+// which bounds the generic kernel above at ~60 us.  Here a CTA owns an 8 x 32 pixel tile, one thread per output pixel,
+// and first stages the input patch the tile can reach with offsets up to DS_R (8) pixels -- all channels, zero-filled
+// outside the image (which IS the reference's per-corner zero padding and its (-1,H)x(-1,W) test, .cuh:37-48,180) --
+// in shared memory, so the data-dependent gathers become shared-memory reads.  A corner outside the staged patch
+// (|offset| > DS_R) takes the global-memory path with the explicit tests.  Weights are staged transposed
+// ([c][t][o], o padded to 16) and read as broadcast float4s.  45 us against 60 us at C2 x 8; ncu: 27 M warp
+// instructions, 44 % of them the patch fill's index arithmetic, issue-bound at 1.8 IPC with 16 warps per SM.
+// Measured and not kept: two threads per pixel on alternate channels (51 us), two 8-channel passes (64 us), a
+// warp-per-row fill (slower than the flat loop), and a TMA box for the patch (one cp.async.bulk.tensor per CTA; it ran
+// for 16 input channels but raised an illegal-instruction fault with fewer, cause not found, so it is not shipped).
+constexpr int DS_TY = 8, DS_TX = 32, DS_MAXC = 16;
+static int ds_halo() {
+  static const int r = getenv("SF_DCN_R") ? atoi(getenv("SF_DCN_R")) : 8;   // sweep hook (tools/)
+  return r;
+}
+
+__global__ void __launch_bounds__(DS_TY * DS_TX)
+dcn_small_kernel(const DcnParams p, int RH, int RW, int RWp, int DS_R) {
+  extern __shared__ __align__(16) float ds_smem[];
+  const int T = p.kh * p.kw, M = p.Ho * p.Wo;
+  float* wsm = ds_smem;                                   // [Cin*T][16]
+  float* reg = ds_smem + p.Cin * T * DS_MAXC;             // [Cin][RH][RWp]
+  const int tid = threadIdx.x, b = blockIdx.z;
+  const int ty0 = blockIdx.y * DS_TY, tx0 = blockIdx.x * DS_TX;
+  const int RY0 = ty0 * p.sh - p.ph - DS_R, RX0 = tx0 * p.sw - p.pw - DS_R;
+  const size_t HW = static_cast<size_t>(p.H) * p.W;
+
+  for (int e = tid; e < p.Cin * T * DS_MAXC; e += DS_TY * DS_TX) {
+    const int o = e % DS_MAXC, k = e / DS_MAXC;           // k = c*T + t
+    wsm[e] = o < p.Cout ? __ldg(p.weight + static_cast<size_t>(o) * p.Cin * T + k) : 0.f;
+  }
+  const int RHW = RH * RW;
+  for (int e = tid; e < p.Cin * RHW; e += DS_TY * DS_TX) {
+    const int c = e / RHW, r = e - c * RHW, yy = r / RW, xx = r - yy * RW;
+    const int gy = RY0 + yy, gx = RX0 + xx;
+    float v = 0.f;
+    if (gy >= 0 && gy < p.H && gx >= 0 && gx < p.W) v = __ldg(p.in + (static_cast<size_t>(b) * p.Cin + c) * HW + gy * p.W + gx);
+    reg[(c * RH + yy) * RWp + xx] = v;
+  }
+  __syncthreads();
+
+  const int yo = ty0 + tid / DS_TX, xo = tx0 + tid % DS_TX;
+  if (yo >= p.Ho || xo >= p.Wo) return;
+  const int pix = yo * p.Wo + xo, cpdg = p.Cin / p.dg;
+  float acc[DS_MAXC];
+#pragma unroll
+  for (int o = 0; o < DS_MAXC; ++o) acc[o] = 0.f;
+
+  for (int dgi = 0; dgi < p.dg; ++dgi) {
+    const size_t ob = ((static_cast<size_t>(b) * p.dg + dgi) * 2 * T) * M + pix;
+    for (int t = 0; t < T; ++t) {
+      const int i = t / p.kw, j = t - i * p.kw;
+      const float oh = __ldg(p.offset + ob + static_cast<size_t>(2 * t) * M);
+      const float ow = __ldg(p.offset + ob + static_cast<size_t>(2 * t + 1) * M);
+      const float m = p.mask ? __ldg(p.mask + ((static_cast<size_t>(b) * p.dg + dgi) * T + t) * M + pix) : 1.f;
+      const float h_im = (float)(yo * p.sh - p.ph + i * p.dh) + oh;
+      const float w_im = (float)(xo * p.sw - p.pw + j * p.dw) + ow;
+      const float hlf = floorf(h_im), wlf = floorf(w_im);
+      const float lh = h_im - hlf, lw = w_im - wlf, hh = 1.f - lh, hw = 1.f - lw;
+      const float w1 = hh * hw, w2 = hh * lw, w3 = lh * hw, w4 = lh * lw;
+      const bool staged = hlf >= (float)RY0 && hlf <= (float)(RY0 + RH - 2) && wlf >= (float)RX0 &&
+                          wlf <= (float)(RX0 + RW - 2);
+      if (staged) {
+        const float* q = reg + ((int)hlf - RY0) * RWp + ((int)wlf - RX0);
+        for (int c = dgi * cpdg; c < (dgi + 1) * cpdg; ++c) {
+          const float* qc = q + c * RH * RWp;
+          const float val = (w1 * qc[0] + w2 * qc[1] + w3 * qc[RWp] + w4 * qc[RWp + 1]) * m;
+          const float4* wr = reinterpret_cast<const float4*>(wsm + (c * T + t) * DS_MAXC);
+#pragma unroll
+          for (int o4 = 0; o4 < DS_MAXC / 4; ++o4) {
+            const float4 w = wr[o4];
+            acc[4 * o4] = fmaf(w.x, val, acc[4 * o4]);
+            acc[4 * o4 + 1] = fmaf(w.y, val, acc[4 * o4 + 1]);
+            acc[4 * o4 + 2] = fmaf(w.z, val, acc[4 * o4 + 2]);
+            acc[4 * o4 + 3] = fmaf(w.w, val, acc[4 * o4 + 3]);
+          }
+        }
+      } else if (h_im > -1.f && w_im > -1.f && h_im < (float)p.H && w_im < (float)p.W) {
+        const int hl = (int)hlf, wl = (int)wlf;
+        const bool t0 = hl >= 0, l0 = wl >= 0, b1 = hl + 1 <= p.H - 1, r1 = wl + 1 <= p.W - 1;
+        for (int c = dgi * cpdg; c < (dgi + 1) * cpdg; ++c) {
+          const float* src = p.in + (static_cast<size_t>(b) * p.Cin + c) * HW + static_cast<ptrdiff_t>(hl) * p.W + wl;
+          const float v1 = (t0 && l0) ? __ldg(src) : 0.f, v2 = (t0 && r1) ? __ldg(src + 1) : 0.f;
+          const float v3 = (b1 && l0) ? __ldg(src + p.W) : 0.f, v4 = (b1 && r1) ? __ldg(src + p.W + 1) : 0.f;
+          const float val = (w1 * v1 + w2 * v2 + w3 * v3 + w4 * v4) * m;
+          const float* wr = wsm + (c * T + t) * DS_MAXC;
+#pragma unroll
+          for (int o = 0; o < DS_MAXC; ++o) acc[o] = fmaf(wr[o], val, acc[o]);
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int o = 0; o < DS_MAXC; ++o)
+    if (o < p.Cout) p.out[(static_cast<size_t>(b) * p.Cout + o) * M + pix] = acc[o] + __ldg(p.bias + o);
+}
+
+static void dcn_small_region(const DcnParams& p, int* RH, int* RW, int* RWp, size_t* smem) {
+  const int DS_R = ds_halo();
+  *RH = (DS_TY - 1) * p.sh + p.dh * (p.kh - 1) + 2 * DS_R + 2;
+  *RW = (DS_TX - 1) * p.sw + p.dw * (p.kw - 1) + 2 * DS_R + 2;
+  *RWp = *RW | 1;                                          // odd pitch: rows land in different banks
+  *smem = (static_cast<size_t>(p.Cin) * p.kh * p.kw * DS_MAXC + static_cast<size_t>(p.Cin) * *RH * *RWp) * 4;
+}
+
+static bool dcn_small_eligible(const DcnParams& p) {
+  if (p.G != 1 || p.Cin > DS_MAXC || p.Cout > DS_MAXC || p.B > 65535) return false;
+  int RH, RW, RWp;
+  size_t smem;
+  dcn_small_region(p, &RH, &RW, &RWp, &smem);
+  return smem <= 100 * 1024;
+}
+
+static int launch_dcn_small(const DcnParams& p, cudaStream_t s) {
+  int RH, RW, RWp;
+  size_t smem;
+  dcn_small_region(p, &RH, &RW, &RWp, &smem);
+  SF_CUDA(cudaFuncSetAttribute(dcn_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+  dim3 grid(ceil_div(p.Wo, DS_TX), ceil_div(p.Ho, DS_TY), p.B);
+  SF_CHECK_ARG(grid.y <= 65535, "dcn_forward: output too tall");
+  dcn_small_kernel<<<grid, DS_TY * DS_TX, smem, s>>>(p, RH, RW, RWp, ds_halo());
+  SF_LAUNCH_CHECK();
+  return SF_OK;
+}
+
 }  // namespace sf
 
 static int dcn_forward_impl(const float* input, const float* weight, const float* bias, const float* offset,
@@ -207,6 +337,10 @@ static int dcn_forward_impl(const float* input, const float* weight, const float
     if (handled) return SF_OK;
     SF_CHECK_ARG(algo != SF_ALGO_TC, "dcn_forward: the tensor-core path needs %zu workspace bytes (got %zu) and <= 256 "
                  "output channels per group", dcn_tc_workspace_bytes(Cin, Cout, kh, kw, group), workspace_bytes);
+  }
+  if (dcn_small_eligible(p)) {
+    static const bool off = getenv("SF_DCN_SMALL") && atoi(getenv("SF_DCN_SMALL")) == 0;   // A/B timing hook (tools/)
+    if (!off) return launch_dcn_small(p, s);
   }
   if (Cog <= 16) return launch_dcn<16, 128>(p, s);
   if (Cog <= 32) return launch_dcn<32, 128>(p, s);
