@@ -177,7 +177,7 @@ static int launch_dcn(const DcnParams& p, cudaStream_t s) {
 // outside the image (which IS the reference's per-corner zero padding and its (-1,H)x(-1,W) test, .cuh:37-48,180) --
 // in shared memory, so the data-dependent gathers become shared-memory reads.  A corner outside the staged patch
 // (|offset| > DS_R) takes the global-memory path with the explicit tests.  Weights are staged transposed
-// ([c][t][o], o padded to 16) and read as broadcast float4s.  45 us against 60 us at C2 x 8; ncu: 27 M warp
+// ([c][t][o], o padded to 16) and read as broadcast float4s.  43 us against 60 us at C2 x 8; ncu (first version): 27 M warp
 // instructions, 44 % of them the patch fill's index arithmetic, issue-bound at 1.8 IPC with 16 warps per SM.
 // Measured and not kept: two threads per pixel on alternate channels (51 us), two 8-channel passes (64 us), a
 // warp-per-row fill (slower than the flat loop), and a TMA box for the patch (one cp.async.bulk.tensor per CTA; it ran
@@ -189,7 +189,7 @@ static int ds_halo() {
 }
 
 __global__ void __launch_bounds__(DS_TY * DS_TX)
-dcn_small_kernel(const DcnParams p, int RH, int RW, int RWp, int DS_R) {
+dcn_small_kernel(const DcnParams p, int RH, int RW, int RWp, int DS_R, unsigned rw_magic) {
   extern __shared__ __align__(16) float ds_smem[];
   const int T = p.kh * p.kw, M = p.Ho * p.Wo;
   float* wsm = ds_smem;                                   // [Cin*T][16]
@@ -203,13 +203,18 @@ dcn_small_kernel(const DcnParams p, int RH, int RW, int RWp, int DS_R) {
     const int o = e % DS_MAXC, k = e / DS_MAXC;           // k = c*T + t
     wsm[e] = o < p.Cout ? __ldg(p.weight + static_cast<size_t>(o) * p.Cin * T + k) : 0.f;
   }
+  // flat over the RH x RW cells of one channel plane; r / RW by multiply-high (exact: r < 2^16, magic = 2^32/RW + 1)
   const int RHW = RH * RW;
-  for (int e = tid; e < p.Cin * RHW; e += DS_TY * DS_TX) {
-    const int c = e / RHW, r = e - c * RHW, yy = r / RW, xx = r - yy * RW;
-    const int gy = RY0 + yy, gx = RX0 + xx;
-    float v = 0.f;
-    if (gy >= 0 && gy < p.H && gx >= 0 && gx < p.W) v = __ldg(p.in + (static_cast<size_t>(b) * p.Cin + c) * HW + gy * p.W + gx);
-    reg[(c * RH + yy) * RWp + xx] = v;
+  for (int c = 0; c < p.Cin; ++c) {
+    const float* plane = p.in + (static_cast<size_t>(b) * p.Cin + c) * HW;
+    float* dstc = reg + c * RH * RWp;
+    for (int r = tid; r < RHW; r += DS_TY * DS_TX) {
+      const int yy = static_cast<int>(__umulhi(static_cast<unsigned>(r), rw_magic)), xx = r - yy * RW;
+      const int gy = RY0 + yy, gx = RX0 + xx;
+      float v = 0.f;
+      if (gy >= 0 && gy < p.H && gx >= 0 && gx < p.W) v = __ldg(plane + gy * p.W + gx);
+      dstc[yy * RWp + xx] = v;
+    }
   }
   __syncthreads();
 
@@ -292,7 +297,9 @@ static int launch_dcn_small(const DcnParams& p, cudaStream_t s) {
   SF_CUDA(cudaFuncSetAttribute(dcn_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
   dim3 grid(ceil_div(p.Wo, DS_TX), ceil_div(p.Ho, DS_TY), p.B);
   SF_CHECK_ARG(grid.y <= 65535, "dcn_forward: output too tall");
-  dcn_small_kernel<<<grid, DS_TY * DS_TX, smem, s>>>(p, RH, RW, RWp, ds_halo());
+  SF_CHECK_ARG(RH * RW < 65536, "dcn_forward: patch too large");
+  const unsigned rw_magic = static_cast<unsigned>((1ULL << 32) / static_cast<unsigned>(RW)) + 1u;
+  dcn_small_kernel<<<grid, DS_TY * DS_TX, smem, s>>>(p, RH, RW, RWp, ds_halo(), rw_magic);
   SF_LAUNCH_CHECK();
   return SF_OK;
 }
