@@ -98,11 +98,13 @@ def guidance_band(cv_rows, disp_rows, left_rows, right_src, band, **kw):
     return ops.guidance_band(cv_rows, disp_rows, left_rows, right_src, band.height, band.y0, band.ys0, **kw)
 
 
-def upsample_convex_band(disp_src, mask_src, band, factor=8, mask_scale=1.0, gather=None):
+def upsample_convex_band(disp_src, mask_src, band, factor=8, mask_scale=1.0, gather=None, root=None):
     """Convex upsampling of a band: disparity and mask on the source rows (1-row halo); returns the band's
     ``rows*factor`` output rows (the halo rows are not computed).  ``gather``: a ``dist.PeerGather`` over whole-map
     buffers [N,1,height*factor,W*factor]; the band's rows are then also stored into every rank's buffer by the same
-    kernel (NVLink peer stores), which replaces the all-gather of the full-resolution map."""
+    kernel (NVLink peer stores), which replaces the all-gather of the full-resolution map.  ``root``: store into that
+    rank's buffer only (the gather-to-device-0 of the reference's ``nn.DataParallel``, trainer_DLC_GRU.py:102-106):
+    1/world of the peer traffic."""
     if not band.covers(1):
         raise ValueError("convex upsampling needs a 1-row halo")
     if disp_src.shape[2] != band.ys1 - band.ys0:
@@ -112,7 +114,8 @@ def upsample_convex_band(disp_src, mask_src, band, factor=8, mask_scale=1.0, gat
     if gather is not None:
         if gather.numel_total < N * bstride:
             raise ValueError("gather buffer must hold [N,1,height*factor,W*factor] floats")
-        peers, off = gather.peer_ptrs, band.y0 * factor * W * factor
+        peers = gather.peer_ptrs if root is None else [gather.peer_ptrs[int(root)]]
+        off = band.y0 * factor * W * factor
     return ops.upsample_convex_rows(disp_src, mask_src, band.halo_top(), band.rows, factor=factor,
                                     mask_scale=mask_scale, peers=peers, peer_offset=off, peer_batch_stride=bstride)
 

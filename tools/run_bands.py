@@ -6,7 +6,7 @@ Every rank builds the same seeded whole-image tensors, keeps only the rows a ban
 (its band + halo) and runs, per step: cost volume + fused soft-argmin / local window (no halo), the guidance stage
 (warp with a 1-row halo), the shipped 16->16 DCN (data-dependent halo) and convex x8 upsampling (1-row halo); the
 band's full-resolution disparity rows reach every rank through peer stores fused into the upsampling kernel
-(--nccl: one NCCL all-gather per step instead).  Rank 0 checks the gathered map against
+(--nccl: one NCCL all-gather per step instead; --root: peer stores to rank 0 only, the reference's gather-to-device-0).  Rank 0 checks the gathered map against
 the whole-image computation on its own GPU and prints one JSON line (strong scaling: the pair is fixed)."""
 import json
 import os
@@ -68,14 +68,15 @@ def main():
         if float(flags.item()) < 1.0:
             pg = None
         else:
-            gather_mode = "P2P stores fused into the upsampling kernel (NVLink peer mappings)"
+            gather_mode = "P2P stores fused into the upsampling kernel (NVLink peer mappings)" + \
+                (", to rank 0 only" if "--root" in sys.argv else ", to every rank")
 
     def band_pass():
         cv1, disp1 = sfb.lcv_band(lf1, rf1, D)
         cv, disp = b1.crop(cv1).contiguous(), b1.crop(disp1).contiguous()
         err, unc = sfb.guidance_band(cv, disp, mine["left_i"], mine["right_i"], band)
         y = sfb.dcn_band(mine["x"], mine["wt"], mine["bias"], mine["off"], mine["msk"], band, halo=halo)
-        up = sfb.upsample_convex_band(disp1, um1, b1, gather=pg)
+        up = sfb.upsample_convex_band(disp1, um1, b1, gather=pg, root=0 if "--root" in sys.argv else None)
         return disp, err, unc, y, up
 
     side = torch.cuda.Stream()
