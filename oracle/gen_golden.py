@@ -275,6 +275,16 @@ def main():
                 blob["%s_%d" % (name, k)] = t
     save("gradients", **blob)
 
+    # ---- gradients of the variance window (a5) through the unmodified reference module; added after the others
+    vblob = {}
+    for cvalid in (0, 1):
+        gv = np.load(os.path.join(OUT, "variance_window_valid%d.npz" % cvalid))
+        res = grads(lambda c, d: vlc.Variance_Based_Local_Cost_Volume(float(gv["gamma"]), int(gv["n_points"]))(
+            c, d, bool(cvalid)), torch.from_numpy(gv["cv"]), torch.from_numpy(gv["cur"]))
+        for k, t in enumerate(res):
+            vblob["var_valid%d_%d" % (cvalid, k)] = t
+    save("gradients_variance", **vblob)
+
     # ---- f1 upsample_simple8 (models/utils/upsample.py:40-43) with its gradient; own seed: added after the others
     from models.utils.upsample import upsample_simple8
     torch.manual_seed(79)

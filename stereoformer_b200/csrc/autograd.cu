@@ -155,7 +155,7 @@ struct WinBwdParams {
   const float* cv; const float* disp; const float* lo; const float* up; const float* gout;
   float* gcv; float* gdisp; float* glo; float* gup;
   int B, D, H, W, mode, n_points, consider_valid, recip;
-  float radius;
+  float radius;   // SF_WIN_FIXED: the radius; SF_WIN_VARIANCE: gamma
 };
 
 constexpr int WB_TPB = 128;
@@ -175,8 +175,25 @@ local_window_bwd_kernel(const WinBwdParams p) {
     const float* src = p.cv + b * D * HW + r;
     const float cur = p.disp[i], g = p.gout[i];
     float lower_raw, upper_raw, pre0 = 0.f, pre1 = 0.f;
+    float vm = 0.f, vs = 1.f, var = 0.f, sigma = 0.f, extra = 0.f;   // variance mode: soft-max statistics of the column
     if (p.mode == SF_WIN_FIXED) {
       lower_raw = sfm::fsub(cur, p.radius); upper_raw = sfm::fadd(cur, p.radius);
+    } else if (p.mode == SF_WIN_VARIANCE) {
+      // GetVarince + bounds, variance_local_cost_volume.py:12-25, 38-42 (the forward's arithmetic, window.cu)
+      vm = -INFINITY;
+      for (int d = 0; d < D; ++d) vm = fmaxf(vm, __ldg(src + d * HW));
+      vs = 0.f;
+      float acc = 0.f;
+      for (int d = 0; d < D; ++d) {
+        const float ex = __expf(__ldg(src + d * HW) - vm), e = sfm::fsub((float)d, cur);
+        vs += ex;
+        acc = fmaf(ex, sfm::fmul(e, e), acc);
+      }
+      var = acc / vs;
+      sigma = sfm::fsqrt(var);
+      const float gs = sfm::fmul(p.radius, sigma);
+      lower_raw = sfm::fsub(cur, gs); upper_raw = sfm::fadd(cur, gs);
+      if (p.consider_valid) extra = (upper_raw > (float)(r % p.W)) ? 1.f : 0.f;
     } else if (p.mode == SF_WIN_OFFSETS) {
       lower_raw = sfm::fsub(cur, p.lo[i]); upper_raw = sfm::fadd(cur, p.up[i]);
     } else if (p.mode == SF_WIN_HEAD) {
@@ -185,7 +202,8 @@ local_window_bwd_kernel(const WinBwdParams p) {
     } else {
       lower_raw = p.lo[i]; upper_raw = p.up[i];
     }
-    const sfm::Window w = sfm::make_window(lower_raw, upper_raw, D, N, p.consider_valid, 0, 0.f, p.recip);
+    const sfm::Window w = sfm::make_window(lower_raw, upper_raw, D, N, p.consider_valid, p.mode == SF_WIN_VARIANCE,
+                                           extra, p.recip);
     // pass 1: soft-max statistics and the expectation
     float m = -INFINITY;
     for (int k = 0; k <= N; ++k) {
@@ -223,11 +241,30 @@ local_window_bwd_kernel(const WinBwdParams p) {
       g_upper += g_raw * t;
     }
     if (!p.consider_valid) {                                          // torch.clamp backward: pass-through inside [min, max]
-      if (!(lower_raw >= 0.f)) g_lower = 0.f;
-      if (!(upper_raw >= 0.f && upper_raw <= (float)D)) g_upper = 0.f;
+      if (p.mode == SF_WIN_VARIANCE) {                                // both bounds clamped to [0, D-1] (:52-53)
+        if (!(lower_raw >= 0.f && lower_raw <= (float)(D - 1))) g_lower = 0.f;
+        if (!(upper_raw >= 0.f && upper_raw <= (float)(D - 1))) g_upper = 0.f;
+      } else {
+        if (!(lower_raw >= 0.f)) g_lower = 0.f;
+        if (!(upper_raw >= 0.f && upper_raw <= (float)D)) g_upper = 0.f;
+      }
     }
     if (p.mode == SF_WIN_FIXED) {
       g_cur += g_lower + g_upper;
+    } else if (p.mode == SF_WIN_VARIANCE) {
+      // bounds = cur -+ gamma * sigma, sigma = sqrt(var), var = sum_d p_d (d - cur)^2, p = softmax(cv):
+      //   g_var = gamma (g_upper - g_lower) / (2 sigma);  g_cv[d] += p_d g_var ((d-cur)^2 - var);
+      //   g_cur += g_lower + g_upper - 2 g_var sum_d p_d (d - cur)
+      g_cur += g_lower + g_upper;
+      const float g_var = p.radius * (g_upper - g_lower) * 0.5f / sigma;
+      float mean_e = 0.f;
+      const float vinv = 1.0f / vs;
+      for (int d = 0; d < D; ++d) {
+        const float pd = __expf(__ldg(src + d * HW) - vm) * vinv, e = (float)d - cur;
+        col[d * WB_TPB + threadIdx.x] += pd * g_var * (e * e - var);
+        mean_e = fmaf(pd, e, mean_e);
+      }
+      g_cur -= 2.0f * g_var * mean_e;
     } else if (p.mode == SF_WIN_OFFSETS) {
       g_cur += g_lower + g_upper;
       if (p.glo) p.glo[i] = -g_lower;
@@ -329,9 +366,9 @@ extern "C" int sf_local_window_backward_f32(const float* cv, const float* disp, 
   using namespace sf;
   SF_CHECK_ARG(cv && disp && grad_out, "local_window_backward: null pointer (the fused soft-argmin form has no backward)");
   SF_CHECK_ARG(B > 0 && D > 0 && H > 0 && W > 0 && n_points > 0, "local_window_backward: non-positive dimension");
-  SF_CHECK_ARG(mode == SF_WIN_FIXED || mode == SF_WIN_OFFSETS || mode == SF_WIN_ABSOLUTE || mode == SF_WIN_HEAD,
-               "local_window_backward: mode %d has no backward (the variance window is forward-only)", mode);
-  SF_CHECK_ARG(mode == SF_WIN_FIXED || lo, "local_window_backward: this mode needs the bound tensors");
+  SF_CHECK_ARG(mode == SF_WIN_FIXED || mode == SF_WIN_VARIANCE || mode == SF_WIN_OFFSETS || mode == SF_WIN_ABSOLUTE ||
+                   mode == SF_WIN_HEAD, "local_window_backward: unknown mode %d", mode);
+  SF_CHECK_ARG(mode == SF_WIN_FIXED || mode == SF_WIN_VARIANCE || lo, "local_window_backward: this mode needs the bound tensors");
   SF_CHECK_ARG((mode != SF_WIN_OFFSETS && mode != SF_WIN_ABSOLUTE) || up, "local_window_backward: upper bound tensor missing");
   const size_t smem = static_cast<size_t>(D) * WB_TPB * sizeof(float);
   SF_CHECK_ARG(smem <= 200 * 1024, "local_window_backward: D=%d too large", D);

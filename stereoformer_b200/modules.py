@@ -166,7 +166,11 @@ class Variance_Based_Local_Cost_Volume(nn.Module):
         return _run(lambda cv, d: ops.local_window(cv, d, mode=SF_WIN_VARIANCE, gamma=self.garma,
                                                    n_points=self.sample_points, consider_valid=consider_valid,
                                                    div_mode=self.div_mode),
-                    "Variance_Based_Local_Cost_Volume", old_cost_volume, cur_disparity)
+                    "Variance_Based_Local_Cost_Volume", old_cost_volume, cur_disparity,
+                    bwd=lambda a, g, n: ops.local_window_backward(
+                        a[0], a[1], None, None, g, mode=SF_WIN_VARIANCE, radius=self.garma,
+                        n_points=self.sample_points, consider_valid=consider_valid, div_mode=self.div_mode,
+                        needs=(n[0], n[1], False, False))[:2])
 
 
 def dlc_window(old_cost_volume, cur_disp, lower_offset, upper_offset, sample_points, consider_valid=True,

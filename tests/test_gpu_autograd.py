@@ -76,6 +76,34 @@ def test_fixed_window_backward(valid):
 
 
 @pytest.mark.parametrize("valid", [0, 1])
+def test_variance_window_backward(valid):
+    """a5: Variance_Based_Local_Cost_Volume under autograd against the reference module's own gradients (golden) and
+    against autograd through the oracle on a second, larger input."""
+    import stereoformer_b200 as sf
+    g = load_golden("variance_window_valid%d" % valid)
+    gg = load_golden("gradients_variance")
+    m = sf.Variance_Based_Local_Cost_Volume(float(g["gamma"]), int(g["n_points"]))
+    m.div_mode = 0
+    cg, dg = _leaf(g["cv"].cuda()), _leaf(g["cur"].cuda())
+    gc, gd = torch.autograd.grad(m(cg, dg, bool(valid)), [cg, dg], gg["var_valid%d_0" % valid].cuda())
+    _close(gc, gg["var_valid%d_1" % valid], "grad_cv (reference)")
+    _close(gd, gg["var_valid%d_2" % valid], "grad_disp (reference)")
+    torch.manual_seed(33)
+    cv = (torch.randn(2, 24, 17, 40) * 3 - 2).abs()
+    cur = torch.rand(2, 1, 17, 40) * 23
+    c, d = _leaf(cv), _leaf(cur)
+    ref = O.variance_local_cost_volume(c, d, 0.7, 10, bool(valid))
+    go = torch.randn_like(ref)
+    rc, rd = torch.autograd.grad(ref, [c, d], go)
+    m2 = sf.Variance_Based_Local_Cost_Volume(0.7, 10)
+    m2.div_mode = 0
+    cg, dg = _leaf(cv.cuda()), _leaf(cur.cuda())
+    gc, gd = torch.autograd.grad(m2(cg, dg, bool(valid)), [cg, dg], go.cuda())
+    _close(gc, rc, "grad_cv")
+    _close(gd, rd, "grad_disp")
+
+
+@pytest.mark.parametrize("valid", [0, 1])
 @pytest.mark.parametrize("mode", ["offsets", "absolute", "head"])
 def test_dlc_window_backward(valid, mode):
     import stereoformer_b200 as sf
@@ -180,12 +208,12 @@ def test_lc_chain_trains():
 
 
 def test_forward_only_ops_still_raise():
+    """Operators without a backward kernel refuse to be differentiated instead of silently dropping gradients."""
     import stereoformer_b200 as sf
-    cv = torch.randn(1, 8, 4, 16, device="cuda", requires_grad=True)
-    d = torch.rand(1, 1, 4, 16, device="cuda") * 7
-    out = sf.Variance_Based_Local_Cost_Volume(1, 10)(cv, d)
+    q = torch.randn(1, 64, 2, 16, device="cuda", dtype=torch.bfloat16, requires_grad=True)
+    out = sf.EpipolarCrossAttention(8)(q, q.detach(), q.detach())
     with pytest.raises(NotImplementedError):
-        out.sum().backward()
+        out.float().sum().backward()
 
 
 # ------------------------------------------------------------------------------------------ DLC-GRU step, trainable

@@ -175,3 +175,13 @@ def test_oracle_autograd_matches_reference_autograd():
     wp = load_golden("disp_warp")
     _grads(lambda i, d: O.disp_warp(i, d, "border"), g, "warp_border", wp["img"], wp["disp"])
     _grads(lambda i, d: O.disp_warp(i, d, "zeros"), g, "warp_zeros", wp["img"], wp["disp"])
+
+
+def test_oracle_variance_window_gradients_match_reference():
+    """a5 under autograd: gradients of the unmodified Variance_Based_Local_Cost_Volume (through sigma = sqrt(sum p (d -
+    disp)^2), the [0, D-1] clamps / the three invalid masks and the sampler) against the oracle's graph."""
+    g = load_golden("gradients_variance")
+    for valid in (0, 1):
+        w = load_golden("variance_window_valid%d" % valid)
+        _grads(lambda c, d: O.variance_local_cost_volume(c, d, float(w["gamma"]), int(w["n_points"]), bool(valid)), g,
+               "var_valid%d" % valid, w["cv"], w["cur"])
