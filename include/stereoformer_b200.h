@@ -154,6 +154,8 @@ SF_API int sf_corr_volume_backward_f32(const float* left, const float* right, co
                                        float* grad_right, int B, int C, int H, int W, int D, int groups, void* stream);
 SF_API int sf_soft_argmin_backward_f32(const float* cv, const float* grad_disp, float* grad_cv, int B, int D, int H,
                                        int W, int match_similarity, void* stream);
+/* modes FIXED (radius), VARIANCE (radius = gamma: the chain through sigma = sqrt(sum_d p_d (d - disp)^2) is included),
+ * OFFSETS / ABSOLUTE (lo, up given; grad_lo / grad_up produced), HEAD (lo = pre-ReLU head output [B,2,H,W]). */
 SF_API int sf_local_window_backward_f32(const float* cv, const float* disp, const float* lo, const float* up,
                                         const float* grad_out, float* grad_cv, float* grad_disp, float* grad_lo,
                                         float* grad_up, int B, int D, int H, int W, int mode, float radius,
