@@ -170,3 +170,28 @@ def test_dcn_whole_image_matches_oracle_c5_rows(mods):
     ref = dcn_c.dcn_forward(x, wt, bias, off, msk, (1, 1), (1, 1), (1, 1), 1, 1)
     got = ops.dcn_forward(x.cuda(), wt.cuda(), bias.cuda(), off.cuda(), msk.cuda(), (1, 1), (1, 1), (1, 1), 1, 1)
     assert torch.allclose(got.cpu(), ref, rtol=1e-5, atol=1e-5)
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_corr1d_and_attention_bands_bit_exact(mods, world):
+    """The other row-local operators of the path: CorrBlock1D (pyramid + lookup, a8/a9) and the band attention (a11)
+    computed on a band's rows equal the same rows of the whole-image call bit for bit."""
+    ops, bands, sfd = mods
+    torch.manual_seed(12)
+    H, W, C = 16, 240, 64
+    f1, f2 = torch.randn(1, C, H, W, device="cuda"), torch.randn(1, C, H, W, device="cuda")
+    coords = torch.cat((torch.arange(W, device="cuda").float().view(1, 1, 1, W).repeat(1, 1, H, 1) -
+                        torch.rand(1, 1, H, W, device="cuda") * 40, torch.zeros(1, 1, H, W, device="cuda")), 1)
+    pyr = ops.corr1d_pyramid(f1, f2, 4)
+    look = ops.corr1d_lookup(pyr, coords, 4, 4)
+    q, k, v = (torch.randn(1, 64, H, W, device="cuda").bfloat16() for _ in range(3))
+    att = ops.epipolar_attention(q, k, v, 48)
+    parts_l, parts_a, parts_p0 = [], [], []
+    for b in _bands(bands, sfd, H, world, 0):
+        pb = ops.corr1d_pyramid(b.interior(f1), b.interior(f2), 4)
+        parts_p0.append(pb[0])
+        parts_l.append(ops.corr1d_lookup(pb, b.interior(coords), 4, 4))
+        parts_a.append(ops.epipolar_attention(b.interior(q), b.interior(k), b.interior(v), 48))
+    assert torch.equal(torch.cat(parts_p0, 0), pyr[0])          # [B*H*W1, 1, 1, W2] is band-major for one pair
+    assert torch.equal(torch.cat(parts_l, 2), look)
+    assert torch.equal(torch.cat(parts_a, 2), att)
