@@ -123,6 +123,15 @@ SF_API int sf_corr1d_lookup_f32(const float* const* levels, const int* widths, i
                                 const float* coords, float* out, float* dbg_x0, float* dbg_src, int B, int H, int W1,
                                 int div_mode, void* stream);
 
+/* a9 alternative: PytorchAlternateCorrBlock1D.__call__  corr/corr.py:8-51 (on-the-fly correlation, no all-pairs
+ * volume): f1 [B,C,H,W1], f2 [B,C,H,W2], coords [B,2,H,W1] (x, y) -> out [B,num_levels*(2*radius+1),H,W1].
+ * workspace: as many bytes as the workspace query below returns, for the x-pooled right feature maps; dbg_src:
+ * optional [B,L*(2r+1),H,W1,2] un-normalised sampling coordinates.  num_levels <= 4, radius <= 4, H > 1. */
+SF_API size_t sf_corr1d_alt_workspace_bytes(int B, int C, int H, int W2, int num_levels);
+SF_API int sf_corr1d_alt_f32(const float* f1, const float* f2, const float* coords, float* out, float* dbg_src,
+                             void* workspace, size_t workspace_bytes, int B, int C, int H, int W1, int W2,
+                             int num_levels, int radius, int div_mode, void* stream);
+
 /* a10: DCN.modulated_deform_conv_forward  deform/src/vision.cpp:8 -> deform/src/modulated_deform_conv.h:10-44 ->
  * deform/src/cuda/modulated_deform_conv_cuda.cu:19-121; mask == NULL gives DCN.deform_conv_forward
  * (deform/src/deform_conv.h:10-25).  out [B,Cout,Ho,Wo] with the reference's output-size formula. */

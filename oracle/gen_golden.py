@@ -285,6 +285,17 @@ def main():
             vblob["var_valid%d_%d" % (cvalid, k)] = t
     save("gradients_variance", **vblob)
 
+    # ---- a9 alternative: PytorchAlternateCorrBlock1D (corr/corr.py:8-51); own seed: added after the others
+    from models.IterativeLocalCostVolume.corr.corr import PytorchAlternateCorrBlock1D
+    torch.manual_seed(80)
+    a1, a2 = torch.randn(2, 16, 5, 24), torch.randn(2, 16, 5, 24)
+    xs = torch.arange(24).float().view(1, 1, 1, 24).repeat(2, 1, 5, 1) - torch.rand(2, 1, 5, 24) * 8
+    ys = torch.arange(5).float().view(1, 1, 5, 1).repeat(2, 1, 1, 24)
+    ac = torch.cat((xs, ys), 1)
+    ac[0, 0, 0, :4] = torch.tensor([0., 3., 23., -2.5])
+    save("corr1d_alt", f1=a1, f2=a2, coords=ac, radius=2, num_levels=3,
+         out=PytorchAlternateCorrBlock1D(a1, a2, num_levels=3, radius=2)(ac))
+
     # ---- f1 upsample_simple8 (models/utils/upsample.py:40-43) with its gradient; own seed: added after the others
     from models.utils.upsample import upsample_simple8
     torch.manual_seed(79)

@@ -281,6 +281,31 @@ def corr1d_lookup(pyramid, coords, radius=4, num_levels=4, recip=False):
     return torch.cat(out, dim=-1).permute(0, 3, 1, 2).contiguous().float()
 
 
+def corr1d_alt(f1, f2, coords, radius=4, num_levels=4, recip=False):
+    """PytorchAlternateCorrBlock1D.__call__ / .corr, corr/corr.py:15-51: per level, the x-pooled right map is sampled at
+    (x/2^i + dx, y) with grid_sample(align_corners=True) after the reference's own 2*x/(W-1) - 1 normalisation, dotted
+    with the left map over channels and divided by sqrt(C)."""
+    B, C, H, W1 = f1.shape
+    c = coords.permute(0, 2, 3, 1)
+    dx = torch.linspace(-radius, radius, 2 * radius + 1).to(coords.device)
+    out = []
+    fm2 = f2
+    for i in range(num_levels):
+        Wl = fm2.shape[3]
+        x0 = c[..., 0:1] / 2 ** i + dx.view(1, 1, 1, -1)                   # centroid + delta (:42-44)
+        y0 = c[..., 1:2].expand_as(x0)
+        xg = _sdiv(2 * x0, Wl - 1, recip) - 1
+        yg = _sdiv(2 * y0, H - 1, recip) - 1
+        lv = []
+        for t in range(2 * radius + 1):
+            grid = torch.stack((xg[..., t], yg[..., t]), dim=-1)           # [B,H,W1,2]
+            samp = F.grid_sample(fm2, grid, align_corners=True)
+            lv.append(torch.sum(samp * f1, dim=1))
+        out.append(torch.stack(lv, dim=1).permute(0, 2, 3, 1) / torch.sqrt(torch.tensor(C).float()))
+        fm2 = F.avg_pool2d(fm2, [1, 2], stride=[1, 2])
+    return torch.cat(out, dim=-1).permute(0, 3, 1, 2).contiguous().float()
+
+
 # --------------------------------------------------------------------------- a10 (python form; C form in dcn_oracle.c)
 def dcn_forward(inp, weight, bias, offset, mask, stride, pad, dil, groups, dgroups):
     """deform/src/cuda/modulated_deform_conv_cuda.cu:75-118 + modulated_deform_im2col_cuda.cuh:25-54,

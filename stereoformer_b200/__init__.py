@@ -7,7 +7,8 @@ There is no CPU fallback: operators raise if the library is missing or a tensor 
 from . import _lib  # noqa: F401
 from . import ops  # noqa: F401
 from .modules import (CorrBlock1D, CostVolume, DisparityEstimation, DisparityEstimationWithProb,  # noqa: F401
-                      EpipolarCrossAttention, LocalCostVolume, LRwarp_error, Variance_Based_Local_Cost_Volume,
+                      EpipolarCrossAttention, LocalCostVolume, LRwarp_error, PytorchAlternateCorrBlock1D,
+                      Variance_Based_Local_Cost_Volume,
                       build_corr, build_cost_volume_from_volume, build_gwc_volume, disp_warp, dlc_window,
                       guidance_inputs, upsample_convex8, upsample_simple8)
 from .dcn_modules import (DeformConv, DeformConvPack, ModulatedDeformConv, ModulatedDeformConvPack,  # noqa: F401

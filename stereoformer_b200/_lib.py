@@ -29,6 +29,8 @@ SIGNATURES = {
     "sf_guidance_band_f32": [_p] * 6 + [_c_int] * 10 + [_p, _p],
     "sf_corr1d_pyramid_f32": [_p, _p, _p] + [_c_int] * 7 + [_p],
     "sf_corr1d_lookup_f32": [_p, _p, _c_int, _c_int, _p, _p, _p, _p] + [_c_int] * 4 + [_p],
+    "sf_corr1d_alt_workspace_bytes": [_c_int] * 5,
+    "sf_corr1d_alt_f32": [_p] * 6 + [ctypes.c_size_t] + [_c_int] * 8 + [_p],
     "sf_dcn_forward_f32": [_p] * 6 + [_c_int] * 15 + [_p],
     "sf_corr_volume_backward_f32": [_p] * 5 + [_c_int] * 6 + [_p],
     "sf_soft_argmin_backward_f32": [_p] * 3 + [_c_int] * 5 + [_p],
@@ -55,7 +57,7 @@ SIGNATURES = {
     "sf_gru_blend_f32": [_p, ctypes.c_longlong, _p, _p, _p] + [_c_int] * 5 + [_p],
 }
 
-RESTYPES = {"sf_dcn_workspace_bytes": ctypes.c_size_t}   # everything else returns an int status code
+RESTYPES = {"sf_dcn_workspace_bytes": ctypes.c_size_t, "sf_corr1d_alt_workspace_bytes": ctypes.c_size_t}   # everything else returns an int status code
 
 _lib = None
 

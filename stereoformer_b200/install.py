@@ -40,7 +40,8 @@ PATCHES = {
     "models.LocalCostVolume.Attempts.pure_learning_method": {
         "build_cost_volume_from_volume": _m.build_cost_volume_from_volume, "disp_warp": _m.disp_warp},
     "models.CrossAttentionCostVolume.GWC_Cost_Volume": {"build_gwc_volume": _m.build_gwc_volume},
-    "models.IterativeLocalCostVolume.corr.corr": {"CorrBlock1D": _m.CorrBlock1D},
+    "models.IterativeLocalCostVolume.corr.corr": {"CorrBlock1D": _m.CorrBlock1D,
+                                                  "PytorchAlternateCorrBlock1D": _m.PytorchAlternateCorrBlock1D},
     "models.utils.upsample": {"upsample_convex8": _m.upsample_convex8, "upsample_simple8": _m.upsample_simple8},
     "utils.disparity_warper": {"disp_warp": _m.disp_warp, "LRwarp_error": _m.LRwarp_error},
 }

@@ -242,6 +242,22 @@ class CorrBlock1D:
         return lv[0].view(B, H, W1, 1, W2)
 
 
+class PytorchAlternateCorrBlock1D:
+    """models/IterativeLocalCostVolume/corr/corr.py:8-51: the on-the-fly variant (no all-pairs volume)."""
+
+    def __init__(self, fmap1, fmap2, num_levels=4, radius=4):
+        self.num_levels = num_levels
+        self.radius = radius
+        self.corr_pyramid = []
+        self.fmap1 = fmap1
+        self.fmap2 = fmap2
+        self.div_mode = DEFAULT_DIV_MODE
+
+    def __call__(self, coords):
+        return _run(lambda c, a, b: ops.corr1d_alt(a, b, c, self.radius, self.num_levels, self.div_mode),
+                    "PytorchAlternateCorrBlock1D", coords, self.fmap1, self.fmap2)
+
+
 # ----------------------------------------------------------------------------- attention (spec-derived)
 class EpipolarCrossAttention(nn.Module):
     """Band-restricted epipolar row cross-attention.  The reference's

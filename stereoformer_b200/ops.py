@@ -271,6 +271,24 @@ def corr1d_lookup(pyramid, coords, radius=4, num_levels=4, div_mode=SF_DIV_TRUE,
     return (out, dict(x0=x0, src=src)) if debug else out
 
 
+def corr1d_alt(f1, f2, coords, radius=4, num_levels=4, div_mode=SF_DIV_TRUE, debug=False):
+    """PytorchAlternateCorrBlock1D.__call__: on-the-fly correlation lookup -> [B, L*(2r+1), H, W1]."""
+    f1, f2, coords = _chk(f1, "fmap1", dim=4), _chk(f2, "fmap2", dim=4), _chk(coords, "coords", dim=4)
+    B, C, H, W1 = f1.shape
+    W2 = f2.shape[3]
+    if f2.shape[:3] != (B, C, H) or coords.shape != (B, 2, H, W1):
+        raise ValueError("fmap2 must be [B,C,H,W2] and coords [B,2,H,W1]")
+    taps = 2 * radius + 1
+    out = torch.empty((B, num_levels * taps, H, W1), device=f1.device, dtype=torch.float32)
+    src = torch.empty((B, num_levels * taps, H, W1, 2), device=f1.device, dtype=torch.float32) if debug else None
+    with torch.cuda.device(f1.device):
+        nws = int(_lib.lib().sf_corr1d_alt_workspace_bytes(B, C, H, W2, int(num_levels)))
+        ws = torch.empty(max(nws, 1), device=f1.device, dtype=torch.uint8)
+        _lib.call("sf_corr1d_alt_f32", _ptr(f1), _ptr(f2), _ptr(coords), _ptr(out), _ptr(src), _ptr(ws),
+                  ctypes.c_size_t(nws), B, C, H, W1, W2, int(num_levels), int(radius), int(div_mode), _stream())
+    return (out, dict(src=src)) if debug else out
+
+
 def dcn_forward(inp, weight, bias, offset, mask, stride, padding, dilation, groups, deformable_groups,
                 algo=SF_ALGO_AUTO):
     """DCNv2 (mask given) / DCNv1 (mask None) forward -> [B,Cout,Ho,Wo].

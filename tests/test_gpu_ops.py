@@ -299,6 +299,42 @@ def test_upsample_simple8(ops, shape):
         sf.upsample_simple8(dev(d), mode="nearest")
 
 
+def test_corr1d_alt(ops):
+    """PytorchAlternateCorrBlock1D: golden vector of the reference class, the oracle on a second shape (bit-exact
+    sampling coordinates, values <= 1e-4 of the magnitude), and -- pooling and correlation commute -- agreement with the
+    volume form (CorrBlock1D) at the config-3 row shape."""
+    import stereoformer_b200 as sf
+    g = load_golden("corr1d_alt")
+    r, L = int(g["radius"]), int(g["num_levels"])
+    out, dbg = ops.corr1d_alt(dev(g["f1"]), dev(g["f2"]), dev(g["coords"]), r, L, div_mode=ops.SF_DIV_TRUE, debug=True)
+    assert out.shape == g["out"].shape and close_rel(out, g["out"])
+    # un-normalised sampling coordinates against the oracle's round trip, bit for bit
+    B, _, H, W = g["coords"].shape
+    cx = g["coords"][:, :1].permute(0, 2, 3, 1).reshape(-1)
+    for lvl in range(L):
+        Wl = W >> lvl
+        _, xg = O.corr1d_lookup_coords(cx, lvl, r, Wl)
+        ix = ((xg + 1) * 0.5) * (Wl - 1)
+        got = dbg["src"][:, lvl * (2 * r + 1):(lvl + 1) * (2 * r + 1), :, :, 0].permute(0, 2, 3, 1).reshape(-1, 2 * r + 1)
+        assert torch.equal(got.cpu(), ix)
+    blk = sf.PytorchAlternateCorrBlock1D(dev(g["f1"]), dev(g["f2"]), num_levels=L, radius=r)
+    blk.div_mode = 0
+    assert torch.equal(blk(dev(g["coords"])), out)
+    torch.manual_seed(49)
+    f1, f2 = torch.randn(1, 40, 6, 52), torch.randn(1, 40, 6, 52)
+    coords = torch.cat((torch.arange(52.).view(1, 1, 1, 52).repeat(1, 1, 6, 1) - torch.rand(1, 1, 6, 52) * 20,
+                        torch.arange(6.).view(1, 1, 6, 1).repeat(1, 1, 1, 52) + torch.rand(1, 1, 6, 52) * 0.5), 1)
+    assert close_rel(ops.corr1d_alt(dev(f1), dev(f2), dev(coords), 4, 4, div_mode=ops.SF_DIV_TRUE),
+                     O.corr1d_alt(f1, f2, coords, 4, 4))           # fractional y: two-row bilinear
+    f1, f2 = torch.randn(2, 256, 8, 240, device="cuda"), torch.randn(2, 256, 8, 240, device="cuda")
+    coords = torch.cat((torch.arange(240., device="cuda").view(1, 1, 1, 240).repeat(2, 1, 8, 1) -
+                        torch.rand(2, 1, 8, 240, device="cuda") * 60,
+                        torch.arange(8., device="cuda").view(1, 1, 8, 1).repeat(2, 1, 1, 240)), 1)
+    reg = sf.CorrBlock1D(f1, f2, num_levels=4, radius=4)
+    reg.div_mode = 0
+    assert close_rel(ops.corr1d_alt(f1, f2, coords, 4, 4, div_mode=ops.SF_DIV_TRUE), reg(coords), rtol=2e-4)
+
+
 # ------------------------------------------------------------------------------------------ drop-in modules
 def test_dropin_modules_chain():
     """The LowCNN LC hot-path chain (baseline.py:114-127) through the drop-in nn.Modules."""

@@ -185,3 +185,9 @@ def test_oracle_variance_window_gradients_match_reference():
         w = load_golden("variance_window_valid%d" % valid)
         _grads(lambda c, d: O.variance_local_cost_volume(c, d, float(w["gamma"]), int(w["n_points"]), bool(valid)), g,
                "var_valid%d" % valid, w["cv"], w["cur"])
+
+
+def test_corr1d_alt():
+    """a9 alternative (PytorchAlternateCorrBlock1D, corr/corr.py:8-51): the oracle reproduces the reference bit for bit."""
+    g = load_golden("corr1d_alt")
+    assert eq(O.corr1d_alt(g["f1"], g["f2"], g["coords"], int(g["radius"]), int(g["num_levels"])), g["out"])
