@@ -6,7 +6,7 @@
 // 2*x/(W-1) - 1, 2*y/(H-1) - 1 (:19-20); the sample is dotted with the left feature over the channels and divided by
 // sqrt(C) (:31).  Output [B, L*(2r+1), H, W] float32, level-major like CorrBlock1D.
 //
-// One thread per left pixel.  Per level the 2r+1 sampling descriptors (corner index, two x weights) are computed once
+// One thread per (left pixel, level).  The 2r+1 sampling descriptors (corner index, two x weights) are computed once
 // and kept in registers together with the 2r+1 accumulators; the channel loop then issues coalesced loads (adjacent
 // threads = adjacent pixels whose sampling positions are adjacent).  The row weights come from the same normalise /
 // un-normalise round trip as the reference's (for integer cy the second row has weight 0 and is not loaded).
@@ -61,7 +61,8 @@ __global__ void __launch_bounds__(128) corr1d_alt_kernel(const AltParams p) {
   const float scale = sqrtf((float)p.C);
   const float* f1p = p.f1 + b * p.C * HW + r;
 
-  for (int l = 0; l < p.num_levels; ++l) {
+  {
+    const int l = blockIdx.y;                             // one level per thread: 4x the threads in flight
     const int Wl = p.W2[l];
     const size_t plane = static_cast<size_t>(p.H) * Wl;
     const float* base = p.f2[l] + b * p.C * plane;
@@ -150,7 +151,7 @@ extern "C" int sf_corr1d_alt_f32(const float* f1, const float* f2, const float* 
     ws += n;
   }
   const size_t n = static_cast<size_t>(B) * H * W1;
-  corr1d_alt_kernel<<<static_cast<unsigned>((n + 127) / 128), 128, 0, s>>>(p);
+  corr1d_alt_kernel<<<dim3(static_cast<unsigned>((n + 127) / 128), num_levels), 128, 0, s>>>(p);
   SF_LAUNCH_CHECK();
   return SF_OK;
 }
