@@ -6,7 +6,7 @@
 // 2*x/(W-1) - 1, 2*y/(H-1) - 1 (:19-20); the sample is dotted with the left feature over the channels and divided by
 // sqrt(C) (:31).  Output [B, L*(2r+1), H, W] float32, level-major like CorrBlock1D.
 //
-// One thread per (left pixel, level).  The 2r+1 sampling descriptors (corner index, two x weights) are computed once
+// One thread per (left pixel, level).  The 2r+1 sampling descriptors (clamped corner indices, four weights) are computed once
 // and kept in registers together with the 2r+1 accumulators; the channel loop then issues coalesced loads (adjacent
 // threads = adjacent pixels whose sampling positions are adjacent).  The row weights come from the same normalise /
 // un-normalise round trip as the reference's (for integer cy the second row has weight 0 and is not loaded).
@@ -66,19 +66,23 @@ __global__ void __launch_bounds__(128) corr1d_alt_kernel(const AltParams p) {
     const int Wl = p.W2[l];
     const size_t plane = static_cast<size_t>(p.H) * Wl;
     const float* base = p.f2[l] + b * p.C * plane;
-    int xi[CA_MAXT];
-    float wx0[CA_MAXT], wx1[CA_MAXT], acc[CA_MAXT];
+    // per tap: two clamped column indices and four corner weights; a corner outside the map keeps a valid address and
+    // gets weight 0 (ATen skips it: the same sum), so the channel loop is branch-free
+    int xa[CA_MAXT], xb[CA_MAXT];
+    float w00[CA_MAXT], w01[CA_MAXT], w10[CA_MAXT], w11[CA_MAXT], acc[CA_MAXT];
 #pragma unroll
     for (int t = 0; t < CA_MAXT; ++t) {
-      acc[t] = 0.f; xi[t] = -2; wx0[t] = wx1[t] = 0.f;
+      acc[t] = 0.f; xa[t] = xb[t] = 0; w00[t] = w01[t] = w10[t] = w11[t] = 0.f;
       if (t < taps) {
         const float x0 = sfm::lookup_x0(cx, l, (float)(t - p.radius));
         const float ix = sfm::lookup_unnorm(sfm::lookup_norm(x0, Wl, p.recip), Wl);
         const float fx = floorf(ix);
         if (fx >= -1.f && fx < (float)Wl) {
-          xi[t] = (int)fx;
-          wx0[t] = (fx + 1.f) - ix;
-          wx1[t] = ix - fx;
+          const int x = (int)fx;
+          const float wx0 = (fx + 1.f) - ix, wx1 = ix - fx;
+          xa[t] = max(x, 0); xb[t] = min(x + 1, Wl - 1);
+          if (x >= 0) { w00[t] = row0 ? wx0 * wy0 : 0.f; w10[t] = row1 ? wx0 * wy1 : 0.f; }
+          if (x + 1 < Wl) { w01[t] = row0 ? wx1 * wy0 : 0.f; w11[t] = row1 ? wx1 * wy1 : 0.f; }
         }
         if (p.dbg_src) {
           const size_t o = ((b * p.num_levels * taps + static_cast<size_t>(l * taps + t)) * HW + r) * 2;
@@ -86,24 +90,30 @@ __global__ void __launch_bounds__(128) corr1d_alt_kernel(const AltParams p) {
         }
       }
     }
+    const int ya = row0 ? y0 : (row1 ? y0 + 1 : 0), yb = row1 ? y0 + 1 : ya;   // valid rows even when a weight is 0
     for (int c = 0; c < p.C; ++c) {
       const float a = __ldg(f1p + c * HW);
-      const float* q0 = base + c * plane + static_cast<ptrdiff_t>(y0) * Wl;
+      const float* q0 = base + c * plane + static_cast<ptrdiff_t>(ya) * Wl;
+      const float* q1 = base + c * plane + static_cast<ptrdiff_t>(yb) * Wl;
+      if (row1) {
 #pragma unroll
-      for (int t = 0; t < CA_MAXT; ++t) {
-        if (t >= taps || xi[t] < -1) continue;
-        const int x = xi[t];
-        // ATen grid_sampler_2d: nw, ne, sw, se in this order, corners outside the map contribute nothing
-        float v = 0.f;
-        if (row0) {
-          if (x >= 0) v += __ldg(q0 + x) * (wx0[t] * wy0);
-          if (x + 1 < Wl) v += __ldg(q0 + x + 1) * (wx1[t] * wy0);
+        for (int t = 0; t < CA_MAXT; ++t) {
+          if (t >= taps) continue;
+          // ATen grid_sampler_2d order: nw, ne, sw, se
+          float v = __ldg(q0 + xa[t]) * w00[t];
+          v += __ldg(q0 + xb[t]) * w01[t];
+          v += __ldg(q1 + xa[t]) * w10[t];
+          v += __ldg(q1 + xb[t]) * w11[t];
+          acc[t] = fmaf(v, a, acc[t]);
         }
-        if (row1) {
-          if (x >= 0) v += __ldg(q0 + Wl + x) * (wx0[t] * wy1);
-          if (x + 1 < Wl) v += __ldg(q0 + Wl + x + 1) * (wx1[t] * wy1);
+      } else {
+#pragma unroll
+        for (int t = 0; t < CA_MAXT; ++t) {
+          if (t >= taps) continue;
+          float v = __ldg(q0 + xa[t]) * w00[t];
+          v += __ldg(q0 + xb[t]) * w01[t];
+          acc[t] = fmaf(v, a, acc[t]);
         }
-        acc[t] = fmaf(v, a, acc[t]);
       }
     }
     float* o = p.out + (b * p.num_levels * taps + static_cast<size_t>(l * taps)) * HW + r;
