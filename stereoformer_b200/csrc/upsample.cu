@@ -154,28 +154,47 @@ __device__ __forceinline__ Lerp1 simple_index(float scale, int dst, int in) {
 }
 
 __global__ void __launch_bounds__(128)
-upsample_simple_kernel(const float* __restrict__ disp, float* __restrict__ out, int nrows, int H, int W, int F,
-                       float sh, float sw) {
-  // a block walks output rows (n*Ho + yo); a thread keeps its float4 column and that column's x weights across rows
+upsample_simple_kernel(const float* __restrict__ disp, float* __restrict__ out, int H, int W, int F, float sh,
+                       float sw) {
+  // blockIdx.z = image, blockIdx.y = float4-column chunk, blockIdx.x strides the image's output rows.  A thread keeps
+  // its float4 column: for F >= 4 its 4 outputs read at most 3 consecutive source cells (4 * scale < 1), so a row costs
+  // 6 loads (3 cells x 2 source rows) and the x weights / cell selectors are computed once.
   const int Ho = H * F, Wo = W * F, Wq = Wo >> 2;
   const int xq = blockIdx.y * blockDim.x + threadIdx.x;
   if (xq >= Wq) return;
   Lerp1 lx[4];
 #pragma unroll
   for (int j = 0; j < 4; ++j) lx[j] = simple_index(sw, 4 * xq + j, W);
-  for (int row = blockIdx.x; row < nrows; row += gridDim.x) {
-    const int yo = row % Ho, b = row / Ho;
+  const int c0 = lx[0].i0, c1 = min(c0 + 1, W - 1), c2 = min(c0 + 2, W - 1);
+  const bool compact = lx[3].i1 <= c0 + 2;               // always true for F >= 4
+  const float* img = disp + static_cast<size_t>(blockIdx.z) * H * W;
+  float* oimg = out + static_cast<size_t>(blockIdx.z) * Ho * Wo + 4 * xq;
+  for (int yo = blockIdx.x; yo < Ho; yo += gridDim.x) {
     const Lerp1 ly = simple_index(sh, yo, H);
-    const float* r0 = disp + (static_cast<size_t>(b) * H + ly.i0) * W;
-    const float* r1 = disp + (static_cast<size_t>(b) * H + ly.i1) * W;
+    const float* r0 = img + ly.i0 * W;
+    const float* r1 = img + ly.i1 * W;
     float res[4];
+    if (compact) {
+      const float t0 = __ldg(r0 + c0), t1 = __ldg(r0 + c1), t2 = __ldg(r0 + c2);
+      const float b0 = __ldg(r1 + c0), b1 = __ldg(r1 + c1), b2 = __ldg(r1 + c2);
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const float top = __fadd_rn(__fmul_rn(lx[j].l0, __ldg(r0 + lx[j].i0)), __fmul_rn(lx[j].l1, __ldg(r0 + lx[j].i1)));
-      const float bot = __fadd_rn(__fmul_rn(lx[j].l0, __ldg(r1 + lx[j].i0)), __fmul_rn(lx[j].l1, __ldg(r1 + lx[j].i1)));
-      res[j] = __fmul_rn((float)F, __fadd_rn(__fmul_rn(ly.l0, top), __fmul_rn(ly.l1, bot)));
+      for (int j = 0; j < 4; ++j) {
+        const int d0 = lx[j].i0 - c0, d1 = lx[j].i1 - c0;
+        const float ta = d0 == 0 ? t0 : t1, tb = d1 == 0 ? t0 : (d1 == 1 ? t1 : t2);
+        const float ba = d0 == 0 ? b0 : b1, bb = d1 == 0 ? b0 : (d1 == 1 ? b1 : b2);
+        const float top = __fadd_rn(__fmul_rn(lx[j].l0, ta), __fmul_rn(lx[j].l1, tb));
+        const float bot = __fadd_rn(__fmul_rn(lx[j].l0, ba), __fmul_rn(lx[j].l1, bb));
+        res[j] = __fmul_rn((float)F, __fadd_rn(__fmul_rn(ly.l0, top), __fmul_rn(ly.l1, bot)));
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float top = __fadd_rn(__fmul_rn(lx[j].l0, __ldg(r0 + lx[j].i0)), __fmul_rn(lx[j].l1, __ldg(r0 + lx[j].i1)));
+        const float bot = __fadd_rn(__fmul_rn(lx[j].l0, __ldg(r1 + lx[j].i0)), __fmul_rn(lx[j].l1, __ldg(r1 + lx[j].i1)));
+        res[j] = __fmul_rn((float)F, __fadd_rn(__fmul_rn(ly.l0, top), __fmul_rn(ly.l1, bot)));
+      }
     }
-    stg_cs_f4(out + static_cast<size_t>(row) * Wo + 4 * xq, make_float4(res[0], res[1], res[2], res[3]));
+    stg_cs_f4(oimg + static_cast<size_t>(yo) * Wo, make_float4(res[0], res[1], res[2], res[3]));
   }
 }
 
@@ -324,12 +343,12 @@ extern "C" int sf_upsample_simple_f32(const float* disp, float* out, int N, int 
   SF_CHECK_ARG((reinterpret_cast<uintptr_t>(out) & 15) == 0, "upsample_simple: out must be 16-byte aligned");
   float sh, sw;
   if (int rc = simple_scales(H, W, factor, &sh, &sw)) return rc;
-  const long long rows = 1LL * N * H * factor;
-  SF_CHECK_ARG(rows < (1LL << 31), "upsample_simple: too many output rows");
+  SF_CHECK_ARG(N <= 65535, "upsample_simple: more than 65535 images per call");
   const int ychunks = (W * factor / 4 + 127) / 128;
-  dim3 grid(static_cast<unsigned>(min(rows, static_cast<long long>(sm_count()) * 16 / ychunks + 1)), ychunks);
-  upsample_simple_kernel<<<grid, 128, 0, static_cast<cudaStream_t>(stream)>>>(disp, out, static_cast<int>(rows), H, W,
-                                                                              factor, sh, sw);
+  SF_CHECK_ARG(ychunks <= 65535, "upsample_simple: output too wide");
+  const int per_img = max(1, min(H * factor, sm_count() * 16 / (ychunks * N) + 1));   // ~16 CTAs per SM in all
+  dim3 grid(per_img, ychunks, N);
+  upsample_simple_kernel<<<grid, 128, 0, static_cast<cudaStream_t>(stream)>>>(disp, out, H, W, factor, sh, sw);
   SF_LAUNCH_CHECK();
   return SF_OK;
 }
