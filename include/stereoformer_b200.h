@@ -32,6 +32,7 @@ extern "C" {
 #define SF_WIN_VARIANCE 1 /* variance_local_cost_volume.py: bounds = disp -/+ gamma * sigma        */
 #define SF_WIN_OFFSETS 2  /* Attempts/update.py:279-282: bounds = disp - lo, disp + up (tensors)   */
 #define SF_WIN_ABSOLUTE 3 /* pure_learning_method.py:112: lo/up ARE the bounds                     */
+#define SF_WIN_VARIANCE_BOUNDS 5 /* lo/up ARE the bounds, under the variance window's validity / clamp rules (variance_local_cost_volume.py:44-53); forward only: separates the index arithmetic from sigma's exp() rounding in the parity tests */
 #define SF_WIN_HEAD 4     /* as OFFSETS, lo = OffsetPredictionHead conv2 output [B,2,H,W] before relu2 (update.py:96-105): ReLU + chunk fused; up unused */
 
 /* scalar-division rounding (tensor / python scalar): PyTorch CPU divides, PyTorch CUDA multiplies

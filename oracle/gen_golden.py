@@ -127,9 +127,24 @@ def main():
     cvv = torch.randn(2, 24, 6, 40)
     curv = R["DisparityEstimation"](24, True)(cvv).unsqueeze(1)
     for cvalid in (True, False):
+        sigma = vlc.GetVarince(torch.softmax(cvv, 1), curv)
+        # bounds / candidates exactly as Variance_Based_Local_Cost_Volume.forward computes them (:41-66)
+        lo0, up0 = curv - 1 * sigma, curv + 1 * sigma
+        lo, up = lo0, up0
+        if cvalid:
+            xs = torch.arange(40).view(1, 1, 1, 40).repeat(1, 1, 6, 1).type_as(curv)
+            inv = torch.clamp((lo < 0).float() + (up >= 23).float() + (up > xs).float(), max=1.0)
+        else:
+            lo, up = torch.clamp(lo, min=0, max=23), torch.clamp(up, min=0, max=23)
+        step = (up - lo) * 1.0 / 20
+        cand = lo + torch.arange(21).type_as(cvv).view(1, 21, 1, 1) * step
+        if cvalid:
+            cand = cand * (1 - inv) + inv * curv.repeat(1, 21, 1, 1)
+        jf, ic = sampler_trace(vlc, cvv, cand)
         save("variance_window_valid%d" % int(cvalid), cv=cvv, cur=curv, gamma=1.0, n_points=20,
              out=vlc.Variance_Based_Local_Cost_Volume(1, 20)(cvv, curv, cvalid),
-             sigma=vlc.GetVarince(torch.softmax(cvv, 1), curv))
+             sigma=sigma, lo=lo0, up=up0, cand=cand, idx_floor=jf, idx_ceil=ic,
+             local=vlc.build_cost_volume_from_volume(cvv, cand))
 
     # ---- a6 DLC window tail + uncertainty volume (update.py:279-313, :86) -------------
     upd = R["upd"]

@@ -10,7 +10,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libsfb200.so")
 
 SF_ALGO_AUTO, SF_ALGO_TMA, SF_ALGO_GENERIC, SF_ALGO_TC = 0, 1, 2, 3
-SF_WIN_FIXED, SF_WIN_VARIANCE, SF_WIN_OFFSETS, SF_WIN_ABSOLUTE, SF_WIN_HEAD = 0, 1, 2, 3, 4
+SF_WIN_FIXED, SF_WIN_VARIANCE, SF_WIN_OFFSETS, SF_WIN_ABSOLUTE, SF_WIN_HEAD, SF_WIN_VARIANCE_BOUNDS = 0, 1, 2, 3, 4, 5
 SF_DIV_TRUE, SF_DIV_RECIP = 0, 1
 
 _c_int, _c_float, _p = ctypes.c_int, ctypes.c_float, ctypes.c_void_p

@@ -131,8 +131,11 @@ local_window_kernel(const __grid_constant__ CUtensorMap mapCV, const WindowParam
   } else {
     lower = p.lo[pix];
     upper = p.up[pix];
+    // SF_WIN_VARIANCE_BOUNDS: the caller's bounds under the variance window's rules (variance_local_cost_volume.py:44-53)
+    if (p.mode == SF_WIN_VARIANCE_BOUNDS && p.consider_valid) extra = (upper > (float)x) ? 1.f : 0.f;
   }
-  const sfm::Window w = sfm::make_window(lower, upper, D, N, p.consider_valid, p.mode == SF_WIN_VARIANCE, extra, p.recip);
+  const bool var_rules = p.mode == SF_WIN_VARIANCE || p.mode == SF_WIN_VARIANCE_BOUNDS;
+  const sfm::Window w = sfm::make_window(lower, upper, D, N, p.consider_valid, var_rules, extra, p.recip);
 
   // ---- N+1 samples; soft-max over them (max first, then independent exponentials); expectation of the candidates
   const size_t dbg0 = (static_cast<size_t>(b) * (N + 1) * p.H + y) * p.W + x;
@@ -262,8 +265,8 @@ static int local_window_impl(const float* cv, const float* disp, const float* lo
   using namespace sf;
   SF_CHECK_ARG(cv && out, "local_window: null pointer");
   SF_CHECK_ARG(B > 0 && D > 0 && H > 0 && W > 0 && n_points > 0, "local_window: non-positive dimension");
-  SF_CHECK_ARG(mode >= SF_WIN_FIXED && mode <= SF_WIN_HEAD, "local_window: unknown mode %d", mode);
-  SF_CHECK_ARG((mode != SF_WIN_OFFSETS && mode != SF_WIN_ABSOLUTE) || (lo && up),
+  SF_CHECK_ARG(mode >= SF_WIN_FIXED && mode <= SF_WIN_VARIANCE_BOUNDS, "local_window: unknown mode %d", mode);
+  SF_CHECK_ARG((mode != SF_WIN_OFFSETS && mode != SF_WIN_ABSOLUTE && mode != SF_WIN_VARIANCE_BOUNDS) || (lo && up),
                "local_window: this mode needs the lo/up bound tensors");
   SF_CHECK_ARG(mode != SF_WIN_HEAD || lo, "local_window: SF_WIN_HEAD needs the [B,2,H,W] head output in lo");
   SF_CHECK_ARG(static_cast<size_t>(D) * WIN_TPB * 4 <= 200 * 1024, "local_window: D=%d too large for the staged tile", D);

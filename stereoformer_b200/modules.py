@@ -19,6 +19,12 @@ from ._lib import SF_DIV_RECIP, SF_DIV_TRUE, SF_WIN_ABSOLUTE, SF_WIN_FIXED, SF_W
 DEFAULT_DIV_MODE = SF_DIV_RECIP
 
 
+def _div(obj):
+    """div_mode of a module; reference instances that carry our grafted forward (install.py) have no such attribute."""
+    dm = getattr(obj, "div_mode", None)
+    return DEFAULT_DIV_MODE if dm is None else dm
+
+
 class _ForwardOnly(torch.autograd.Function):
     """Runs ``fn(*args)`` outside autograd; differentiating through it raises."""
 
@@ -137,39 +143,43 @@ def build_cost_volume_from_volume(old_volume, sampling_candidates):
 class LocalCostVolume(nn.Module):
     """models/LocalCostVolume/Attempts/fixed_local_cost_volume.py:13-58."""
 
+    div_mode = None          # None = DEFAULT_DIV_MODE at call time
+
     def __init__(self, radius=4, sample_points=10) -> None:
         super().__init__()
         self.radius = radius
         self.sample_points = sample_points
-        self.div_mode = DEFAULT_DIV_MODE
 
     def forward(self, old_cost_volume, cur_disparity, consider_valid=False):
+        dm = _div(self)
         return _run(lambda cv, d: ops.local_window(cv, d, mode=SF_WIN_FIXED, radius=self.radius,
                                                    n_points=self.sample_points, consider_valid=consider_valid,
-                                                   div_mode=self.div_mode),
+                                                   div_mode=dm),
                     "LocalCostVolume", old_cost_volume, cur_disparity,
                     bwd=lambda a, g, n: ops.local_window_backward(
                         a[0], a[1], None, None, g, SF_WIN_FIXED, self.radius, self.sample_points, consider_valid,
-                        self.div_mode, (n[0], n[1], False, False))[:2])
+                        dm, (n[0], n[1], False, False))[:2])
 
 
 class Variance_Based_Local_Cost_Volume(nn.Module):
     """models/LocalCostVolume/Attempts/variance_local_cost_volume.py:28-78."""
 
+    div_mode = None
+
     def __init__(self, garma=1, sample_points=10):
         super().__init__()
         self.sample_points = sample_points
         self.garma = garma
-        self.div_mode = DEFAULT_DIV_MODE
 
     def forward(self, old_cost_volume, cur_disparity, consider_valid=False):
+        dm = _div(self)
         return _run(lambda cv, d: ops.local_window(cv, d, mode=SF_WIN_VARIANCE, gamma=self.garma,
                                                    n_points=self.sample_points, consider_valid=consider_valid,
-                                                   div_mode=self.div_mode),
+                                                   div_mode=dm),
                     "Variance_Based_Local_Cost_Volume", old_cost_volume, cur_disparity,
                     bwd=lambda a, g, n: ops.local_window_backward(
                         a[0], a[1], None, None, g, mode=SF_WIN_VARIANCE, radius=self.garma,
-                        n_points=self.sample_points, consider_valid=consider_valid, div_mode=self.div_mode,
+                        n_points=self.sample_points, consider_valid=consider_valid, div_mode=dm,
                         needs=(n[0], n[1], False, False))[:2])
 
 
@@ -224,13 +234,12 @@ class CorrBlock1D:
     def __init__(self, fmap1, fmap2, num_levels=4, radius=4):
         self.num_levels = num_levels
         self.radius = radius
-        self.div_mode = DEFAULT_DIV_MODE
         # forward-only: under autograd the pyramid carries a backward that raises instead of silently dropping gradients
         self.corr_pyramid = list(_run(lambda a, b: tuple(ops.corr1d_pyramid(a, b, num_levels, extra_level=True)),
                                       "CorrBlock1D", fmap1, fmap2))
 
     def __call__(self, coords):
-        return _run(lambda c, *pyr: ops.corr1d_lookup(list(pyr), c, self.radius, self.num_levels, self.div_mode),
+        return _run(lambda c, *pyr: ops.corr1d_lookup(list(pyr), c, self.radius, self.num_levels, _div(self)),
                     "CorrBlock1D", coords, *self.corr_pyramid)
 
     @staticmethod
@@ -251,10 +260,9 @@ class PytorchAlternateCorrBlock1D:
         self.corr_pyramid = []
         self.fmap1 = fmap1
         self.fmap2 = fmap2
-        self.div_mode = DEFAULT_DIV_MODE
 
     def __call__(self, coords):
-        return _run(lambda c, a, b: ops.corr1d_alt(a, b, c, self.radius, self.num_levels, self.div_mode),
+        return _run(lambda c, a, b: ops.corr1d_alt(a, b, c, self.radius, self.num_levels, _div(self)),
                     "PytorchAlternateCorrBlock1D", coords, self.fmap1, self.fmap2)
 
 

@@ -11,7 +11,7 @@ import torch
 
 from . import _lib
 from ._lib import (SF_ALGO_AUTO, SF_ALGO_GENERIC, SF_ALGO_TC, SF_ALGO_TMA, SF_DIV_RECIP, SF_DIV_TRUE, SF_WIN_ABSOLUTE,
-                   SF_WIN_FIXED, SF_WIN_HEAD, SF_WIN_OFFSETS, SF_WIN_VARIANCE)
+                   SF_WIN_FIXED, SF_WIN_HEAD, SF_WIN_OFFSETS, SF_WIN_VARIANCE, SF_WIN_VARIANCE_BOUNDS)
 
 __all__ = ["corr_volume", "gwc_volume", "shift_volume", "soft_argmin", "local_window", "sample_volume", "disp_warp",
            "guidance", "corr1d_pyramid", "corr1d_lookup", "dcn_forward", "dcn_backward", "corr_volume_backward", "soft_argmin_backward",

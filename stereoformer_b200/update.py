@@ -53,8 +53,11 @@ class ConvGRU(nn.Module):
         s = _m._run(lambda b, h, x: ops.gru_reset(b, h, x), "ConvGRU", zb[:, C:], prev_h, input,
                     bwd=lambda a, gs, n: ops.gru_reset_backward(a[0], a[1], a[2].shape, gs, n))
         g = self.conv_g(s)
-        return _m._run(lambda z, gg, h: ops.gru_blend(z, gg, h, self.softsign), "ConvGRU", zb[:, :C], g, prev_h,
-                       bwd=lambda a, gh, n: ops.gru_blend_backward(a[0], a[1], a[2], gh, self.softsign, n))
+        softsign = getattr(self, "softsign", None)
+        if softsign is None:                 # a reference instance carrying this forward (install.py)
+            softsign = isinstance(self.conv_gg[1], nn.Softsign)
+        return _m._run(lambda z, gg, h: ops.gru_blend(z, gg, h, softsign), "ConvGRU", zb[:, :C], g, prev_h,
+                       bwd=lambda a, gh, n: ops.gru_blend_backward(a[0], a[1], a[2], gh, softsign, n))
 
 
 class BasicGuidanceNet(nn.Module):
@@ -81,7 +84,7 @@ class BasicGuidanceNet(nn.Module):
         return left_image, right_image
 
     def forward(self, old_cost_volume, cur_disp, left_image, right_image):
-        cur_left, cur_right = self.resize_images(cur_disp, left_image, right_image)
+        cur_left, cur_right = BasicGuidanceNet.resize_images(cur_disp, left_image, right_image)
         error_map, uncertainty_volume = _m.guidance_inputs(old_cost_volume, cur_disp, cur_left, cur_right)
         error_feature = self.disparity_error_encoder(error_map)
         uncertainty_feature = self.uncertain_encoder(uncertainty_volume)
@@ -129,8 +132,8 @@ class DisparityUpdateDLC(nn.Module):
     def forward(self, old_cost_volume, cur_disp, left_image, right_image, hidden_state=None, consider_valid=True):
         offset_features = self.encoder(old_cost_volume, cur_disp, left_image, right_image)
         hidden_state = self.gru(offset_features, hidden_state)
-        disp = _head_window(old_cost_volume, cur_disp, self.offset.forward_pre(hidden_state), self.sample_points,
-                            consider_valid)
+        disp = _head_window(old_cost_volume, cur_disp, OffsetPredictionHead.forward_pre(self.offset, hidden_state),
+                            self.sample_points, consider_valid)
         return disp, hidden_state
 
 
@@ -154,14 +157,139 @@ class DisparityUpdateDLCWithMask(nn.Module):
         offset_features = self.encoder(old_cost_volume, cur_disp, left_image, right_image)
         hidden_state = self.gru(offset_features, hidden_state)
         mask = self.mask(hidden_state)
-        disp = _head_window(old_cost_volume, cur_disp, self.offset.forward_pre(hidden_state), self.sample_points,
-                            consider_valid)
+        disp = _head_window(old_cost_volume, cur_disp, OffsetPredictionHead.forward_pre(self.offset, hidden_state),
+                            self.sample_points, consider_valid)
         return disp, hidden_state, mask
 
     def forward(self, old_cost_volume, cur_disp, left_image, right_image, hidden_state=None, consider_valid=True):
-        disp, hidden_state, mask = self.step(old_cost_volume, cur_disp, left_image, right_image, hidden_state,
-                                             consider_valid)
-        return disp, hidden_state, self.MASK_SCALE * mask
+        disp, hidden_state, mask = DisparityUpdateDLCWithMask.step(self, old_cost_volume, cur_disp, left_image,
+                                                                   right_image, hidden_state, consider_valid)
+        return disp, hidden_state, DisparityUpdateDLCWithMask.MASK_SCALE * mask
+
+
+class DisparityUpdateDLCWithMaskV2(DisparityUpdateDLCWithMask):
+    """Attempts/updatev2.py:168-251: the GRU also sees a 256 -> 64 encoding of the left 1/8 feature map."""
+
+    def __init__(self, input_channels, feature_dim, hidden_dim, sample_points=10):
+        nn.Module.__init__(self)
+        self.sample_points = sample_points
+        self.hidden_dim = hidden_dim
+        self.feature_dim = feature_dim
+        width = self.hidden_dim * 2 + self.feature_dim
+        self.encoder = BasicGuidanceNet(input_channels=input_channels, hidden_layer=self.hidden_dim)
+        self.feature_encode = nn.Sequential(nn.Conv2d(256, 64, kernel_size=3, stride=1, padding=1, bias=False),
+                                            nn.BatchNorm2d(64), nn.ReLU(inplace=True))
+        self.gru = ConvGRU(nb_channel=width, softsign=False)
+        self.offset = OffsetPredictionHead(input_dim=width, hidden_dim=64)
+        self.mask = nn.Sequential(nn.Conv2d(width, 256, 3, padding=1), nn.ReLU(inplace=True),
+                                  nn.Conv2d(256, 64 * 9, 1, padding=0))
+
+    def step(self, old_cost_volume, cur_disp, left_image, right_image, hidden_state, left_feature, consider_valid):
+        offset_features = self.encoder(old_cost_volume, cur_disp, left_image, right_image)
+        input_features = torch.cat((offset_features, self.feature_encode(left_feature)), dim=1)
+        hidden_state = self.gru(input_features, hidden_state)
+        mask = self.mask(hidden_state)
+        disp = _head_window(old_cost_volume, cur_disp, OffsetPredictionHead.forward_pre(self.offset, hidden_state),
+                            self.sample_points, consider_valid)
+        return disp, hidden_state, mask
+
+    def forward(self, old_cost_volume, cur_disp, left_image, right_image, hidden_state=None, left_feature=None,
+                consider_valid=True):
+        disp, hidden_state, mask = DisparityUpdateDLCWithMaskV2.step(
+            self, old_cost_volume, cur_disp, left_image, right_image, hidden_state, left_feature, consider_valid)
+        return disp, hidden_state, DisparityUpdateDLCWithMask.MASK_SCALE * mask
+
+
+# ----------------------------------------------------------------------------- single-shot DLC (SmallUNet bounds)
+class _ResBlock(nn.Module):
+    """models/BasicBlocks/resnet.py:20-48 (parameter names kept)."""
+    conv2_factory = staticmethod(lambda n: nn.Conv2d(n, n, kernel_size=3, padding=1))
+
+    def __init__(self, n_in, n_out, kernel_size=3, stride=1):
+        super().__init__()
+        self.conv1 = nn.Conv2d(n_in, n_out, kernel_size=kernel_size, stride=stride, padding=1)
+        self.bn1 = nn.BatchNorm2d(n_out)
+        self.relu = nn.ReLU(inplace=True)
+        self.conv2 = self.conv2_factory(n_out)
+        self.bn2 = nn.BatchNorm2d(n_out)
+        self.shortcut = None
+        if stride != 1 or n_out != n_in:
+            self.shortcut = nn.Sequential(nn.Conv2d(n_in, n_out, kernel_size=1, stride=stride), nn.BatchNorm2d(n_out))
+
+    def forward(self, x):
+        residual = x if self.shortcut is None else self.shortcut(x)
+        out = self.bn2(self.conv2(self.relu(self.bn1(self.conv1(x)))))
+        out += residual
+        return self.relu(out)
+
+
+class _DeformBlock(_ResBlock):
+    """models/BasicBlocks/resnet.py:51-79: the second convolution is a ModulatedDeformConvPack (a10)."""
+
+    @staticmethod
+    def conv2_factory(n):
+        from .dcn_modules import ModulatedDeformConvPack
+        return ModulatedDeformConvPack(n, n, kernel_size=3, stride=1, padding=1)
+
+
+class SmallUNet(nn.Module):
+    """Attempts/pure_learning_method.py:35-75."""
+
+    def __init__(self, input_channels, hidden_layer=32):
+        super().__init__()
+        self.input_channels = input_channels
+        self.hidden_layers = hidden_layer
+        self.uncertain_encoder = nn.Sequential(
+            nn.Conv2d(self.input_channels, self.hidden_layers, kernel_size=3, stride=1, padding=1, bias=False),
+            nn.BatchNorm2d(self.hidden_layers), nn.ReLU(inplace=True))
+        self.disparity_error_encoder = nn.Sequential(
+            nn.Conv2d(3, self.hidden_layers, kernel_size=3, stride=1, padding=1, bias=False),
+            nn.BatchNorm2d(self.hidden_layers), nn.ReLU(inplace=True))
+        self.feature_fusion1 = _ResBlock(self.hidden_layers * 2, self.hidden_layers, 3, 1)
+        self.feature_fusion2 = _DeformBlock(self.hidden_layers, self.hidden_layers // 2, 3, 1)
+        self.offset_prediction = nn.Sequential(
+            nn.Conv2d(self.hidden_layers // 2, 2, kernel_size=3, padding=1, stride=1), nn.ReLU(inplace=True))
+
+    def forward(self, disparity_error, uncertainity_volume):
+        info = torch.cat((self.disparity_error_encoder(disparity_error),
+                          self.uncertain_encoder(uncertainity_volume)), dim=1)
+        offset = self.offset_prediction(self.feature_fusion2(self.feature_fusion1(info)))
+        return torch.chunk(offset, 2, dim=1)
+
+
+class PureLearningLocalCostVolume(nn.Module):
+    """Attempts/pure_learning_method.py:78-143: the two SmallUNet outputs ARE the window bounds (:112).
+    with_bounds=True is pure_learning_method_w_super.py: bounds = cur_disp -/+ outputs (:111-113), also returned (:145)."""
+
+    with_bounds = False
+
+    def __init__(self, sample_points=10, with_bounds=False):
+        super().__init__()
+        self.sample_points = sample_points
+        self.with_bounds = with_bounds
+        self.offset_prediction_network = SmallUNet(input_channels=24, hidden_layer=32)
+
+    def forward(self, old_cost_volume, cur_disp, left_image, right_image, consider_valid=False):
+        cur_left, cur_right = BasicGuidanceNet.resize_images(cur_disp, left_image, right_image)
+        error_map, uncertainty_volume = _m.guidance_inputs(old_cost_volume, cur_disp, cur_left, cur_right)
+        first, second = self.offset_prediction_network(error_map, uncertainty_volume)
+        if not self.with_bounds:
+            return _m.dlc_window(old_cost_volume, cur_disp, first, second, self.sample_points, consider_valid,
+                                 absolute=True)
+        disp = _m.dlc_window(old_cost_volume, cur_disp, first, second, self.sample_points, consider_valid)
+        lower_bound, upper_bound = cur_disp - first, cur_disp + second
+        if not consider_valid:                                     # :120-121: the returned bounds are the clamped ones
+            lower_bound = torch.clamp(lower_bound, min=0)
+            upper_bound = torch.clamp(upper_bound, min=0, max=old_cost_volume.size(1))
+        return disp, lower_bound, upper_bound
+
+
+class PureLearningLocalCostVolumeWithBounds(PureLearningLocalCostVolume):
+    """Attempts/pure_learning_method_w_super.py:78-145."""
+    with_bounds = True
+
+    def __init__(self, sample_points=10):
+        super().__init__(sample_points, with_bounds=True)
 
 
 class DlcGruRefiner:

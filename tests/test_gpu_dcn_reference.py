@@ -1,0 +1,80 @@
+"""a10 pinned on the REFERENCE'S OWN compiled extension (oracle/_ref/native/DCN.so, built from the unmodified
+deform/src sources for sm_100a): forward and backward of the drop-in against it, random offsets and masks."""
+import pytest
+import torch
+
+from oracle import refenv
+
+pytestmark = [pytest.mark.gpu, pytest.mark.skipif(not refenv.available()["dcn"],
+                                                  reason="reference DCN extension not built")]
+
+
+def _ref():
+    refenv.activate(dcn="reference")
+    import sys
+    import stereoformer_b200.DCN as ours
+    mod = sys.modules["DCN"]
+    if mod is ours:                       # an earlier test installed the drop-in under the name
+        import importlib.util
+        import os
+        so = os.path.join(refenv.NATIVE_DST, "DCN.so")
+        spec = importlib.util.spec_from_file_location("DCN", so)
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+    return mod
+
+
+CASES = [  # B, Cin, Cout, H, W, groups, dg, stride, pad, dil
+    (2, 4, 4, 4, 4, 2, 1, 1, 1, 1),            # deform/test.py:15-18 shape
+    (2, 16, 16, 34, 60, 1, 1, 1, 1, 1),        # the shipped 16->16 layer (dcn_small_kernel)
+    (1, 64, 128, 40, 56, 1, 2, 1, 1, 1),       # deform/test.py:526 (tcgen05 path)
+    (1, 128, 128, 31, 45, 1, 1, 1, 1, 1),      # disp_residual.py:213 (tcgen05 path)
+    (2, 32, 48, 23, 37, 1, 4, 2, 1, 1),        # stride 2
+    (1, 24, 24, 20, 33, 3, 3, 1, 2, 2),        # groups, dilation
+]
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_forward_matches_reference_extension(case):
+    import stereoformer_b200.DCN as ours
+    ref = _ref()
+    B, Cin, Cout, H, W, G, dg, s, p, d = case
+    torch.manual_seed(3)
+    x = torch.randn(B, Cin, H, W, device="cuda")
+    w = torch.randn(Cout, Cin // G, 3, 3, device="cuda") * 0.1
+    b = torch.randn(Cout, device="cuda")
+    Ho = (H + 2 * p - (d * 2 + 1)) // s + 1
+    Wo = (W + 2 * p - (d * 2 + 1)) // s + 1
+    off = torch.randn(B, dg * 18, Ho, Wo, device="cuda") * 2
+    msk = torch.sigmoid(torch.randn(B, dg * 9, Ho, Wo, device="cuda"))
+    args = (3, 3, s, s, p, p, d, d, G, dg, 64)
+    want = ref.modulated_deform_conv_forward(x, w, b, off, msk, *args)
+    got = ours.modulated_deform_conv_forward(x, w, b, off, msk, *args)
+    assert got.shape == want.shape
+    scale = want.abs().max()
+    assert (got - want).abs().max() <= 1e-4 * scale, float((got - want).abs().max() / scale)
+    want1 = ref.deform_conv_forward(x, w, b, off, *args)
+    got1 = ours.deform_conv_forward(x, w, b, off, *args)
+    assert (got1 - want1).abs().max() <= 1e-4 * want1.abs().max()
+
+
+@pytest.mark.parametrize("case", CASES[:3] + CASES[4:])
+def test_backward_matches_reference_extension(case):
+    import stereoformer_b200.DCN as ours
+    ref = _ref()
+    B, Cin, Cout, H, W, G, dg, s, p, d = case
+    torch.manual_seed(4)
+    x = torch.randn(B, Cin, H, W, device="cuda")
+    w = torch.randn(Cout, Cin // G, 3, 3, device="cuda") * 0.1
+    b = torch.randn(Cout, device="cuda")
+    Ho = (H + 2 * p - (d * 2 + 1)) // s + 1
+    Wo = (W + 2 * p - (d * 2 + 1)) // s + 1
+    off = torch.randn(B, dg * 18, Ho, Wo, device="cuda") * 2
+    msk = torch.sigmoid(torch.randn(B, dg * 9, Ho, Wo, device="cuda"))
+    go = torch.randn(B, Cout, Ho, Wo, device="cuda")
+    args = (3, 3, s, s, p, p, d, d, G, dg, 64)
+    want = ref.modulated_deform_conv_backward(x, w, b, off, msk, go, *args)
+    got = ours.modulated_deform_conv_backward(x, w, b, off, msk, go, *args)
+    for name, g, r in zip(("input", "offset", "mask", "weight", "bias"), got, want):
+        scale = r.abs().max().clamp_min(1e-6)
+        assert (g - r).abs().max() <= 2e-4 * scale, (name, float((g - r).abs().max() / scale))

@@ -1,0 +1,75 @@
+"""The reference's own networks with the drop-ins installed, on a B200 (missing #1).
+
+The SAME network object (unmodified reference code from oracle/_ref, reference initialisers under seed 1024, eval mode)
+runs a synthetic 544x960 pair twice: stock (PyTorch eager ops + the reference's compiled DCN extension) and with
+stereoformer_b200 installed.  north_star's bar: <= 1e-3 px EPE on the output (full-resolution) disparity.
+"""
+import json
+import os
+
+import pytest
+import torch
+
+from oracle import refenv
+
+pytestmark = [pytest.mark.gpu,
+              pytest.mark.skipif(refenv.ref_root() is None, reason="no copy of the reference reachable")]
+
+EPE_TOL = 1e-3       # px, north_star
+
+
+@pytest.fixture(autouse=True)
+def _true_fp32():
+    old = torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cudnn.allow_tf32 = False          # "reference PyTorch path" in fp32, no TF32 convolutions
+    torch.backends.cuda.matmul.allow_tf32 = False
+    yield
+    torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = old
+
+
+def _record(res):
+    out = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out")
+    try:
+        os.makedirs(out, exist_ok=True)
+        with open(os.path.join(out, "fullmodel_parity.jsonl"), "a") as f:
+            f.write(json.dumps(res) + "\n")
+    except OSError:
+        pass
+
+
+@pytest.mark.parametrize("variant,batch", [("lc", 2), ("var", 1), ("dlc", 1), ("dlc_super", 1), ("dlc_gru", 1),
+                                           ("dlc_gru2", 1)])
+def test_lowcnn_dropins_match_stock(variant, batch):
+    from tools import fullmodel
+    if variant in ("dlc", "dlc_super") and not refenv.available()["dcn"]:
+        pytest.skip("the stock forward needs the reference's DCN extension (oracle/_ref/native/DCN.so)")
+    res = fullmodel.compare(variant, batch, 544, 960, torch.device("cuda", 0))
+    print(res)
+    _record(res)
+    assert res["disp_max"] > 1.0, "degenerate network output"
+    assert res["epe"] <= EPE_TOL, res
+
+
+def test_lowcnn_config5_shape():
+    """BASELINE configs[4] shape class: maxdisp 384 (D=48 at 1/8), DLC with the DCN layer, reduced to 992x1440 to keep
+    the eager stock forward small."""
+    from tools import fullmodel
+    if not refenv.available()["dcn"]:
+        pytest.skip("needs the reference's DCN extension")
+    res = fullmodel.compare("dlc", 1, 992, 1440, torch.device("cuda", 0), d8=48)
+    print(res)
+    _record(res)
+    assert res["epe"] <= EPE_TOL, res
+
+
+def test_stock_forward_unchanged_after_uninstall():
+    from tools import fullmodel
+    from tools.synth import stereo_pair
+    dev = torch.device("cuda", 0)
+    net = fullmodel.build_net("lc", dev)
+    left, right, _ = stereo_pair(1, 256, 512, device=dev)
+    a = fullmodel.forward(net, "lc", left, right)
+    with fullmodel.dropins():
+        fullmodel.forward(net, "lc", left, right)
+    b = fullmodel.forward(net, "lc", left, right)
+    assert torch.equal(a, b)

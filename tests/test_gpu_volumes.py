@@ -186,13 +186,44 @@ def test_dlc_window_golden(ops, valid):
 
 
 @pytest.mark.parametrize("valid", [0, 1])
-def test_variance_window_golden(ops, valid):
+def test_variance_window_indices_bit_exact_given_reference_bounds(ops, valid):
+    """a5 (VERDICT r1 missing #4): with the reference's own bounds disp -/+ gamma * sigma fed in, the variance window's
+    candidates, floor / ceil indices and interpolated samples are bit-exact -- the validity rule `upper > x`, the
+    [0, D-1] clamps and the index arithmetic of variance_local_cost_volume.py:44-66 (the only part of a5 that differs
+    from a4) carry no tolerance."""
     g = load_golden("variance_window_valid%d" % valid)
-    out = ops.local_window(dev(g["cv"]), dev(g["cur"]), mode=ops.SF_WIN_VARIANCE, gamma=g["gamma"],
-                           n_points=g["n_points"], consider_valid=bool(valid), div_mode=ops.SF_DIV_TRUE)
-    # bounds depend on exp(): not bit-comparable; a flipped validity decision shows up as a large error
-    err = (out.cpu() - g["out"]).abs()
-    assert err.median() < 1e-4 and (err < 1e-3).float().mean() > 0.995
+    out, dbg = ops.local_window(dev(g["cv"]), dev(g["cur"]), dev(g["lo"]), dev(g["up"]),
+                                mode=ops.SF_WIN_VARIANCE_BOUNDS, n_points=g["n_points"], consider_valid=bool(valid),
+                                div_mode=ops.SF_DIV_TRUE, debug=True)
+    _check_window(out, dbg, g)
+
+
+@pytest.mark.parametrize("valid", [0, 1])
+def test_variance_window_golden(ops, valid):
+    """a5 end to end (the kernel derives sigma itself: exp() and the sum order differ from ATen in the last bits, so
+    the bounds are not bit-comparable).  Every pixel whose indices differ from the reference's must be explained by a
+    bound or candidate sitting within float rounding of a decision threshold; all other pixels must match to 1e-3 px
+    with identical indices."""
+    g = load_golden("variance_window_valid%d" % valid)
+    out, dbg = ops.local_window(dev(g["cv"]), dev(g["cur"]), mode=ops.SF_WIN_VARIANCE, gamma=g["gamma"],
+                                n_points=g["n_points"], consider_valid=bool(valid), div_mode=ops.SF_DIV_TRUE,
+                                debug=True)
+    D, W = g["cv"].shape[1], g["cv"].shape[3]
+    same = (dbg["idx_floor"].cpu().long() == g["idx_floor"]).all(1) & (dbg["idx_ceil"].cpu().long() == g["idx_ceil"]).all(1)
+    err = (out.cpu() - g["out"]).abs().squeeze(1)
+    assert err[same].max() < 1e-3
+    assert (dbg["cand"].cpu() - g["cand"])[same.unsqueeze(1).expand_as(g["cand"])].abs().max() < 1e-4
+    # pixels with different indices: a candidate within 1e-4 of an integer (ceil / floor flips), or a bound within
+    # 1e-4 of a validity threshold (0, D-1, x)
+    cand, lo, up = g["cand"], g["lo"].squeeze(1), g["up"].squeeze(1)
+    near_int = ((cand - cand.round()).abs() < 1e-4).any(1)
+    xs = torch.arange(W, dtype=torch.float32).view(1, 1, W)
+    near_thr = (lo.abs() < 1e-4) | ((up - (D - 1)).abs() < 1e-4) | ((up - xs).abs() < 1e-4)
+    unexplained = ~same & ~near_int & ~near_thr
+    print("variance window valid=%d: %d of %d pixels differ in an index, %d unexplained; max err %.3g"
+          % (valid, int((~same).sum()), same.numel(), int(unexplained.sum()), float(err.max())))
+    assert int(unexplained.sum()) == 0
+    assert float((~same).float().mean()) < 0.02
 
 
 def test_sample_volume_golden(ops):

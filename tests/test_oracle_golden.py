@@ -55,6 +55,16 @@ def test_variance_window(valid):
     g = load_golden("variance_window_valid%d" % valid)
     assert eq(O.disparity_sigma(torch.softmax(g["cv"], 1), g["cur"]), g["sigma"])
     assert eq(O.variance_local_cost_volume(g["cv"], g["cur"], g["gamma"], g["n_points"], bool(valid)), g["out"])
+    # window indices / candidates of the variance window (north_star: bit-exact), from the reference's own bounds
+    cv, cur, D, W = g["cv"], g["cur"], g["cv"].shape[1], g["cv"].shape[3]
+    sigma = O.disparity_sigma(torch.softmax(cv, 1), cur)
+    lower, upper = cur - g["gamma"] * sigma, cur + g["gamma"] * sigma
+    assert eq(lower, g["lo"]) and eq(upper, g["up"])
+    extra = (upper > torch.arange(W, dtype=cur.dtype).view(1, 1, 1, W)).float() if valid else None
+    cand, _ = O.window_candidates(lower, upper, cur, D, g["n_points"], bool(valid), "variance", extra)
+    assert eq(cand, g["cand"])
+    jf, ic = O.window_indices(cand, D)
+    assert eq(jf, g["idx_floor"]) and eq(ic, g["idx_ceil"])
 
 
 @pytest.mark.parametrize("valid", [0, 1])
