@@ -1,20 +1,26 @@
 #!/usr/bin/env python
 """bench.py -- stereo pairs/s of the StereoFormer hot path on B200 (BASELINE.json metric).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--no-configs] [--gather root|all|nccl]
 
 Workload (BASELINE.json configs[1], named in config.workload): the LocalCostVolume hot path of LowCNN at
 SceneFlow 544x960, maxdisp 192 -> 1/8 grid 68x120, 256 feature channels, D=24, batch 8 pairs per GPU
 (weak scaling: every rank processes its own 8 pairs).  One step = correlation cost volume (a1) +
 fused soft-argmin / local disparity-window sampling (a3+a4) over the batch; with N>1 the disparity maps are
-all-gathered over NCCL on a side stream (north_star: NCCL only gathers disparity maps).
+gathered on rank 0 (what the reference's nn.DataParallel does) by peer stores fused into the window kernel, with a
+per-step arrival signal and a consumer-side wait kernel inside the timed graphs.
 
-value : pairs/s, inputs resident in HBM, steps replayed from CUDA graphs, CUDA-event timed, max over ranks.
+value : pairs/s, inputs resident in HBM, steps replayed from CUDA graphs, CUDA-event timed, max over ranks.  Blocks of
+        exactly --steps steps are repeated until >= 100 ms have been timed; the MEDIAN block is reported.
 e2e   : pairs/s through the public module API with HOST (pinned) feature buffers: H2D of both feature maps
-        and D2H of the refined disparity inside the timed region.
+        (double-buffered on a copy stream) and D2H of the refined disparity inside the timed region.
 roofline : the dominant kernel (corr_volume_tc_kernel) alone, algorithmic bytes / CUDA-event time vs the
         measured HBM peak (MEASURED_PEAKS.json).
-cpu_baseline / --impl reference : the oracle's CPU port of the same chain on the host cores.
+gpu_eager_reference : the UNMODIFIED reference modules (oracle/_ref) running the same chain eagerly on the same GPU.
+cpu_baseline / --impl reference : the UNMODIFIED reference modules on the host cores (kind "reference"); the oracle's
+        port only when no copy of the reference travelled to the box (kind "port").
+configs : the other BASELINE configs, the DCN shapes and the full model (tools/bench_configs.py), N = 1 only; at N > 1
+        config 5 runs as N row bands (strong scaling).
 """
 import argparse
 import json
@@ -34,6 +40,7 @@ WORKLOAD = "LowCNN LocalCostVolume hot path (corr volume + soft-argmin + local w
            "(1/8 grid 68x120, C=256, D=24), batch 8 pairs per GPU"
 ALG_BYTES_CV = (2 * C + D) * H8 * W8 * 4          # per pair, SURVEY 8d
 ALG_BYTES_WIN = (D + 2) * H8 * W8 * 4
+MIN_TIMED_MS = 100.0
 
 
 def peaks():
@@ -101,55 +108,102 @@ class ClockSampler(threading.Thread):
                 "samples": len(s)}
 
 
-def make_features(device, seed):
+def make_features(seed):
     g = torch.Generator(device="cpu").manual_seed(seed)
     fl = torch.randn(B_PER_GPU, C, H8, W8, generator=g)
     fr = torch.randn(B_PER_GPU, C, H8, W8, generator=g)
     return fl, fr
 
 
-def cpu_chain(fl, fr):
-    """The reference's CPU path for this chain, as restated by the oracle (checker, bench baseline only)."""
-    from oracle import stereo_oracle as O
-    cv = O.corr_volume(fl, fr, D)
-    d0 = O.soft_argmin(cv).unsqueeze(1)
-    return O.local_cost_volume(cv, d0, RADIUS, NPTS, True)
+# ----------------------------------------------------------------------------- the reference arm / comparators
+def reference_chain():
+    """(callable, kind): the UNMODIFIED reference modules CostVolume -> DisparityEstimation -> LocalCostVolume
+    (build_cost_volume.py:18-54, estimation.py:14-33, fixed_local_cost_volume.py:18-58), exactly the calls of
+    LowCNN.forward baseline.py:114-127, from the copy under oracle/_ref; the oracle's port when that copy is absent."""
+    try:
+        from oracle import refenv
+        if refenv.activate(dcn=None) is None:
+            raise ImportError("no copy of the reference")
+        import importlib
+        import warnings
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            cvm = importlib.import_module("models.utils.build_cost_volume").CostVolume(D, "correlation")
+            est = importlib.import_module("models.utils.estimation").DisparityEstimation(D, True)
+            lc = importlib.import_module("models.LocalCostVolume.Attempts.fixed_local_cost_volume") \
+                .LocalCostVolume(radius=RADIUS, sample_points=NPTS)
 
+        def chain(fl, fr):
+            with torch.no_grad():
+                cv = cvm(fl, fr)
+                d0 = est(cv).unsqueeze(1)
+                return lc(cv, d0, True)
+        return chain, "reference"
+    except Exception:
+        from oracle import stereo_oracle as O
 
-def time_cpu(reps, fl, fr):
-    torch.set_num_threads(os.cpu_count() or 1)
-    cpu_chain(fl[:1], fr[:1])
-    best = float("inf")
-    for _ in range(reps):
-        t0 = time.perf_counter()
-        cpu_chain(fl, fr)
-        best = min(best, time.perf_counter() - t0)
-    return best
+        def chain(fl, fr):
+            cv = O.corr_volume(fl, fr, D)
+            d0 = O.soft_argmin(cv).unsqueeze(1)
+            return O.local_cost_volume(cv, d0, RADIUS, NPTS, True)
+        return chain, "port"
 
 
 def run_reference(args, rank):
+    """--impl reference: the reference's own CPU implementation of the chain on the box's host cores (rank 0 only)."""
     if rank != 0:
         return
-    fl, fr = make_features("cpu", 1024)
+    chain, kind = reference_chain()
+    fl, fr = make_features(1024)
     torch.set_num_threads(os.cpu_count() or 1)
     for _ in range(max(1, min(args.warmup, 2))):
-        cpu_chain(fl, fr)
-    t0 = time.perf_counter()
+        chain(fl, fr)
+    times = []
     for _ in range(args.steps):
-        cpu_chain(fl, fr)
-    dt = time.perf_counter() - t0
+        t0 = time.perf_counter()
+        chain(fl, fr)
+        times.append(time.perf_counter() - t0)
+    dt = sum(times)
     v = args.steps * B_PER_GPU / dt
     cores = torch.get_num_threads()
+    arm = "the unmodified reference modules (oracle/_ref copy of models/utils/build_cost_volume.py, estimation.py, " \
+          "Attempts/fixed_local_cost_volume.py) on the host cores" if kind == "reference" else \
+          "oracle CPU port (no copy of the reference on this box)"
     line = {"impl": "reference", "metric": "stereo pairs/s", "value": v, "unit": "pairs/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "arm": "oracle CPU port of the reference's PyTorch path (the reference is "
-                       "Python and cannot travel to the GPU box)"},
-            "cpu_baseline": {"value": v, "unit": "pairs/s", "cores": cores, "kind": "port",
-                             "sample": "%d steps x %d pairs, full chain" % (args.steps, B_PER_GPU)},
+            "config": {"workload": WORKLOAD},
+            "arm": arm,
+            "cpu_baseline": {"value": v, "unit": "pairs/s", "cores": cores, "kind": kind,
+                             "sample": "%d steps x %d pairs, full chain, torch %d threads" % (args.steps, B_PER_GPU, cores)},
             "e2e": {"value": v, "unit": "pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
+
+
+def bind_to_gpu_numa_node(local_rank):
+    """Pin this process to the CPUs of the NUMA node the GPU hangs off, so pinned host buffers are node-local."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        bus = pynvml.nvmlDeviceGetPciInfo(pynvml.nvmlDeviceGetHandleByIndex(local_rank)).busId
+        bus = (bus.decode() if isinstance(bus, bytes) else bus).lower()
+        if len(bus.split(":")[0]) == 8:
+            bus = bus[4:]
+        node = int(open("/sys/bus/pci/devices/%s/numa_node" % bus).read())
+        if node < 0:
+            return None
+        cpus = []
+        for part in open("/sys/devices/system/node/node%d/cpulist" % node).read().strip().split(","):
+            a, _, b = part.partition("-")
+            cpus += list(range(int(a), int(b or a) + 1))
+        allowed = set(os.sched_getaffinity(0)) & set(cpus)
+        if allowed:
+            os.sched_setaffinity(0, allowed)
+            return node
+    except Exception:
+        pass
+    return None
 
 
 def main():
@@ -159,6 +213,10 @@ def main():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-configs", action="store_true", help="skip the per-config entries (headline only)")
+    ap.add_argument("--configs", default="", help="comma-separated subset of the config entries")
+    ap.add_argument("--gather", default="root", choices=["root", "all", "nccl"],
+                    help="N>1: fused signalled gather to rank 0 (default) / to every rank, or NCCL all-gather per step")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -168,6 +226,7 @@ def main():
         run_reference(args, rank)
         return
 
+    numa = bind_to_gpu_numa_node(local_rank)
     import torch.distributed as dist
     import stereoformer_b200 as sf
     from stereoformer_b200 import ops
@@ -186,61 +245,65 @@ def main():
 
     # ---- inputs: 3 rotating feature sets per rank (each step reads 134 MB > L2; rotation rules out L2 reuse)
     NSETS = 3
-    host = [make_features("cpu", 1024 + 97 * rank + i) for i in range(NSETS)]
+    host = [make_features(1024 + 97 * rank + i) for i in range(NSETS)]
     sets = [(a.to(dev), b.to(dev)) for a, b in host]
-    gather_buf = torch.empty(world * B_PER_GPU, 1, H8, W8, device=dev) if world > 1 else None
-    side = torch.cuda.Stream(device=dev)
-
     dbuf = [torch.empty(B_PER_GPU, 1, H8, W8, device=dev) for _ in range(NSETS)]
+    NPIX = B_PER_GPU * H8 * W8
 
-    # N > 1: the disparity gather (north_star: the only exchange of the path).  Preferred: the window kernel stores
-    # its result straight into every rank's gather buffer through NVLink peer mappings (torch symmetric memory), so
-    # the gather is part of the step graph and costs no host call; fallback: an NCCL all-gather after each step.
-    pg, gather_mode = None, "none"
+    # N > 1: the disparity gather (north_star: the only exchange of the path), fused into the window kernel with
+    # completion semantics (dist.SignalledGather); NCCL all-gather per step as the fallback / comparison.
+    sg, gather_mode = None, "none (1 GPU)"
+    gathered = None
     if world > 1:
-        try:
-            from stereoformer_b200.dist import PeerGather
-            pg = PeerGather(B_PER_GPU * H8 * W8, dev)
-            gather_mode = "P2P stores fused into the window kernel (NVLink peer mappings)"
-        except Exception as e:            # noqa: BLE001 -- any failure of the symmetric-memory plumbing
-            pg, gather_mode = None, "NCCL all_gather_into_tensor per step (symmetric memory unavailable: %s)" % type(e).__name__
-        flags = torch.tensor([1.0 if pg is not None else 0.0], device=dev)
-        dist.all_reduce(flags, op=dist.ReduceOp.MIN)
-        if float(flags.item()) < 1.0:
-            pg = None
-            if gather_mode.startswith("P2P"):
-                gather_mode = "NCCL all_gather_into_tensor per step (symmetric memory unavailable on a peer)"
+        if args.gather != "nccl":
+            try:
+                from stereoformer_b200.dist import SignalledGather
+                sg = SignalledGather(NPIX, dev, dst_ranks=(0,) if args.gather == "root" else tuple(range(world)))
+                gather_mode = "peer stores fused into the window kernel (NVLink), to %s; per-step arrival word per " \
+                              "source rank + consumer wait kernel inside the timed graphs; double-buffered slots" \
+                              % ("rank 0 (DataParallel semantics)" if args.gather == "root" else "every rank")
+            except Exception as e:            # noqa: BLE001 -- any failure of the symmetric-memory plumbing
+                sg, gather_mode = None, "NCCL all_gather_into_tensor per step (symmetric memory unavailable: %s)" \
+                    % type(e).__name__
+            flags = torch.tensor([1.0 if sg is not None else 0.0], device=dev)
+            dist.all_reduce(flags, op=dist.ReduceOp.MIN)
+            if float(flags.item()) < 1.0:
+                sg = None
+                if not gather_mode.startswith("NCCL"):
+                    gather_mode = "NCCL all_gather_into_tensor per step (symmetric memory unavailable on a peer)"
+        else:
+            gather_mode = "NCCL all_gather_into_tensor per step"
+        gathered = [torch.empty(world * B_PER_GPU, 1, H8, W8, device=dev) for _ in range(NSETS)]
+    consumer = sg is not None and sg.is_consumer
+
+    def window(i, cv):
+        out = ops.local_window(cv, None, mode=ops.SF_WIN_FIXED, radius=RADIUS, n_points=NPTS, consider_valid=True,
+                               div_mode=ops.SF_DIV_RECIP, out=dbuf[i % NSETS], gather=sg)
+        if consumer:
+            sg.wait(gathered[i % NSETS])          # step i is complete on this rank when this kernel retires
+        return out
 
     def step(i, cv_out=None):
         fl, fr = sets[i % NSETS]
-        cv = ops.corr_volume(fl, fr, D, out=cv_out)
-        return window(i, cv)
+        return window(i, ops.corr_volume(fl, fr, D, out=cv_out))
 
-    def window(i, cv):
-        return ops.local_window(cv, None, mode=ops.SF_WIN_FIXED, radius=RADIUS, n_points=NPTS, consider_valid=True,
-                                div_mode=ops.SF_DIV_RECIP, out=dbuf[i % NSETS],
-                                peers=pg.peer_ptrs if pg is not None else None,
-                                peer_offset=pg.offset() if pg is not None else 0)
-
-    # CUDA graphs keep the host launch path (ctypes + tensor-map encoding, ~25 us per step) off the device timeline.
-    # A step = 2 kernel launches of this library.  `single[i]`: one step.  `pipe`: GSTEPS consecutive steps whose
-    # window kernel (5 us, plus the NVLink drain of its peer stores at N > 1) runs on a second captured stream
-    # underneath the NEXT step's cost-volume kernel -- the software pipelining any multi-batch caller gets from two
-    # streams; every step still does all of its work, the cost volumes are double-buffered.
-    GSTEPS = 4 * NSETS
-    NCV = 3                                                  # cost-volume buffers in flight
+    # CUDA graphs keep the host launch path off the device timeline.  A step = 2 kernel launches of this library (+ the
+    # wait kernel on a consuming rank).  `single[i]`: one step.  pipe(n): n consecutive steps whose window kernel runs
+    # on a second captured stream underneath the NEXT step's cost-volume kernel -- the software pipelining any
+    # multi-batch caller gets from two streams; every step still does all of its work, the cost volumes are
+    # triple-buffered.
+    NCV = 3
     cvbuf = [torch.empty(B_PER_GPU, D, H8, W8, device=dev) for _ in range(NCV)]
     cap = torch.cuda.Stream(device=dev)
     win = torch.cuda.Stream(device=dev)
-    single = []
-
     cvs = [torch.cuda.Stream(device=dev) for _ in range(2)]
+    single = []
 
     def capture_pipe(nsteps):
         """nsteps consecutive steps.  Cost-volume kernels alternate between two captured streams, so the persistent
-        CTAs of step j+1 move onto each SM as soon as step j's CTA there has finished its tiles (no idle tail: 4352
-        tiles over 148 SMs is 29.4 per SM); the window kernels run on a third stream.  Only data dependencies are
-        kept: window(j) after cv(j), cv(j) after the window kernel that last read its buffer."""
+        CTAs of step j+1 move onto each SM as soon as step j's CTA there has finished its tiles; the window (and
+        wait) kernels run on a third stream.  Only data dependencies are kept: window(j) after cv(j), cv(j) after
+        the window kernel that last read its buffer."""
         g = torch.cuda.CUDAGraph()
         with torch.cuda.graph(g, stream=cap):
             fork = torch.cuda.Event()
@@ -266,57 +329,81 @@ def main():
                 cap.wait_stream(st)
         return g
 
+    use_pipe = world == 1 or sg is not None
+    # the timed block is exactly --steps steps: one pipelined graph of that many steps when it is small enough to
+    # capture quickly, else graphs of GBLOCK steps plus one graph for the remainder
+    GBLOCK = 12
+    K = args.steps
     with torch.cuda.stream(cap):
         for i in range(NSETS):
             step(i)
-        torch.cuda.synchronize()
+        barrier()
         for i in range(NSETS):
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g, stream=cap):
                 step(i)
             single.append(g)
-        pipes = [(GSTEPS, capture_pipe(GSTEPS)), (NSETS, capture_pipe(NSETS))]
-    pipe = pipes[0][1]
+        pipes = {}
+        if use_pipe:
+            if K <= 48:
+                pipes[K] = capture_pipe(K)
+            else:
+                pipes[GBLOCK] = capture_pipe(GBLOCK)
+                if K % GBLOCK:
+                    pipes[K % GBLOCK] = capture_pipe(K % GBLOCK)
     torch.cuda.synchronize()
 
-    def run_steps(first, count):
-        """Steps first .. first+count-1: pipelined graphs while GSTEPS-aligned blocks remain, single steps otherwise."""
-        i, end = first, first + count
-        while i < end:
-            blk = [(n, g) for n, g in pipes if end - i >= n] if (i % NSETS == 0 and (pg is not None or world == 1)) else []
-            if blk:
-                blk[0][1].replay()
-                i += blk[0][0]
-            else:
+    def run_block():
+        """Exactly K steps."""
+        if use_pipe:
+            left = K
+            for n in sorted(pipes, reverse=True):
+                while left >= n:
+                    pipes[n].replay()
+                    left -= n
+            assert left == 0
+        else:
+            for i in range(K):
                 single[i % NSETS].replay()
-                if world > 1 and pg is None:
-                    dist.all_gather_into_tensor(gather_buf, dbuf[i % NSETS])
-                i += 1
+                dist.all_gather_into_tensor(gathered[i % NSETS], dbuf[i % NSETS])
 
-    run_steps(0, max(args.warmup, GSTEPS))
+    # ---- warm-up, with the per-step check of the gather: after every single step the consumer's gathered tensor must
+    # equal an NCCL all-gather of that step's maps
+    gather_checked = 0
+    for i in range(max(args.warmup, 3)):
+        single[i % NSETS].replay()
+        if world > 1:
+            want = torch.empty(world * B_PER_GPU, 1, H8, W8, device=dev)
+            dist.all_gather_into_tensor(want, dbuf[i % NSETS])
+            if consumer:
+                assert torch.equal(gathered[i % NSETS], want), "step %d: fused gather != NCCL all-gather" % i
+                gather_checked += 1
+    run_block()
     barrier()
+
+    # ---- timed region: blocks of exactly K steps until >= MIN_TIMED_MS; median block, max over ranks per block
     sampler = ClockSampler(local_rank)
     sampler.start()
+    blocks = []
+    total = 0.0
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    run_steps(0, args.steps)
-    e1.record()
-    barrier()
-    ms = e0.elapsed_time(e1)
+    while total < MIN_TIMED_MS and len(blocks) < 2000:
+        barrier()
+        e0.record()
+        run_block()
+        e1.record()
+        barrier()
+        t = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        blocks.append(float(t.item()))
+        total += blocks[-1]
     clocks = sampler.finish()
-    t = torch.tensor([ms], device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms = float(t.item())
-    value = world * B_PER_GPU * args.steps / (ms * 1e-3)
-
-    if pg is not None:
-        # the fused gather must have delivered every rank's last disparities into this rank's buffer
-        pg.sync()
-        last = (args.steps - 1) % NSETS
-        want = torch.empty(world * B_PER_GPU, 1, H8, W8, device=dev)
-        dist.all_gather_into_tensor(want, dbuf[last])
-        assert torch.equal(pg.buffer.view_as(want), want), "P2P disparity gather does not match the NCCL all-gather"
+    sb = sorted(blocks)
+    ms = sb[len(sb) // 2]
+    value = world * B_PER_GPU * K / (ms * 1e-3)
+    if sg is not None:
+        sg.check()
 
     # ---- dominant kernel alone (roofline): graph of NSETS cost-volume launches, one per feature set
     kg = torch.cuda.CUDAGraph()
@@ -326,86 +413,174 @@ def main():
     for i in range(3):
         kg.replay()
     torch.cuda.synchronize()
-    nk = max(7, min(args.steps, 200) // NSETS)
+    nk = 200
     e0.record()
     for i in range(nk):
         kg.replay()
     e1.record()
     torch.cuda.synchronize()
     k_ms = e0.elapsed_time(e1) / (nk * NSETS)
-    # the same step without any overlap (one serial 2-kernel graph per step): the denominator for the kernel's share of
-    # the step, comparable with an ncu launch list (which serialises kernels)
-    ns = 3 * NSETS
+    # the same step without any overlap (one serial graph per step): the denominator for the kernel's share of the
+    # step, comparable with an ncu launch list (which serialises kernels)
+    barrier()
+    ns = 30 * NSETS
     e0.record()
     for i in range(ns):
         single[i % NSETS].replay()
     e1.record()
-    torch.cuda.synchronize()
+    barrier()
     serial_ms = e0.elapsed_time(e1) / ns
+    # host launch path: the same step launched eagerly through the module-level API (ctypes + tensor-map lookup)
+    e0.record()
+    for i in range(60):
+        step(i, cvbuf[i % NCV]) if world == 1 else None
+    e1.record()
+    torch.cuda.synchronize()
+    eager_step_us = e0.elapsed_time(e1) / 60 * 1e3 if world == 1 else None
     peak, peak_src = peaks()
     achieved = B_PER_GPU * ALG_BYTES_CV / (k_ms * 1e-3) / 1e9
     traffic = traffic_from_profile()
 
-    # ---- end to end through the public module API, host buffers
+    # ---- end to end through the public module API, host buffers; H2D double-buffered on a copy stream
     pin = [(a.pin_memory(), b.pin_memory()) for a, b in host]
-    out_host = torch.empty(B_PER_GPU, 1, H8, W8).pin_memory()
+    out_host = [torch.empty(B_PER_GPU, 1, H8, W8).pin_memory() for _ in range(2)]
     cvm, lc = sf.CostVolume(D, "correlation"), sf.LocalCostVolume(RADIUS, NPTS)
     est = sf.DisparityEstimation(D)
+    copy_s = torch.cuda.Stream(device=dev)
+    stage = [(torch.empty(B_PER_GPU, C, H8, W8, device=dev), torch.empty(B_PER_GPU, C, H8, W8, device=dev))
+             for _ in range(2)]
+    staged = [torch.cuda.Event() for _ in range(2)]
+    freed = [torch.cuda.Event() for _ in range(2)]
+    main_s = torch.cuda.current_stream()
 
-    def e2e_step(i):
-        a, b = pin[i % NSETS]
-        fl, fr = a.to(dev, non_blocking=True), b.to(dev, non_blocking=True)
-        cv = cvm(fl, fr)
-        d0 = est(cv).unsqueeze(1)
-        out_host.copy_(lc(cv, d0, True), non_blocking=True)
+    def e2e_run(n):
+        for k in range(2):
+            freed[k].record(main_s)
+        for i in range(n + 1):
+            if i < n:                                   # upload step i
+                k = i % 2
+                with torch.cuda.stream(copy_s):
+                    copy_s.wait_event(freed[k])
+                    stage[k][0].copy_(pin[i % NSETS][0], non_blocking=True)
+                    stage[k][1].copy_(pin[i % NSETS][1], non_blocking=True)
+                    staged[k].record(copy_s)
+            if i >= 1:                                  # compute step i-1 while step i uploads
+                k = (i - 1) % 2
+                main_s.wait_event(staged[k])
+                cv = cvm(*stage[k])
+                d0 = est(cv).unsqueeze(1)
+                out_host[k].copy_(lc(cv, d0, True), non_blocking=True)
+                freed[k].record(main_s)
 
-    ne = max(3, min(args.steps, 30))
-    for i in range(3):
-        e2e_step(i)
+    ne = max(6, min(K, 40))
+    e2e_run(4)
     barrier()
     e0.record()
-    for i in range(ne):
-        e2e_step(i)
+    e2e_run(ne)
     e1.record()
     barrier()
     t = torch.tensor([e0.elapsed_time(e1)], device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_v = world * B_PER_GPU * ne / (float(t.item()) * 1e-3)
+    e2e_ms = float(t.item())
+    e2e_v = world * B_PER_GPU * ne / (e2e_ms * 1e-3)
     h2d = 2 * B_PER_GPU * C * H8 * W8 * 4
     d2h = B_PER_GPU * H8 * W8 * 4
 
-    # ---- parity spot check of what was just timed (oracle as checker only) + CPU baseline on rank 0
-    cpu_base = None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+    # ---- parity of what was just timed (oracle as checker only), comparators and CPU baseline on rank 0
+    cpu_base, parity, gpu_ref = None, None, None
+    if rank == 0:
+        from oracle import stereo_oracle as O
         fl, fr = host[0]
-        pipe.replay()                                   # the pipelined path that was timed; dbuf[0] = feature set 0
+        single[0].replay()                              # the graph path that was timed; dbuf[0] = feature set 0
         torch.cuda.synchronize()
         got = dbuf[0].cpu()
-        want = cpu_chain(fl[:2], fr[:2])
-        err = (got[:2] - want).abs()
-        assert err.median() < 1e-3, "bench parity check failed: median |disp err| %g" % err.median()
-        best = time_cpu(5, fl, fr)
-        cpu_base = {"value": B_PER_GPU / best, "unit": "pairs/s", "cores": torch.get_num_threads(), "kind": "port",
-                    "sample": "best of 5 passes over one batch of %d pairs (oracle CPU port, full chain)" % B_PER_GPU}
+        cv_o = O.corr_volume(fl, fr, D)
+        want = O.local_cost_volume(cv_o, O.soft_argmin(cv_o).unsqueeze(1), RADIUS, NPTS, True, recip=True)
+        err = (got - want).abs()
+        cv_err = float((ops.corr_volume(*sets[0], D).cpu() - cv_o).abs().max() / cv_o.abs().max())
+        parity = {"epe": float(err.mean()), "max": float(err.max()), "unit": "px at 1/8 scale (x8 at full resolution)",
+                  "cost_volume_max_rel": cv_err, "against": "oracle fp32 chain on the CPU, all %d pairs of set 0" % B_PER_GPU,
+                  "note": "max is set by isolated pixels whose validity test (upper >= D-1) flips"}
+        assert parity["epe"] * 8 <= 1e-3, "bench parity check failed: EPE %g px (full resolution)" % (parity["epe"] * 8)
+        assert cv_err <= 1e-4, "bench parity check failed: cost volume %g relative" % cv_err
+    if rank == 0 and not args.no_cpu_baseline:
+        chain, kind = reference_chain()
+        # the same unmodified chain eagerly on this GPU: what a user of the reference runs today
+        try:
+            gfl, gfr = sets[0]
+            for _ in range(2):
+                chain(gfl, gfr)
+            torch.cuda.synchronize()
+            e0.record()
+            for i in range(5):
+                chain(*sets[i % NSETS])
+            e1.record()
+            torch.cuda.synchronize()
+            g_ms = e0.elapsed_time(e1) / 5
+            gerr = (chain(gfl, gfr) - dbuf[0]).abs()
+            gpu_ref = {"value": B_PER_GPU / g_ms * 1e3, "unit": "pairs/s", "ms_per_step": g_ms, "kind": kind,
+                       "what": "the unmodified reference modules, PyTorch eager on the same GPU (1 GPU)",
+                       "epe_vs_ours": float(gerr.mean()), "max_vs_ours": float(gerr.max())}
+        except Exception as ex:          # noqa: BLE001
+            gpu_ref = {"error": "%s: %s" % (type(ex).__name__, str(ex)[:200])}
+        if world == 1:
+            torch.set_num_threads(os.cpu_count() or 1)
+            fl, fr = host[0]
+            chain(fl[:1], fr[:1])
+            best = float("inf")
+            for _ in range(5):
+                t0 = time.perf_counter()
+                chain(fl, fr)
+                best = min(best, time.perf_counter() - t0)
+            cpu_base = {"value": B_PER_GPU / best, "unit": "pairs/s", "cores": torch.get_num_threads(), "kind": kind,
+                        "sample": "best of 5 passes over one batch of %d pairs, full chain" % B_PER_GPU}
+
+    # ---- the other configs
+    configs = {}
+    if not args.no_configs:
+        from tools import bench_configs
+        pk = bench_configs.peaks()
+        want_cfg = set(x for x in args.configs.split(",") if x) or None
+        if world == 1:
+            configs = bench_configs.run_single_gpu(dev, want_cfg)
+        if want_cfg is None or "c5_bands" in want_cfg:
+            try:
+                configs["c5_bands"] = bench_configs.c5_bands(dev, pk, world, rank)
+            except Exception as ex:      # noqa: BLE001
+                configs["c5_bands"] = {"error": "%s: %s" % (type(ex).__name__, str(ex)[:300])}
 
     if rank == 0:
-        line = {"metric": "stereo pairs/s", "value": value, "unit": "pairs/s", "n_gpus": world, "steps": args.steps,
-                "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+        n_kernels = 2 + (1 if consumer else 0)
+        line = {"metric": "stereo pairs/s", "value": value, "unit": "pairs/s", "n_gpus": world, "steps": K,
+                "warmup": args.warmup, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": {"workload": WORKLOAD, "pairs_per_gpu_per_step": B_PER_GPU, "parallelism": "pairs sharded "
-                           "across %d rank(s); disparity gather: %s" % (world, gather_mode),
-                           "l2": "each step reads 134 MB of features (> 126 MB L2) from one of 3 rotating sets", "launch": "CUDA graphs of %d steps (2 kernels per step); consecutive steps overlap on captured streams (window kernel of step i and the tail of its cost volume under the cost volume of step i+1)" % GSTEPS},
-                "roofline": {"kernel": "corr_volume_tc_kernel (tcgen05, bf16 hi/mid split)", "bound": "hbm", "achieved": achieved, "peak": peak,
-                             "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                "config": {"workload": WORKLOAD, "pairs_per_gpu_per_step": B_PER_GPU,
+                           "parallelism": "pairs sharded across %d rank(s); disparity gather: %s" % (world, gather_mode),
+                           "l2": "each step reads 134 MB of features (> 126 MB L2) from one of 3 rotating sets",
+                           "launch": "CUDA graphs, %d-step block(s); consecutive steps overlap on captured streams "
+                                     "(window kernel of step i and the tail of its cost volume under the cost volume "
+                                     "of step i+1)" % (max(pipes) if pipes else 1),
+                           "timing": "blocks of exactly %d steps, repeated %d times (%.0f ms timed), median block, max "
+                                     "over ranks per block" % (K, len(blocks), total)},
+                "timed_blocks": len(blocks), "timed_region_ms": total, "block_ms_min": sb[0], "block_ms_max": sb[-1],
+                "roofline": {"kernel": "corr_volume_tc_kernel (tcgen05, bf16 hi/mid split)", "bound": "hbm",
+                             "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                             "traffic": traffic, "peak_source": peak_src,
                              "alg_bytes_per_launch": B_PER_GPU * ALG_BYTES_CV, "us_per_launch": k_ms * 1e3,
-                             "serial_step_us": serial_ms * 1e3, "share_of_serial_step": k_ms / serial_ms},
-                "cpu_baseline": cpu_base,
+                             "serial_step_us": serial_ms * 1e3, "share_of_serial_step": k_ms / serial_ms,
+                             "eager_api_step_us": eager_step_us},
+                "cpu_baseline": cpu_base, "gpu_eager_reference": gpu_ref, "parity": parity,
                 "e2e": {"value": e2e_v, "unit": "pairs/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                        "steps": ne},
-                "gpu_launches": 2 * args.steps, "clocks": clocks}
+                        "steps": ne, "h2d_gbs_per_gpu": h2d * ne / (e2e_ms * 1e-3) / 1e9,
+                        "bound": "PCIe host->device copy of the fp32 feature maps (134 MB per step per GPU); uploads are "
+                                 "double-buffered on a copy stream under the kernels", "numa_node": numa},
+                "gather_steps_checked_in_warmup": gather_checked,
+                "gpu_launches": n_kernels * K * len(blocks), "gpu_launches_per_step": n_kernels, "clocks": clocks,
+                "configs": configs}
         print(json.dumps(line), flush=True)
     if world > 1:
+        dist.barrier()
         dist.destroy_process_group()
 
 

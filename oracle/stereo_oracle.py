@@ -361,8 +361,8 @@ def epipolar_attention(q, k, v, band):
     B, C, H, W = q.shape
     qf, kf, vf = q.float(), k.float(), v.float()
     s = torch.einsum("bcyq,bcyk->byqk", qf, kf) / math.sqrt(C)
-    xq = torch.arange(W).view(W, 1)
-    xk = torch.arange(W).view(1, W)
+    xq = torch.arange(W, device=q.device).view(W, 1)
+    xk = torch.arange(W, device=q.device).view(1, W)
     valid = ((xq - xk) >= 0) & ((xq - xk) < band)
     s = s.masked_fill(~valid, float("-inf"))
     p = torch.softmax(s, dim=-1)

@@ -134,6 +134,31 @@ __device__ __forceinline__ void stg_cs_f4(float* p, float4 v) {
   asm volatile("st.global.cs.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
                : "memory");
 }
+// System-scope release / acquire on 64-bit words that live in peer-mapped (NVLink) memory: the signal words of the
+// fused multi-GPU gather (window.cu, gather.cu).
+__device__ __forceinline__ void st_release_sys_u64(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys_u64(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+// Spin until *p >= want; gives up after ~4e9 cycles (a peer died) and raises the block's error word instead of
+// hanging the GPU.  Returns false on timeout.
+__device__ __forceinline__ bool spin_until_ge_sys(const unsigned long long* p, unsigned long long want,
+                                                  unsigned long long* err_word) {
+  if (ld_acquire_sys_u64(p) >= want) return true;
+  const long long t0 = clock64();
+  while (ld_acquire_sys_u64(p) < want) {
+    __nanosleep(64);
+    if (clock64() - t0 > 4000000000LL) {
+      *err_word = 1ULL;
+      return false;
+    }
+  }
+  return true;
+}
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }

@@ -39,6 +39,12 @@ struct WindowParams {
   float* peers[SF_MAX_PEERS];
   int n_peers;
   long long peer_off;
+  // completion protocol of sf_local_window_gather_signal_f32 (null sig_local: plain stores, no signalling)
+  unsigned long long* sig_local;
+  unsigned long long* sig_peers[SF_MAX_PEERS];
+  int peer_ranks[SF_MAX_PEERS];
+  int my_rank;
+  long long slot_stride;
 };
 
 struct SoftStats { float m, s, e; };  // running max, sum exp, sum exp * d
@@ -72,13 +78,24 @@ local_window_kernel(const __grid_constant__ CUtensorMap mapCV, const WindowParam
   const int x0 = seg * TPB, x = x0 + threadIdx.x;
   const size_t HW = static_cast<size_t>(p.H) * p.W;
 
+  if (p.use_tma && threadIdx.x == 0) {
+    mbar_init(&bar, 1);
+    fence_mbar_init();
+    mbar_expect_tx(&bar, p.D * TPB * 4);
+    tma_load_3d(tile, &mapCV, &bar, x0, y, b * p.D);
+  }
+  // signalled gather: this launch is step `step` of the rank; its slot was last used by step - 2, which every
+  // destination must have consumed (the wait is normally satisfied long before: two steps of slack)
+  unsigned long long step = 0;
+  long long slot_off = 0;
+  if (p.sig_local) {
+    step = p.sig_local[SF_SIG_EPOCH];
+    slot_off = static_cast<long long>(step & 1ULL) * p.slot_stride;
+    if (threadIdx.x == 0 && step >= 2)
+      for (int r = 0; r < p.n_peers; ++r)
+        spin_until_ge_sys(p.sig_local + SF_SIG_CONSUMED + p.peer_ranks[r], step - 1, p.sig_local + SF_SIG_ERROR);
+  }
   if (p.use_tma) {
-    if (threadIdx.x == 0) {
-      mbar_init(&bar, 1);
-      fence_mbar_init();
-      mbar_expect_tx(&bar, p.D * TPB * 4);
-      tma_load_3d(tile, &mapCV, &bar, x0, y, b * p.D);
-    }
     __syncthreads();
     mbar_wait(&bar, 0);
   } else {
@@ -86,7 +103,7 @@ local_window_kernel(const __grid_constant__ CUtensorMap mapCV, const WindowParam
     for (int d = 0; d < p.D; ++d) tile[d * TPB + threadIdx.x] = (x < p.W) ? src[d * HW + x] : 0.f;
     __syncthreads();
   }
-  if (x >= p.W) return;
+  if (x < p.W) {
 
   const float* col = tile + threadIdx.x;
   auto cvat = [&](int d) { return col[d * TPB]; };
@@ -174,7 +191,22 @@ local_window_kernel(const __grid_constant__ CUtensorMap mapCV, const WindowParam
   }
   const float res = e / s;
   p.out[pix] = res;
-  for (int r = 0; r < p.n_peers; ++r) p.peers[r][p.peer_off + static_cast<long long>(pix)] = res;
+  for (int r = 0; r < p.n_peers; ++r) p.peers[r][p.peer_off + slot_off + static_cast<long long>(pix)] = res;
+  }  // x < W
+  if (p.sig_local) {
+    // every CTA fences its peer stores, the last one to finish publishes the step to the destinations
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence_system();
+      const unsigned long long prev = atomicAdd(p.sig_local + SF_SIG_CTA_DONE, 1ULL);
+      if (prev == gridDim.x - 1) {
+        p.sig_local[SF_SIG_CTA_DONE] = 0ULL;
+        __threadfence_system();
+        for (int r = 0; r < p.n_peers; ++r) st_release_sys_u64(p.sig_peers[r] + SF_SIG_ARRIVED + p.my_rank, step + 1);
+        p.sig_local[SF_SIG_EPOCH] = step + 1;
+      }
+    }
+  }
 }
 
 // DisparityEstimation(.WithProb).forward  models/utils/estimation.py:14-62: no reuse -> straight coalesced loads.
@@ -261,7 +293,9 @@ static int local_window_impl(const float* cv, const float* disp, const float* lo
                              float* disp0_out, float* dbg_cand, int* dbg_idx_floor, int* dbg_idx_ceil,
                              float* dbg_local, int B, int D, int H, int W, int mode, float radius, float gamma,
                              int n_points, int consider_valid, int div_mode, float* const* h_peers, int n_peers,
-                             long long peer_offset, void* stream) {
+                             long long peer_offset, void* stream, unsigned long long* const* h_peer_sig = nullptr,
+                             const int* h_peer_ranks = nullptr, long long slot_stride = 0,
+                             unsigned long long* sig_local = nullptr, int my_rank = 0) {
   using namespace sf;
   SF_CHECK_ARG(cv && out, "local_window: null pointer");
   SF_CHECK_ARG(B > 0 && D > 0 && H > 0 && W > 0 && n_points > 0, "local_window: non-positive dimension");
@@ -282,6 +316,17 @@ static int local_window_impl(const float* cv, const float* disp, const float* lo
   p.peer_off = peer_offset;
   for (int r = 0; r < SF_MAX_PEERS; ++r) p.peers[r] = r < n_peers ? h_peers[r] : nullptr;
   for (int r = 0; r < n_peers; ++r) SF_CHECK_ARG(p.peers[r] != nullptr, "local_window: null peer pointer %d", r);
+  p.sig_local = sig_local; p.my_rank = my_rank; p.slot_stride = slot_stride;
+  for (int r = 0; r < SF_MAX_PEERS; ++r) { p.sig_peers[r] = nullptr; p.peer_ranks[r] = 0; }
+  if (sig_local) {
+    SF_CHECK_ARG(n_peers > 0 && h_peer_sig && h_peer_ranks && slot_stride > 0 && my_rank >= 0 && my_rank < 16,
+                 "local_window: the signalled gather needs destinations, their signal blocks / ranks and a slot stride");
+    for (int r = 0; r < n_peers; ++r) {
+      SF_CHECK_ARG(h_peer_sig[r] != nullptr && h_peer_ranks[r] >= 0 && h_peer_ranks[r] < 16,
+                   "local_window: bad signal block / rank of destination %d", r);
+      p.sig_peers[r] = h_peer_sig[r]; p.peer_ranks[r] = h_peer_ranks[r];
+    }
+  }
   // CTA width: 128 pixels, or 32 when the row is short enough that single-warp CTAs waste fewer lanes; single-warp CTAs
   // (3 KB of shared memory at D = 24) also fit next to a resident persistent kernel, so a caller that pipelines the
   // window under the next batch's cost volume (bench.py) gets real overlap
@@ -326,6 +371,19 @@ extern "C" int sf_local_window_gather_f32(const float* cv, const float* disp, co
                                           long long peer_offset, void* stream) {
   return local_window_impl(cv, disp, lo, up, out, nullptr, nullptr, nullptr, nullptr, nullptr, B, D, H, W, mode, radius,
                            gamma, n_points, consider_valid, div_mode, h_peers, n_peers, peer_offset, stream);
+}
+
+extern "C" int sf_local_window_gather_signal_f32(const float* cv, const float* disp, const float* lo, const float* up,
+                                                 float* out, int B, int D, int H, int W, int mode, float radius,
+                                                 float gamma, int n_points, int consider_valid, int div_mode,
+                                                 float* const* h_peer_data, unsigned long long* const* h_peer_sig,
+                                                 const int* h_peer_ranks, int n_peers, long long peer_offset,
+                                                 long long slot_stride, unsigned long long* sig_local, int my_rank,
+                                                 void* stream) {
+  SF_CHECK_ARG(sig_local != nullptr, "local_window_gather_signal: null signal block");
+  return local_window_impl(cv, disp, lo, up, out, nullptr, nullptr, nullptr, nullptr, nullptr, B, D, H, W, mode, radius,
+                           gamma, n_points, consider_valid, div_mode, h_peer_data, n_peers, peer_offset, stream,
+                           h_peer_sig, h_peer_ranks, slot_stride, sig_local, my_rank);
 }
 
 extern "C" int sf_sample_volume_f32(const float* cv, const float* cand, float* out, int* idx_floor, int* idx_ceil,

@@ -89,12 +89,14 @@ def soft_argmin(cv, match_similarity=True, with_prob=False):
 
 def local_window(cv, disp=None, lo=None, up=None, mode=SF_WIN_FIXED, radius=0.0, gamma=1.0, n_points=10,
                  consider_valid=False, div_mode=SF_DIV_TRUE, debug=False, return_disp0=False, out=None, peers=None,
-                 peer_offset=0):
+                 peer_offset=0, gather=None):
     """Local disparity-window sampling + soft-max expectation -> [B,1,H,W] (written into ``out`` when given).
 
     debug=True additionally returns dict(cand, idx_floor, idx_ceil, local) for the bit-exact checks.
     peers: list of device pointers (ints) of every rank's gather buffer (NVLink peer mappings, see
-    dist.PeerGather); the result is also stored at element ``peer_offset`` + pixel index of each of them."""
+    dist.PeerGather); the result is also stored at element ``peer_offset`` + pixel index of each of them.
+    gather: a ``dist.SignalledGather``; the result goes to its destinations' slots with the completion protocol of
+    sf_local_window_gather_signal_f32 (consumers call ``gather.wait()``)."""
     cv = _chk(cv, "old_cost_volume", dim=4)
     B, D, H, W = cv.shape
     if disp is not None:
@@ -115,6 +117,18 @@ def local_window(cv, disp=None, lo=None, up=None, mode=SF_WIN_FIXED, radius=0.0,
                    idx_floor=torch.empty((B, K, H, W), device=cv.device, dtype=torch.int32),
                    idx_ceil=torch.empty((B, K, H, W), device=cv.device, dtype=torch.int32),
                    local=torch.empty((B, K, H, W), device=cv.device, dtype=torch.float32))
+    if gather is not None:
+        if debug or return_disp0 or peers:
+            raise ValueError("gather cannot be combined with debug / return_disp0 / peers")
+        if B * H * W != gather.numel_per_rank:
+            raise ValueError("gather was sized for %d elements per rank, got %d" % (gather.numel_per_rank, B * H * W))
+        with torch.cuda.device(cv.device):
+            _lib.call("sf_local_window_gather_signal_f32", _ptr(cv), _ptr(disp), _ptr(lo), _ptr(up), _ptr(out), B, D, H,
+                      W, int(mode), float(radius), float(gamma), int(n_points), int(bool(consider_valid)),
+                      int(div_mode), gather.c_dst_data, gather.c_dst_sig, gather.c_dst_ranks, len(gather.dst_ranks),
+                      ctypes.c_longlong(gather.offset()), ctypes.c_longlong(gather.slot_stride),
+                      ctypes.c_void_p(gather.sig_ptrs[gather.rank]), gather.rank, _stream())
+        return out
     if peers:
         if debug or return_disp0:
             raise ValueError("peers cannot be combined with debug / return_disp0")

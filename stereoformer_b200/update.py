@@ -273,7 +273,7 @@ class PureLearningLocalCostVolume(nn.Module):
         cur_left, cur_right = BasicGuidanceNet.resize_images(cur_disp, left_image, right_image)
         error_map, uncertainty_volume = _m.guidance_inputs(old_cost_volume, cur_disp, cur_left, cur_right)
         first, second = self.offset_prediction_network(error_map, uncertainty_volume)
-        if not self.with_bounds:
+        if not getattr(self, "with_bounds", False):     # reference instances carry this forward (install.py)
             return _m.dlc_window(old_cost_volume, cur_disp, first, second, self.sample_points, consider_valid,
                                  absolute=True)
         disp = _m.dlc_window(old_cost_volume, cur_disp, first, second, self.sample_points, consider_valid)

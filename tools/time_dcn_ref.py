@@ -56,7 +56,7 @@ def graph_time(fn, reps=5, inner=3):
     return e0.elapsed_time(e1) / (reps * inner) * 1e3
 
 
-def run(shapes=SHAPES, peaks=None):
+def run(shapes=SHAPES, quiet=False):
     from oracle import refenv              # comparator only
     refenv.activate(dcn="reference")
     import DCN as refdcn
@@ -94,7 +94,8 @@ def run(shapes=SHAPES, peaks=None):
         res["tflops"] = flops / res["ours_us"] / 1e6
         res["gbs"] = nbytes / res["ours_us"] / 1e3
         out[name] = res
-        print(json.dumps({name: res}), flush=True)
+        if not quiet:
+            print(json.dumps({name: res}), flush=True)
     return out
 
 
