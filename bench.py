@@ -258,7 +258,7 @@ def main():
         if args.gather != "nccl":
             try:
                 from stereoformer_b200.dist import SignalledGather
-                sg = SignalledGather(NPIX, dev, dst_ranks=(0,) if args.gather == "root" else tuple(range(world)))
+                sg = SignalledGather((B_PER_GPU, H8, W8), dev, dst_ranks=(0,) if args.gather == "root" else tuple(range(world)))
                 gather_mode = "peer stores fused into the window kernel (NVLink), to %s; per-step arrival word per " \
                               "source rank + consumer wait kernel inside the timed graphs; double-buffered slots" \
                               % ("rank 0 (DataParallel semantics)" if args.gather == "root" else "every rank")

@@ -81,47 +81,45 @@ SF_API int sf_local_window_gather_f32(const float* cv, const float* disp, const 
                                       int consider_valid, int div_mode, float* const* h_peers, int n_peers,
                                       long long peer_offset, void* stream);
 
-/* The same with COMPLETION SEMANTICS (what an NCCL gather gives and plain peer stores do not): double-buffered
- * slots, a per-step arrival word per source rank and back-pressure from the consumer.
+/* The same with COMPLETION SEMANTICS (what an NCCL gather gives and plain peer stores do not), as a low-latency
+ * flag-in-data protocol (the scheme of NCCL's LL protocol): no fences and no per-step host call on the data path.
  *
- * Every rank owns one signal block of SF_SIG_WORDS 64-bit words in peer-mapped memory (zero-initialised):
- *   [SF_SIG_EPOCH]              steps this rank has produced          (written by its own window kernel)
- *   [SF_SIG_CTA_DONE]           last-CTA election counter of the window kernel
- *   [SF_SIG_WAIT_EPOCH]         steps this rank has consumed          (written by its own wait kernel)
- *   [SF_SIG_WAIT_CTA]           last-CTA election counter of the wait kernel
- *   [SF_SIG_ERROR]              set to 1 when a spin timed out (a peer never arrived)
- *   [SF_SIG_ARRIVED  + src]     steps of rank `src` whose stores have landed in THIS rank's slots
- *                               (st.release.sys by src's last CTA, after every CTA fenced its stores)
- *   [SF_SIG_CONSUMED + dst]     steps consumer `dst` has finished reading out of its slots (written by dst's wait
- *                               kernel into every producer's block): a producer reuses slot (s & 1) for step s only
+ *   slots    : on every destination rank, 2 slots of `slot_stride` 8-byte words {fp32 value, uint32 flag}; step s of
+ *              a producer stores pixel i as ONE 8-byte store {value, (uint32)(s + 1)} at
+ *              peer_data[r] + (s & 1) * slot_stride + peer_offset + i.  8-byte stores are single transactions, so a
+ *              consumer that reads flag == s + 1 has the value of step s.
+ *   signals  : every rank owns SF_SIG_WORDS 64-bit words in peer-mapped memory (zero-initialised):
+ *     [SF_SIG_TICKET]           CTA tickets of this rank's window kernel: a CTA's step is ticket / gridDim (launches of
+ *                               one gather all have the same grid; kernels of a stream run one after the other)
+ *     [SF_SIG_WAIT_TICKET]      the same for this rank's wait kernel
+ *     [SF_SIG_WAIT_CTA]         last-CTA election of the wait kernel
+ *     [SF_SIG_ERROR]            set to 1 when a spin timed out (a peer never arrived / never consumed)
+ *     [SF_SIG_CONSUMED + dst]   steps consumer `dst` has finished reading (st.release.sys by dst's wait kernel into
+ *                               every producer's block): back-pressure, a producer reuses slot (s & 1) for step s only
  *                               once every destination has consumed step s - 2
- * Step s of the producer stores pixel i at  peer_data[r] + (s & 1) * slot_stride + peer_offset + i.
  * h_peer_data / h_peer_sig / h_peer_ranks: HOST arrays over the n_peers destinations (rank 0 only = the reference's
  * DataParallel gather to device 0, trainer_DLC_GRU.py:102-106; all ranks = all-gather). */
 #define SF_SIG_WORDS 64
-#define SF_SIG_EPOCH 0
-#define SF_SIG_CTA_DONE 1
-#define SF_SIG_WAIT_EPOCH 2
+#define SF_SIG_TICKET 0
+#define SF_SIG_WAIT_TICKET 2
 #define SF_SIG_WAIT_CTA 3
 #define SF_SIG_ERROR 4
-#define SF_SIG_ARRIVED 8
 #define SF_SIG_CONSUMED 24
 SF_API int sf_local_window_gather_signal_f32(const float* cv, const float* disp, const float* lo, const float* up,
                                              float* out, int B, int D, int H, int W, int mode, float radius,
                                              float gamma, int n_points, int consider_valid, int div_mode,
-                                             float* const* h_peer_data, unsigned long long* const* h_peer_sig,
-                                             const int* h_peer_ranks, int n_peers, long long peer_offset,
-                                             long long slot_stride, unsigned long long* sig_local, int my_rank,
-                                             void* stream);
+                                             unsigned long long* const* h_peer_data,
+                                             unsigned long long* const* h_peer_sig, const int* h_peer_ranks,
+                                             int n_peers, long long peer_offset, long long slot_stride,
+                                             unsigned long long* sig_local, void* stream);
 
-/* Consumer side of the protocol above, one launch per step on the consuming rank: waits until step
- * s = sig_local[SF_SIG_WAIT_EPOCH] of every source rank has arrived, copies slot (s & 1) (n_elems floats at
- * slots + (s & 1) * slot_stride) to `out` when out != NULL (the gathered [N*B,1,H,W] tensor, like an all-gather
- * output), then publishes CONSUMED = s + 1 to every source (h_src_sig: HOST array of the sources' signal blocks,
- * h_src_ranks their ranks) and advances its own WAIT_EPOCH. */
-SF_API int sf_gather_wait_f32(unsigned long long* sig_local, unsigned long long* const* h_src_sig,
-                              const int* h_src_ranks, int n_src, int my_rank, const float* slots,
-                              long long slot_stride, float* out, long long n_elems, void* stream);
+/* Consumer side of the protocol above, one launch per step on a consuming rank: for step s (from its own ticket
+ * counter) it polls every word of slot (s & 1) until the flag is s + 1, writes the n_elems values to `out` (the
+ * gathered [N*B,1,H,W] tensor, like an all-gather output), then publishes CONSUMED = s + 1 to every source
+ * (h_src_sig: HOST array of the n_src sources' signal blocks).  When this kernel retires, step s is complete. */
+SF_API int sf_gather_wait_f32(unsigned long long* sig_local, unsigned long long* const* h_src_sig, int n_src,
+                              int my_rank, const unsigned long long* slots, long long slot_stride, float* out,
+                              long long n_elems, void* stream);
 
 /* build_cost_volume_from_volume(old_volume, sampling_candidates)  fixed_local_cost_volume.py:61-80 (defined
  * identically in 5 reference files).  cand/out [B,K,H,W]; bit-exact; idx_* optional int32 [B,K,H,W]. */

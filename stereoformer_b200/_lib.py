@@ -23,8 +23,8 @@ SIGNATURES = {
     "sf_local_window_f32": [_p] * 10 + [_c_int] * 5 + [_c_float, _c_float] + [_c_int] * 3 + [_p],
     "sf_local_window_gather_f32": [_p] * 5 + [_c_int] * 5 + [_c_float, _c_float] + [_c_int] * 3 + [_p, _c_int, ctypes.c_longlong, _p],
     "sf_local_window_gather_signal_f32": [_p] * 5 + [_c_int] * 5 + [_c_float, _c_float] + [_c_int] * 3 +
-                                         [_p, _p, _p, _c_int, ctypes.c_longlong, ctypes.c_longlong, _p, _c_int, _p],
-    "sf_gather_wait_f32": [_p, _p, _p, _c_int, _c_int, _p, ctypes.c_longlong, _p, ctypes.c_longlong, _p],
+                                         [_p, _p, _p, _c_int, ctypes.c_longlong, ctypes.c_longlong, _p, _p],
+    "sf_gather_wait_f32": [_p, _p, _c_int, _c_int, _p, ctypes.c_longlong, _p, ctypes.c_longlong, _p],
     "sf_sample_volume_f32": [_p] * 5 + [_c_int] * 5 + [_p],
     "sf_disp_warp_f32": [_p] * 6 + [_c_int] * 6 + [_p, _p],
     "sf_guidance_f32": [_p] * 6 + [_c_int] * 6 + [_p, _p],

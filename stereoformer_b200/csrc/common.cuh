@@ -139,6 +139,11 @@ __device__ __forceinline__ void stg_cs_f4(float* p, float4 v) {
 __device__ __forceinline__ void st_release_sys_u64(unsigned long long* p, unsigned long long v) {
   asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
+// relaxed system-scope store: with a preceding __threadfence_system() this is the release pattern, one fence for
+// any number of destinations
+__device__ __forceinline__ void st_relaxed_sys_u64(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
 __device__ __forceinline__ unsigned long long ld_acquire_sys_u64(const unsigned long long* p) {
   unsigned long long v;
   asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
@@ -158,6 +163,15 @@ __device__ __forceinline__ bool spin_until_ge_sys(const unsigned long long* p, u
     }
   }
   return true;
+}
+// 8-byte {value, flag} words of the flag-in-data gather: single-transaction system-scope store / volatile load
+__device__ __forceinline__ void st_ll_sys(unsigned long long* p, float v, uint32_t flag) {
+  asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1, %2};" ::"l"(p), "r"(__float_as_uint(v)), "r"(flag) : "memory");
+}
+__device__ __forceinline__ uint2 ld_ll_sys(const unsigned long long* p) {
+  uint2 v;
+  asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p));
+  return v;
 }
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");

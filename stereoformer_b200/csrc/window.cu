@@ -41,9 +41,8 @@ struct WindowParams {
   long long peer_off;
   // completion protocol of sf_local_window_gather_signal_f32 (null sig_local: plain stores, no signalling)
   unsigned long long* sig_local;
-  unsigned long long* sig_peers[SF_MAX_PEERS];
+  unsigned long long* ll_peers[SF_MAX_PEERS];   // destinations' {value, flag} slots
   int peer_ranks[SF_MAX_PEERS];
-  int my_rank;
   long long slot_stride;
 };
 
@@ -84,16 +83,16 @@ local_window_kernel(const __grid_constant__ CUtensorMap mapCV, const WindowParam
     mbar_expect_tx(&bar, p.D * TPB * 4);
     tma_load_3d(tile, &mapCV, &bar, x0, y, b * p.D);
   }
-  // signalled gather: this launch is step `step` of the rank; its slot was last used by step - 2, which every
-  // destination must have consumed (the wait is normally satisfied long before: two steps of slack)
-  unsigned long long step = 0;
-  long long slot_off = 0;
-  if (p.sig_local) {
-    step = p.sig_local[SF_SIG_EPOCH];
-    slot_off = static_cast<long long>(step & 1ULL) * p.slot_stride;
-    if (threadIdx.x == 0 && step >= 2)
+  // signalled gather: a CTA's ticket gives the step of this launch (all launches of one gather have the same grid and
+  // run one after the other); the step's slot was last used by step - 2, which every destination must have consumed
+  // (normally satisfied long before: two steps of slack)
+  __shared__ unsigned long long s_step;
+  if (p.sig_local && threadIdx.x == 0) {
+    const unsigned long long step = atomicAdd(p.sig_local + SF_SIG_TICKET, 1ULL) / gridDim.x;
+    if (step >= 2)
       for (int r = 0; r < p.n_peers; ++r)
         spin_until_ge_sys(p.sig_local + SF_SIG_CONSUMED + p.peer_ranks[r], step - 1, p.sig_local + SF_SIG_ERROR);
+    s_step = step;
   }
   if (p.use_tma) {
     __syncthreads();
@@ -191,22 +190,14 @@ local_window_kernel(const __grid_constant__ CUtensorMap mapCV, const WindowParam
   }
   const float res = e / s;
   p.out[pix] = res;
-  for (int r = 0; r < p.n_peers; ++r) p.peers[r][p.peer_off + slot_off + static_cast<long long>(pix)] = res;
-  }  // x < W
   if (p.sig_local) {
-    // every CTA fences its peer stores, the last one to finish publishes the step to the destinations
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      __threadfence_system();
-      const unsigned long long prev = atomicAdd(p.sig_local + SF_SIG_CTA_DONE, 1ULL);
-      if (prev == gridDim.x - 1) {
-        p.sig_local[SF_SIG_CTA_DONE] = 0ULL;
-        __threadfence_system();
-        for (int r = 0; r < p.n_peers; ++r) st_release_sys_u64(p.sig_peers[r] + SF_SIG_ARRIVED + p.my_rank, step + 1);
-        p.sig_local[SF_SIG_EPOCH] = step + 1;
-      }
-    }
+    const unsigned long long step = s_step;       // written before the __syncthreads that follows the tile load
+    const long long at = static_cast<long long>(step & 1ULL) * p.slot_stride + p.peer_off + static_cast<long long>(pix);
+    for (int r = 0; r < p.n_peers; ++r) st_ll_sys(p.ll_peers[r] + at, res, static_cast<uint32_t>(step + 1));
+  } else {
+    for (int r = 0; r < p.n_peers; ++r) p.peers[r][p.peer_off + static_cast<long long>(pix)] = res;
   }
+  }  // x < W
 }
 
 // DisparityEstimation(.WithProb).forward  models/utils/estimation.py:14-62: no reuse -> straight coalesced loads.
@@ -293,9 +284,8 @@ static int local_window_impl(const float* cv, const float* disp, const float* lo
                              float* disp0_out, float* dbg_cand, int* dbg_idx_floor, int* dbg_idx_ceil,
                              float* dbg_local, int B, int D, int H, int W, int mode, float radius, float gamma,
                              int n_points, int consider_valid, int div_mode, float* const* h_peers, int n_peers,
-                             long long peer_offset, void* stream, unsigned long long* const* h_peer_sig = nullptr,
-                             const int* h_peer_ranks = nullptr, long long slot_stride = 0,
-                             unsigned long long* sig_local = nullptr, int my_rank = 0) {
+                             long long peer_offset, void* stream, const int* h_peer_ranks = nullptr,
+                             long long slot_stride = 0, unsigned long long* sig_local = nullptr) {
   using namespace sf;
   SF_CHECK_ARG(cv && out, "local_window: null pointer");
   SF_CHECK_ARG(B > 0 && D > 0 && H > 0 && W > 0 && n_points > 0, "local_window: non-positive dimension");
@@ -316,15 +306,15 @@ static int local_window_impl(const float* cv, const float* disp, const float* lo
   p.peer_off = peer_offset;
   for (int r = 0; r < SF_MAX_PEERS; ++r) p.peers[r] = r < n_peers ? h_peers[r] : nullptr;
   for (int r = 0; r < n_peers; ++r) SF_CHECK_ARG(p.peers[r] != nullptr, "local_window: null peer pointer %d", r);
-  p.sig_local = sig_local; p.my_rank = my_rank; p.slot_stride = slot_stride;
-  for (int r = 0; r < SF_MAX_PEERS; ++r) { p.sig_peers[r] = nullptr; p.peer_ranks[r] = 0; }
+  p.sig_local = sig_local; p.slot_stride = slot_stride;
+  for (int r = 0; r < SF_MAX_PEERS; ++r) { p.ll_peers[r] = nullptr; p.peer_ranks[r] = 0; }
   if (sig_local) {
-    SF_CHECK_ARG(n_peers > 0 && h_peer_sig && h_peer_ranks && slot_stride > 0 && my_rank >= 0 && my_rank < 16,
-                 "local_window: the signalled gather needs destinations, their signal blocks / ranks and a slot stride");
+    SF_CHECK_ARG(n_peers > 0 && h_peer_ranks && slot_stride > 0,
+                 "local_window: the signalled gather needs destinations, their ranks and a slot stride");
     for (int r = 0; r < n_peers; ++r) {
-      SF_CHECK_ARG(h_peer_sig[r] != nullptr && h_peer_ranks[r] >= 0 && h_peer_ranks[r] < 16,
-                   "local_window: bad signal block / rank of destination %d", r);
-      p.sig_peers[r] = h_peer_sig[r]; p.peer_ranks[r] = h_peer_ranks[r];
+      SF_CHECK_ARG(h_peer_ranks[r] >= 0 && h_peer_ranks[r] < 16, "local_window: bad rank of destination %d", r);
+      SF_CHECK_ARG((reinterpret_cast<uintptr_t>(h_peers[r]) & 7) == 0, "local_window: slot %d not 8-byte aligned", r);
+      p.ll_peers[r] = reinterpret_cast<unsigned long long*>(h_peers[r]); p.peer_ranks[r] = h_peer_ranks[r];
     }
   }
   // CTA width: 128 pixels, or 32 when the row is short enough that single-warp CTAs waste fewer lanes; single-warp CTAs
@@ -376,14 +366,15 @@ extern "C" int sf_local_window_gather_f32(const float* cv, const float* disp, co
 extern "C" int sf_local_window_gather_signal_f32(const float* cv, const float* disp, const float* lo, const float* up,
                                                  float* out, int B, int D, int H, int W, int mode, float radius,
                                                  float gamma, int n_points, int consider_valid, int div_mode,
-                                                 float* const* h_peer_data, unsigned long long* const* h_peer_sig,
-                                                 const int* h_peer_ranks, int n_peers, long long peer_offset,
-                                                 long long slot_stride, unsigned long long* sig_local, int my_rank,
-                                                 void* stream) {
+                                                 unsigned long long* const* h_peer_data,
+                                                 unsigned long long* const* h_peer_sig, const int* h_peer_ranks,
+                                                 int n_peers, long long peer_offset, long long slot_stride,
+                                                 unsigned long long* sig_local, void* stream) {
   SF_CHECK_ARG(sig_local != nullptr, "local_window_gather_signal: null signal block");
+  (void)h_peer_sig;   // the producers only read their own block; kept in the signature for symmetry with the wait
   return local_window_impl(cv, disp, lo, up, out, nullptr, nullptr, nullptr, nullptr, nullptr, B, D, H, W, mode, radius,
-                           gamma, n_points, consider_valid, div_mode, h_peer_data, n_peers, peer_offset, stream,
-                           h_peer_sig, h_peer_ranks, slot_stride, sig_local, my_rank);
+                           gamma, n_points, consider_valid, div_mode, reinterpret_cast<float* const*>(h_peer_data),
+                           n_peers, peer_offset, stream, h_peer_ranks, slot_stride, sig_local);
 }
 
 extern "C" int sf_sample_volume_f32(const float* cv, const float* cand, float* out, int* idx_floor, int* idx_ceil,

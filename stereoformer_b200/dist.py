@@ -96,20 +96,20 @@ class PeerGather:
 
 
 class SignalledGather:
-    """Gather of per-rank results with COMPLETION semantics, fused into the producing kernel.
+    """Gather of per-rank disparity maps with COMPLETION semantics, fused into the producing kernel.
 
-    Producers (every rank) store their slice straight into the destinations' slots over NVLink from inside the window
-    kernel (``ops.local_window(..., gather=self)``); each step ends with an arrival word per source rank
-    (st.release.sys by the kernel's last CTA).  Consumers call ``wait(out)`` once per step on their stream: a small
-    kernel that waits for every source's arrival, copies the slot into ``out`` [world * numel_per_rank] and releases
-    the slot to the producers (back-pressure: slots are double-buffered, a producer is at most two steps ahead of the
-    slowest consumer).  ``dst_ranks``: (0,) = gather to rank 0, what the reference's ``nn.DataParallel`` does
-    (train_file/trainer_DLC_GRU.py:102-106); all ranks = all-gather.  Everything is stream-ordered and graph-capturable;
-    no host call per step.  Protocol: include/stereoformer_b200.h (sf_local_window_gather_signal_f32)."""
+    Producers (every rank) store {value, step flag} words straight into the destinations' slots over NVLink from inside
+    the window kernel (``ops.local_window(..., gather=self)``); no fence, no extra launch, no host call.  Consumers call
+    ``wait(out)`` once per step on their stream: a small kernel that polls the slot until every word carries the
+    step's flag, unpacks it into ``out`` [world * B, 1, H, W] and releases the slot to the producers (back-pressure:
+    slots are double-buffered, a producer is at most two steps ahead of the slowest consumer).  ``dst_ranks``: (0,) =
+    gather to rank 0, what the reference's ``nn.DataParallel`` does (train_file/trainer_DLC_GRU.py:102-106); all ranks
+    = all-gather.  Everything is stream-ordered and graph-capturable: step counters live in device memory.
+    Protocol: include/stereoformer_b200.h (sf_local_window_gather_signal_f32)."""
 
     SIG_WORDS, SIG_ERROR = 64, 4
 
-    def __init__(self, numel_per_rank, device, dst_ranks=(0,), group=None):
+    def __init__(self, shape, device, dst_ranks=(0,), group=None):
         import ctypes
         import torch.distributed._symmetric_memory as symm_mem
         self.group = group if group is not None else dist.group.WORLD
@@ -117,12 +117,15 @@ class SignalledGather:
         self.rank = dist.get_rank(self.group)
         if self.world > 8:
             raise ValueError("at most 8 ranks (SF_MAX_PEERS)")
-        self.numel_per_rank = int(numel_per_rank)
+        self.shape = tuple(int(v) for v in shape)            # (B, H, W) of every rank's maps: fixes the kernel grids
+        if len(self.shape) != 3:
+            raise ValueError("shape = (B, H, W) of one rank's disparity maps")
+        self.numel_per_rank = self.shape[0] * self.shape[1] * self.shape[2]
         self.dst_ranks = tuple(sorted(set(int(r) for r in dst_ranks)))
         if not self.dst_ranks or min(self.dst_ranks) < 0 or max(self.dst_ranks) >= self.world:
             raise ValueError("bad destination ranks %r" % (dst_ranks,))
-        self.slot_stride = (self.world * self.numel_per_rank + 3) // 4 * 4
-        self.slots = symm_mem.empty(2 * self.slot_stride, dtype=torch.float32, device=device)
+        self.slot_stride = self.world * self.numel_per_rank          # 8-byte words per slot
+        self.slots = symm_mem.empty(2 * self.slot_stride, dtype=torch.int64, device=device)
         self.signals = symm_mem.empty(self.SIG_WORDS, dtype=torch.int64, device=device)
         self.slots.zero_()
         self.signals.zero_()
@@ -133,33 +136,32 @@ class SignalledGather:
         self.sig_ptrs = [int(p) for p in self._h_sig.buffer_ptrs]
         if any(p == 0 for p in self.data_ptrs + self.sig_ptrs):
             raise RuntimeError("symmetric memory rendezvous returned no peer mappings")
-        dist.barrier(group=self.group)               # every block is zeroed before anyone signals
+        dist.barrier(group=self.group)               # every block is zeroed before anyone stores
         nd = len(self.dst_ranks)
         self.c_dst_data = (ctypes.c_void_p * nd)(*[ctypes.c_void_p(self.data_ptrs[r]) for r in self.dst_ranks])
         self.c_dst_sig = (ctypes.c_void_p * nd)(*[ctypes.c_void_p(self.sig_ptrs[r]) for r in self.dst_ranks])
         self.c_dst_ranks = (ctypes.c_int * nd)(*self.dst_ranks)
         self.c_src_sig = (ctypes.c_void_p * self.world)(*[ctypes.c_void_p(p) for p in self.sig_ptrs])
-        self.c_src_ranks = (ctypes.c_int * self.world)(*range(self.world))
         self.is_consumer = self.rank in self.dst_ranks
 
     def offset(self):
         return self.rank * self.numel_per_rank
 
-    def wait(self, out=None):
-        """Consumer side of one step (stream-ordered): ``out`` receives the gathered [world * numel_per_rank] floats."""
+    def wait(self, out):
+        """Consumer side of one step (stream-ordered): ``out`` receives the gathered world * B * H * W floats."""
         import ctypes
         from . import _lib
         if not self.is_consumer:
             raise RuntimeError("rank %d is not a destination of this gather" % self.rank)
         n = self.world * self.numel_per_rank
-        if out is not None and (out.dtype != torch.float32 or out.numel() != n or not out.is_contiguous() or
-                                out.device != self.slots.device):
+        if (out.dtype != torch.float32 or out.numel() != n or not out.is_contiguous() or
+                out.device != self.slots.device):
             raise ValueError("out must be a contiguous fp32 tensor of %d elements on the gather's device" % n)
         with torch.cuda.device(self.slots.device):
-            _lib.call("sf_gather_wait_f32", ctypes.c_void_p(self.sig_ptrs[self.rank]), self.c_src_sig, self.c_src_ranks,
-                      self.world, self.rank, ctypes.c_void_p(self.slots.data_ptr()),
-                      ctypes.c_longlong(self.slot_stride), ctypes.c_void_p(out.data_ptr() if out is not None else 0),
-                      ctypes.c_longlong(n), ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+            _lib.call("sf_gather_wait_f32", ctypes.c_void_p(self.sig_ptrs[self.rank]), self.c_src_sig, self.world,
+                      self.rank, ctypes.c_void_p(self.slots.data_ptr()), ctypes.c_longlong(self.slot_stride),
+                      ctypes.c_void_p(out.data_ptr()), ctypes.c_longlong(n),
+                      ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
         return out
 
     def check(self):

@@ -120,14 +120,14 @@ def local_window(cv, disp=None, lo=None, up=None, mode=SF_WIN_FIXED, radius=0.0,
     if gather is not None:
         if debug or return_disp0 or peers:
             raise ValueError("gather cannot be combined with debug / return_disp0 / peers")
-        if B * H * W != gather.numel_per_rank:
-            raise ValueError("gather was sized for %d elements per rank, got %d" % (gather.numel_per_rank, B * H * W))
+        if (B, H, W) != gather.shape:
+            raise ValueError("gather was built for maps of shape %r, got %r" % (gather.shape, (B, H, W)))
         with torch.cuda.device(cv.device):
             _lib.call("sf_local_window_gather_signal_f32", _ptr(cv), _ptr(disp), _ptr(lo), _ptr(up), _ptr(out), B, D, H,
                       W, int(mode), float(radius), float(gamma), int(n_points), int(bool(consider_valid)),
                       int(div_mode), gather.c_dst_data, gather.c_dst_sig, gather.c_dst_ranks, len(gather.dst_ranks),
                       ctypes.c_longlong(gather.offset()), ctypes.c_longlong(gather.slot_stride),
-                      ctypes.c_void_p(gather.sig_ptrs[gather.rank]), gather.rank, _stream())
+                      ctypes.c_void_p(gather.sig_ptrs[gather.rank]), _stream())
         return out
     if peers:
         if debug or return_disp0:

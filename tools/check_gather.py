@@ -21,7 +21,7 @@ def main():
     dist.init_process_group("nccl", device_id=dev)
     B, D, H, W = 2, 24, 17, 120
     for dst in ((0,), tuple(range(world))):
-        sg = SignalledGather(B * H * W, dev, dst_ranks=dst)
+        sg = SignalledGather((B, H, W), dev, dst_ranks=dst)
         out = torch.empty(B, 1, H, W, device=dev)
         gathered = torch.empty(world * B, 1, H, W, device=dev)
         steps = 9
