@@ -25,6 +25,8 @@ extern "C" {
 #define SF_ALGO_AUTO 0
 #define SF_ALGO_TMA 1     /* force the TMA + FFMA (cost volume) / TMA + tcgen05 (attention) kernel; errors if the shape does not fit */
 #define SF_ALGO_GENERIC 2 /* shape-agnostic CUDA kernel (any W / alignment) */
+#define SF_ALGO_EXACT 4   /* fp32 FFMA arithmetic (no bf16 operand split), the fastest such kernel that fits the shape: what the
+                             drop-ins use under stereoformer_b200.set_precision("exact") */
 #define SF_ALGO_TC 3      /* cost volume on tcgen05 (bf16 hi/mid split, fp32 TMEM accumulation); errors if the shape does not fit */
 
 /* window modes of sf_local_window_f32 */

@@ -6,6 +6,7 @@ There is no CPU fallback: operators raise if the library is missing or a tensor 
 """
 from . import _lib  # noqa: F401
 from . import ops  # noqa: F401
+from .ops import get_precision, precision, set_precision  # noqa: F401
 from .modules import (CorrBlock1D, CostVolume, DisparityEstimation, DisparityEstimationWithProb,  # noqa: F401
                       EpipolarCrossAttention, LocalCostVolume, LRwarp_error, PytorchAlternateCorrBlock1D,
                       Variance_Based_Local_Cost_Volume,

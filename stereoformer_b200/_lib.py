@@ -7,9 +7,10 @@ import ctypes
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libsfb200.so")
+# tools/ that use the tuning hooks (sweeps, timelines) set SF_TUNING_LIB=1 to load the -DSF_TUNING build instead
+LIB_PATH = os.path.join(HERE, "libsfb200_tuning.so" if os.environ.get("SF_TUNING_LIB") == "1" else "libsfb200.so")
 
-SF_ALGO_AUTO, SF_ALGO_TMA, SF_ALGO_GENERIC, SF_ALGO_TC = 0, 1, 2, 3
+SF_ALGO_AUTO, SF_ALGO_TMA, SF_ALGO_GENERIC, SF_ALGO_TC, SF_ALGO_EXACT = 0, 1, 2, 3, 4
 SF_WIN_FIXED, SF_WIN_VARIANCE, SF_WIN_OFFSETS, SF_WIN_ABSOLUTE, SF_WIN_HEAD, SF_WIN_VARIANCE_BOUNDS = 0, 1, 2, 3, 4, 5
 SF_DIV_TRUE, SF_DIV_RECIP = 0, 1
 

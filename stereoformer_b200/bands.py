@@ -76,7 +76,7 @@ class RowBand:
 
 
 def lcv_band(left_rows, right_rows, max_disp, radius=2.0, n_points=20, consider_valid=False, div_mode=SF_DIV_RECIP,
-             algo=SF_ALGO_AUTO, peers=None):
+             algo=None, peers=None):
     """LocalCostVolume hot path (a1 + a3 + a4) on a band's own rows: [B,C,rows,W] features -> (cv, disp).
     Row-local: no halo, same kernels as the whole image."""
     cv = ops.corr_volume(left_rows, right_rows, max_disp, algo=algo)
@@ -132,7 +132,7 @@ def dcn_halo_rows(offset, kernel_h, padding_h, dilation_h):
 
 
 def dcn_band(inp_src, weight, bias, offset_src, mask_src, band, stride=(1, 1), padding=(1, 1), dilation=(1, 1),
-             groups=1, deformable_groups=1, halo=None, algo=SF_ALGO_AUTO):
+             groups=1, deformable_groups=1, halo=None, algo=None):
     """DCN forward on a row band.  All of input / offset / mask are given on the source rows [ys0, ys1) (the offset
     convolution of the reference's DCN pack runs on the same haloed input); the result is cropped to the band.
     Raises ``ValueError`` naming the halo the offsets need when the band's is too small."""

@@ -26,7 +26,16 @@ def _deps_mtime():
     return max(os.path.getmtime(h) for h in hdrs)
 
 
-def build(force=False, verbose=False):
+def build(force=False, verbose=False, tuning=False):
+    """tuning=True: the -DSF_TUNING build (env-driven sweeps, component-isolation kernels, clock64 timelines) for
+    tools/, written to libsfb200_tuning.so; the product library never reads the environment."""
+    flags = FLAGS + (["-DSF_TUNING"] if tuning else [])
+    obj_dir = OBJ + ("_tuning" if tuning else "")
+    lib = LIB.replace("libsfb200.so", "libsfb200_tuning.so") if tuning else LIB
+    return _build(force, verbose, flags, obj_dir, lib)
+
+
+def _build(force, verbose, FLAGS, OBJ, LIB):
     os.makedirs(OBJ, exist_ok=True)
     srcs = sorted(glob.glob(os.path.join(CSRC, "*.cu")))
     hm = _deps_mtime()
@@ -59,4 +68,4 @@ def build(force=False, verbose=False):
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="--verbose" in sys.argv))
+    print(build(force="--force" in sys.argv, verbose="--verbose" in sys.argv, tuning="--tuning" in sys.argv))

@@ -5,6 +5,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #define SF_OK 0
@@ -49,6 +50,15 @@ int make_tmap_3d_bf16_sw128(CUtensorMap* out, const void* base, uint64_t n0, uin
                             uint32_t b2);
 
 static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
+
+// Tuning hooks (pipeline-shape sweeps, component-isolation kernels, clock64 timelines) exist only in the
+// -DSF_TUNING build that tools/ use (python -m stereoformer_b200.build --tuning -> libsfb200_tuning.so).  The product
+// library never reads the environment: tuning_env() is a constant nullptr there and the hooks compile away.
+#ifdef SF_TUNING
+static inline const char* tuning_env(const char* name) { return getenv(name); }
+#else
+static inline const char* tuning_env(const char*) { return nullptr; }
+#endif
 
 }  // namespace sf
 

@@ -167,6 +167,7 @@ extern "C" int sf_corr1d_pyramid_f32(const float* f1, const float* f2, float* co
   SF_CHECK_ARG(B > 0 && C > 0 && H > 0 && W1 > 0 && W2 > 0, "corr1d_pyramid: non-positive dimension");
   SF_CHECK_ARG(n_out >= 1 && n_out <= C1_MAXLEV, "corr1d_pyramid: 1..%d pyramid tensors supported, got %d", C1_MAXLEV,
                n_out);
+  if (algo == SF_ALGO_EXACT) algo = SF_ALGO_GENERIC;      // the FFMA pyramid kernel is the exact path
   SF_CHECK_ARG(algo == SF_ALGO_AUTO || algo == SF_ALGO_GENERIC || algo == SF_ALGO_TMA, "corr1d_pyramid: unknown algo %d",
                algo);
   for (int l = 0; l < n_out; ++l) SF_CHECK_ARG(levels[l] && (W2 >> l) > 0, "corr1d_pyramid: level %d is empty or null", l);

@@ -523,7 +523,7 @@ static int launch_corr_ring_cfg(const float* L, const float* R, float* out, int 
 static int cv_variant() {
   static int v = -1;
   if (v < 0) {
-    const char* e = getenv("SF_CV_VARIANT");
+    const char* e = tuning_env("SF_CV_VARIANT");
     v = e ? atoi(e) : 0;
   }
   return v;
@@ -533,7 +533,8 @@ template <int DT, int NDB>
 static int launch_corr_tma(const float* L, const float* R, float* out, int nBG, int Cg, int H, int W, int D,
                            cudaStream_t stream) {
   constexpr int NCS = CV_NCW / NDB;
-  switch (cv_variant()) {
+#ifdef SF_TUNING
+  switch (cv_variant()) {                            // pipeline-shape sweep (tools/ only)
     case 10: return launch_corr_ring_cfg<DT, NDB, 4, 20 / NCS>(L, R, out, nBG, Cg, H, W, D, stream);
     case 11: return launch_corr_ring_cfg<DT, NDB, 8, 8 / NCS>(L, R, out, nBG, Cg, H, W, D, stream);
     case 12: return launch_corr_ring_cfg<DT, NDB, 4, 16 / NCS>(L, R, out, nBG, Cg, H, W, D, stream);
@@ -553,6 +554,7 @@ static int launch_corr_tma(const float* L, const float* R, float* out, int nBG, 
     case 6: return launch_corr_tma_cfg<DT, NDB, 8, 10>(L, R, out, nBG, Cg, H, W, D, stream);
     default: break;
   }
+#endif
   // measured on B200 (tools/time_cv.py): one disparity block -> private-ring kernel, 3 CTAs/SM once there are
   // enough row tiles for >= 3 rounds, else 2 CTAs/SM with 8-channel stages; several blocks -> producer-warp kernel
   if (NDB == 1) {
@@ -576,15 +578,20 @@ extern "C" int sf_corr_volume_f32(const float* left, const float* right, float* 
   const int Cg = C / groups, nBG = B * groups;
   const bool tma_ok = (W % 4 == 0) && ((reinterpret_cast<uintptr_t>(left) | reinterpret_cast<uintptr_t>(right) |
                                         reinterpret_cast<uintptr_t>(out)) & 15) == 0;
+  SF_CHECK_ARG(algo >= SF_ALGO_AUTO && algo <= SF_ALGO_EXACT, "corr_volume: unknown algo %d", algo);
   SF_CHECK_ARG(algo != SF_ALGO_TMA || tma_ok, "corr_volume: TMA path needs W %% 4 == 0 and 16-byte aligned pointers");
   {
     // tensor-core path: default whenever the channel count makes the 32-channel MMA chunks worthwhile
     const int v = cv_variant();
     const bool tc_ok = corr_tc_supported(left, right, out, nBG, Cg, H, W, D);
     SF_CHECK_ARG(algo != SF_ALGO_TC || tc_ok, "corr_volume: shape / alignment does not fit the tcgen05 kernel");
-    if (algo == SF_ALGO_TC || (v >= 30 && v <= 99 && tc_ok) || (algo == SF_ALGO_AUTO && v == 0 && tc_ok && Cg >= 32))
-      return launch_corr_tc(left, right, out, nBG, Cg, H, W, D, v >= 30 ? v - 30 : 0, s);
+    // (tuning build: SF_CV_VARIANT 30..99 selects a component-isolation variant, and only when the caller left the
+    // choice open -- an explicit algo is never overridden)
+    const bool sweep = algo == SF_ALGO_AUTO && v >= 30 && v <= 99 && tc_ok;
+    if (algo == SF_ALGO_TC || sweep || (algo == SF_ALGO_AUTO && v == 0 && tc_ok && Cg >= 32))
+      return launch_corr_tc(left, right, out, nBG, Cg, H, W, D, sweep ? v - 30 : 0, s);
   }
+  // SF_ALGO_EXACT: fp32 FFMA arithmetic, the fastest kernel that fits the shape
   if (algo == SF_ALGO_GENERIC || !tma_ok) {
     size_t n = static_cast<size_t>(nBG) * D * H * W;
     int grid = static_cast<int>(min(static_cast<size_t>(sm_count()) * 16, (n + 255) / 256));

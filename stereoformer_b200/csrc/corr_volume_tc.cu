@@ -386,7 +386,7 @@ int launch_corr_tc(const float* L, const float* R, float* out, int nBG, int Cg, 
   CorrTcParams p;
   SF_CHECK_ARG(corr_tc_plan(p, nBG, Cg, H, W, D), "corr_volume: shape does not fit the tcgen05 kernel");
   {
-    const char* e = getenv("SF_CV_TS");   // tuning hook: device pointer of a [4][128] int64 timeline buffer
+    const char* e = tuning_env("SF_CV_TS");   // tuning build only: device pointer of a [4][128] int64 timeline buffer
     p.ts = e ? reinterpret_cast<long long*>(strtoull(e, nullptr, 16)) : nullptr;
   }
   CUtensorMap mL, mR, mO;
@@ -404,15 +404,19 @@ int launch_corr_tc(const float* L, const float* R, float* out, int nBG, int Cg, 
     SF_LAUNCH_CHECK();
     return SF_OK;
   };
-  switch (dbg) {
+#ifdef SF_TUNING
+  switch (dbg) {                                     // component-isolation variants (tools/ only)
     case 13: return go(corr_volume_tc_kernel<13>);   // loads + barrier protocol only
     case 2: return go(corr_volume_tc_kernel<2>);     // everything but the loads
     case 14: return go(corr_volume_tc_kernel<14>);   // conversion only
     case 11: return go(corr_volume_tc_kernel<11>);   // MMA only
     case 8: return go(corr_volume_tc_kernel<8>);     // no epilogue
     case 12: return go(corr_volume_tc_kernel<12>);   // loads + conversion
-    default: return go(corr_volume_tc_kernel<0>);
+    default: break;
   }
+#endif
+  (void)dbg;
+  return go(corr_volume_tc_kernel<0>);
 }
 
 }  // namespace sf

@@ -184,7 +184,7 @@ static int launch_dcn(const DcnParams& p, cudaStream_t s) {
 // for 16 input channels but raised an illegal-instruction fault with fewer, cause not found, so it is not shipped).
 constexpr int DS_TY = 8, DS_TX = 32, DS_MAXC = 16;
 static int ds_halo() {
-  static const int r = getenv("SF_DCN_R") ? atoi(getenv("SF_DCN_R")) : 8;   // sweep hook (tools/)
+  static const int r = tuning_env("SF_DCN_R") ? atoi(tuning_env("SF_DCN_R")) : 8;   // sweep hook (tuning build)
   return r;
 }
 
@@ -274,6 +274,343 @@ dcn_small_kernel(const DcnParams p, int RH, int RW, int RWp, int DS_R, unsigned 
     if (o < p.Cout) p.out[(static_cast<size_t>(b) * p.Cout + o) * M + pix] = acc[o] + __ldg(p.bias + o);
 }
 
+// ---- TMA-staged variant (default when the input rows are 16-byte aligned): the patch [Cin][RH][RWb] is ONE
+// cp.async.bulk.tensor box per CTA (out-of-image cells arrive as zeros: the reference's zero padding), which removes the
+// fill loop that was 44 % of the instructions of the kernel above; the 16-wide output accumulation runs as packed
+// FFMA2 (fma.rn.f32x2: two IEEE fp32 FMAs per instruction, results identical to scalar FFMA) and a thread owns PPT
+// output pixels (rows yl and yl + 4), so each broadcast weight load feeds 2 x 16 FMAs.
+__device__ __forceinline__ void ffma2(unsigned long long& acc, unsigned long long w, float v) {
+  asm("{\n\t.reg .b64 vv;\n\tmov.b64 vv, {%2, %2};\n\tfma.rn.f32x2 %0, %1, vv, %0;\n\t}" : "+l"(acc) : "l"(w), "f"(v));
+}
+
+template <int PPT>
+__global__ void __launch_bounds__(DS_TY * DS_TX / PPT)
+dcn_small_tma_kernel(const __grid_constant__ CUtensorMap mapIn, const DcnParams p, int RH, int RWb, int DS_R) {
+  constexpr int NTH = DS_TY * DS_TX / PPT, YSTEP = DS_TY / PPT;
+  extern __shared__ __align__(128) unsigned char ds_raw[];
+  const int T = p.kh * p.kw, M = p.Ho * p.Wo;
+  float* reg = reinterpret_cast<float*>(ds_raw);                  // [Cin][RH][RWb]
+  float* wsm = reg + p.Cin * RH * RWb;                            // [Cin*T][16]
+  uint64_t* bar = reinterpret_cast<uint64_t*>(wsm + p.Cin * T * DS_MAXC);
+  const int tid = threadIdx.x, b = blockIdx.z;
+  const int ty0 = blockIdx.y * DS_TY, tx0 = blockIdx.x * DS_TX;
+  // the innermost TMA coordinate must be a multiple of 4 floats (16 bytes; anything else raises an illegal-instruction
+  // fault -- tools/probe_tma_box.cu): the patch starts at the aligned column at or left of the reachable one, the box
+  // (RWb) is wide enough for any of the four shifts
+  const int RY0 = ty0 * p.sh - p.ph - DS_R, RXr = tx0 * p.sw - p.pw - DS_R;
+  const int RX0 = RXr - (((RXr % 4) + 4) % 4);
+  const size_t HW = static_cast<size_t>(p.H) * p.W;
+  if (tid == 0) {
+    mbar_init(bar, 1);
+    fence_mbar_init();
+    mbar_expect_tx(bar, static_cast<uint32_t>(p.Cin * RH * RWb * 4));
+    tma_load_3d(reg, &mapIn, bar, RX0, RY0, b * p.Cin);
+  }
+  for (int e = tid; e < p.Cin * T * DS_MAXC; e += NTH) {
+    const int o = e % DS_MAXC, k = e / DS_MAXC;           // k = c*T + t
+    wsm[e] = o < p.Cout ? __ldg(p.weight + static_cast<size_t>(o) * p.Cin * T + k) : 0.f;
+  }
+  __syncthreads();
+  mbar_wait(bar, 0);
+
+  const int xo = tx0 + tid % DS_TX, yl = tid / DS_TX;
+  int yo[PPT], pix[PPT];
+  bool live[PPT];
+#pragma unroll
+  for (int k = 0; k < PPT; ++k) {
+    yo[k] = ty0 + yl + k * YSTEP;
+    live[k] = yo[k] < p.Ho && xo < p.Wo;
+    pix[k] = live[k] ? yo[k] * p.Wo + xo : 0;
+  }
+  if (!live[0]) return;                                   // rows only grow with k: nothing to do for this thread
+  const int cpdg = p.Cin / p.dg, plane = RH * RWb;
+  unsigned long long acc[PPT][DS_MAXC / 2];
+#pragma unroll
+  for (int k = 0; k < PPT; ++k)
+#pragma unroll
+    for (int o = 0; o < DS_MAXC / 2; ++o) acc[k][o] = 0ULL;
+
+  for (int dgi = 0; dgi < p.dg; ++dgi) {
+    for (int t = 0; t < T; ++t) {
+      const int i = t / p.kw, j = t - i * p.kw;
+      float w1[PPT], w2[PPT], w3[PPT], w4[PPT], mk[PPT], h_im[PPT], w_im[PPT], hlf[PPT], wlf[PPT];
+      const float* q[PPT];
+      bool staged = true;
+#pragma unroll
+      for (int k = 0; k < PPT; ++k) {
+        const size_t ob = ((static_cast<size_t>(b) * p.dg + dgi) * 2 * T) * M + pix[k];
+        const float oh = __ldg(p.offset + ob + static_cast<size_t>(2 * t) * M);
+        const float ow = __ldg(p.offset + ob + static_cast<size_t>(2 * t + 1) * M);
+        mk[k] = p.mask ? __ldg(p.mask + ((static_cast<size_t>(b) * p.dg + dgi) * T + t) * M + pix[k]) : 1.f;
+        h_im[k] = (float)(yo[k] * p.sh - p.ph + i * p.dh) + oh;
+        w_im[k] = (float)(xo * p.sw - p.pw + j * p.dw) + ow;
+        hlf[k] = floorf(h_im[k]); wlf[k] = floorf(w_im[k]);
+        const float lh = h_im[k] - hlf[k], lw = w_im[k] - wlf[k], hh = 1.f - lh, hw = 1.f - lw;
+        w1[k] = hh * hw; w2[k] = hh * lw; w3[k] = lh * hw; w4[k] = lh * lw;
+        const bool st = hlf[k] >= (float)RY0 && hlf[k] <= (float)(RY0 + RH - 2) && wlf[k] >= (float)RX0 &&
+                        wlf[k] <= (float)(RX0 + RWb - 2);
+        staged = staged && (st || !live[k]);
+        q[k] = reg + (st ? ((int)hlf[k] - RY0) * RWb + ((int)wlf[k] - RX0) : 0);
+        if (!live[k]) mk[k] = 0.f;
+      }
+      if (staged) {
+        const float* wr0 = wsm + (dgi * cpdg * T + t) * DS_MAXC;
+        for (int c = 0; c < cpdg; ++c) {
+          float val[PPT];
+#pragma unroll
+          for (int k = 0; k < PPT; ++k) {
+            const float* qc = q[k] + (dgi * cpdg + c) * plane;
+            val[k] = (w1[k] * qc[0] + w2[k] * qc[1] + w3[k] * qc[RWb] + w4[k] * qc[RWb + 1]) * mk[k];
+          }
+          const ulonglong2* wr = reinterpret_cast<const ulonglong2*>(wr0 + c * T * DS_MAXC);
+#pragma unroll
+          for (int o4 = 0; o4 < DS_MAXC / 4; ++o4) {
+            const ulonglong2 w = wr[o4];
+#pragma unroll
+            for (int k = 0; k < PPT; ++k) {
+              ffma2(acc[k][2 * o4], w.x, val[k]);
+              ffma2(acc[k][2 * o4 + 1], w.y, val[k]);
+            }
+          }
+        }
+      } else {
+        // some corner of this thread lies outside the staged patch (|offset| > DS_R): explicit tests, global loads
+#pragma unroll
+        for (int k = 0; k < PPT; ++k) {
+          if (!live[k]) continue;
+          if (!(h_im[k] > -1.f && w_im[k] > -1.f && h_im[k] < (float)p.H && w_im[k] < (float)p.W)) continue;
+          const int hl = (int)hlf[k], wl = (int)wlf[k];
+          const bool t0 = hl >= 0, l0 = wl >= 0, b1 = hl + 1 <= p.H - 1, r1 = wl + 1 <= p.W - 1;
+          for (int c = dgi * cpdg; c < (dgi + 1) * cpdg; ++c) {
+            const float* src = p.in + (static_cast<size_t>(b) * p.Cin + c) * HW + static_cast<ptrdiff_t>(hl) * p.W + wl;
+            const float v1 = (t0 && l0) ? __ldg(src) : 0.f, v2 = (t0 && r1) ? __ldg(src + 1) : 0.f;
+            const float v3 = (b1 && l0) ? __ldg(src + p.W) : 0.f, v4 = (b1 && r1) ? __ldg(src + p.W + 1) : 0.f;
+            const float val = (w1[k] * v1 + w2[k] * v2 + w3[k] * v3 + w4[k] * v4) * mk[k];
+            const ulonglong2* wr = reinterpret_cast<const ulonglong2*>(wsm + (c * T + t) * DS_MAXC);
+#pragma unroll
+            for (int o4 = 0; o4 < DS_MAXC / 4; ++o4) {
+              const ulonglong2 w = wr[o4];
+              ffma2(acc[k][2 * o4], w.x, val);
+              ffma2(acc[k][2 * o4 + 1], w.y, val);
+            }
+          }
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < PPT; ++k) {
+    if (!live[k]) continue;
+#pragma unroll
+    for (int o2 = 0; o2 < DS_MAXC / 2; ++o2) {
+      const float lo = __uint_as_float(static_cast<unsigned>(acc[k][o2] & 0xffffffffULL));
+      const float hi = __uint_as_float(static_cast<unsigned>(acc[k][o2] >> 32));
+      if (2 * o2 < p.Cout) p.out[(static_cast<size_t>(b) * p.Cout + 2 * o2) * M + pix[k]] = lo + __ldg(p.bias + 2 * o2);
+      if (2 * o2 + 1 < p.Cout)
+        p.out[(static_cast<size_t>(b) * p.Cout + 2 * o2 + 1) * M + pix[k]] = hi + __ldg(p.bias + 2 * o2 + 1);
+    }
+  }
+}
+
+// ---- 2-CTA cluster variant (dg == 1, even Cin): the kernel above is latency-bound at 8 warps per SM (ncu: 31 % issue
+// slots used, short-scoreboard stalls; the 16-channel patch allows 2 CTAs per SM).  Here a CTA PAIR shares a pixel tile:
+// each CTA stages HALF of the input channels (half the patch: 4 CTAs per SM) and accumulates its partial sums for all
+// 16 outputs; the halves are exchanged through distributed shared memory (each CTA finalises 8 output channels), so
+// twice as many warps work on the same tile and the global stores are split as well.
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void st_peer_smem_f32(const float* local_ptr, uint32_t peer, float v) {
+  uint32_t ra;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ra) : "r"(smem_u32(local_ptr)), "r"(peer));
+  asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(ra), "f"(v) : "memory");
+}
+
+__device__ __forceinline__ unsigned long long pick_pair(const unsigned long long (&a)[DS_MAXC / 2], int idx) {
+  unsigned long long v = a[0];
+#pragma unroll
+  for (int j = 1; j < DS_MAXC / 2; ++j)
+    if (j == idx) v = a[j];                      // predicated moves: no dynamic register indexing
+  return v;
+}
+
+template <int PPT, int CS>
+__global__ void __cluster_dims__(CS, 1, 1) __launch_bounds__(DS_TY * DS_TX / PPT, 2 * CS)   // <2,2>: 4 x 128 threads, <1,4>: 8 x 256
+dcn_small_pair_kernel(const __grid_constant__ CUtensorMap mapIn, const DcnParams p, int RH, int RWb, int DS_R) {
+  constexpr int NTH = DS_TY * DS_TX / PPT, YSTEP = DS_TY / PPT, NPIX = DS_TY * DS_TX, OW = DS_MAXC / CS;
+  extern __shared__ __align__(128) unsigned char ds_raw[];
+  const int T = p.kh * p.kw, M = p.Ho * p.Wo, Ch = p.Cin / CS;
+  float* reg = reinterpret_cast<float*>(ds_raw);                  // [Ch][RH][RWb]; later the exchange buffer [CS-1][OW][NPIX]
+  float* wsm = reg + Ch * RH * RWb;                               // [Ch*T][16]
+  uint64_t* bar = reinterpret_cast<uint64_t*>(wsm + Ch * T * DS_MAXC);
+  const uint32_t rank = cluster_ctarank();
+  const int c_first = static_cast<int>(rank) * Ch;
+  const int tid = threadIdx.x, b = blockIdx.z;
+  const int ty0 = blockIdx.y * DS_TY, tx0 = (blockIdx.x / CS) * DS_TX;
+  const int RY0 = ty0 * p.sh - p.ph - DS_R, RXr = tx0 * p.sw - p.pw - DS_R;
+  const int RX0 = RXr - (((RXr % 4) + 4) % 4);                    // 16-byte aligned TMA column (see above)
+  const size_t HW = static_cast<size_t>(p.H) * p.W;
+  if (tid == 0) {
+    mbar_init(bar, 1);
+    fence_mbar_init();
+    mbar_expect_tx(bar, static_cast<uint32_t>(Ch * RH * RWb * 4));
+    tma_load_3d(reg, &mapIn, bar, RX0, RY0, b * p.Cin + c_first);
+  }
+  for (int e = tid; e < Ch * T * DS_MAXC; e += NTH) {
+    const int o = e % DS_MAXC, k = e / DS_MAXC;           // k = c_local*T + t
+    wsm[e] = o < p.Cout ? __ldg(p.weight + static_cast<size_t>(o) * p.Cin * T + c_first * T + k) : 0.f;
+  }
+  __syncthreads();
+  mbar_wait(bar, 0);
+
+  const int xo = tx0 + tid % DS_TX, yl = tid / DS_TX;
+  int yo[PPT], pix[PPT];
+  bool live[PPT];
+#pragma unroll
+  for (int k = 0; k < PPT; ++k) {
+    yo[k] = ty0 + yl + k * YSTEP;
+    live[k] = yo[k] < p.Ho && xo < p.Wo;
+    pix[k] = live[k] ? yo[k] * p.Wo + xo : 0;
+  }
+  const int plane = RH * RWb;
+  unsigned long long acc[PPT][DS_MAXC / 2];
+#pragma unroll
+  for (int k = 0; k < PPT; ++k)
+#pragma unroll
+    for (int o = 0; o < DS_MAXC / 2; ++o) acc[k][o] = 0ULL;
+
+  // sampling descriptors of tap t + 1 are fetched while tap t is accumulated
+  float oh[PPT], ow[PPT], om[PPT];
+  auto fetch = [&](int t) {
+#pragma unroll
+    for (int k = 0; k < PPT; ++k) {
+      const size_t ob = (static_cast<size_t>(b) * 2 * T) * M + pix[k];
+      oh[k] = __ldg(p.offset + ob + static_cast<size_t>(2 * t) * M);
+      ow[k] = __ldg(p.offset + ob + static_cast<size_t>(2 * t + 1) * M);
+      om[k] = p.mask ? __ldg(p.mask + (static_cast<size_t>(b) * T + t) * M + pix[k]) : 1.f;
+    }
+  };
+  if (live[0]) fetch(0);
+  for (int t = 0; t < T && live[0]; ++t) {
+    const int i = t / p.kw, j = t - i * p.kw;
+    float w1[PPT], w2[PPT], w3[PPT], w4[PPT], mk[PPT], h_im[PPT], w_im[PPT], hlf[PPT], wlf[PPT];
+    const float* q[PPT];
+    bool staged = true;
+#pragma unroll
+    for (int k = 0; k < PPT; ++k) {
+      mk[k] = live[k] ? om[k] : 0.f;
+      h_im[k] = (float)(yo[k] * p.sh - p.ph + i * p.dh) + oh[k];
+      w_im[k] = (float)(xo * p.sw - p.pw + j * p.dw) + ow[k];
+      hlf[k] = floorf(h_im[k]); wlf[k] = floorf(w_im[k]);
+      const float lh = h_im[k] - hlf[k], lw = w_im[k] - wlf[k], hh = 1.f - lh, hw = 1.f - lw;
+      w1[k] = hh * hw; w2[k] = hh * lw; w3[k] = lh * hw; w4[k] = lh * lw;
+      const bool st = hlf[k] >= (float)RY0 && hlf[k] <= (float)(RY0 + RH - 2) && wlf[k] >= (float)RX0 &&
+                      wlf[k] <= (float)(RX0 + RWb - 2);
+      staged = staged && (st || !live[k]);
+      q[k] = reg + (st ? ((int)hlf[k] - RY0) * RWb + ((int)wlf[k] - RX0) : 0);
+    }
+    if (t + 1 < T) fetch(t + 1);
+    if (staged) {
+      const float* wr0 = wsm + t * DS_MAXC;
+      for (int c = 0; c < Ch; ++c) {
+        float val[PPT];
+#pragma unroll
+        for (int k = 0; k < PPT; ++k) {
+          const float* qc = q[k] + c * plane;
+          val[k] = (w1[k] * qc[0] + w2[k] * qc[1] + w3[k] * qc[RWb] + w4[k] * qc[RWb + 1]) * mk[k];
+        }
+        const ulonglong2* wr = reinterpret_cast<const ulonglong2*>(wr0 + c * T * DS_MAXC);
+#pragma unroll
+        for (int o4 = 0; o4 < DS_MAXC / 4; ++o4) {
+          const ulonglong2 w = wr[o4];
+#pragma unroll
+          for (int k = 0; k < PPT; ++k) {
+            ffma2(acc[k][2 * o4], w.x, val[k]);
+            ffma2(acc[k][2 * o4 + 1], w.y, val[k]);
+          }
+        }
+      }
+    } else {
+      // some corner of this thread lies outside the staged patch (|offset| > DS_R): explicit tests, global loads
+#pragma unroll
+      for (int k = 0; k < PPT; ++k) {
+        if (!live[k]) continue;
+        if (!(h_im[k] > -1.f && w_im[k] > -1.f && h_im[k] < (float)p.H && w_im[k] < (float)p.W)) continue;
+        const int hl = (int)hlf[k], wl = (int)wlf[k];
+        const bool t0 = hl >= 0, l0 = wl >= 0, b1 = hl + 1 <= p.H - 1, r1 = wl + 1 <= p.W - 1;
+        for (int c = 0; c < Ch; ++c) {
+          const float* src = p.in + (static_cast<size_t>(b) * p.Cin + c_first + c) * HW + static_cast<ptrdiff_t>(hl) * p.W + wl;
+          const float v1 = (t0 && l0) ? __ldg(src) : 0.f, v2 = (t0 && r1) ? __ldg(src + 1) : 0.f;
+          const float v3 = (b1 && l0) ? __ldg(src + p.W) : 0.f, v4 = (b1 && r1) ? __ldg(src + p.W + 1) : 0.f;
+          const float val = (w1[k] * v1 + w2[k] * v2 + w3[k] * v3 + w4[k] * v4) * mk[k];
+          const ulonglong2* wr = reinterpret_cast<const ulonglong2*>(wsm + (c * T + t) * DS_MAXC);
+#pragma unroll
+          for (int o4 = 0; o4 < DS_MAXC / 4; ++o4) {
+            const ulonglong2 w = wr[o4];
+            ffma2(acc[k][2 * o4], w.x, val);
+            ffma2(acc[k][2 * o4 + 1], w.y, val);
+          }
+        }
+      }
+    }
+  }
+  // ---- exchange: rank r finalises output channels [r*OW, (r+1)*OW); the other slices of this CTA's partial sums go
+  // to their owners' shared memory (a patch is dead once every CTA of the cluster has passed the first cluster barrier)
+  cluster_sync_all();
+#pragma unroll
+  for (int d = 1; d < CS; ++d) {
+    const uint32_t peer = (rank + d) % CS;
+    const int slot = static_cast<int>(rank) - (rank > peer ? 1 : 0);        // my index among the peer's senders
+#pragma unroll
+    for (int k = 0; k < PPT; ++k) {
+#pragma unroll
+      for (int o2 = 0; o2 < OW / 2; ++o2) {
+        const unsigned long long v = pick_pair(acc[k], static_cast<int>(peer) * (OW / 2) + o2);
+        float* dst = reg + (slot * OW + 2 * o2) * NPIX + k * NTH + tid;
+        st_peer_smem_f32(dst, peer, __uint_as_float(static_cast<unsigned>(v & 0xffffffffULL)));
+        st_peer_smem_f32(dst + NPIX, peer, __uint_as_float(static_cast<unsigned>(v >> 32)));
+      }
+    }
+  }
+  cluster_sync_all();
+#pragma unroll
+  for (int k = 0; k < PPT; ++k) {
+    if (!live[k]) continue;
+#pragma unroll
+    for (int o2 = 0; o2 < OW / 2; ++o2) {
+      const unsigned long long v = pick_pair(acc[k], static_cast<int>(rank) * (OW / 2) + o2);
+      const int o = static_cast<int>(rank) * OW + 2 * o2;
+      float lo = __uint_as_float(static_cast<unsigned>(v & 0xffffffffULL));
+      float hi = __uint_as_float(static_cast<unsigned>(v >> 32));
+      // partial sums are added in rank order (fixed association: results do not depend on which CTA finalises)
+      float plo[CS], phi[CS];
+#pragma unroll
+      for (int r = 0; r < CS; ++r) { plo[r] = 0.f; phi[r] = 0.f; }
+#pragma unroll
+      for (int sl = 0; sl < CS - 1; ++sl) {
+        const int sender = sl + (sl >= static_cast<int>(rank) ? 1 : 0);
+        const float a0 = reg[(sl * OW + 2 * o2) * NPIX + k * NTH + tid], a1 = reg[(sl * OW + 2 * o2 + 1) * NPIX + k * NTH + tid];
+#pragma unroll
+        for (int r = 0; r < CS; ++r)
+          if (r == sender) { plo[r] = a0; phi[r] = a1; }
+      }
+#pragma unroll
+      for (int r = 0; r < CS; ++r)
+        if (r == static_cast<int>(rank)) { plo[r] = lo; phi[r] = hi; }
+      lo = plo[0]; hi = phi[0];
+#pragma unroll
+      for (int r = 1; r < CS; ++r) { lo += plo[r]; hi += phi[r]; }
+      if (o < p.Cout) p.out[(static_cast<size_t>(b) * p.Cout + o) * M + pix[k]] = lo + __ldg(p.bias + o);
+      if (o + 1 < p.Cout) p.out[(static_cast<size_t>(b) * p.Cout + o + 1) * M + pix[k]] = hi + __ldg(p.bias + o + 1);
+    }
+  }
+}
+
 static void dcn_small_region(const DcnParams& p, int* RH, int* RW, int* RWp, size_t* smem) {
   const int DS_R = ds_halo();
   *RH = (DS_TY - 1) * p.sh + p.dh * (p.kh - 1) + 2 * DS_R + 2;
@@ -294,6 +631,56 @@ static int launch_dcn_small(const DcnParams& p, cudaStream_t s) {
   int RH, RW, RWp;
   size_t smem;
   dcn_small_region(p, &RH, &RW, &RWp, &smem);
+  // TMA-staged variant: needs a tensor map over the input (16-byte aligned rows) and a box that fits next to a second CTA
+  const int RWb = (RW + 3 + 3) & ~3;          // + 3: the patch origin is rounded down to a multiple of 4 columns
+  const size_t smem_t = (static_cast<size_t>(p.Cin) * RH * RWb + static_cast<size_t>(p.Cin) * p.kh * p.kw * DS_MAXC) * 4 + 16;
+  static const int ppt_env = tuning_env("SF_DCN_PPT") ? atoi(tuning_env("SF_DCN_PPT")) : 2;   // A/B hook (tuning build)
+  if (p.W % 4 == 0 && (reinterpret_cast<uintptr_t>(p.in) & 15) == 0 && RWb <= 256 && RH <= 256 && smem_t <= 110 * 1024 &&
+      ppt_env != 0) {
+    CUtensorMap mapIn;
+    int rc = make_tmap_3d_f32(&mapIn, p.in, p.W, p.H, static_cast<uint64_t>(p.B) * p.Cin, RWb, RH, p.Cin);
+    if (rc) return rc;
+    dim3 grid(ceil_div(p.Wo, DS_TX), ceil_div(p.Ho, DS_TY), p.B);
+    SF_CHECK_ARG(grid.y <= 65535, "dcn_forward: output too tall");
+    static const int pair_env = tuning_env("SF_DCN_PAIR") ? atoi(tuning_env("SF_DCN_PAIR")) : 2;   // A/B hook (tuning build)
+    // CTA cluster per tile, 1/CS of the input channels each (dg == 1: the shipped layer); measured at 16 -> 16, 8 x 68x120:
+    // one CTA 29.8 us, pairs 28.2 us (default); quads (4 channels per CTA, one pixel per thread) need 8 x 256 threads per
+    // SM = 32 registers per thread and spill: 67 us
+    int CS = (pair_env == 2 || pair_env == 4) ? pair_env : 0;
+    if (CS == 4 && p.Cin % 4 != 0) CS = 2;
+    if (CS && (p.dg != 1 || p.Cin % CS != 0)) CS = 0;
+    if (CS) {
+      const int Ch = p.Cin / CS;
+      const size_t patch = static_cast<size_t>(Ch) * RH * RWb;
+      const size_t xch = static_cast<size_t>(CS - 1) * (DS_MAXC / CS) * DS_TY * DS_TX;
+      if (patch < xch) CS = 0;
+    }
+    if (CS) {
+      const int Ch = p.Cin / CS;
+      const size_t smem_p = (static_cast<size_t>(Ch) * RH * RWb + static_cast<size_t>(Ch) * p.kh * p.kw * DS_MAXC) * 4 + 16;
+      CUtensorMap mapH;
+      rc = make_tmap_3d_f32(&mapH, p.in, p.W, p.H, static_cast<uint64_t>(p.B) * p.Cin, RWb, RH, Ch);
+      if (rc) return rc;
+      dim3 grid2(CS * grid.x, grid.y, grid.z);
+      auto go = [&](auto kern, int nth) -> int {
+        SF_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem_p)));
+        kern<<<grid2, nth, smem_p, s>>>(mapH, p, RH, RWb, ds_halo());
+        SF_LAUNCH_CHECK();
+        return SF_OK;
+      };
+      if (CS == 4) return go(dcn_small_pair_kernel<1, 4>, DS_TY * DS_TX);
+      return go(dcn_small_pair_kernel<2, 2>, DS_TY * DS_TX / 2);
+    }
+    if (ppt_env == 1) {
+      SF_CUDA(cudaFuncSetAttribute(dcn_small_tma_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem_t)));
+      dcn_small_tma_kernel<1><<<grid, DS_TY * DS_TX, smem_t, s>>>(mapIn, p, RH, RWb, ds_halo());
+    } else {
+      SF_CUDA(cudaFuncSetAttribute(dcn_small_tma_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem_t)));
+      dcn_small_tma_kernel<2><<<grid, DS_TY * DS_TX / 2, smem_t, s>>>(mapIn, p, RH, RWb, ds_halo());
+    }
+    SF_LAUNCH_CHECK();
+    return SF_OK;
+  }
   SF_CUDA(cudaFuncSetAttribute(dcn_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
   dim3 grid(ceil_div(p.Wo, DS_TX), ceil_div(p.Ho, DS_TY), p.B);
   SF_CHECK_ARG(grid.y <= 65535, "dcn_forward: output too tall");
@@ -319,6 +706,7 @@ static int dcn_forward_impl(const float* input, const float* weight, const float
                "channels(%d) and channels_out(%d) must divide group(%d)", Cin, Cout, group);
   SF_CHECK_ARG(deformable_group > 0 && Cin % deformable_group == 0,
                "channels(%d) must divide deformable_group(%d)", Cin, deformable_group);
+  if (algo == SF_ALGO_EXACT) algo = SF_ALGO_GENERIC;      // the FFMA kernels (dcn_small / dcn_forward) are the exact path
   SF_CHECK_ARG(algo == SF_ALGO_AUTO || algo == SF_ALGO_GENERIC || algo == SF_ALGO_TC, "dcn_forward: unknown algo %d", algo);
   DcnParams p;
   p.in = input; p.weight = weight; p.bias = bias; p.offset = offset; p.mask = mask; p.out = out;
@@ -346,7 +734,7 @@ static int dcn_forward_impl(const float* input, const float* weight, const float
                  "output channels per group", dcn_tc_workspace_bytes(Cin, Cout, kh, kw, group), workspace_bytes);
   }
   if (dcn_small_eligible(p)) {
-    static const bool off = getenv("SF_DCN_SMALL") && atoi(getenv("SF_DCN_SMALL")) == 0;   // A/B timing hook (tools/)
+    static const bool off = tuning_env("SF_DCN_SMALL") && atoi(tuning_env("SF_DCN_SMALL")) == 0;   // A/B hook (tuning build)
     if (!off) return launch_dcn_small(p, s);
   }
   if (Cog <= 16) return launch_dcn<16, 128>(p, s);

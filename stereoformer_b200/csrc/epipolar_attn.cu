@@ -83,6 +83,7 @@ extern "C" int sf_epipolar_attn_bf16(const void* q, const void* k, const void* v
   SF_CHECK_ARG(q && k && v && out, "epipolar_attn: null pointer");
   SF_CHECK_ARG(B > 0 && C > 0 && H > 0 && W > 0, "epipolar_attn: non-positive dimension");
   SF_CHECK_ARG(band >= 1 && band <= ATT_MAXBAND, "epipolar_attn: band must be in 1..%d, got %d", ATT_MAXBAND, band);
+  if (algo == SF_ALGO_EXACT) algo = SF_ALGO_GENERIC;      // fp32-accumulating FFMA kernel
   SF_CHECK_ARG(algo == SF_ALGO_AUTO || algo == SF_ALGO_GENERIC || algo == SF_ALGO_TMA, "epipolar_attn: unknown algo %d",
                algo);
   // tcgen05 path (SF_ALGO_TMA forces it): needs C % 64 == 0, C <= 256, W % 8 == 0, band <= 64, no score output

@@ -374,11 +374,11 @@ int launch_attn_tc(const void* q, const void* k, const void* v, void* out, int B
   p.o_col = C <= 128 ? 384 : 256;
   p.tma_out = C <= 128 ? 1 : 0;
   {
-    const char* d = getenv("SF_ATTN_DBG");
+    const char* d = tuning_env("SF_ATTN_DBG");
     p.dbg = d ? atoi(d) : 0;
-    const char* f = getenv("SF_ATTN_DEFER");
+    const char* f = tuning_env("SF_ATTN_DEFER");
     if (f) p.defer = atoi(f);
-    const char* e = getenv("SF_ATTN_TS");   // tuning hook: device pointer of a [3][128] int64 timeline buffer
+    const char* e = tuning_env("SF_ATTN_TS");   // tuning hook: device pointer of a [3][128] int64 timeline buffer
     p.ts = e ? reinterpret_cast<long long*>(strtoull(e, nullptr, 16)) : nullptr;
   }
   CUtensorMap mq, mk, mv, mo;

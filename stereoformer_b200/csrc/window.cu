@@ -320,9 +320,10 @@ static int local_window_impl(const float* cv, const float* disp, const float* lo
   // CTA width: 128 pixels, or 32 when the row is short enough that single-warp CTAs waste fewer lanes; single-warp CTAs
   // (3 KB of shared memory at D = 24) also fit next to a resident persistent kernel, so a caller that pipelines the
   // window under the next batch's cost volume (bench.py) gets real overlap
-  static const int env_tpb = []() { const char* e = getenv("SF_WIN_TPB"); return e ? atoi(e) : 0; }();
+  static const int env_tpb = []() { const char* e = tuning_env("SF_WIN_TPB"); return e ? atoi(e) : 0; }();
   const bool debug = dbg_cand || dbg_idx_floor || dbg_idx_ceil || dbg_local;
-  const int tpb = (env_tpb == 32 || env_tpb == 128) ? env_tpb : ((!debug && W <= 256) ? 32 : 128);
+  // (the debug instantiation is 128 wide: the sweep hook never applies to it)
+  const int tpb = debug ? 128 : (env_tpb == 32 || env_tpb == 128) ? env_tpb : (W <= 256 ? 32 : 128);
   p.nseg = ceil_div(W, tpb);
   p.use_tma = (W % 4 == 0) && D <= 256 && (reinterpret_cast<uintptr_t>(cv) & 15) == 0;
   CUtensorMap map;

@@ -10,7 +10,7 @@ import ctypes
 import torch
 
 from . import _lib
-from ._lib import (SF_ALGO_AUTO, SF_ALGO_GENERIC, SF_ALGO_TC, SF_ALGO_TMA, SF_DIV_RECIP, SF_DIV_TRUE, SF_WIN_ABSOLUTE,
+from ._lib import (SF_ALGO_AUTO, SF_ALGO_EXACT, SF_ALGO_GENERIC, SF_ALGO_TC, SF_ALGO_TMA, SF_DIV_RECIP, SF_DIV_TRUE, SF_WIN_ABSOLUTE,
                    SF_WIN_FIXED, SF_WIN_HEAD, SF_WIN_OFFSETS, SF_WIN_VARIANCE, SF_WIN_VARIANCE_BOUNDS)
 
 __all__ = ["corr_volume", "gwc_volume", "shift_volume", "soft_argmin", "local_window", "sample_volume", "disp_warp",
@@ -18,6 +18,48 @@ __all__ = ["corr_volume", "gwc_volume", "shift_volume", "soft_argmin", "local_wi
            "local_window_backward", "sample_volume_backward", "disp_warp_backward", "gru_reset_backward",
            "gru_blend_backward", "guidance_backward", "upsample_convex_backward", "epipolar_attention", "upsample_convex",
            "gru_reset", "gru_blend"]
+
+
+# ----------------------------------------------------------------------------- precision of the contraction kernels
+# "fast" (default): contractions with >= 32 channels per group run on tcgen05 with a bf16 hi + mid operand split
+#   (~16-bit operand mantissa, fp32 accumulation): cost / group-wise volumes and the CorrBlock1D pyramid agree with the
+#   fp32 reference to ~5e-6 of the volume's magnitude (north_star allows 1e-4), DCN to ~1e-5 of max |out|.
+# "exact": fp32 FFMA kernels everywhere (the reference's 1e-5 analytic DCN tests, bit-level work).
+# Operators called with an explicit algo= are not affected.
+_PRECISION = "fast"
+
+
+def set_precision(mode):
+    """'fast' or 'exact'; returns the previous mode."""
+    global _PRECISION
+    if mode not in ("fast", "exact"):
+        raise ValueError("precision must be 'fast' or 'exact'")
+    old, _PRECISION = _PRECISION, mode
+    return old
+
+
+def get_precision():
+    return _PRECISION
+
+
+class precision:
+    """with ops.precision('exact'): ..."""
+
+    def __init__(self, mode):
+        self.mode = mode
+
+    def __enter__(self):
+        self.old = set_precision(self.mode)
+
+    def __exit__(self, *exc):
+        set_precision(self.old)
+        return False
+
+
+def _algo(algo):
+    if algo is None:
+        return SF_ALGO_EXACT if _PRECISION == "exact" else SF_ALGO_AUTO
+    return int(algo)
 
 
 def _chk(t, name, dtype=torch.float32, dim=None):
@@ -40,7 +82,7 @@ def _stream():
     return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
-def corr_volume(left, right, max_disp, groups=1, algo=SF_ALGO_AUTO, out=None):
+def corr_volume(left, right, max_disp, groups=1, algo=None, out=None):
     """CostVolume('correlation') / build_gwc_volume.  Returns [B,D,H,W] (groups=1) or [B,G,D,H,W]
     (written into ``out`` when given)."""
     left, right = _chk(left, "left_feature", dim=4), _chk(right, "right_feature", dim=4)
@@ -54,7 +96,7 @@ def corr_volume(left, right, max_disp, groups=1, algo=SF_ALGO_AUTO, out=None):
         raise ValueError("out must be a contiguous fp32 CUDA tensor of shape %s" % (shape,))
     with torch.cuda.device(left.device):
         _lib.call("sf_corr_volume_f32", _ptr(left), _ptr(right), _ptr(out), B, C, H, W, int(max_disp), int(groups),
-                  int(algo), _stream())
+                  _algo(algo), _stream())
     return out
 
 
@@ -252,7 +294,7 @@ def guidance(cv, disp, left, right, div_mode=SF_DIV_TRUE, flag=None):
     return err, unc
 
 
-def corr1d_pyramid(f1, f2, num_levels=4, extra_level=True, algo=SF_ALGO_AUTO):
+def corr1d_pyramid(f1, f2, num_levels=4, extra_level=True, algo=None):
     """CorrBlock1D pyramid: list of [B*H*W1,1,1,W2>>l]; extra_level keeps the reference's unused last level."""
     f1, f2 = _chk(f1, "fmap1", dim=4), _chk(f2, "fmap2", dim=4)
     B, C, H, W1 = f1.shape
@@ -264,7 +306,7 @@ def corr1d_pyramid(f1, f2, num_levels=4, extra_level=True, algo=SF_ALGO_AUTO):
     arr = (ctypes.c_void_p * n_out)(*[t.data_ptr() for t in lv])
     with torch.cuda.device(f1.device):
         _lib.call("sf_corr1d_pyramid_f32", _ptr(f1), _ptr(f2), ctypes.cast(arr, ctypes.c_void_p), n_out, B, C, H, W1, W2,
-                  int(algo), _stream())
+                  _algo(algo), _stream())
     return lv
 
 
@@ -304,7 +346,7 @@ def corr1d_alt(f1, f2, coords, radius=4, num_levels=4, div_mode=SF_DIV_TRUE, deb
 
 
 def dcn_forward(inp, weight, bias, offset, mask, stride, padding, dilation, groups, deformable_groups,
-                algo=SF_ALGO_AUTO):
+                algo=None):
     """DCNv2 (mask given) / DCNv1 (mask None) forward -> [B,Cout,Ho,Wo].
 
     algo: SF_ALGO_AUTO (tcgen05 implicit GEMM from 32 channels per group, exact FFMA kernel below),
@@ -334,11 +376,13 @@ def dcn_forward(inp, weight, bias, offset, mask, stride, padding, dilation, grou
                       Cin, H, W, Cout, kh, kw, sh, sw, ph, pw, dh, dw, int(groups), int(deformable_groups), _stream())
         return out
     with torch.cuda.device(inp.device):
-        nws = int(_lib.lib().sf_dcn_workspace_bytes(Cin, Cout, kh, kw, int(groups))) if algo != SF_ALGO_GENERIC else 0
+        algo = _algo(algo)
+        nws = int(_lib.lib().sf_dcn_workspace_bytes(Cin, Cout, kh, kw, int(groups))) \
+            if algo not in (SF_ALGO_GENERIC, SF_ALGO_EXACT) else 0
         ws = torch.empty(nws, device=inp.device, dtype=torch.uint8) if nws else None   # bf16 hi/mid weights (scratch)
         _lib.call("sf_dcn_forward_ws_f32", _ptr(inp), _ptr(weight), _ptr(bias), _ptr(offset), _ptr(mask), _ptr(out), B,
                   Cin, H, W, Cout, kh, kw, sh, sw, ph, pw, dh, dw, int(groups), int(deformable_groups), _ptr(ws),
-                  ctypes.c_size_t(nws), int(algo), _stream())
+                  ctypes.c_size_t(nws), algo, _stream())
     return out
 
 
@@ -507,7 +551,7 @@ def dcn_backward(inp, weight, offset, mask, grad_out, stride, padding, dilation,
     return g_in, g_off, g_mask, g_w, g_b
 
 
-def epipolar_attention(q, k, v, band, return_scores=False, algo=SF_ALGO_AUTO, out=None):
+def epipolar_attention(q, k, v, band, return_scores=False, algo=None, out=None):
     """Band-restricted epipolar row cross-attention, bf16 [B,C,H,W] in/out (spec-derived)."""
     q, k, v = (_chk(t, n, dtype=torch.bfloat16, dim=4) for t, n in ((q, "q"), (k, "k"), (v, "v")))
     if not (q.shape == k.shape == v.shape):
@@ -520,7 +564,7 @@ def epipolar_attention(q, k, v, band, return_scores=False, algo=SF_ALGO_AUTO, ou
     sc = torch.empty((B, band, H, W), device=q.device, dtype=torch.float32) if return_scores else None
     with torch.cuda.device(q.device):
         _lib.call("sf_epipolar_attn_bf16", _ptr(q), _ptr(k), _ptr(v), _ptr(out), _ptr(sc), B, C, H, W, int(band),
-                  int(algo), _stream())
+                  _algo(algo), _stream())
     return (out, sc) if return_scores else out
 
 

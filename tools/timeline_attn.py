@@ -1,4 +1,5 @@
 """Dev tool: per-role clock64 timeline of CTA 0 of the tcgen05 band-attention kernel (SF_ATTN_TS hook)."""
+import os; os.environ.setdefault("SF_TUNING_LIB", "1")   # needs the -DSF_TUNING build (python -m stereoformer_b200.build --tuning)
 import os, sys, torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from stereoformer_b200 import ops
