@@ -314,3 +314,36 @@ def test_window_fused_peer_gather_single_rank(ops):
         assert b[:n].abs().sum() == 0 and b[2 * n:].abs().sum() == 0
     with pytest.raises(ValueError):
         ops.local_window(cv, None, n_points=20, peers=[bufs[0].data_ptr()] * 9)
+
+
+@pytest.mark.parametrize("name,shape", [("C2", (8, 256, 68, 120, 24)), ("C5", (1, 256, 248, 360, 48))])
+def test_whole_chain_epe_at_baseline_shapes(ops, name, shape):
+    """the default (tensor-core) cost volume -> soft-argmin -> local window chain against the fp32
+    oracle chain at the BASELINE shapes, asserted on the MEAN (EPE) and the MAX of |disp - ref|, not on a median.
+    north_star: <= 1e-3 px EPE on the output disparity (1/8-scale px here; x8 at full resolution is asserted too)."""
+    torch.manual_seed(1024)
+    B, C, H, W, D = shape
+    fl, fr = torch.randn(B, C, H, W), torch.randn(B, C, H, W)
+    # features with structure: the right map is the left map shifted by a smooth disparity, plus noise, so that the
+    # soft-argmin is peaked and windows sit all over [0, D-1] (incl. the validity edges)
+    disp = torch.rand(B, 1, H, 1) * (D - 2)
+    xs = torch.arange(W).view(1, 1, 1, W).float()
+    idx = (xs - disp.round()).long().clamp(0, W - 1).expand(B, C, H, W)
+    fr = 0.7 * torch.gather(fl, 3, idx) + 0.3 * fr
+    fl, fr = fl * 4, fr * 4
+    cv = ops.corr_volume(dev(fl), dev(fr), D)
+    out = ops.local_window(cv, None, mode=ops.SF_WIN_FIXED, radius=2, n_points=20, consider_valid=True,
+                           div_mode=ops.SF_DIV_RECIP)
+    cv_ref = O.corr_volume(dev(fl), dev(fr), D)                 # oracle tensor program, fp32, evaluated on the device
+    ref = O.local_cost_volume(cv_ref, O.soft_argmin(cv_ref).unsqueeze(1), 2, 20, True, recip=True)
+    err = (out - ref).abs()
+    rel = float((cv - cv_ref).abs().max() / cv_ref.abs().max())
+    print("%s chain: cost volume %.2e of max, disparity EPE %.3e px, max %.3e px, pixels over 1e-3: %d of %d"
+          % (name, rel, float(err.mean()), float(err.max()), int((err > 1e-3).sum()), err.numel()))
+    assert rel <= 1e-4
+    assert float(err.mean()) * 8 <= 1e-3                        # EPE at full resolution
+    # the maximum is bounded too: a pixel may only be far off where a validity decision (lower < 0, upper >= D-1) of the
+    # reference sits within float rounding of its threshold
+    d0 = O.soft_argmin(cv_ref).unsqueeze(1)
+    near = ((d0 - 2).abs() < 1e-3) | ((d0 + 2 - (D - 1)).abs() < 1e-3)
+    assert float(err[~near].max()) <= 1e-2

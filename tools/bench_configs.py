@@ -259,13 +259,19 @@ def full_model(dev, pk, variant="lc", batch=8, height=544, width=960):
     try:
         net = fullmodel.build_net(variant, dev)
         left, right, _ = stereo_pair(batch, height, width, device=dev)
+        import stereoformer_b200 as sf
         ref = fullmodel.forward(net, variant, left, right)
         ms_ref = fullmodel.time_forward(net, variant, left, right)
         with fullmodel.dropins():
             got = fullmodel.forward(net, variant, left, right)
             ms_ours = fullmodel.time_forward(net, variant, left, right)
+            with sf.precision("exact"):
+                err_exact = (fullmodel.forward(net, variant, left, right) - ref).abs()
         err = (got - ref).abs()
+        floor = (fullmodel.forward(net, variant, torch.nextafter(left, left + 1), right) - ref).abs()
         return {"variant": variant, "shape": [batch, 3, height, width], "us": ms_ours * 1e3,
+                "parity_epe_exact_precision": float(err_exact.mean()), "parity_max_exact_precision": float(err_exact.max()),
+                "stock_vs_stock_1ulp_input_epe": float(floor.mean()),
                 "pairs_per_s": batch / ms_ours * 1e3, "gpu_eager_reference_us": ms_ref * 1e3,
                 "gpu_eager_reference_pairs_per_s": batch / ms_ref * 1e3, "speedup_vs_gpu_eager_reference": ms_ref / ms_ours,
                 "parity_epe": float(err.mean()), "parity_max_err": float(err.max()),

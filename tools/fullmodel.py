@@ -97,19 +97,36 @@ class dropins:
         return False
 
 
-def compare(variant, batch, height, width, device, seed=1024, d8=None):
-    """Stock vs drop-in forward of the same network object on the same synthetic pair."""
+def _stats(err):
+    err = err.abs().flatten()
+    return {"epe": float(err.mean()), "max": float(err.max()),
+            "p99": float(torch.quantile(err[:: max(1, err.numel() // 1000000)], 0.99)),
+            "frac_over_1e-3": float((err > 1e-3).float().mean())}
+
+
+def compare(variant, batch, height, width, device, seed=1024, d8=None, precisions=("fast",), sensitivity=False):
+    """Stock vs drop-in forward of the same network object on the same synthetic pair.  precisions: which settings of
+    stereoformer_b200.set_precision to run (the first one fills the top-level epe / max keys).  sensitivity=True also
+    measures the STOCK network against itself with the left image moved by one ulp: the conditioning of the (random-
+    init, untrained) network, i.e. the floor below which no implementation that is not bit-identical can stay."""
+    import stereoformer_b200 as sf
     from tools.synth import stereo_pair
     net = build_net(variant, device, seed, d8)
     left, right, _ = stereo_pair(batch, height, width, maxdisp=8 * (d8 or 24), seed=seed, device=device)
     ref = forward(net, variant, left, right)
-    with dropins():
-        got = forward(net, variant, left, right)
-    err = (got - ref).abs().flatten()
-    return {"variant": variant, "shape": [batch, height, width], "epe": float(err.mean()), "max": float(err.max()),
-            "p99": float(torch.quantile(err[:: max(1, err.numel() // 1000000)], 0.99)),
-            "frac_over_1e-3": float((err > 1e-3).float().mean()), "disp_mean": float(ref.mean()),
-            "disp_max": float(ref.max())}
+    res = {"variant": variant, "shape": [batch, height, width], "disp_mean": float(ref.mean()),
+           "disp_max": float(ref.max())}
+    for i, mode in enumerate(precisions):
+        with sf.precision(mode), dropins():
+            got = forward(net, variant, left, right)
+        st = _stats(got - ref)
+        res[mode] = st
+        if i == 0:
+            res.update(st)
+            res["precision"] = mode
+    if sensitivity:
+        res["stock_vs_stock_1ulp_input"] = _stats(forward(net, variant, torch.nextafter(left, left + 1), right) - ref)
+    return res
 
 
 def time_forward(net, variant, left, right, reps=5):
