@@ -86,9 +86,9 @@ SF_API int sf_local_window_gather_f32(const float* cv, const float* disp, const 
 /* The same with COMPLETION SEMANTICS (what an NCCL gather gives and plain peer stores do not), as a low-latency
  * flag-in-data protocol (the scheme of NCCL's LL protocol): no fences and no per-step host call on the data path.
  *
- *   slots    : on every destination rank, 2 slots of `slot_stride` 8-byte words {fp32 value, uint32 flag}; step s of
- *              a producer stores pixel i as ONE 8-byte store {value, (uint32)(s + 1)} at
- *              peer_data[r] + (s & 1) * slot_stride + peer_offset + i.  8-byte stores are single transactions, so a
+ *   slots    : on every destination rank, SF_GATHER_SLOTS slots of `slot_stride` 8-byte words {fp32 value, uint32 flag};
+ *              step s of a producer stores pixel i as ONE 8-byte store {value, (uint32)(s + 1)} at
+ *              peer_data[r] + (s % SF_GATHER_SLOTS) * slot_stride + peer_offset + i.  8-byte stores are single transactions, so a
  *              consumer that reads flag == s + 1 has the value of step s.
  *   signals  : every rank owns SF_SIG_WORDS 64-bit words in peer-mapped memory (zero-initialised):
  *     [SF_SIG_TICKET]           CTA tickets of this rank's window kernel: a CTA's step is ticket / gridDim (launches of
@@ -97,10 +97,11 @@ SF_API int sf_local_window_gather_f32(const float* cv, const float* disp, const 
  *     [SF_SIG_WAIT_CTA]         last-CTA election of the wait kernel
  *     [SF_SIG_ERROR]            set to 1 when a spin timed out (a peer never arrived / never consumed)
  *     [SF_SIG_CONSUMED + dst]   steps consumer `dst` has finished reading (st.release.sys by dst's wait kernel into
- *                               every producer's block): back-pressure, a producer reuses slot (s & 1) for step s only
- *                               once every destination has consumed step s - 2
+ *                               every producer's block): back-pressure, a producer reuses a slot for step s only once
+ *                               every destination has consumed step s - SF_GATHER_SLOTS
  * h_peer_data / h_peer_sig / h_peer_ranks: HOST arrays over the n_peers destinations (rank 0 only = the reference's
  * DataParallel gather to device 0, trainer_DLC_GRU.py:102-106; all ranks = all-gather). */
+#define SF_GATHER_SLOTS 4
 #define SF_SIG_WORDS 64
 #define SF_SIG_TICKET 0
 #define SF_SIG_WAIT_TICKET 2
@@ -116,7 +117,7 @@ SF_API int sf_local_window_gather_signal_f32(const float* cv, const float* disp,
                                              unsigned long long* sig_local, void* stream);
 
 /* Consumer side of the protocol above, one launch per step on a consuming rank: for step s (from its own ticket
- * counter) it polls every word of slot (s & 1) until the flag is s + 1, writes the n_elems values to `out` (the
+ * counter) it polls every word of slot (s % SF_GATHER_SLOTS) until the flag is s + 1, writes the n_elems values to `out` (the
  * gathered [N*B,1,H,W] tensor, like an all-gather output), then publishes CONSUMED = s + 1 to every source
  * (h_src_sig: HOST array of the n_src sources' signal blocks).  When this kernel retires, step s is complete. */
 SF_API int sf_gather_wait_f32(unsigned long long* sig_local, unsigned long long* const* h_src_sig, int n_src,

@@ -26,7 +26,7 @@ __global__ void __launch_bounds__(256) gather_wait_kernel(const GatherWaitParams
   __syncthreads();
   const unsigned long long step = s_step;
   const uint32_t want = static_cast<uint32_t>(step + 1);
-  const unsigned long long* src = p.slots + static_cast<long long>(step & 1ULL) * p.slot_stride;
+  const unsigned long long* src = p.slots + static_cast<long long>(step % SF_GATHER_SLOTS) * p.slot_stride;
   bool timed_out = false;
   // 4 independent polls in flight per thread (a system-scope load is a long round trip; one at a time made this
   // kernel 17 us for 1 MB); words that have not arrived yet are re-polled individually
@@ -85,7 +85,9 @@ extern "C" int sf_gather_wait_f32(unsigned long long* sig_local, unsigned long l
     SF_CHECK_ARG(h_src_sig[r] != nullptr, "gather_wait: null signal block of source %d", r);
     p.src_sig[r] = h_src_sig[r];
   }
-  // a fixed grid per gather size (the ticket counter divides by it): 4 words per thread, at most 148 CTAs
+  // a fixed grid per gather size (the ticket counter divides by it): 4 words per thread in one round of polls, at most
+  // 148 CTAs.  (The CTAs cannot share an SM with the consumer's persistent cost-volume CTA -- registers -- so what counts
+  // is their total SM time: 32 CTAs with 4-5 poll rounds each measured slower than 148 with one, 35.6 vs 33.3 us/step.)
   long long want = (n_elems + 256 * 4 - 1) / (256 * 4);
   int grid = static_cast<int>(want < 1 ? 1 : (want > 148 ? 148 : want));
   gather_wait_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(p);

@@ -84,14 +84,15 @@ local_window_kernel(const __grid_constant__ CUtensorMap mapCV, const WindowParam
     tma_load_3d(tile, &mapCV, &bar, x0, y, b * p.D);
   }
   // signalled gather: a CTA's ticket gives the step of this launch (all launches of one gather have the same grid and
-  // run one after the other); the step's slot was last used by step - 2, which every destination must have consumed
-  // (normally satisfied long before: two steps of slack)
+  // run one after the other); the step's slot was last used by step - SF_GATHER_SLOTS, which every destination must have
+  // consumed (normally satisfied long before: SF_GATHER_SLOTS steps of slack between producer and consumer)
   __shared__ unsigned long long s_step;
   if (p.sig_local && threadIdx.x == 0) {
     const unsigned long long step = atomicAdd(p.sig_local + SF_SIG_TICKET, 1ULL) / gridDim.x;
-    if (step >= 2)
+    if (step >= SF_GATHER_SLOTS)
       for (int r = 0; r < p.n_peers; ++r)
-        spin_until_ge_sys(p.sig_local + SF_SIG_CONSUMED + p.peer_ranks[r], step - 1, p.sig_local + SF_SIG_ERROR);
+        spin_until_ge_sys(p.sig_local + SF_SIG_CONSUMED + p.peer_ranks[r], step - (SF_GATHER_SLOTS - 1),
+                          p.sig_local + SF_SIG_ERROR);
     s_step = step;
   }
   if (p.use_tma) {
@@ -192,7 +193,7 @@ local_window_kernel(const __grid_constant__ CUtensorMap mapCV, const WindowParam
   p.out[pix] = res;
   if (p.sig_local) {
     const unsigned long long step = s_step;       // written before the __syncthreads that follows the tile load
-    const long long at = static_cast<long long>(step & 1ULL) * p.slot_stride + p.peer_off + static_cast<long long>(pix);
+    const long long at = static_cast<long long>(step % SF_GATHER_SLOTS) * p.slot_stride + p.peer_off + static_cast<long long>(pix);
     for (int r = 0; r < p.n_peers; ++r) st_ll_sys(p.ll_peers[r] + at, res, static_cast<uint32_t>(step + 1));
   } else {
     for (int r = 0; r < p.n_peers; ++r) p.peers[r][p.peer_off + static_cast<long long>(pix)] = res;

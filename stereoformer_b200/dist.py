@@ -102,12 +102,12 @@ class SignalledGather:
     the window kernel (``ops.local_window(..., gather=self)``); no fence, no extra launch, no host call.  Consumers call
     ``wait(out)`` once per step on their stream: a small kernel that polls the slot until every word carries the
     step's flag, unpacks it into ``out`` [world * B, 1, H, W] and releases the slot to the producers (back-pressure:
-    slots are double-buffered, a producer is at most two steps ahead of the slowest consumer).  ``dst_ranks``: (0,) =
+    four slots: a producer is at most four steps ahead of the slowest consumer).  ``dst_ranks``: (0,) =
     gather to rank 0, what the reference's ``nn.DataParallel`` does (train_file/trainer_DLC_GRU.py:102-106); all ranks
     = all-gather.  Everything is stream-ordered and graph-capturable: step counters live in device memory.
     Protocol: include/stereoformer_b200.h (sf_local_window_gather_signal_f32)."""
 
-    SIG_WORDS, SIG_ERROR = 64, 4
+    SIG_WORDS, SIG_ERROR, SLOTS = 64, 4, 4          # SF_SIG_WORDS, SF_SIG_ERROR, SF_GATHER_SLOTS
 
     def __init__(self, shape, device, dst_ranks=(0,), group=None):
         import ctypes
@@ -125,7 +125,7 @@ class SignalledGather:
         if not self.dst_ranks or min(self.dst_ranks) < 0 or max(self.dst_ranks) >= self.world:
             raise ValueError("bad destination ranks %r" % (dst_ranks,))
         self.slot_stride = self.world * self.numel_per_rank          # 8-byte words per slot
-        self.slots = symm_mem.empty(2 * self.slot_stride, dtype=torch.int64, device=device)
+        self.slots = symm_mem.empty(self.SLOTS * self.slot_stride, dtype=torch.int64, device=device)
         self.signals = symm_mem.empty(self.SIG_WORDS, dtype=torch.int64, device=device)
         self.slots.zero_()
         self.signals.zero_()
