@@ -67,5 +67,32 @@ def _build(force, verbose, FLAGS, OBJ, LIB):
     return LIB
 
 
+def build_torch_ext(force=False):
+    """The torch C++-extension front end (csrc/torch_ext.cpp -> _sfb200_torch.so, in-tree): pybind11 functions that
+    forward to the C ABI of libsfb200.so.  g++ only (no device code)."""
+    import sysconfig
+    import torch
+    from torch.utils import cpp_extension as ce
+    src = os.path.join(CSRC, "torch_ext.cpp")
+    out = os.path.join(HERE, "_sfb200_torch.so")
+    hdr = os.path.join(HERE, "..", "include", "stereoformer_b200.h")
+    if not force and os.path.exists(out) and os.path.getmtime(out) >= max(os.path.getmtime(src), os.path.getmtime(hdr),
+                                                                           os.path.getmtime(LIB)):
+        return out
+    tl = os.path.join(os.path.dirname(torch.__file__), "lib")
+    cmd = ["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-w", "-DTORCH_EXTENSION_NAME=_sfb200_torch",
+           "-DTORCH_API_INCLUDE_EXTENSION_H", "-D_GLIBCXX_USE_CXX11_ABI=%d" % int(torch._C._GLIBCXX_USE_CXX11_ABI)] + \
+          ["-I" + p for p in ce.include_paths()] + ["-I" + sysconfig.get_paths()["include"], "-I/usr/local/cuda/include",
+                                                    src, "-o", out, "-L" + HERE, "-l:libsfb200.so", "-L" + tl, "-lc10",
+                                                    "-ltorch", "-ltorch_cpu", "-ltorch_python", "-lc10_cuda",
+                                                    "-Wl,-rpath,$ORIGIN", "-Wl,-rpath," + tl]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("torch extension build failed:\n%s" % r.stderr[-4000:])
+    return out
+
+
 if __name__ == "__main__":
     print(build(force="--force" in sys.argv, verbose="--verbose" in sys.argv, tuning="--tuning" in sys.argv))
+    if "--tuning" not in sys.argv:
+        print(build_torch_ext(force="--force" in sys.argv))

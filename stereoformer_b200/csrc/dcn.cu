@@ -644,10 +644,9 @@ static int launch_dcn_small(const DcnParams& p, cudaStream_t s) {
     SF_CHECK_ARG(grid.y <= 65535, "dcn_forward: output too tall");
     static const int pair_env = tuning_env("SF_DCN_PAIR") ? atoi(tuning_env("SF_DCN_PAIR")) : 2;   // A/B hook (tuning build)
     // CTA cluster per tile, 1/CS of the input channels each (dg == 1: the shipped layer); measured at 16 -> 16, 8 x 68x120:
-    // one CTA 29.8 us, pairs 28.2 us (default); quads (4 channels per CTA, one pixel per thread) need 8 x 256 threads per
-    // SM = 32 registers per thread and spill: 67 us
-    int CS = (pair_env == 2 || pair_env == 4) ? pair_env : 0;
-    if (CS == 4 && p.Cin % 4 != 0) CS = 2;
+    // one CTA 29.8 us, pairs 28.2 us (default); quads (the kernel is templated on the cluster size: 4 channels per CTA,
+    // one pixel per thread) need 8 x 256 threads per SM = 32 registers per thread and spill: 67 us, not instantiated
+    int CS = pair_env == 2 ? 2 : 0;
     if (CS && (p.dg != 1 || p.Cin % CS != 0)) CS = 0;
     if (CS) {
       const int Ch = p.Cin / CS;
@@ -668,7 +667,6 @@ static int launch_dcn_small(const DcnParams& p, cudaStream_t s) {
         SF_LAUNCH_CHECK();
         return SF_OK;
       };
-      if (CS == 4) return go(dcn_small_pair_kernel<1, 4>, DS_TY * DS_TX);
       return go(dcn_small_pair_kernel<2, 2>, DS_TY * DS_TX / 2);
     }
     if (ppt_env == 1) {

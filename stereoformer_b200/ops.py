@@ -62,6 +62,20 @@ def _algo(algo):
     return int(algo)
 
 
+# The torch C++-extension front end (csrc/torch_ext.cpp; same C ABI underneath) takes the plain calls of the operators
+# that the reference's eager forward issues every step; ctypes remains the binding for everything else and the
+# fallback when the extension has not been built.
+try:
+    from . import _sfb200_torch as _ext
+except ImportError:          # pragma: no cover -- built by stereoformer_b200.build / __graft_entry__.build()
+    _ext = None
+
+
+def _plain(*ts):
+    return all(t is None or (torch.is_tensor(t) and t.is_cuda and t.dtype == torch.float32 and t.is_contiguous())
+               for t in ts)
+
+
 def _chk(t, name, dtype=torch.float32, dim=None):
     if not torch.is_tensor(t):
         raise TypeError("%s must be a tensor" % name)
@@ -85,6 +99,8 @@ def _stream():
 def corr_volume(left, right, max_disp, groups=1, algo=None, out=None):
     """CostVolume('correlation') / build_gwc_volume.  Returns [B,D,H,W] (groups=1) or [B,G,D,H,W]
     (written into ``out`` when given)."""
+    if _ext is not None and _plain(left, right, out) and left.dim() == 4:
+        return _ext.corr_volume(left, right, int(max_disp), int(groups), _algo(algo), out)
     left, right = _chk(left, "left_feature", dim=4), _chk(right, "right_feature", dim=4)
     if left.shape != right.shape:
         raise ValueError("feature shapes differ: %s vs %s" % (tuple(left.shape), tuple(right.shape)))
@@ -119,6 +135,8 @@ def shift_volume(left, right, max_disp, concat=False):
 
 
 def soft_argmin(cv, match_similarity=True, with_prob=False):
+    if _ext is not None and not with_prob and _plain(cv) and cv.dim() == 4:
+        return _ext.soft_argmin(cv, bool(match_similarity))
     cv = _chk(cv, "cost_volume", dim=4)
     B, D, H, W = cv.shape
     disp = torch.empty((B, H, W), device=cv.device, dtype=torch.float32)
@@ -139,6 +157,10 @@ def local_window(cv, disp=None, lo=None, up=None, mode=SF_WIN_FIXED, radius=0.0,
     dist.PeerGather); the result is also stored at element ``peer_offset`` + pixel index of each of them.
     gather: a ``dist.SignalledGather``; the result goes to its destinations' slots with the completion protocol of
     sf_local_window_gather_signal_f32 (consumers call ``gather.wait()``)."""
+    if (_ext is not None and not debug and not return_disp0 and not peers and gather is None and
+            _plain(cv, disp, lo, up, out) and cv.dim() == 4):
+        return _ext.local_window(cv, disp, lo, up, int(mode), float(radius), float(gamma), int(n_points),
+                                 bool(consider_valid), int(div_mode), out)
     cv = _chk(cv, "old_cost_volume", dim=4)
     B, D, H, W = cv.shape
     if disp is not None:
@@ -570,6 +592,8 @@ def epipolar_attention(q, k, v, band, return_scores=False, algo=None, out=None):
 
 def upsample_convex(disp, mask, factor=8, mask_scale=1.0, out=None):
     """Convex upsampling; ``mask_scale`` multiplies the mask first (the `.25 *` of Attempts/update.py:273)."""
+    if _ext is not None and out is None and _plain(disp, mask) and disp.dim() == 4 and mask.dim() == 4:
+        return _ext.upsample_convex(disp, mask, int(factor), float(mask_scale))
     disp, mask = _chk(disp, "disp", dim=4), _chk(mask, "mask", dim=4)
     N, _, H, W = disp.shape
     if mask.shape != (N, 9 * factor * factor, H, W):
