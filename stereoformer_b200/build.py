@@ -76,8 +76,8 @@ def build_torch_ext(force=False):
     src = os.path.join(CSRC, "torch_ext.cpp")
     out = os.path.join(HERE, "_sfb200_torch.so")
     hdr = os.path.join(HERE, "..", "include", "stereoformer_b200.h")
-    if not force and os.path.exists(out) and os.path.getmtime(out) >= max(os.path.getmtime(src), os.path.getmtime(hdr),
-                                                                           os.path.getmtime(LIB)):
+    # (dynamically linked against libsfb200.so: only the front end's own source and the ABI header matter)
+    if not force and os.path.exists(out) and os.path.getmtime(out) >= max(os.path.getmtime(src), os.path.getmtime(hdr)):
         return out
     tl = os.path.join(os.path.dirname(torch.__file__), "lib")
     cmd = ["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-w", "-DTORCH_EXTENSION_NAME=_sfb200_torch",

@@ -178,8 +178,7 @@ corr_volume_tc_kernel(const __grid_constant__ CUtensorMap mapL, const __grid_con
       for (int kc = 0; kc < p.nch; ++kc) {
         if (!(DBG & 2)) mbar_wait(&stg_full[s], ph);
         if (threadIdx.x == 32) ts_mark(p, 1, nts);
-        mbar_wait(&op_empty[o], pho);
-        if (threadIdx.x == 32) ts_mark(p, 1, nts);
+        if (DBG & 1) mbar_wait(&op_empty[o], pho);
         if (!(DBG & 1)) {
           const float* Rs = Rp + s * (VT_STAGE / 4);
           const float* Ts = Tp + s * (VT_STAGE / 4);
@@ -196,6 +195,16 @@ corr_volume_tc_kernel(const __grid_constant__ CUtensorMap mapL, const __grid_con
             if (8 * tsub >= nv) t[0] = zero4;
             if (8 * (tsub + 2) >= nv) t[1] = zero4;
           }
+          // the staged fp32 rows are in registers: hand the ring slot back to the TMA producer NOW, before the
+          // conversion (a slot used to be held ~1200 cycles per chunk on top of the ~3800-cycle load latency; the slot
+          // turnaround, not the converters, set the chunk rate -- tools/timeline_cv.py)
+#pragma unroll
+          for (int i = 0; i < 4; ++i) asm volatile("" ::"f"(r[i].x), "f"(r[i].y), "f"(r[i].z), "f"(r[i].w));
+          asm volatile("" ::"f"(t[0].x), "f"(t[0].y), "f"(t[0].z), "f"(t[0].w), "f"(t[1].x), "f"(t[1].y), "f"(t[1].z), "f"(t[1].w));
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&stg_empty[s]);
+          mbar_wait(&op_empty[o], pho);                          // only now is the operand buffer needed
+          if (threadIdx.x == 32) ts_mark(p, 1, nts);
           unsigned char* bm = Bm + o * VT_OP;
           if (str) {
 #pragma unroll
@@ -212,7 +221,7 @@ corr_volume_tc_kernel(const __grid_constant__ CUtensorMap mapL, const __grid_con
         if (threadIdx.x == 32) ts_mark(p, 1, nts);
         if (lane == 0) {
           mbar_arrive(&op_full[o]);
-          mbar_arrive(&stg_empty[s]);
+          if (DBG & 1) mbar_arrive(&stg_empty[s]);
         }
         if (++s == p.NS) { s = 0; ph ^= 1; }
         if (++o == VT_NOPS) { o = 0; pho ^= 1; }
@@ -229,15 +238,23 @@ corr_volume_tc_kernel(const __grid_constant__ CUtensorMap mapL, const __grid_con
     for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
       for (int kc = 0; kc < p.nch; ++kc) {
         if (!(DBG & 2)) mbar_wait(&stg_full[s], ph);
-        mbar_wait(&op_empty[o], pho);
-        tc_fence_after();
+        if (DBG & 1) { mbar_wait(&op_empty[o], pho); tc_fence_after(); }
         if (!(DBG & 1)) {
           const float* As = Ap + s * (VT_STAGE / 4);
           const int nvc = p.Cg - kc * VT_KC;       // valid channels of this chunk (ragged last chunk only)
           uint32_t ahi[16], amid[16];
+          float av[VT_KC];
+#pragma unroll
+          for (int c = 0; c < VT_KC; ++c) av[c] = As[c * VT_PL];
+#pragma unroll
+          for (int c = 0; c < VT_KC; c += 4) asm volatile("" ::"f"(av[c]), "f"(av[c + 1]), "f"(av[c + 2]), "f"(av[c + 3]));
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&stg_empty[s]);            // slot released before the conversion (see the B converters)
+          mbar_wait(&op_empty[o], pho);                          // the A stage in tensor memory is free again
+          tc_fence_after();
 #pragma unroll
           for (int c = 0; c < 16; ++c) {
-            float a0 = As[(2 * c) * VT_PL], a1 = As[(2 * c + 1) * VT_PL];
+            float a0 = av[2 * c], a1 = av[2 * c + 1];
             if (nvc < VT_KC) {
               if (2 * c >= nvc) a0 = 0.f;
               if (2 * c + 1 >= nvc) a1 = 0.f;
@@ -255,7 +272,7 @@ corr_volume_tc_kernel(const __grid_constant__ CUtensorMap mapL, const __grid_con
         __syncwarp();
         if (lane == 0) {
           mbar_arrive(&op_full[o]);
-          mbar_arrive(&stg_empty[s]);
+          if (DBG & 1) mbar_arrive(&stg_empty[s]);
         }
         if (++s == p.NS) { s = 0; ph ^= 1; }
         if (++o == VT_NOPS) { o = 0; pho ^= 1; }

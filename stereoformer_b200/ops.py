@@ -6,6 +6,7 @@ current PyTorch stream and returns freshly allocated CUDA tensors.  CPU tensors 
 (deform/src/modulated_deform_conv.h:43); nothing here computes on the host.
 """
 import ctypes
+import os
 
 import torch
 
@@ -69,6 +70,8 @@ try:
     from . import _sfb200_torch as _ext
 except ImportError:          # pragma: no cover -- built by stereoformer_b200.build / __graft_entry__.build()
     _ext = None
+if os.environ.get("SF_TUNING_LIB") == "1":
+    _ext = None              # the extension is linked against the product library; tools/ want the tuning build
 
 
 def _plain(*ts):
