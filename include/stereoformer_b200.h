@@ -91,8 +91,9 @@ SF_API int sf_local_window_gather_f32(const float* cv, const float* disp, const 
  *              peer_data[r] + (s % SF_GATHER_SLOTS) * slot_stride + peer_offset + i.  8-byte stores are single transactions, so a
  *              consumer that reads flag == s + 1 has the value of step s.
  *   signals  : every rank owns SF_SIG_WORDS 64-bit words in peer-mapped memory (zero-initialised):
- *     [SF_SIG_TICKET]           CTA tickets of this rank's window kernel: a CTA's step is ticket / gridDim (launches of
- *                               one gather all have the same grid; kernels of a stream run one after the other)
+ *     [SF_SIG_TICKET16 + r]     CTA tickets of this rank's window kernel, r = blockIdx % 16: a CTA's step is its ticket /
+ *                               (number of CTAs with that r) -- launches of one gather all have the same grid and
+ *                               kernels of a stream run one after the other
  *     [SF_SIG_WAIT_TICKET]      the same for this rank's wait kernel
  *     [SF_SIG_WAIT_CTA]         last-CTA election of the wait kernel
  *     [SF_SIG_ERROR]            set to 1 when a spin timed out (a peer never arrived / never consumed)
@@ -103,7 +104,7 @@ SF_API int sf_local_window_gather_f32(const float* cv, const float* disp, const 
  * DataParallel gather to device 0, trainer_DLC_GRU.py:102-106; all ranks = all-gather). */
 #define SF_GATHER_SLOTS 4
 #define SF_SIG_WORDS 64
-#define SF_SIG_TICKET 0
+#define SF_SIG_TICKET16 32
 #define SF_SIG_WAIT_TICKET 2
 #define SF_SIG_WAIT_CTA 3
 #define SF_SIG_ERROR 4

@@ -88,7 +88,11 @@ local_window_kernel(const __grid_constant__ CUtensorMap mapCV, const WindowParam
   // consumed (normally satisfied long before: SF_GATHER_SLOTS steps of slack between producer and consumer)
   __shared__ unsigned long long s_step;
   if (p.sig_local && threadIdx.x == 0) {
-    const unsigned long long step = atomicAdd(p.sig_local + SF_SIG_TICKET, 1ULL) / gridDim.x;
+    // 16 ticket counters (CTAs with the same blockIdx % 16 share one): ~2000 atomics on ONE word serialise at L2 and
+    // every CTA waits for its return value before it may store
+    const unsigned lane16 = blockIdx.x & 15u;
+    const unsigned n_mine = (gridDim.x - lane16 + 15u) >> 4;
+    const unsigned long long step = atomicAdd(p.sig_local + SF_SIG_TICKET16 + lane16, 1ULL) / n_mine;
     if (step >= SF_GATHER_SLOTS)
       for (int r = 0; r < p.n_peers; ++r)
         spin_until_ge_sys(p.sig_local + SF_SIG_CONSUMED + p.peer_ranks[r], step - (SF_GATHER_SLOTS - 1),
