@@ -195,6 +195,21 @@ SF_API int sf_dcn_forward_ws_f32(const float* input, const float* weight, const 
                                  int stride_h, int stride_w, int pad_h, int pad_w, int dil_h, int dil_w, int group,
                                  int deformable_group, void* workspace, size_t workspace_bytes, int algo, void* stream);
 
+/* a10 without any allocation: NO COUNTERPART IN THE REFERENCE; added for
+ * callers that cannot call cudaMalloc (CUDA-graph capture, tight serving loops, harnesses that forbid it).  Same
+ * operator, arguments and algo values as sf_dcn_forward_ws_f32, but the scratch for the bf16 hi/mid copy of the weights
+ * is a file-scope device array of SF_DCN_STATIC_SCRATCH_BYTES inside the library (every GPU that loads the library
+ * holds it until exit; csrc/dcn_static.cu).  Shapes whose sf_dcn_workspace_bytes exceeds that limit are rejected with
+ * SF_ERR_ARG (use sf_dcn_forward_ws_f32).  Calls no cudaMalloc / cudaFree / allocating library routine.  All calls on a
+ * device share the array: each call rewrites the region it uses, so nothing carries over, but calls that OVERLAP on the
+ * GPU (other streams, concurrent graph replays) race on it and must be serialised by the caller. */
+#define SF_DCN_STATIC_SCRATCH_BYTES (4 * 1024 * 1024)   /* 256 -> 256 channels 3x3 needs 2.25 MiB */
+SF_API size_t sf_dcn_static_scratch_bytes(void);
+SF_API int sf_dcn_forward_static_f32(const float* input, const float* weight, const float* bias, const float* offset,
+                                     const float* mask, float* out, int B, int Cin, int H, int W, int Cout, int kh,
+                                     int kw, int stride_h, int stride_w, int pad_h, int pad_w, int dil_h, int dil_w,
+                                     int group, int deformable_group, int algo, void* stream);
+
 /* f3: backward passes of the pure-PyTorch operators = the gradients autograd derives for the reference modules.
  * Any grad_* output may be NULL (skipped).
  *   sf_corr_volume_backward_f32   a1/a2  build_cost_volume.py:39-47, GWC_Cost_Volume.py:14-24 (groups as the forward)

@@ -40,7 +40,7 @@ def test_header_arity_matches_binding(so):
     for name, args in so.SIGNATURES.items():
         m = re.search(r"\b%s\s*\(([^;]*?)\)\s*;" % name, txt, re.S)
         assert m, name
-        assert len([a for a in m.group(1).split(",") if a.strip()]) == len(args), name
+        assert len([a for a in m.group(1).split(",") if a.strip() not in ("", "void")]) == len(args), name
 
 
 def test_cpu_tensors_fail_loudly(so):
