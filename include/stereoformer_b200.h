@@ -221,6 +221,12 @@ SF_API int sf_dcn_forward_static_f32(const float* input, const float* weight, co
  *   sf_disp_warp_backward_f32     a7     disparity_warper.py:83-106 (grad_img is zero-filled here, atomics) */
 SF_API int sf_corr_volume_backward_f32(const float* left, const float* right, const float* grad_cv, float* grad_left,
                                        float* grad_right, int B, int C, int H, int W, int D, int groups, void* stream);
+/* same with a kernel choice: SF_ALGO_AUTO (tcgen05 band product with the bf16 hi/mid split from 64 channels per group
+ * when channels per group % 32 == 0, W % 4 == 0, D <= 65; else the fp32 FFMA kernel), SF_ALGO_GENERIC / SF_ALGO_EXACT
+ * (always the FFMA kernel = sf_corr_volume_backward_f32), SF_ALGO_TC (force; errors if the shape does not fit). */
+SF_API int sf_corr_volume_backward_ex_f32(const float* left, const float* right, const float* grad_cv,
+                                          float* grad_left, float* grad_right, int B, int C, int H, int W, int D,
+                                          int groups, int algo, void* stream);
 SF_API int sf_soft_argmin_backward_f32(const float* cv, const float* grad_disp, float* grad_cv, int B, int D, int H,
                                        int W, int match_similarity, void* stream);
 /* modes FIXED (radius), VARIANCE (radius = gamma: the chain through sigma = sqrt(sum_d p_d (d - disp)^2) is included),

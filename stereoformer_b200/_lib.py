@@ -37,6 +37,7 @@ SIGNATURES = {
     "sf_corr1d_alt_f32": [_p] * 6 + [ctypes.c_size_t] + [_c_int] * 8 + [_p],
     "sf_dcn_forward_f32": [_p] * 6 + [_c_int] * 15 + [_p],
     "sf_corr_volume_backward_f32": [_p] * 5 + [_c_int] * 6 + [_p],
+    "sf_corr_volume_backward_ex_f32": [_p] * 5 + [_c_int] * 7 + [_p],
     "sf_soft_argmin_backward_f32": [_p] * 3 + [_c_int] * 5 + [_p],
     "sf_local_window_backward_f32": [_p] * 9 + [_c_int] * 5 + [_c_float] + [_c_int] * 3 + [_p],
     "sf_sample_volume_backward_f32": [_p] * 5 + [_c_int] * 5 + [_p],

@@ -317,15 +317,51 @@ sample_volume_bwd_kernel(const float* __restrict__ cv, const float* __restrict__
 
 }  // namespace sf
 
+namespace sf {
+bool corr_bwd_tc_supported(const float* L, const float* R, const float* G, const float* gL, const float* gR, int nBG,
+                           int Cg, int H, int W, int D);
+int launch_corr_bwd_tc(const float* L, const float* R, const float* G, float* gL, float* gR, int nBG, int Cg, int H,
+                       int W, int D, cudaStream_t stream);
+}  // namespace sf
+
+static int corr_volume_backward_impl(const float* left, const float* right, const float* grad_cv, float* grad_left,
+                                     float* grad_right, int B, int C, int H, int W, int D, int groups, int algo,
+                                     void* stream);
+
 extern "C" int sf_corr_volume_backward_f32(const float* left, const float* right, const float* grad_cv, float* grad_left,
                                            float* grad_right, int B, int C, int H, int W, int D, int groups,
                                            void* stream) {
+  return corr_volume_backward_impl(left, right, grad_cv, grad_left, grad_right, B, C, H, W, D, groups, SF_ALGO_GENERIC,
+                                   stream);
+}
+
+extern "C" int sf_corr_volume_backward_ex_f32(const float* left, const float* right, const float* grad_cv,
+                                              float* grad_left, float* grad_right, int B, int C, int H, int W, int D,
+                                              int groups, int algo, void* stream) {
+  return corr_volume_backward_impl(left, right, grad_cv, grad_left, grad_right, B, C, H, W, D, groups, algo, stream);
+}
+
+static int corr_volume_backward_impl(const float* left, const float* right, const float* grad_cv, float* grad_left,
+                                     float* grad_right, int B, int C, int H, int W, int D, int groups, int algo,
+                                     void* stream) {
   using namespace sf;
   SF_CHECK_ARG(left && right && grad_cv, "corr_volume_backward: null pointer");
   SF_CHECK_ARG(B > 0 && C > 0 && H > 0 && W > 0 && D > 0, "corr_volume_backward: non-positive dimension");
   SF_CHECK_ARG(groups > 0 && C % groups == 0, "corr_volume_backward: channels %d not divisible by groups %d", C, groups);
   SF_CHECK_ARG(B <= 65535 && groups <= 65535, "corr_volume_backward: batch or group count too large");
   if (!grad_left && !grad_right) return SF_OK;
+  if (algo == SF_ALGO_EXACT) algo = SF_ALGO_GENERIC;
+  SF_CHECK_ARG(algo == SF_ALGO_AUTO || algo == SF_ALGO_GENERIC || algo == SF_ALGO_TC,
+               "corr_volume_backward: unknown algo %d", algo);
+  if (algo != SF_ALGO_GENERIC) {
+    // tensor-core path from 64 channels per group (two TMEM lane quarters); below that the FFMA kernel is HBM-bound too
+    const bool fits = corr_bwd_tc_supported(left, right, grad_cv, grad_left, grad_right, B * groups, C / groups, H, W, D);
+    SF_CHECK_ARG(fits || algo != SF_ALGO_TC, "corr_volume_backward: shape does not fit the tcgen05 kernel "
+                 "(channels per group %% 32, W %% 4, D <= 65, 16-byte aligned pointers)");
+    if (fits && (algo == SF_ALGO_TC || C / groups >= 64))
+      return launch_corr_bwd_tc(left, right, grad_cv, grad_left, grad_right, B * groups, C / groups, H, W, D,
+                                static_cast<cudaStream_t>(stream));
+  }
   const size_t smem = static_cast<size_t>(D) * W * sizeof(float);
   const int use_smem = smem <= 160 * 1024;
   dim3 grid(H, B, groups);

@@ -412,8 +412,9 @@ def dcn_forward(inp, weight, bias, offset, mask, stride, padding, dilation, grou
 
 
 # ----------------------------------------------------------------------------- backward passes
-def corr_volume_backward(left, right, grad_cv, max_disp, groups=1, needs=(True, True)):
-    """Gradients of corr_volume / gwc_volume w.r.t. (left, right)."""
+def corr_volume_backward(left, right, grad_cv, max_disp, groups=1, needs=(True, True), algo=None):
+    """Gradients of corr_volume / gwc_volume w.r.t. (left, right).  algo as corr_volume: the precision switch picks the
+    tcgen05 band product ("fast", from 64 channels per group) or the fp32 FFMA kernel ("exact")."""
     left, right = _chk(left, "left_feature", dim=4), _chk(right, "right_feature", dim=4)
     grad_cv = _chk(grad_cv, "grad_cost_volume")
     B, C, H, W = left.shape
@@ -422,8 +423,8 @@ def corr_volume_backward(left, right, grad_cv, max_disp, groups=1, needs=(True, 
     gl = torch.empty_like(left) if needs[0] else None
     gr = torch.empty_like(right) if needs[1] else None
     with torch.cuda.device(left.device):
-        _lib.call("sf_corr_volume_backward_f32", _ptr(left), _ptr(right), _ptr(grad_cv), _ptr(gl), _ptr(gr), B, C, H, W,
-                  int(max_disp), int(groups), _stream())
+        _lib.call("sf_corr_volume_backward_ex_f32", _ptr(left), _ptr(right), _ptr(grad_cv), _ptr(gl), _ptr(gr), B, C, H,
+                  W, int(max_disp), int(groups), _algo(algo), _stream())
     return gl, gr
 
 

@@ -42,6 +42,54 @@ def test_corr_volume_backward(shape, D, groups):
     assert torch.equal(gl2, gl)
 
 
+@pytest.mark.parametrize("shape,D,groups", [((2, 256, 5, 120), 24, 1),      # the bench grid's row width: one ragged segment
+                                            ((1, 128, 3, 360), 48, 1),      # C5 row width: 3 segments, 2 K blocks per band
+                                            ((1, 64, 2, 132), 8, 1),        # 2 segments, the second almost empty
+                                            ((1, 96, 2, 64), 65, 1),        # widest halo, ragged channel block (3 quarters)
+                                            ((1, 320, 2, 200), 33, 1),      # 3 channel blocks, the last with 2 quarters
+                                            ((2, 256, 3, 48), 12, 4)])      # group-wise: 64 channels per group
+def test_corr_volume_backward_tensor_core(shape, D, groups):
+    """The tcgen05 band-product backward (csrc/corr_volume_bwd_tc.cu) against the fp32 FFMA kernel and against autograd
+    through the oracle; one-sided calls must give the same bits as the two-sided one."""
+    from stereoformer_b200 import ops
+    torch.manual_seed(22)
+    L, R = torch.randn(*shape), torch.randn(*shape)
+    lc, rc = _leaf(L), _leaf(R)
+    ref = O.corr_volume(lc, rc, D) if groups == 1 else O.gwc_volume(lc, rc, D, groups)
+    go = torch.randn_like(ref)
+    rl, rr = torch.autograd.grad(ref, [lc, rc], go)
+    Lc, Rc, G = L.cuda(), R.cuda(), go.cuda().contiguous()
+    gl, gr = ops.corr_volume_backward(Lc, Rc, G, D, groups, algo=ops.SF_ALGO_TC)
+    el, er = ops.corr_volume_backward(Lc, Rc, G, D, groups, algo=ops.SF_ALGO_GENERIC)
+    for got, exact, want, name in ((gl, el, rl, "grad_left"), (gr, er, rr, "grad_right")):
+        scale = want.abs().max().item()
+        e_tc = (got.cpu() - want).abs().max().item()
+        e_ex = (exact.cpu() - want).abs().max().item()
+        print("%s %s D=%d: tcgen05 %.2e, FFMA %.2e of max |grad| %.3f" % (name, shape, D, e_tc / scale, e_ex / scale, scale))
+        assert e_ex <= 1e-5 * scale
+        assert e_tc <= 1e-4 * scale
+    gl1, none = ops.corr_volume_backward(Lc, Rc, G, D, groups, needs=(True, False), algo=ops.SF_ALGO_TC)
+    none2, gr1 = ops.corr_volume_backward(Lc, Rc, G, D, groups, needs=(False, True), algo=ops.SF_ALGO_TC)
+    assert none is None and none2 is None
+    assert torch.equal(gl1, gl) and torch.equal(gr1, gr)
+
+
+def test_corr_volume_backward_precision_switch_and_limits():
+    import stereoformer_b200 as sf
+    from stereoformer_b200 import ops
+    torch.manual_seed(23)
+    L, R, G = torch.randn(1, 128, 2, 64).cuda(), torch.randn(1, 128, 2, 64).cuda(), torch.randn(1, 16, 2, 64).cuda()
+    tc = ops.corr_volume_backward(L, R, G, 16, algo=ops.SF_ALGO_TC)
+    fast = ops.corr_volume_backward(L, R, G, 16)
+    with sf.precision("exact"):
+        exact = ops.corr_volume_backward(L, R, G, 16)
+    ffma = ops.corr_volume_backward(L, R, G, 16, algo=ops.SF_ALGO_GENERIC)
+    assert torch.equal(fast[0], tc[0]) and torch.equal(fast[1], tc[1])
+    assert torch.equal(exact[0], ffma[0]) and torch.equal(exact[1], ffma[1])
+    with pytest.raises(ValueError, match="does not fit"):                     # 24 channels per group
+        ops.corr_volume_backward(L[:, :24].contiguous(), R[:, :24].contiguous(), G, 16, algo=ops.SF_ALGO_TC)
+
+
 @pytest.mark.parametrize("sim", [True, False])
 def test_soft_argmin_backward(sim):
     import stereoformer_b200 as sf
