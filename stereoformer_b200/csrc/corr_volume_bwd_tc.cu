@@ -79,9 +79,9 @@ corr_volume_bwd_tc_kernel(const __grid_constant__ CUtensorMap mapL, const __grid
   uint64_t* band_empty = g_full + 6;            // [2]  MMA commit -> band warps
   uint64_t* a_full = g_full + 8;                // [2]  converters (8 warps) -> MMA
   uint64_t* a_empty = g_full + 10;              // [2]  MMA commit -> converters
-  uint64_t* d_full = g_full + 12;               // MMA commit -> epilogue
-  uint64_t* d_empty = g_full + 13;              // epilogue (4 warps) -> MMA
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(g_full + 14);
+  uint64_t* d_full = g_full + 12;               // [2]  MMA commit -> epilogue, per 64-pixel half of the accumulator
+  uint64_t* d_empty = g_full + 14;              // [2]  epilogue (4 warps) -> MMA
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(g_full + 16);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const bool both = p.sides == 3;
@@ -95,8 +95,8 @@ corr_volume_bwd_tc_kernel(const __grid_constant__ CUtensorMap mapL, const __grid
       mbar_init(&g_full[s], 1); mbar_init(&g_empty[s], 4);
       mbar_init(&band_full[s], 4); mbar_init(&band_empty[s], 1);
       mbar_init(&a_full[s], BT_NCONV); mbar_init(&a_empty[s], 1);
+      mbar_init(&d_full[s], 1); mbar_init(&d_empty[s], 4);
     }
-    mbar_init(d_full, 1); mbar_init(d_empty, 4);
     fence_mbar_init();
     tma_prefetch_desc(side ? &mapL : &mapR);
     tma_prefetch_desc(&mapG);
@@ -223,23 +223,26 @@ corr_volume_bwd_tc_kernel(const __grid_constant__ CUtensorMap mapL, const __grid
         for (int cb = 0; cb < p.ncb; ++cb, ++si) {
           const int ab = si & 1;
           mbar_wait(&a_full[ab], (si >> 1) & 1);
-          mbar_wait(d_empty, (si & 1) ^ 1);
-          tc_fence_after();
           const uint32_t a_hi = tmem + BT_A_BASE + ab * p.Kg, a_mid = a_hi + halfA;
-          for (int j = 0; j < 4; ++j) {
-            const uint32_t bj = band + j * 2 * half_off;
-            for (int s = 0; s < p.nks; ++s) {
-              const uint32_t boff = (s >> 2) * 4096 + (s & 3) * 32;
-              const uint64_t dbh = make_smem_desc(bj + boff, 16, 1024);
-              const uint64_t dbm = make_smem_desc(bj + half_off + boff, 16, 1024);
-              const uint32_t ac = 16 * j + 8 * s;
-              umma_bf16_ts(tmem + 32 * j, a_hi + ac, dbh, idesc, s != 0);
-              umma_bf16_ts(tmem + 32 * j, a_hi + ac, dbm, idesc, true);
-              umma_bf16_ts(tmem + 32 * j, a_mid + ac, dbh, idesc, true);
+          // the accumulator is handed over in two 64-pixel halves: the epilogue drains half 0 while half 1 is computed
+          for (int h = 0; h < 2; ++h) {
+            mbar_wait(&d_empty[h], (si & 1) ^ 1);
+            tc_fence_after();
+            for (int j = 2 * h; j < 2 * h + 2; ++j) {
+              const uint32_t bj = band + j * 2 * half_off;
+              for (int s = 0; s < p.nks; ++s) {
+                const uint32_t boff = (s >> 2) * 4096 + (s & 3) * 32;
+                const uint64_t dbh = make_smem_desc(bj + boff, 16, 1024);
+                const uint64_t dbm = make_smem_desc(bj + half_off + boff, 16, 1024);
+                const uint32_t ac = 16 * j + 8 * s;
+                umma_bf16_ts(tmem + 32 * j, a_hi + ac, dbh, idesc, s != 0);
+                umma_bf16_ts(tmem + 32 * j, a_hi + ac, dbm, idesc, true);
+                umma_bf16_ts(tmem + 32 * j, a_mid + ac, dbh, idesc, true);
+              }
             }
+            umma_commit(&d_full[h]);
           }
           umma_commit(&a_empty[ab]);
-          umma_commit(d_full);
         }
         umma_commit(&band_empty[bb]);
       }
@@ -259,37 +262,39 @@ corr_volume_bwd_tc_kernel(const __grid_constant__ CUtensorMap mapL, const __grid
       const int x0 = seg * 128;
       for (int cb = 0; cb < p.ncb; ++cb, ++si) {
         const bool valid = cb * 128 + 32 * q < p.Cg;
-        mbar_wait(d_full, si & 1);
-        tc_fence_after();
-#pragma unroll 1
-        for (int jb = 0; jb < 4; ++jb) {
-          uint32_t raw[32];
-          tmem_ld32(trow + 32 * jb, raw);
+        for (int h = 0; h < 2; ++h) {
+          mbar_wait(&d_full[h], si & 1);
+          tc_fence_after();
+          uint32_t raw[2][32];
+          tmem_ld32(trow + 64 * h, raw[0]);
+          tmem_ld32(trow + 64 * h + 32, raw[1]);
           tmem_ld_wait();
-          if (jb == 3) {
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(d_empty);
-          }
-          if (valid && x0 + 32 * jb < p.W) {
-            unsigned char* buf = stage + (nst & 1) * 4096;
-            if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
-            __syncwarp();
-            unsigned char* rowp = buf + lane * 128;
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&d_empty[h]);          // the half is in registers: the next MMAs may overwrite it
 #pragma unroll
-            for (int c = 0; c < 8; ++c) {
-              float4 v;
-              v.x = __uint_as_float(raw[4 * c]) * inv; v.y = __uint_as_float(raw[4 * c + 1]) * inv;
-              v.z = __uint_as_float(raw[4 * c + 2]) * inv; v.w = __uint_as_float(raw[4 * c + 3]) * inv;
-              *reinterpret_cast<float4*>(rowp + ((c ^ sw) << 4)) = v;
+          for (int e = 0; e < 2; ++e) {
+            const int xb = x0 + 64 * h + 32 * e;
+            if (valid && xb < p.W) {
+              unsigned char* buf = stage + (nst & 1) * 4096;
+              if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+              __syncwarp();
+              unsigned char* rowp = buf + lane * 128;
+#pragma unroll
+              for (int c = 0; c < 8; ++c) {
+                float4 v;
+                v.x = __uint_as_float(raw[e][4 * c]) * inv; v.y = __uint_as_float(raw[e][4 * c + 1]) * inv;
+                v.z = __uint_as_float(raw[e][4 * c + 2]) * inv; v.w = __uint_as_float(raw[e][4 * c + 3]) * inv;
+                *reinterpret_cast<float4*>(rowp + ((c ^ sw) << 4)) = v;
+              }
+              fence_proxy_async_smem();
+              __syncwarp();
+              if (lane == 0) {
+                bt_tma_store_3d(mapO, buf, xb, y, bg * p.Cg + cb * 128 + 32 * q);
+                asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+              }
+              ++nst;
             }
-            fence_proxy_async_smem();
-            __syncwarp();
-            if (lane == 0) {
-              bt_tma_store_3d(mapO, buf, x0 + 32 * jb, y, bg * p.Cg + cb * 128 + 32 * q);
-              asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-            }
-            ++nst;
           }
         }
       }
@@ -319,7 +324,7 @@ static bool corr_bwd_tc_plan(CorrBwdTcParams& p, int nBG, int Cg, int H, int W, 
   p.g_bytes = D * p.Kg * 4;
   p.g_pitch = ceil_div(p.g_bytes, 128) * 128;
   p.band_bytes = 4 * 2 * p.nkb * 4096;
-  const int budget = 232448 - 1024 - BT_OUT_BYTES - 256;
+  const int budget = 232448 - 1024 - BT_OUT_BYTES - 512;
   for (int cfg = 0; cfg < 3; ++cfg) {                 // prefer double-buffered bands and gradient tiles
     p.NB = cfg < 2 ? 2 : 1;
     p.NG = cfg < 1 ? 2 : 1;
@@ -357,7 +362,7 @@ int launch_corr_bwd_tc(const float* L, const float* R, const float* G, float* gL
   rc = make_tmap_3d_f32_swz(&mGR, gR ? gR : gL, W, H, rows, 32, 1, 32, 128);
   if (rc) return rc;
   const size_t smem = static_cast<size_t>(p.NB) * p.band_bytes + BT_OUT_BYTES + static_cast<size_t>(p.NG) * p.g_pitch +
-                      static_cast<size_t>(p.NS) * p.stage_bytes + 256;
+                      static_cast<size_t>(p.NS) * p.stage_bytes + 512;
   int grid;
   if (sides == 3) grid = min(2 * p.ntiles, sm_count() & ~1);
   else grid = min(p.ntiles, sm_count());
