@@ -25,6 +25,7 @@
 // Algorithmic bytes per pixel: (4*Cg + D) * 4 per group (features read once, gradients written once; the volume gradient
 // is read once per side).  Error of the 3-term split ~2^-16 per product, like the forward.
 #include <cuda_bf16.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 #include "tc_common.cuh"
@@ -39,17 +40,18 @@ constexpr int BT_WARP_EPI = BT_WARP_MMA + 1;      // 14..17 (warp & 3 = TMEM lan
 constexpr int BT_THREADS = (BT_WARP_EPI + 4) * 32;
 constexpr int BT_MAXNS = 8;
 constexpr int BT_A_BASE = 128;                    // TMEM: accumulator at columns [0,128), A buffers behind it
-constexpr int BT_OUT_BYTES = 4 * 2 * 4096;        // epilogue staging: 4 warps x 2 x [32 ch][32 px] fp32
+constexpr int BT_OUT_TILE = 4096;                 // one epilogue staging tile: [32 ch][32 px] fp32 (4 warps x NO of them)
 
 struct CorrBwdTcParams {
   int Cg, H, W, D, nBG;
   int HL;            // halo of the K window: multiple of 16, >= D-1, <= 64
   int Kg;            // 128 + HL source pixels per tile
   int P;             // Kg + 4: row pitch of a staged feature row (floats)
-  int nks;           // k-steps (16 source pixels) per sub-tile: (32 + HL) / 16
-  int nkb;           // 64-element K blocks per sub-tile: 1 (HL <= 32) or 2
+  int SW;            // output pixels per sub-tile (MMA N): 32 (16 only through the tuning hook)
+  int nks;           // k-steps (16 source pixels) per sub-tile: (SW + HL) / 16
+  int nkb;           // 64-element K blocks per sub-tile: ceil((SW + HL) / 64)
   int nseg, ntiles, ncb;
-  int NS, NG, NB;    // feature stages, gradient-tile stages, band buffers
+  int NS, NG, NB, NO;   // feature stages, gradient-tile stages, band buffers, staging tiles per epilogue warp (1, 2 or 4)
   int stage_bytes, g_bytes, g_pitch, band_bytes;   // g_bytes: bytes of one gradient box, g_pitch: its 128-byte aligned slot
   int sides;         // bit 0: gL wanted, bit 1: gR wanted
 };
@@ -67,8 +69,8 @@ corr_volume_bwd_tc_kernel(const __grid_constant__ CUtensorMap mapL, const __grid
   using namespace sftc;
   extern __shared__ __align__(1024) unsigned char smem[];
   unsigned char* sBand = smem;                                     // [NB][4 sub-tiles][hi | mid][nkb][32 rows][128 B]
-  unsigned char* sOut = sBand + p.NB * p.band_bytes;               // [4 warps][2][32 ch][128 B]
-  unsigned char* sG = sOut + BT_OUT_BYTES;                         // [NG][D][Kg] fp32
+  unsigned char* sOut = sBand + p.NB * p.band_bytes;               // [4 warps][NO][32 ch][128 B]
+  unsigned char* sG = sOut + 4 * p.NO * BT_OUT_TILE;                         // [NG][D][Kg] fp32
   unsigned char* sStage = sG + p.NG * p.g_pitch;                   // [NS][32 ch][P] fp32
   uint64_t* bars = reinterpret_cast<uint64_t*>(sStage + p.NS * p.stage_bytes);
   uint64_t* stg_full = bars;                    // [NS] TMA -> converters
@@ -113,30 +115,45 @@ corr_volume_bwd_tc_kernel(const __grid_constant__ CUtensorMap mapL, const __grid
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
 
+  // work units: (row tile, block of 128 channels); a CTA takes a CONTIGUOUS range of units of its side, so the channel
+  // blocks of one row tile mostly share the gradient tile and its band matrix (rebuilt only when the tile changes)
+  const int nunits = p.ntiles * p.ncb;
+  const int ub = static_cast<int>(static_cast<long long>(t0) * nunits / tstep);
+  const int ue = static_cast<int>(static_cast<long long>(t0 + 1) * nunits / tstep);
   if (warp == 0) {
     // ================================================================= TMA producer
     if (lane == 0) {
       const CUtensorMap* mapF = side ? &mapL : &mapR;
-      int s = 0, ph = 1, it = 0;
-      for (int tile = t0; tile < p.ntiles; tile += tstep, ++it) {
+      // The gradient tiles are a second, independent stream: they are issued whenever their slot is free and never block
+      // the feature ring (with one slot the next tile can only be fetched after the band warps have consumed the last).
+      int gi = 0, gu = ub;
+      auto pump_g = [&]() {
+        if (gu >= ue) return;
+        const int gs = gi % p.NG;
+        if (!mbar_try_wait(&g_empty[gs], ((gi / p.NG) & 1) ^ 1)) return;
+        const int tile = gu / p.ncb;
+        const int seg = tile % p.nseg, t2 = tile / p.nseg;
+        mbar_expect_tx(&g_full[gs], p.g_bytes);
+        tma_load_3d(sG + gs * p.g_pitch, &mapG, &g_full[gs], seg * 128, t2 % p.H, (t2 / p.H) * p.D);
+        ++gi;
+        gu = (tile + 1) * p.ncb;                     // first unit of the next row tile
+      };
+      int s = 0, ph = 1;
+      for (int u = ub; u < ue; ++u) {
+        const int tile = u / p.ncb, cb = u - tile * p.ncb;
         const int seg = tile % p.nseg, t2 = tile / p.nseg;
         const int y = t2 % p.H, bg = t2 / p.H;
-        const int x0 = seg * 128;
-        const int gs = it % p.NG;
-        mbar_wait(&g_empty[gs], ((it / p.NG) & 1) ^ 1);
-        mbar_expect_tx(&g_full[gs], p.g_bytes);
-        tma_load_3d(sG + gs * p.g_pitch, &mapG, &g_full[gs], x0, y, bg * p.D);
-        const int xf = side ? x0 : x0 - p.HL;
-        for (int cb = 0; cb < p.ncb; ++cb) {
-          const int nq = min(4, (p.Cg - cb * 128) >> 5);
-          for (int q = 0; q < nq; ++q) {
-            mbar_wait(&stg_empty[s], ph);
-            mbar_expect_tx(&stg_full[s], p.stage_bytes);
-            tma_load_3d(sStage + s * p.stage_bytes, mapF, &stg_full[s], xf, y, bg * p.Cg + cb * 128 + 32 * q);
-            if (++s == p.NS) { s = 0; ph ^= 1; }
-          }
+        const int xf = side ? seg * 128 : seg * 128 - p.HL;
+        const int nq = min(4, (p.Cg - cb * 128) >> 5);
+        pump_g();
+        for (int q = 0; q < nq; ++q) {
+          while (!mbar_try_wait(&stg_empty[s], ph)) pump_g();
+          mbar_expect_tx(&stg_full[s], p.stage_bytes);
+          tma_load_3d(sStage + s * p.stage_bytes, mapF, &stg_full[s], xf, y, bg * p.Cg + cb * 128 + 32 * q);
+          if (++s == p.NS) { s = 0; ph ^= 1; }
         }
       }
+      while (gu < ue) pump_g();
     }
   } else if (warp < BT_WARP_BAND) {
     // ================================================================= converters: feature rows -> tensor memory (A)
@@ -145,64 +162,67 @@ corr_volume_bwd_tc_kernel(const __grid_constant__ CUtensorMap mapL, const __grid
     const int st0 = kh ? (nst + 1) >> 1 : 0, st1 = kh ? nst : (nst + 1) >> 1;
     const uint32_t lane_base = static_cast<uint32_t>(32 * q) << 16;
     const int half = p.Kg >> 1;
-    int s = 0, ph = 0, si = 0;
-    for (int tile = t0; tile < p.ntiles; tile += tstep) {
-      for (int cb = 0; cb < p.ncb; ++cb, ++si) {
-        const int nq = min(4, (p.Cg - cb * 128) >> 5);
-        const int ab = si & 1;
-        mbar_wait(&a_empty[ab], ((si >> 1) & 1) ^ 1);
-        tc_fence_after();
-        const uint32_t ta = tmem + BT_A_BASE + ab * p.Kg + lane_base;
-        for (int qq = 0; qq < nq; ++qq) {
-          if (qq == q) {
-            mbar_wait(&stg_full[s], ph);
-            const float4* row = reinterpret_cast<const float4*>(sStage + s * p.stage_bytes) + lane * (p.P >> 2);
-            for (int st = st0; st < st1; ++st) {
-              uint32_t hi[8], mid[8];
+    int s = 0, ph = 0, it = 0;
+    for (int u = ub; u < ue; ++u, ++it) {
+      const int cb = u % p.ncb;
+      const int nq = min(4, (p.Cg - cb * 128) >> 5);
+      const int ab = it & 1;
+      mbar_wait(&a_empty[ab], ((it >> 1) & 1) ^ 1);
+      tc_fence_after();
+      const uint32_t ta = tmem + BT_A_BASE + ab * p.Kg + lane_base;
+      // every converter warp waits for EVERY stage of the unit in ring order, also those of the other quarters: a
+      // parity wait is only meaningful for a waiter that has seen the previous phase of that slot complete, and slots
+      // move between quarters whenever the ring depth is not a multiple of the quarters per unit
+      for (int qq = 0; qq < nq; ++qq) {
+        mbar_wait(&stg_full[s], ph);
+        if (qq == q) {
+          const float4* row = reinterpret_cast<const float4*>(sStage + s * p.stage_bytes) + lane * (p.P >> 2);
+          for (int st = st0; st < st1; ++st) {
+            uint32_t hi[8], mid[8];
 #pragma unroll
-              for (int i = 0; i < 4; ++i) {
-                const float4 v = row[4 * st + i];
-                const __nv_bfloat162 h0 = __floats2bfloat162_rn(v.x, v.y), h1 = __floats2bfloat162_rn(v.z, v.w);
-                const __nv_bfloat162 m0 = __floats2bfloat162_rn(v.x - __low2float(h0), v.y - __high2float(h0));
-                const __nv_bfloat162 m1 = __floats2bfloat162_rn(v.z - __low2float(h1), v.w - __high2float(h1));
-                hi[2 * i] = *reinterpret_cast<const uint32_t*>(&h0);
-                hi[2 * i + 1] = *reinterpret_cast<const uint32_t*>(&h1);
-                mid[2 * i] = *reinterpret_cast<const uint32_t*>(&m0);
-                mid[2 * i + 1] = *reinterpret_cast<const uint32_t*>(&m1);
-              }
-              tmem_st8(ta + 8 * st, hi);
-              tmem_st8(ta + half + 8 * st, mid);
+            for (int i = 0; i < 4; ++i) {
+              const float4 v = row[4 * st + i];
+              const __nv_bfloat162 h0 = __floats2bfloat162_rn(v.x, v.y), h1 = __floats2bfloat162_rn(v.z, v.w);
+              const __nv_bfloat162 m0 = __floats2bfloat162_rn(v.x - __low2float(h0), v.y - __high2float(h0));
+              const __nv_bfloat162 m1 = __floats2bfloat162_rn(v.z - __low2float(h1), v.w - __high2float(h1));
+              hi[2 * i] = *reinterpret_cast<const uint32_t*>(&h0);
+              hi[2 * i + 1] = *reinterpret_cast<const uint32_t*>(&h1);
+              mid[2 * i] = *reinterpret_cast<const uint32_t*>(&m0);
+              mid[2 * i + 1] = *reinterpret_cast<const uint32_t*>(&m1);
             }
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&stg_empty[s]);
+            tmem_st8(ta + 8 * st, hi);
+            tmem_st8(ta + half + 8 * st, mid);
           }
-          if (++s == p.NS) { s = 0; ph ^= 1; }
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&stg_empty[s]);
         }
-        tmem_st_wait();
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&a_full[ab]);
+        if (++s == p.NS) { s = 0; ph ^= 1; }
       }
+      tmem_st_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&a_full[ab]);
     }
   } else if (warp < BT_WARP_MMA) {
     // ================================================================= band warps: G tile -> band matrix (B operand)
-    const int j = warp - BT_WARP_BAND;                  // sub-tile
-    const int n = 32 * j + lane;                        // output pixel within the tile
-    const int half_off = p.nkb * 4096;
+    const int n = 32 * (warp - BT_WARP_BAND) + lane;    // output pixel within the tile
+    const int sub = n / p.SW, nl = n - sub * p.SW;      // sub-tile and row within it
+    const int kb_bytes = p.SW * 128;                    // one 64-element K block of a sub-tile half
+    const int half_off = p.nkb * kb_bytes;
+    const int sw = nl & 7;
     int it = 0;
-    for (int tile = t0; tile < p.ntiles; tile += tstep, ++it) {
+    for (int u = ub; u < ue; u = (u / p.ncb + 1) * p.ncb, ++it) {      // one pass per row tile of the range
       const int gs = it % p.NG, bb = it % p.NB;
       mbar_wait(&g_full[gs], (it / p.NG) & 1);
       mbar_wait(&band_empty[bb], ((it / p.NB) & 1) ^ 1);
       const float* g = reinterpret_cast<const float*>(sG + gs * p.g_pitch);
-      unsigned char* base = sBand + bb * p.band_bytes + j * 2 * half_off + lane * 128;
-      const int sw = lane & 7;
+      unsigned char* base = sBand + bb * p.band_bytes + sub * 2 * half_off + nl * 128;
       for (int d = 0; d < p.D; ++d) {
         const float v = side ? g[d * p.Kg + n + d] : g[d * p.Kg + n];
-        const int kl = side ? lane + d : lane + p.HL - d;
+        const int kl = side ? nl + d : nl + p.HL - d;
         const __nv_bfloat16 h = __float2bfloat16_rn(v);
         const __nv_bfloat16 m = __float2bfloat16_rn(v - __bfloat162float(h));
-        const int off = (kl >> 6) * 4096 + ((((kl & 63) >> 3) ^ sw) << 4) + (kl & 7) * 2;
+        const int off = (kl >> 6) * kb_bytes + ((((kl & 63) >> 3) ^ sw) << 4) + (kl & 7) * 2;
         *reinterpret_cast<__nv_bfloat16*>(base + off) = h;
         *reinterpret_cast<__nv_bfloat16*>(base + half_off + off) = m;
       }
@@ -213,38 +233,46 @@ corr_volume_bwd_tc_kernel(const __grid_constant__ CUtensorMap mapL, const __grid
   } else if (warp == BT_WARP_MMA) {
     // ================================================================= MMA issuer
     if (lane == 0) {
-      const uint32_t idesc = make_idesc_bf16(128, 32, 0, 0);        // A: TMEM (K-major), B: K-major shared memory
-      const int half_off = p.nkb * 4096, halfA = p.Kg >> 1;
-      int it = 0, si = 0;
-      for (int tile = t0; tile < p.ntiles; tile += tstep, ++it) {
-        const int bb = it % p.NB;
-        mbar_wait(&band_full[bb], (it / p.NB) & 1);
+      const uint32_t idesc = make_idesc_bf16(128, p.SW, 0, 0);      // A: TMEM (K-major), B: K-major shared memory
+      const int kb_bytes = p.SW * 128, half_off = p.nkb * kb_bytes, halfA = p.Kg >> 1;
+      const int nsub_half = 64 / p.SW;
+      int it = 0, ib = -1;
+      for (int u = ub; u < ue; ++u, ++it) {
+        const int cb = u % p.ncb;
+        if (u == ub || cb == 0) {                     // a new row tile: its band matrix
+          ++ib;
+          mbar_wait(&band_full[ib % p.NB], (ib / p.NB) & 1);
+        }
+        const int bb = ib % p.NB, ab = it & 1;
+        mbar_wait(&a_full[ab], (it >> 1) & 1);
         const uint32_t band = smem_u32(sBand + bb * p.band_bytes);
-        for (int cb = 0; cb < p.ncb; ++cb, ++si) {
-          const int ab = si & 1;
-          mbar_wait(&a_full[ab], (si >> 1) & 1);
-          const uint32_t a_hi = tmem + BT_A_BASE + ab * p.Kg, a_mid = a_hi + halfA;
-          // the accumulator is handed over in two 64-pixel halves: the epilogue drains half 0 while half 1 is computed
-          for (int h = 0; h < 2; ++h) {
-            mbar_wait(&d_empty[h], (si & 1) ^ 1);
-            tc_fence_after();
-            for (int j = 2 * h; j < 2 * h + 2; ++j) {
-              const uint32_t bj = band + j * 2 * half_off;
-              for (int s = 0; s < p.nks; ++s) {
-                const uint32_t boff = (s >> 2) * 4096 + (s & 3) * 32;
-                const uint64_t dbh = make_smem_desc(bj + boff, 16, 1024);
-                const uint64_t dbm = make_smem_desc(bj + half_off + boff, 16, 1024);
-                const uint32_t ac = 16 * j + 8 * s;
-                umma_bf16_ts(tmem + 32 * j, a_hi + ac, dbh, idesc, s != 0);
-                umma_bf16_ts(tmem + 32 * j, a_hi + ac, dbm, idesc, true);
-                umma_bf16_ts(tmem + 32 * j, a_mid + ac, dbh, idesc, true);
+        const uint32_t a_hi = tmem + BT_A_BASE + ab * p.Kg, a_mid = a_hi + halfA;
+        // the accumulator is handed over in two 64-pixel halves: the epilogue drains half 0 while half 1 is computed
+        for (int h = 0; h < 2; ++h) {
+          mbar_wait(&d_empty[h], (it & 1) ^ 1);
+          tc_fence_after();
+          for (int j = h * nsub_half; j < (h + 1) * nsub_half; ++j) {
+            // straight-line issue: descriptors are built once per sub-tile and advanced by adding to their address
+            // field (an issue loop with inner loops over the three products cost 28 us per launch: this thread's
+            // instruction stream feeds every MMA of the SM)
+            const uint64_t dbh0 = make_smem_desc(band + j * 2 * half_off, 16, 1024);
+            const uint64_t dbm0 = make_smem_desc(band + j * 2 * half_off + half_off, 16, 1024);
+            const uint32_t d_col = tmem + p.SW * j;
+            const uint32_t ah = a_hi + (p.SW >> 1) * j, am = a_mid + (p.SW >> 1) * j;
+#pragma unroll
+            for (int s = 0; s < 6; ++s) {
+              if (s < p.nks) {
+                const uint32_t step = static_cast<uint32_t>((s >> 2) * (kb_bytes >> 4) + (s & 3) * 2);
+                umma_bf16_ts(d_col, ah + 8 * s, dbh0 + step, idesc, s != 0);
+                umma_bf16_ts(d_col, ah + 8 * s, dbm0 + step, idesc, true);
+                umma_bf16_ts(d_col, am + 8 * s, dbh0 + step, idesc, true);
               }
             }
-            umma_commit(&d_full[h]);
           }
-          umma_commit(&a_empty[ab]);
+          umma_commit(&d_full[h]);
         }
-        umma_commit(&band_empty[bb]);
+        umma_commit(&a_empty[ab]);
+        if (u == ue - 1 || cb == p.ncb - 1) umma_commit(&band_empty[bb]);
       }
     }
   } else {
@@ -252,49 +280,53 @@ corr_volume_bwd_tc_kernel(const __grid_constant__ CUtensorMap mapL, const __grid
     const int q = warp & 3;
     const uint32_t trow = tmem + (static_cast<uint32_t>(32 * q) << 16);
     const CUtensorMap* mapO = side ? &mapGR : &mapGL;
-    unsigned char* stage = sOut + (warp - BT_WARP_EPI) * 2 * 4096;
+    unsigned char* stage = sOut + (warp - BT_WARP_EPI) * p.NO * BT_OUT_TILE;
     const float inv = 1.0f / static_cast<float>(p.Cg);
     const int sw = lane & 7;
-    int si = 0, nst = 0;
-    for (int tile = t0; tile < p.ntiles; tile += tstep) {
+    int it = 0, nst = 0;
+    for (int u = ub; u < ue; ++u, ++it) {
+      const int tile = u / p.ncb, cb = u - tile * p.ncb;
       const int seg = tile % p.nseg, t2 = tile / p.nseg;
       const int y = t2 % p.H, bg = t2 / p.H;
       const int x0 = seg * 128;
-      for (int cb = 0; cb < p.ncb; ++cb, ++si) {
-        const bool valid = cb * 128 + 32 * q < p.Cg;
-        for (int h = 0; h < 2; ++h) {
-          mbar_wait(&d_full[h], si & 1);
-          tc_fence_after();
-          uint32_t raw[2][32];
-          tmem_ld32(trow + 64 * h, raw[0]);
-          tmem_ld32(trow + 64 * h + 32, raw[1]);
-          tmem_ld_wait();
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(&d_empty[h]);          // the half is in registers: the next MMAs may overwrite it
+      const bool valid = cb * 128 + 32 * q < p.Cg;
+#pragma unroll 1
+      for (int h = 0; h < 2; ++h) {
+        mbar_wait(&d_full[h], it & 1);
+        tc_fence_after();
+        uint32_t raw[2][32];
+        tmem_ld32(trow + 64 * h, raw[0]);
+        tmem_ld32(trow + 64 * h + 32, raw[1]);
+        tmem_ld_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&d_empty[h]);          // the half is in registers: the next MMAs may overwrite it
 #pragma unroll
-          for (int e = 0; e < 2; ++e) {
-            const int xb = x0 + 64 * h + 32 * e;
-            if (valid && xb < p.W) {
-              unsigned char* buf = stage + (nst & 1) * 4096;
-              if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
-              __syncwarp();
-              unsigned char* rowp = buf + lane * 128;
-#pragma unroll
-              for (int c = 0; c < 8; ++c) {
-                float4 v;
-                v.x = __uint_as_float(raw[e][4 * c]) * inv; v.y = __uint_as_float(raw[e][4 * c + 1]) * inv;
-                v.z = __uint_as_float(raw[e][4 * c + 2]) * inv; v.w = __uint_as_float(raw[e][4 * c + 3]) * inv;
-                *reinterpret_cast<float4*>(rowp + ((c ^ sw) << 4)) = v;
-              }
-              fence_proxy_async_smem();
-              __syncwarp();
-              if (lane == 0) {
-                bt_tma_store_3d(mapO, buf, xb, y, bg * p.Cg + cb * 128 + 32 * q);
-                asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-              }
-              ++nst;
+        for (int e = 0; e < 2; ++e) {
+          const int xb = x0 + 64 * h + 32 * e;
+          if (valid && xb < p.W) {
+            unsigned char* buf = stage + (nst & (p.NO - 1)) * BT_OUT_TILE;
+            if (lane == 0) {                                // the store issued NO tiles ago has left this tile
+              if (p.NO == 4) asm volatile("cp.async.bulk.wait_group.read 3;" ::: "memory");
+              else if (p.NO == 2) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+              else asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
             }
+            __syncwarp();
+            unsigned char* rowp = buf + lane * 128;
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+              float4 v;
+              v.x = __uint_as_float(raw[e][4 * c]) * inv; v.y = __uint_as_float(raw[e][4 * c + 1]) * inv;
+              v.z = __uint_as_float(raw[e][4 * c + 2]) * inv; v.w = __uint_as_float(raw[e][4 * c + 3]) * inv;
+              *reinterpret_cast<float4*>(rowp + ((c ^ sw) << 4)) = v;
+            }
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) {
+              bt_tma_store_3d(mapO, buf, xb, y, bg * p.Cg + cb * 128 + 32 * q);
+              asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            }
+            ++nst;
           }
         }
       }
@@ -311,28 +343,40 @@ static bool corr_bwd_tc_plan(CorrBwdTcParams& p, int nBG, int Cg, int H, int W, 
   if (Cg % 32 != 0 || W % 4 != 0 || D < 1 || D > 65) return false;
   if (1LL * nBG * Cg >= (1LL << 31) || 1LL * nBG * D >= (1LL << 31)) return false;
   p.HL = max(16, ceil_div(D - 1, 16) * 16);
+  if (const char* e = tuning_env("SF_BT_HL")) p.HL = max(p.HL, atoi(e));          // tuning build only (A/B of the plan)
   p.Kg = 128 + p.HL;
   p.P = p.Kg + 4;
-  p.nks = (32 + p.HL) / 16;
-  p.nkb = ceil_div(32 + p.HL, 64);
+  p.SW = 32;        // 16-pixel sub-tiles keep a 48-wide halo within one K block but double the MMA count: measured slower
+  if (const char* e = tuning_env("SF_BT_SW")) p.SW = atoi(e);
+  p.nks = (p.SW + p.HL) / 16;
+  p.nkb = ceil_div(p.SW + p.HL, 64);
   p.nseg = ceil_div(W, 128);
   p.ncb = ceil_div(Cg, 128);
   const long long nt = 1LL * nBG * H * p.nseg;
-  if (nt >= (1LL << 30)) return false;
+  if (nt * p.ncb >= (1LL << 30)) return false;
   p.ntiles = static_cast<int>(nt);
   p.stage_bytes = 32 * p.P * 4;
   p.g_bytes = D * p.Kg * 4;
   p.g_pitch = ceil_div(p.g_bytes, 128) * 128;
-  p.band_bytes = 4 * 2 * p.nkb * 4096;
-  const int budget = 232448 - 1024 - BT_OUT_BYTES - 512;
-  for (int cfg = 0; cfg < 3; ++cfg) {                 // prefer double-buffered bands and gradient tiles
-    p.NB = cfg < 2 ? 2 : 1;
-    p.NG = cfg < 1 ? 2 : 1;
-    const int rest = budget - p.NB * p.band_bytes - p.NG * p.g_pitch;
-    p.NS = rest > 0 ? min(BT_MAXNS, rest / p.stage_bytes) : 0;
-    if (p.NS >= 4) return true;
+  p.band_bytes = (128 / p.SW) * 2 * p.nkb * p.SW * 128;
+  p.NO = 2;
+  if (const char* e = tuning_env("SF_BT_NO")) p.NO = atoi(e);
+  const int budget = 232448 - 1024 - 4 * p.NO * BT_OUT_TILE - 512;
+  // double-buffered bands first (they keep the MMAs of one tile off the build of the next); the gradient tile gets a
+  // second slot only if the feature ring still holds two units (8 stages): ring depth is what hides the load latency
+  int best = -1;
+  for (int cfg = 0; cfg < 4; ++cfg) {
+    const int NB = cfg < 2 ? 2 : 1, NG = (cfg & 1) ? 1 : 2;
+    const int rest = budget - NB * p.band_bytes - NG * p.g_pitch;
+    const int NS = rest > 0 ? min(BT_MAXNS, rest / p.stage_bytes) : 0;
+    const int score = (NS >= 4 ? 1000 : 0) + (NB == 2 ? 100 : 0) + 10 * NS + NG;
+    if (NS >= 2 && score > best) { best = score; p.NB = NB; p.NG = NG; p.NS = NS; }
   }
-  return p.NS >= 2;
+  if (best < 0) return false;
+  if (const char* e = tuning_env("SF_BT_NG")) p.NG = atoi(e);
+  if (const char* e = tuning_env("SF_BT_NB")) p.NB = atoi(e);
+  if (const char* e = tuning_env("SF_BT_NS")) p.NS = min(p.NS, atoi(e));
+  return true;
 }
 
 bool corr_bwd_tc_supported(const float* L, const float* R, const float* G, const float* gL, const float* gR, int nBG,
@@ -361,11 +405,11 @@ int launch_corr_bwd_tc(const float* L, const float* R, const float* G, float* gL
   if (rc) return rc;
   rc = make_tmap_3d_f32_swz(&mGR, gR ? gR : gL, W, H, rows, 32, 1, 32, 128);
   if (rc) return rc;
-  const size_t smem = static_cast<size_t>(p.NB) * p.band_bytes + BT_OUT_BYTES + static_cast<size_t>(p.NG) * p.g_pitch +
+  const size_t smem = static_cast<size_t>(p.NB) * p.band_bytes + 4 * p.NO * BT_OUT_TILE + static_cast<size_t>(p.NG) * p.g_pitch +
                       static_cast<size_t>(p.NS) * p.stage_bytes + 512;
   int grid;
-  if (sides == 3) grid = min(2 * p.ntiles, sm_count() & ~1);
-  else grid = min(p.ntiles, sm_count());
+  if (sides == 3) grid = min(2 * p.ntiles * p.ncb, sm_count() & ~1);
+  else grid = min(p.ntiles * p.ncb, sm_count());
   SF_CUDA(cudaFuncSetAttribute(corr_volume_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                static_cast<int>(smem)));
   corr_volume_bwd_tc_kernel<<<grid, BT_THREADS, smem, stream>>>(mL, mR, mG, mGL, mGR, p);
