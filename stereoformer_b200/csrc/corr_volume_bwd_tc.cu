@@ -359,22 +359,21 @@ static bool corr_bwd_tc_plan(CorrBwdTcParams& p, int nBG, int Cg, int H, int W, 
   p.g_bytes = D * p.Kg * 4;
   p.g_pitch = ceil_div(p.g_bytes, 128) * 128;
   p.band_bytes = (128 / p.SW) * 2 * p.nkb * p.SW * 128;
-  p.NO = 2;
-  if (const char* e = tuning_env("SF_BT_NO")) p.NO = atoi(e);
-  const int budget = 232448 - 1024 - 4 * p.NO * BT_OUT_TILE - 512;
-  // double-buffered bands first (they keep the MMAs of one tile off the build of the next); the gradient tile gets a
-  // second slot only if the feature ring still holds two units (8 stages): ring depth is what hides the load latency
+  // double-buffered bands first (they keep the MMAs of one tile off the build of the next); a second gradient-tile slot
+  // and a second staging tile per epilogue warp only where they do not cost a feature stage: ring depth is what hides
+  // the load latency (measured at the bench shape: 2 / 3 / 4 / 5 stages = 75.6 / 64.6 / 56.5 / 53.1 us)
   int best = -1;
-  for (int cfg = 0; cfg < 4; ++cfg) {
-    const int NB = cfg < 2 ? 2 : 1, NG = (cfg & 1) ? 1 : 2;
-    const int rest = budget - NB * p.band_bytes - NG * p.g_pitch;
+  for (int cfg = 0; cfg < 8; ++cfg) {
+    const int NB = (cfg & 4) ? 1 : 2, NG = (cfg & 1) ? 1 : 2, NO = (cfg & 2) ? 1 : 2;
+    const int rest = 232448 - 1024 - 512 - 4 * NO * BT_OUT_TILE - NB * p.band_bytes - NG * p.g_pitch;
     const int NS = rest > 0 ? min(BT_MAXNS, rest / p.stage_bytes) : 0;
-    const int score = (NS >= 4 ? 1000 : 0) + (NB == 2 ? 100 : 0) + 10 * NS + NG;
-    if (NS >= 2 && score > best) { best = score; p.NB = NB; p.NG = NG; p.NS = NS; }
+    const int score = (NS >= 4 ? 1000 : 0) + (NB == 2 ? 100 : 0) + 10 * min(NS, 5) + 2 * NO + NG;   // > 5 stages buy nothing
+    if (NS >= 2 && score > best) { best = score; p.NB = NB; p.NG = NG; p.NO = NO; p.NS = NS; }
   }
   if (best < 0) return false;
   if (const char* e = tuning_env("SF_BT_NG")) p.NG = atoi(e);
   if (const char* e = tuning_env("SF_BT_NB")) p.NB = atoi(e);
+  if (const char* e = tuning_env("SF_BT_NO")) p.NO = atoi(e);
   if (const char* e = tuning_env("SF_BT_NS")) p.NS = min(p.NS, atoi(e));
   return true;
 }

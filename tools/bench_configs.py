@@ -125,6 +125,38 @@ def c1_lcv_small(dev, pk):
     return _hbm(e, pk)
 
 
+# ------------------------------------------------------------------------------------------------ C2 backward (f3)
+def c2_cv_backward(dev, pk):
+    """SURVEY 8f-3 at the bench shape: gradient of the correlation cost volume w.r.t. both feature maps (what autograd
+    derives for build_cost_volume.py:39-47), tcgen05 band product vs the fp32 FFMA kernel; parity against autograd
+    through the UNMODIFIED reference module on the same GPU (one pair) when the reference copy travelled."""
+    from stereoformer_b200 import ops
+    B, C, H, W, D = 8, 256, 68, 120, 24
+    g = torch.Generator(device="cpu").manual_seed(9)
+    sets = [tuple(torch.randn(*shp, generator=g).to(dev) for shp in ((B, C, H, W), (B, C, H, W), (B, D, H, W)))
+            for _ in range(3)]
+    us = graph_us(lambda i=0: ops.corr_volume_backward(*sets[i % 3], D, algo=ops.SF_ALGO_TC))
+    us_ffma = graph_us(lambda i=0: ops.corr_volume_backward(*sets[i % 3], D, algo=ops.SF_ALGO_GENERIC), min_ms=15.0)
+    gl, gr = ops.corr_volume_backward(*sets[0], D, algo=ops.SF_ALGO_TC)
+    el, er = ops.corr_volume_backward(*sets[0], D, algo=ops.SF_ALGO_GENERIC)
+    e = {"shape": [B, C, H, W, D], "us": us, "exact_ffma_us": us_ffma, "alg_bytes": (4 * C + D) * B * H * W * 4,
+         "parity_max_err": max(_relerr(gl, el), _relerr(gr, er)),
+         "parity_unit": "relative to max |grad| vs the fp32 FFMA kernel (all 8 pairs)"}
+    try:
+        from oracle import refenv
+        if refenv.activate(dcn=None) is not None:
+            import importlib
+            cvm = importlib.import_module("models.utils.build_cost_volume").CostVolume(D, "correlation")
+            l, r = sets[0][0][:1].clone().requires_grad_(True), sets[0][1][:1].clone().requires_grad_(True)
+            rl, rr = torch.autograd.grad(cvm(l, r), [l, r], sets[0][2][:1])
+            e["parity_vs_reference_autograd"] = max(_relerr(gl[:1], rl), _relerr(gr[:1], rr))
+            e["reference_fwd_plus_bwd_us_8_pairs_eager"] = 8 * eager_us(
+                lambda: torch.autograd.grad(cvm(l, r), [l, r], sets[0][2][:1]), min_ms=10.0)
+    except Exception as ex:          # noqa: BLE001
+        e["reference_error"] = str(ex)[:200]
+    return _hbm(e, pk)
+
+
 # ------------------------------------------------------------------------------------------------ C3 (RAFT-Stereo)
 def c3_corr1d(dev, pk):
     """BASELINE configs[2], CorrBlock1D reading: all-pairs pyramid at (4,256,136,240) + one radius-4 lookup."""
@@ -382,7 +414,7 @@ def c5_bands(dev, pk, world, rank, root_only=True, steps=40):
 def run_single_gpu(dev, want=None):
     """All one-GPU entries; a failing entry is reported, not fatal (the headline must still print)."""
     pk = peaks()
-    table = [("c1", c1_lcv_small), ("c3_corr1d", c3_corr1d), ("c3_dlc_gru", c3_dlc_gru), ("c4_attn", c4_attn),
+    table = [("c1", c1_lcv_small), ("c2_cv_backward", c2_cv_backward), ("c3_corr1d", c3_corr1d), ("c3_dlc_gru", c3_dlc_gru), ("c4_attn", c4_attn),
              ("dcn", dcn_shapes), ("full_model_lc", lambda d, p: full_model(d, p, "lc")),
              ("full_model_dlc_gru", lambda d, p: full_model(d, p, "dlc_gru", batch=2))]
     out = {}
