@@ -10,7 +10,8 @@
 //   * S lives in TMEM columns [0,192), O in [256,256+C).  The soft-max warps read S with tcgen05.ld (thread = query
 //     row), write un-normalised bf16 P rows into the canonical K-major SW128 layout and keep 1/sum in a register;
 //     the epilogue scales O rows and writes bf16.
-// Warp roles: warp 0 TMA producer, warp 1 MMA issuer (+TMEM allocation), warps 2-5 soft-max / epilogue.
+// Warp roles: warp 0 TMA producer, warp 1 MMA issuer (+TMEM allocation), warps 2-9 soft-max, warp 10 TMA store of the
+// output tile, warps 11-14 epilogue (O rows x 1/sum -> bf16): the epilogue of tile t runs beside the soft-max of tile t+1.
 // Algorithmic bytes: 4*C*2 per pixel (Q, K, V read once, O written once).
 #include <cuda_bf16.h>
 
@@ -29,9 +30,10 @@ __device__ __forceinline__ float ex2_approx(float x) {
 
 constexpr int AT_BOX = 8192;            // one TMA box: 64 rows x 128 B
 constexpr int AT_STAGE = 5 * AT_BOX;    // Q chunk (2 boxes) + K chunk (3 boxes) of 64 channels
-constexpr int AT_NSTAGE = 2;
+constexpr int AT_MAXSTAGE = 4;          // Q/K ring depth limit (barrier slots)
 constexpr int AT_PBYTES = 3 * 16384;    // P: 3 key blocks x [128 rows][128 B]
-constexpr int AT_THREADS = 352;         // TMA warp, MMA warp, 8 soft-max/epilogue warps (two per TMEM lane quarter), TMA-store warp
+constexpr int AT_THREADS = 480;         // TMA warp, MMA warp, 8 soft-max warps (two per TMEM lane quarter), TMA-store warp, 4 epilogue warps
+constexpr int AT_WARP_EPI = 11;         // epilogue warps 11..14 (warp & 3 = TMEM lane quarter)
 
 struct AttnParams {
   __nv_bfloat16* out;
@@ -40,7 +42,8 @@ struct AttnParams {
   int ntiles;
   float scale_log2;  // log2(e) / sqrt(C)
   int nS, nO;        // S and O accumulators in TMEM (192 and C columns each)
-  int defer;         // epilogue of tile t - 1 after the soft-max of tile t (needs nO == 2)
+  int nstage;        // Q/K ring depth (2..4): as many 64-channel stages as shared memory holds
+  int nsum;          // slots of the per-row soft-max sums handed to the epilogue warps (4, or 1 where shared memory is full)
   int o_col;         // TMEM column of the O accumulator
   int tma_out;       // epilogue through a shared-memory tile + TMA store (C <= 128)
   int dbg;           // tuning only: 1 skip soft-max/epilogue arithmetic, 2 skip the MMAs, 4 skip V loads' consumers
@@ -58,32 +61,34 @@ epipolar_attn_tc_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
   using namespace sftc;
   extern __shared__ __align__(1024) unsigned char smem[];
   const int NC = p.C / 64;                       // 64-channel chunks
-  unsigned char* sStage = smem;                  // [AT_NSTAGE][AT_STAGE]
-  unsigned char* sV = sStage + AT_NSTAGE * AT_STAGE;   // [3 key blocks][NC][64 rows][128 B]
+  unsigned char* sStage = smem;                  // [nstage][AT_STAGE]
+  unsigned char* sV = sStage + p.nstage * AT_STAGE;   // [3 key blocks][NC][64 rows][128 B]
   unsigned char* sP = sV + 3 * NC * AT_BOX;      // [3][128][128 B]
   unsigned char* sO = sP + AT_PBYTES;            // [NC][2 query halves][64 ch][128 B] output tile (tma_out only)
   uint64_t* bars = reinterpret_cast<uint64_t*>(sO + (p.tma_out ? 2 * NC * AT_BOX : 0));
-  uint64_t* qk_full = bars;            // [2]
-  uint64_t* qk_empty = bars + 2;       // [2]
-  uint64_t* v_full = bars + 4;
-  uint64_t* v_empty = bars + 5;
-  uint64_t* s_full = bars + 6;         // [2]
-  uint64_t* s_empty = bars + 8;        // [2]
-  uint64_t* p_full = bars + 10;
-  uint64_t* o_full = bars + 11;        // [2]
-  uint64_t* o_empty = bars + 13;       // [2]
-  uint64_t* o_staged = bars + 15;      // output tile written to shared memory (256 arrivals)
-  uint64_t* so_free = bars + 16;       // output tile read by the TMA store
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 17);
-  float* sRed = reinterpret_cast<float*>(bars + 18);   // [2 halves][128 rows] row maxima, then the same for partial sums
+  uint64_t* qk_full = bars;            // [AT_MAXSTAGE]
+  uint64_t* qk_empty = bars + 4;       // [AT_MAXSTAGE]
+  uint64_t* v_full = bars + 8;
+  uint64_t* v_empty = bars + 9;
+  uint64_t* s_full = bars + 10;        // [2]
+  uint64_t* s_empty = bars + 12;       // [2]
+  uint64_t* p_full = bars + 14;
+  uint64_t* o_full = bars + 15;        // [2]
+  uint64_t* o_empty = bars + 17;       // [2]
+  uint64_t* o_staged = bars + 19;      // output tile written to shared memory (128 arrivals)
+  uint64_t* so_free = bars + 20;       // output tile read by the TMA store
+  uint64_t* sum_free = bars + 21;      // [4] epilogue threads have read the sums of the slot
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 25);
+  float* sRed = reinterpret_cast<float*>(bars + 26);   // row maxima [2 halves][128 rows], then partial sums [nsum slots][2 halves][128 rows]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
-    for (int s = 0; s < AT_NSTAGE; ++s) { mbar_init(&qk_full[s], 1); mbar_init(&qk_empty[s], 1); }
+    for (int s = 0; s < p.nstage; ++s) { mbar_init(&qk_full[s], 1); mbar_init(&qk_empty[s], 1); }
     mbar_init(v_full, 1); mbar_init(v_empty, 1); mbar_init(p_full, 256);
     for (int i = 0; i < 2; ++i) { mbar_init(&s_full[i], 1); mbar_init(&s_empty[i], 256); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&o_full[i], 1); mbar_init(&o_empty[i], 256); }
-    mbar_init(o_staged, 256); mbar_init(so_free, 1);
+    for (int i = 0; i < 2; ++i) { mbar_init(&o_full[i], 1); mbar_init(&o_empty[i], 128); }
+    mbar_init(o_staged, 128); mbar_init(so_free, 1);
+    for (int i = 0; i < 4; ++i) mbar_init(&sum_free[i], 128);
     fence_mbar_init();
     tma_prefetch_desc(&mapQ); tma_prefetch_desc(&mapK); tma_prefetch_desc(&mapV); tma_prefetch_desc(&mapO);
   }
@@ -102,8 +107,8 @@ epipolar_attn_tc_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
         const int y = r % p.H, b = r / p.H;
         const int q0 = qt * 128, k0 = q0 - 64;
         for (int cc = 0; cc < NC; ++cc) {
-          const int it = t * NC + cc, s = it % AT_NSTAGE;
-          mbar_wait(&qk_empty[s], ((it / AT_NSTAGE) & 1) ^ 1);
+          const int it = t * NC + cc, s = it % p.nstage;
+          mbar_wait(&qk_empty[s], ((it / p.nstage) & 1) ^ 1);
           at_mark(p, 0, nts);
           unsigned char* st = sStage + s * AT_STAGE;
           mbar_expect_tx(&qk_full[s], AT_STAGE);
@@ -134,8 +139,8 @@ epipolar_attn_tc_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
         if (qk_t < ntl) {
           const int sb = qk_t % p.nS;
           if (!s_ok) s_ok = mbar_test(&s_empty[sb], ((qk_t / p.nS) & 1) ^ 1);
-          const int s = it % AT_NSTAGE;
-          if (s_ok && mbar_test(&qk_full[s], (it / AT_NSTAGE) & 1)) {
+          const int s = it % p.nstage;
+          if (s_ok && mbar_test(&qk_full[s], (it / p.nstage) & 1)) {
             tc_fence_after();
             const uint32_t qa = smem_u32(sStage + s * AT_STAGE), ka = qa + 2 * AT_BOX;
             if (!(p.dbg & 2))
@@ -187,24 +192,18 @@ epipolar_attn_tc_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
       }
       asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
     }
-  } else {
-    // =========================================================== soft-max + epilogue
-    // 256 threads: a query row is shared by two threads (warps w and w + 4 of the same TMEM lane quarter) which take
-    // alternate 32-key chunks of the band and half of the output channels each; row maxima and sums are exchanged
-    // through shared memory.  The epilogue of tile t - 1 runs after the soft-max of tile t, so that P V of tile t and
-    // Q^T K of tile t + 1 execute underneath it and these warps never wait for the tensor core.
-    const int quarter = warp & 3, half = (warp - 2) >> 2;
+  } else if (warp >= AT_WARP_EPI) {
+    // =========================================================== epilogue: O rows from TMEM, normalise, bf16, store
+    // one thread per query row (all channels); the two partial soft-max sums of the row come through shared memory,
+    // published before the soft-max threads arrived on p_full (which the MMAs behind o_full have observed)
+    const int quarter = warp & 3;
     const int row = quarter * 32 + lane;
     const uint32_t trow = tmem + (static_cast<uint32_t>(quarter * 32) << 16);
     const size_t HW = static_cast<size_t>(p.H) * p.W;
-    float* sMax = sRed;          // [2 halves][128]
-    float* sSum = sRed + 256;    // [2 halves][128]
-    const int Ch = p.C >> 1;                               // channels of this half in the epilogue
-    int nts = 0;
-    const bool tsw = threadIdx.x == 64;
-
-    // epilogue of local tile te (global tile index etile): O rows from TMEM, normalise, bf16, store
-    auto epilogue = [&](int te, int etile, float mysum) {   // mysum: soft-max denominator of this row
+    const float* sSum = sRed + 256;
+    int te = 0, nts = 0;
+    const bool tsw = threadIdx.x == AT_WARP_EPI * 32;
+    for (int etile = blockIdx.x; etile < p.ntiles; etile += gridDim.x, ++te) {
       const int qt = etile % p.nqt, r = etile / p.nqt;
       const int y = r % p.H, b = r / p.H;
       const int q = qt * 128 + row;
@@ -212,12 +211,15 @@ epipolar_attn_tc_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
       mbar_wait(&o_full[ob], (te / p.nO) & 1);
       tc_fence_after();
       if (tsw) at_mark(p, 2, nts);
+      const int ss = te % p.nsum;
+      const float mysum = sSum[ss * 256 + row] + sSum[ss * 256 + 128 + row];
+      mbar_arrive(&sum_free[ss]);
       const float inv = (mysum > 0.f) ? 1.0f / mysum : 0.f;
       const uint32_t orow_t = trow + p.o_col + ob * p.C;
       if (p.tma_out) {
         // O rows -> [64 ch][64 q] bf16 boxes (SWIZZLE_128B, the layout of the input boxes) -> one TMA store per box
         mbar_wait(so_free, (te & 1) ^ 1);
-        for (int c0 = half * Ch; c0 < (half + 1) * Ch && !(p.dbg & 1); c0 += 32) {
+        for (int c0 = 0; c0 < p.C && !(p.dbg & 1); c0 += 32) {
           uint32_t v[32];
           tmem_ld32(orow_t + c0, v);
           tmem_ld_wait();
@@ -235,7 +237,7 @@ epipolar_attn_tc_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
         mbar_arrive(o_staged);
       } else {
         __nv_bfloat16* orow = p.out + (static_cast<size_t>(b) * p.C) * HW + static_cast<size_t>(y) * p.W + q;
-        for (int c0 = half * Ch; c0 < (half + 1) * Ch; c0 += 32) {
+        for (int c0 = 0; c0 < p.C; c0 += 32) {
           uint32_t v[32];
           tmem_ld32(orow_t + c0, v);
           tmem_ld_wait();
@@ -248,11 +250,22 @@ epipolar_attn_tc_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
         mbar_arrive(&o_empty[ob]);
       }
       if (tsw) at_mark(p, 2, nts);
-    };
-
-    int t = 0, prev_tile = 0;
-    float prev_sum = 0.f;
+    }
+  } else {
+    // =========================================================== soft-max
+    // 256 threads: a query row is shared by two threads (warps w and w + 4 of the same TMEM lane quarter) which take
+    // alternate 32-key chunks of the band; row maxima are exchanged through shared memory, the partial sums go to the
+    // epilogue warps the same way (slots handed back through sum_free).
+    const int quarter = warp & 3, half = (warp - 2) >> 2;
+    const int row = quarter * 32 + lane;
+    const uint32_t trow = tmem + (static_cast<uint32_t>(quarter * 32) << 16);
+    int nts = 0;
+    const bool tsw = threadIdx.x == 64;
+    int t = 0;
     for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x, ++t) {
+      float* sMax = sRed;                            // [2 halves][128]
+      const int ss = t % p.nsum;
+      float* sSum = sRed + 256 + ss * 256;           // [2 halves][128]
       const int qt = tile % p.nqt;
       const int q = qt * 128 + row;
       // valid key columns of this row: j = row + 64 - d, d in [0, min(band, q + 1))
@@ -262,7 +275,7 @@ epipolar_attn_tc_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
       const uint32_t srow = trow + sb * 192;
       mbar_wait(&s_full[sb], (t / p.nS) & 1);
       tc_fence_after();
-      if (tsw) at_mark(p, 2, nts);
+      if (tsw) at_mark(p, 3, nts);
       // warp-uniform chunk range that any row of this warp can touch
       const int wlo = max(0, (quarter * 32 + 64 - p.band + 1) / 32), whi = (quarter * 32 + 31 + 64) / 32;
       // valid keys of a 32-key chunk as a bit mask: one LOP3 per element instead of two compares
@@ -297,7 +310,7 @@ epipolar_attn_tc_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
       const float mb = (nd > 0) ? m * scale : 0.f;
       // P is single-buffered: P V of the previous tile must have read it
       if (t > 0) mbar_wait(&o_full[(t - 1) % p.nO], ((t - 1) / p.nO) & 1);
-      if (tsw) at_mark(p, 2, nts);
+      if (tsw) at_mark(p, 3, nts);
       float sum = 0.f;
       // 32 keys = 4 chunks of 16 B in key block cb/2, chunk index (cb&1)*4 + c
       auto store_p = [&](int cb, const uint32_t* pk) {
@@ -332,18 +345,13 @@ epipolar_attn_tc_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
         for (int cb = half; cb < 6; cb += 2)               // key chunks outside the band of this warp: P = 0
           if (cb < wlo || cb > whi) store_p(cb, zero);
       }
+      mbar_wait(&sum_free[ss], ((t / p.nsum) & 1) ^ 1);   // the epilogue has read the sums this slot held before
       sSum[half * 128 + row] = sum;
       fence_proxy_async_smem();
       mbar_arrive(p_full);
-      named_bar_sync(2 + quarter, 64);                    // (also orders the next tile's sMax write after this tile's read)
-      sum += sSum[(half ^ 1) * 128 + row];
-      if (tsw) at_mark(p, 2, nts);
-      if (!p.defer) epilogue(t, tile, sum);
-      else if (t > 0) epilogue(t - 1, prev_tile, prev_sum);
-      prev_tile = tile;
-      prev_sum = sum;
+      named_bar_sync(2 + quarter, 64);                    // orders the next tile's sMax write after this tile's read
+      if (tsw) at_mark(p, 3, nts);
     }
-    if (p.defer && t > 0) epilogue(t - 1, prev_tile, prev_sum);
   }
   tc_fence_before();
   __syncthreads();
@@ -370,15 +378,24 @@ int launch_attn_tc(const void* q, const void* k, const void* v, void* out, int B
   // which measured faster than 1 S + 2 O with a deferred epilogue); C = 256: 1 S + 1 O
   p.nS = C <= 128 ? 2 : 1;
   p.nO = C == 64 ? 2 : 1;
-  p.defer = p.nO == 2;
   p.o_col = C <= 128 ? 384 : 256;
+  // Shared memory: Q/K ring + V (3 key blocks) + P (48 KB) + the output tile of the TMA store (C <= 128).  Measured with the
+  // clock64 timeline (tools/timeline_attn.py): a Q/K stage is reloaded ~5000 cycles after its MMAs commit and V is held
+  // from its load until P V, so with one tile of buffers the load latency is the tile period.  A third stage paid for by
+  // dropping the output tile (epilogue warps storing bf16 rows straight to global memory) measured SLOWER (74.5 vs 65.0
+  // us at C = 128: the direct stores hold the O accumulator and with it the next P V); the ring stays at two stages.
+  const int NC = C / 64;
   p.tma_out = C <= 128 ? 1 : 0;
+  p.nstage = 2;
+  p.nsum = C <= 128 ? 4 : 1;
   {
     const char* d = tuning_env("SF_ATTN_DBG");
     p.dbg = d ? atoi(d) : 0;
-    const char* f = tuning_env("SF_ATTN_DEFER");
-    if (f) p.defer = atoi(f);
-    const char* e = tuning_env("SF_ATTN_TS");   // tuning hook: device pointer of a [3][128] int64 timeline buffer
+    const char* g = tuning_env("SF_ATTN_NSTAGE");
+    if (g) p.nstage = atoi(g);
+    const char* o = tuning_env("SF_ATTN_TMAOUT");
+    if (o) p.tma_out = atoi(o);
+    const char* e = tuning_env("SF_ATTN_TS");   // tuning hook: device pointer of a [4][128] int64 timeline buffer
     p.ts = e ? reinterpret_cast<long long*>(strtoull(e, nullptr, 16)) : nullptr;
   }
   CUtensorMap mq, mk, mv, mo;
@@ -387,8 +404,7 @@ int launch_attn_tc(const void* q, const void* k, const void* v, void* out, int B
   if ((rc = make_tmap_3d_bf16_sw128(&mk, k, W, H, static_cast<uint64_t>(B) * C, 1, 64))) return rc;
   if ((rc = make_tmap_3d_bf16_sw128(&mv, v, W, H, static_cast<uint64_t>(B) * C, 1, 64))) return rc;
   if ((rc = make_tmap_3d_bf16_sw128(&mo, out, W, H, static_cast<uint64_t>(B) * C, 1, 64))) return rc;
-  const int NC = C / 64;
-  const size_t smem = AT_NSTAGE * AT_STAGE + 3 * NC * AT_BOX + AT_PBYTES + (p.tma_out ? 2 * NC * AT_BOX : 0) + 2304;   // barriers + row maxima/sums
+  const size_t smem = static_cast<size_t>(p.nstage) * AT_STAGE + 3 * NC * AT_BOX + AT_PBYTES + (p.tma_out ? 2 * NC * AT_BOX : 0) + 256 + 1024 + p.nsum * 1024;   // barriers, row maxima, partial sums
   SF_CUDA(cudaFuncSetAttribute(epipolar_attn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                static_cast<int>(smem)));
   const int grid = min(p.ntiles, sm_count());
