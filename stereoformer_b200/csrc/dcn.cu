@@ -725,7 +725,10 @@ static int dcn_forward_impl(const float* input, const float* weight, const float
     q.kh = kh; q.kw = kw; q.sh = stride_h; q.sw = stride_w; q.ph = pad_h; q.pw = pad_w; q.dh = dil_h; q.dw = dil_w;
     q.G = group; q.dg = deformable_group;
     bool handled = false;
-    const int rc = launch_dcn_tc(q, weight, workspace, workspace_bytes, s, &handled);
+    int rc = launch_dcn_tc2(q, weight, workspace, workspace_bytes, s, &handled);   // channels-last gathers (needs the larger workspace)
+    if (rc) return rc;
+    if (handled) return SF_OK;
+    rc = launch_dcn_tc(q, weight, workspace, workspace_bytes, s, &handled);
     if (rc) return rc;
     if (handled) return SF_OK;
     SF_CHECK_ARG(algo != SF_ALGO_TC, "dcn_forward: the tensor-core path needs %zu workspace bytes (got %zu) and <= 256 "
@@ -750,6 +753,13 @@ extern "C" int sf_dcn_forward_f32(const float* input, const float* weight, const
 
 extern "C" size_t sf_dcn_workspace_bytes(int Cin, int Cout, int kh, int kw, int group) {
   return sf::dcn_tc_workspace_bytes(Cin, Cout, kh, kw, group);
+}
+
+extern "C" size_t sf_dcn_workspace_bytes_ex(int B, int Cin, int H, int W, int Cout, int kh, int kw, int group,
+                                            int deformable_group) {
+  const size_t a = sf::dcn_tc_workspace_bytes(Cin, Cout, kh, kw, group);
+  const size_t b = sf::dcn_tc2_workspace_bytes(B, Cin, H, W, Cout, kh, kw, group, deformable_group);
+  return a > b ? a : b;
 }
 
 extern "C" int sf_dcn_forward_ws_f32(const float* input, const float* weight, const float* bias, const float* offset,

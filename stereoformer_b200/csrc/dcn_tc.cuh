@@ -25,4 +25,10 @@ size_t dcn_tc_workspace_bytes(int Cin, int Cout, int kh, int kw, int group);
 int launch_dcn_tc(DcnTcParams p, const float* weight, void* workspace, size_t workspace_bytes, cudaStream_t stream,
                   bool* handled);
 
+// Channels-last variant (dcn_tc2.cu): channels per group and per deformable group multiples of 64.  Its workspace also
+// holds the [B][H*W][Cin] copy of the input; 0 = the shape does not take this path.
+size_t dcn_tc2_workspace_bytes(int B, int Cin, int H, int W, int Cout, int kh, int kw, int group, int deformable_group);
+int launch_dcn_tc2(DcnTcParams p, const float* weight, void* workspace, size_t workspace_bytes, cudaStream_t stream,
+                   bool* handled);
+
 }  // namespace sf

@@ -1,0 +1,359 @@
+// Deformable convolution forward, tensor-core path over a CHANNELS-LAST copy of the input  (SURVEY 8a row a10).
+//
+// Reference: deform/src/cuda/modulated_deform_conv_cuda.cu:19-121 (im2col + addmm), modulated_deform_im2col_cuda.cuh:25-54,
+// 128-194 (the sampling rule).  Same implicit GEMM as dcn_tc.cu (M = 128 output pixels, N = Cout/g, K = Cin/g * kh*kw, bf16
+// hi/mid split, fp32 accumulation in TMEM); what changes is how the column values are produced.  dcn_tc.cu gathers from
+// NCHW with thread = pixel: every load instruction of a warp touches ~20 sectors in ~16 cache lines and the L1 tag stage
+// (one line per cycle) is the limiter (measured: 218k cycles per 128-pixel tile at 128 -> 128 channels).  Here
+//   * a pre-pass writes the input once as [B][H*W][Cin] (dcn_nchw_to_nhwc_kernel, a tiled transpose);
+//   * a gather warp works on TWO pixels at a time, 16 lanes each, a lane owning 4 consecutive channels of the chunk's 64:
+//     the four bilinear corners are four LDG.128 per lane, 256 contiguous bytes per pixel and corner (4 cache lines per
+//     instruction instead of ~16, and every byte of a line is used);
+//   * the interpolated values (x mask) are split into bf16 hi + mid and stored as the A operand in shared memory
+//     (K-major SWIZZLE_128B rows = pixels; 8 bytes per lane, 128 contiguous bytes per pixel);
+//   * the reduction index is ordered (64-channel block, tap, channel): the nine taps of a channel block re-read the same
+//     ~3 input rows x 256 bytes, which stay in L1 (the weights are split in the same order, dcn_split_weights2_kernel);
+//   * the accumulator is double-buffered in TMEM (2 x 256 columns), so the epilogue (+ bias, NCHW rows) of tile t runs
+//     under the gathers and MMAs of tile t + 1.
+// Sampling descriptors (corner offsets, corner weights x mask) are computed once per tile by the warp that uses them.
+// Shapes: channels per group and per deformable group multiples of 64, <= 256 output channels per group; anything else
+// takes dcn_tc.cu / dcn.cu.  fp32 parity: 3-term split, ~2^-16 relative per product (tests: 1e-4 of the output magnitude).
+#include <cuda_bf16.h>
+#include <stdlib.h>
+
+#include "common.cuh"
+#include "tc_common.cuh"
+#include "dcn_tc.cuh"
+#include "../../include/stereoformer_b200.h"
+
+namespace sf {
+
+constexpr int D2_KC = 64;                  // K values per chunk: 64 channels of one tap
+constexpr int D2_NG = 16;                  // gather warps 1..16, 8 pixels of the tile each
+constexpr int D2_WARP_MMA = 1 + D2_NG;     // 17
+constexpr int D2_WARP_EPI = D2_WARP_MMA + 1;   // 18..21 (warp & 3 = TMEM lane quarter)
+constexpr int D2_THREADS = (D2_WARP_EPI + 4) * 32;
+constexpr int D2_MAXST = 4;
+constexpr int D2_ABYTES = 2 * 16384;       // A stage: hi | mid, [128 rows][128 B] each
+
+// [B][C][HW] -> [B][HW][C]
+__global__ void __launch_bounds__(256)
+dcn_nchw_to_nhwc_kernel(const float* __restrict__ in, float* __restrict__ out, int C, int HW) {
+  __shared__ float tile[32][33];
+  const int b = blockIdx.z;
+  const int x0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
+  const int tx = threadIdx.x, ty = threadIdx.y;
+  const float* src = in + static_cast<size_t>(b) * C * HW;
+  float* dst = out + static_cast<size_t>(b) * HW * C;
+#pragma unroll
+  for (int k = 0; k < 32; k += 8) {
+    const int c = c0 + ty + k, x = x0 + tx;
+    tile[ty + k][tx] = (c < C && x < HW) ? __ldg(src + static_cast<size_t>(c) * HW + x) : 0.f;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < 32; k += 8) {
+    const int x = x0 + ty + k, c = c0 + tx;
+    if (x < HW && c < C) dst[static_cast<size_t>(x) * C + c] = tile[tx][ty + k];
+  }
+}
+
+// fp32 weights [Cout][Cig][T] -> bf16 hi / mid [2][Cout][K], reduction index k = (c / 64) * T * 64 + t * 64 + c % 64
+__global__ void dcn_split_weights2_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ ws, int Cout, int K,
+                                          int Cig, int T) {
+  const size_t n = static_cast<size_t>(Cout) * K;
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int k = static_cast<int>(i % K);
+    const size_t o = i / K;
+    const int cc = k / (T * 64), r = k - cc * T * 64;
+    const int t = r >> 6, c = cc * 64 + (r & 63);
+    const float v = w[o * K + static_cast<size_t>(c) * T + t];
+    const __nv_bfloat16 h = __float2bfloat16_rn(v);
+    ws[i] = h;
+    ws[n + i] = __float2bfloat16_rn(v - __bfloat162float(h));
+  }
+}
+
+__device__ __forceinline__ float4 ldg4(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
+
+__global__ void __launch_bounds__(D2_THREADS, 1)
+dcn_tc2_kernel(const __grid_constant__ CUtensorMap mapW, const DcnTcParams p, const float* __restrict__ inT) {
+  using namespace sftc;
+  extern __shared__ __align__(1024) unsigned char smem[];
+  const int T = p.kh * p.kw;
+  const int b_bytes = 2 * p.N * 128;                                // B hi | B mid: [N rows][128 B]
+  const int stage_bytes = D2_ABYTES + b_bytes;
+  unsigned char* sStage = smem;                                     // [NST][A hi | A mid | B hi | B mid]
+  int4* d_off = reinterpret_cast<int4*>(sStage + p.NST * stage_bytes);   // [dg][T][128] corner offsets (elements of inT)
+  float4* d_w = reinterpret_cast<float4*>(d_off + p.dg * T * 128);  // [dg][T][128] corner weights * mask
+  uint64_t* bars = reinterpret_cast<uint64_t*>(d_w + p.dg * T * 128);
+  uint64_t* b_full = bars;                      // [NST] TMA -> MMA
+  uint64_t* a_full = bars + D2_MAXST;           // [NST] gather warps (16) -> MMA
+  uint64_t* st_empty = bars + 2 * D2_MAXST;     // [NST] MMA commit -> TMA producer + gather warps
+  uint64_t* acc_full = bars + 3 * D2_MAXST;     // [2] MMA commit -> epilogue
+  uint64_t* acc_empty = acc_full + 2;           // [2] epilogue (4 warps) -> MMA
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_full + 4);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < p.NST; ++s) { mbar_init(&b_full[s], 1); mbar_init(&a_full[s], D2_NG); mbar_init(&st_empty[s], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 4); }
+    fence_mbar_init();
+    tma_prefetch_desc(&mapW);
+  }
+  if (warp == D2_WARP_MMA) tmem_alloc(tmem_slot, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  const int M = p.Ho * p.Wo;
+  const int Cig = p.Cin / p.G, Cog = p.Cout / p.G;
+
+  if (warp == 0) {
+    // ================================================================= weight producer (TMA)
+    if (lane == 0) {
+      int s = 0, ph = 1;
+      for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
+        const int g = (tile / p.nptile) % p.G;
+        for (int ch = 0; ch < p.nchunk; ++ch) {
+          mbar_wait(&st_empty[s], ph);
+          unsigned char* dst = sStage + s * stage_bytes + D2_ABYTES;
+          mbar_expect_tx(&b_full[s], b_bytes);
+          tma_load_3d(dst, &mapW, &b_full[s], ch * D2_KC, g * Cog, 0);
+          tma_load_3d(dst + p.N * 128, &mapW, &b_full[s], ch * D2_KC, g * Cog, 1);
+          if (++s == p.NST) { s = 0; ph ^= 1; }
+        }
+      }
+    }
+  } else if (warp < D2_WARP_MMA) {
+    // ================================================================= gather warps: column values -> A operand
+    const int gw = warp - 1;                               // pixels 8*gw .. 8*gw+7 of the tile
+    const int hw = lane >> 4, cl = 4 * (lane & 15);        // pixel of the pair, first of this lane's 4 channels
+    const int cpdg = p.Cin / p.dg;
+    const int HW = p.H * p.W;
+    int s = 0, ph = 1;
+    for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
+      const int pt = tile % p.nptile, t2 = tile / p.nptile;
+      const int g = t2 % p.G, b = t2 / p.G;
+      const int pix0 = pt * 128 + 8 * gw;
+      // ---- sampling descriptors of this warp's 8 pixels, all taps and deformable groups (warp-private: no block barrier)
+      //      (modulated_deform_im2col_cuda.cuh:25-54,163-180)
+      __syncwarp();
+      for (int e = lane; e < p.dg * T * 8; e += 32) {
+        const int ex = e & 7, r = e >> 3;
+        const int t = r % T, dgi = r / T;
+        const int pix = pix0 + ex;
+        int4 off = make_int4(0, 0, 0, 0);
+        float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (pix < M) {
+          const int yo = pix / p.Wo, xo = pix % p.Wo;
+          const int i = t / p.kw, j = t % p.kw;
+          const size_t ob = ((static_cast<size_t>(b) * p.dg + dgi) * 2 * T) * M + pix;
+          const float oh = __ldg(p.offset + ob + static_cast<size_t>(2 * t) * M);
+          const float ow = __ldg(p.offset + ob + static_cast<size_t>(2 * t + 1) * M);
+          const float m = p.mask ? __ldg(p.mask + ((static_cast<size_t>(b) * p.dg + dgi) * T + t) * M + pix) : 1.f;
+          const float h_im = (float)(yo * p.sh - p.ph + i * p.dh) + oh;
+          const float w_im = (float)(xo * p.sw - p.pw + j * p.dw) + ow;
+          if (h_im > -1.f && w_im > -1.f && h_im < (float)p.H && w_im < (float)p.W) {
+            const int hl = (int)floorf(h_im), wl = (int)floorf(w_im);
+            const int hh_i = hl + 1, wh_i = wl + 1;
+            const float lh = h_im - (float)hl, lw = w_im - (float)wl;
+            const float hh = 1.f - lh, hw2 = 1.f - lw;
+            const bool t0 = hl >= 0, l0 = wl >= 0, b1 = hh_i <= p.H - 1, r1 = wh_i <= p.W - 1;
+            if (t0 && l0) { off.x = (hl * p.W + wl) * p.Cin; w.x = hh * hw2 * m; }
+            if (t0 && r1) { off.y = (hl * p.W + wh_i) * p.Cin; w.y = hh * lw * m; }
+            if (b1 && l0) { off.z = (hh_i * p.W + wl) * p.Cin; w.z = lh * hw2 * m; }
+            if (b1 && r1) { off.w = (hh_i * p.W + wh_i) * p.Cin; w.w = lh * lw * m; }
+          }
+        }
+        const int di = (dgi * T + t) * 128 + 8 * gw + ex;
+        d_off[di] = off;
+        d_w[di] = w;
+      }
+      __syncwarp();
+      const float* in_b = inT + static_cast<size_t>(b) * HW * p.Cin + static_cast<size_t>(g) * Cig + cl;
+      for (int ch = 0; ch < p.nchunk; ++ch) {
+        const int cc = ch / T, t = ch - cc * T;
+        const int dgi = (g * Cig + cc * 64) / cpdg;
+        const float* src = in_b + cc * 64;
+        const int dbase = (dgi * T + t) * 128 + 8 * gw + hw;
+        mbar_wait(&st_empty[s], ph);
+        unsigned char* a_hi = sStage + s * stage_bytes;
+#pragma unroll
+        for (int i2 = 0; i2 < 4; i2 += 2) {
+          int4 off[2];
+          float4 wt[2], v[2][4];
+#pragma unroll
+          for (int e = 0; e < 2; ++e) {
+            off[e] = d_off[dbase + 2 * (i2 + e)];
+            wt[e] = d_w[dbase + 2 * (i2 + e)];
+          }
+#pragma unroll
+          for (int e = 0; e < 2; ++e) {
+            v[e][0] = ldg4(src + off[e].x); v[e][1] = ldg4(src + off[e].y);
+            v[e][2] = ldg4(src + off[e].z); v[e][3] = ldg4(src + off[e].w);
+          }
+#pragma unroll
+          for (int e = 0; e < 2; ++e) {
+            float4 r;
+            r.x = wt[e].x * v[e][0].x + wt[e].y * v[e][1].x + wt[e].z * v[e][2].x + wt[e].w * v[e][3].x;
+            r.y = wt[e].x * v[e][0].y + wt[e].y * v[e][1].y + wt[e].z * v[e][2].y + wt[e].w * v[e][3].y;
+            r.z = wt[e].x * v[e][0].z + wt[e].y * v[e][1].z + wt[e].z * v[e][2].z + wt[e].w * v[e][3].z;
+            r.w = wt[e].x * v[e][0].w + wt[e].y * v[e][1].w + wt[e].z * v[e][2].w + wt[e].w * v[e][3].w;
+            const __nv_bfloat162 h0 = __floats2bfloat162_rn(r.x, r.y), h1 = __floats2bfloat162_rn(r.z, r.w);
+            const __nv_bfloat162 m0 = __floats2bfloat162_rn(r.x - __low2float(h0), r.y - __high2float(h0));
+            const __nv_bfloat162 m1 = __floats2bfloat162_rn(r.z - __low2float(h1), r.w - __high2float(h1));
+            const int row = 8 * gw + 2 * (i2 + e) + hw;     // A row = pixel of the tile
+            const int kc = (lane & 15) >> 1;                // 16-byte chunk of the row (8 K values)
+            unsigned char* dst = a_hi + (row >> 3) * 1024 + (row & 7) * 128 + ((kc ^ (row & 7)) << 4) + (lane & 1) * 8;
+            *reinterpret_cast<uint2*>(dst) =
+                make_uint2(*reinterpret_cast<const uint32_t*>(&h0), *reinterpret_cast<const uint32_t*>(&h1));
+            *reinterpret_cast<uint2*>(dst + 16384) =
+                make_uint2(*reinterpret_cast<const uint32_t*>(&m0), *reinterpret_cast<const uint32_t*>(&m1));
+          }
+        }
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&a_full[s]);
+        if (++s == p.NST) { s = 0; ph ^= 1; }
+      }
+    }
+  } else if (warp == D2_WARP_MMA) {
+    // ================================================================= MMA issuer
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc_bf16(128, p.N, 0, 0);   // A and B: K-major shared memory
+      int s = 0, ph = 0, t = 0;
+      for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x, ++t) {
+        const int buf = t & 1;
+        mbar_wait(&acc_empty[buf], ((t >> 1) & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t acc = tmem + buf * 256;
+        for (int ch = 0; ch < p.nchunk; ++ch) {
+          mbar_wait(&b_full[s], ph);
+          mbar_wait(&a_full[s], ph);
+          tc_fence_after();
+          const uint32_t a_hi = smem_u32(sStage + s * stage_bytes), a_mid = a_hi + 16384;
+          const uint32_t b_hi = a_hi + D2_ABYTES, b_mid = b_hi + p.N * 128;
+#pragma unroll
+          for (int j = 0; j < D2_KC / 16; ++j) {
+            const uint64_t dah = make_smem_desc(a_hi + j * 32, 16, 1024);
+            const uint64_t dam = make_smem_desc(a_mid + j * 32, 16, 1024);
+            const uint64_t dbh = make_smem_desc(b_hi + j * 32, 16, 1024);
+            const uint64_t dbm = make_smem_desc(b_mid + j * 32, 16, 1024);
+            umma_bf16(acc, dah, dbh, idesc, (ch | j) != 0);
+            umma_bf16(acc, dah, dbm, idesc, true);
+            umma_bf16(acc, dam, dbh, idesc, true);
+          }
+          umma_commit(&st_empty[s]);
+          if (++s == p.NST) { s = 0; ph ^= 1; }
+        }
+        umma_commit(&acc_full[buf]);
+      }
+    }
+  } else {
+    // ================================================================= epilogue: + bias, NCHW rows
+    const int q = warp & 3;
+    int t = 0;
+    for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x, ++t) {
+      const int pt = tile % p.nptile, t2 = tile / p.nptile;
+      const int g = t2 % p.G, b = t2 / p.G;
+      const int pix = pt * 128 + 32 * q + lane;
+      const int buf = t & 1;
+      mbar_wait(&acc_full[buf], (t >> 1) & 1);
+      tc_fence_after();
+      const uint32_t trow = tmem + buf * 256 + (static_cast<uint32_t>(32 * q) << 16);
+      float* orow = p.out + (static_cast<size_t>(b) * p.Cout + static_cast<size_t>(g) * Cog) * M + pix;
+      for (int cb = 0; cb < Cog; cb += 32) {
+        uint32_t raw[32];
+        tmem_ld32(trow + cb, raw);
+        tmem_ld_wait();
+        if (pix < M) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (cb + j < Cog) orow[static_cast<size_t>(cb + j) * M] = __uint_as_float(raw[j]) + __ldg(p.bias + g * Cog + cb + j);
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&acc_empty[buf]);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == D2_WARP_MMA) tmem_free(tmem, 512);
+}
+
+static bool dcn_tc2_plan(DcnTcParams& p, size_t* smem_out) {
+  const int T = p.kh * p.kw;
+  if (p.G <= 0 || p.dg <= 0 || p.Cin % p.G || p.Cout % p.G || p.Cin % p.dg) return false;
+  const int Cig = p.Cin / p.G, Cog = p.Cout / p.G;
+  if (Cig % 64 != 0 || (p.Cin / p.dg) % 64 != 0 || Cog > 256 || Cog < 8) return false;
+  if (1LL * p.H * p.W * p.Cin >= (1LL << 31)) return false;          // corner offsets are 32-bit element indices
+  p.K = Cig * T;
+  p.nchunk = p.K / D2_KC;
+  p.N = ceil_div(Cog, 16) * 16;
+  const size_t desc = static_cast<size_t>(p.dg) * T * 128 * 32;
+  const size_t stage = static_cast<size_t>(D2_ABYTES) + 2 * p.N * 128;
+  if (desc + stage + 256 > 232448) return false;
+  // two stages overlap the gathers of one chunk with the MMAs of the previous one; more only takes L1 away from the
+  // gathers (shared memory and L1 share the SM's 256 KB)
+  p.NST = static_cast<int>(min(static_cast<size_t>(2), (232448 - desc - 256) / stage));
+  if (const char* e = tuning_env("SF_DCN2_NST"))
+    p.NST = static_cast<int>(min(static_cast<size_t>(max(1, atoi(e))), min(static_cast<size_t>(D2_MAXST), (232448 - desc - 256) / stage)));
+  *smem_out = p.NST * stage + desc + 256;
+  const int M = p.Ho * p.Wo;
+  p.nptile = ceil_div(M, 128);
+  const long long nt = 1LL * p.B * p.G * p.nptile;
+  if (nt >= (1LL << 30)) return false;
+  p.ntiles = static_cast<int>(nt);
+  return true;
+}
+
+static size_t align256(size_t x) { return (x + 255) & ~static_cast<size_t>(255); }
+
+// weights (bf16 hi/mid) + the channels-last copy of the input; 0 when the shape does not take this path
+size_t dcn_tc2_workspace_bytes(int B, int Cin, int H, int W, int Cout, int kh, int kw, int group, int deformable_group) {
+  DcnTcParams p{};
+  p.B = B; p.Cin = Cin; p.H = H; p.W = W; p.Cout = Cout; p.kh = kh; p.kw = kw; p.G = group; p.dg = deformable_group;
+  p.Ho = 1; p.Wo = 1;
+  size_t smem = 0;
+  if (B <= 0 || H <= 0 || W <= 0 || !dcn_tc2_plan(p, &smem)) return 0;
+  return align256(static_cast<size_t>(2) * Cout * p.K * sizeof(__nv_bfloat16)) +
+         static_cast<size_t>(B) * H * W * Cin * sizeof(float);
+}
+
+int launch_dcn_tc2(DcnTcParams p, const float* weight, void* workspace, size_t workspace_bytes, cudaStream_t stream,
+                   bool* handled) {
+  *handled = false;
+  size_t smem = 0;
+  if (!dcn_tc2_plan(p, &smem)) return SF_OK;
+  const size_t need = dcn_tc2_workspace_bytes(p.B, p.Cin, p.H, p.W, p.Cout, p.kh, p.kw, p.G, p.dg);
+  if (workspace == nullptr || workspace_bytes < need || (reinterpret_cast<uintptr_t>(workspace) & 127) != 0) return SF_OK;
+  if ((reinterpret_cast<uintptr_t>(p.in) & 15) != 0) return SF_OK;
+  __nv_bfloat16* ws = static_cast<__nv_bfloat16*>(workspace);
+  const size_t wbytes = align256(static_cast<size_t>(2) * p.Cout * p.K * sizeof(__nv_bfloat16));
+  float* inT = reinterpret_cast<float*>(static_cast<unsigned char*>(workspace) + wbytes);
+  {
+    const size_t n = static_cast<size_t>(p.Cout) * p.K;
+    const int grid = static_cast<int>(min(static_cast<size_t>(sm_count()) * 8, (n + 255) / 256));
+    dcn_split_weights2_kernel<<<grid, 256, 0, stream>>>(weight, ws, p.Cout, p.K, p.Cin / p.G, p.kh * p.kw);
+    SF_LAUNCH_CHECK();
+    const int HW = p.H * p.W;
+    dim3 tg(ceil_div(HW, 32), ceil_div(p.Cin, 32), p.B);
+    SF_CHECK_ARG(tg.y <= 65535 && tg.z <= 65535, "dcn_forward: too many channels or images for the channels-last pass");
+    dcn_nchw_to_nhwc_kernel<<<tg, dim3(32, 8), 0, stream>>>(p.in, inT, p.Cin, HW);
+    SF_LAUNCH_CHECK();
+  }
+  CUtensorMap mW;
+  int rc = make_tmap_3d_bf16_sw128(&mW, ws, p.K, p.Cout, 2, p.N, 1);
+  if (rc) return rc;
+  SF_CUDA(cudaFuncSetAttribute(dcn_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+  const int grid = min(p.ntiles, sm_count());
+  dcn_tc2_kernel<<<grid, D2_THREADS, smem, stream>>>(mW, p, inT);
+  SF_LAUNCH_CHECK();
+  *handled = true;
+  return SF_OK;
+}
+
+}  // namespace sf

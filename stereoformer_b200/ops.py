@@ -402,9 +402,9 @@ def dcn_forward(inp, weight, bias, offset, mask, stride, padding, dilation, grou
         return out
     with torch.cuda.device(inp.device):
         algo = _algo(algo)
-        nws = int(_lib.lib().sf_dcn_workspace_bytes(Cin, Cout, kh, kw, int(groups))) \
+        nws = int(_lib.lib().sf_dcn_workspace_bytes_ex(B, Cin, H, W, Cout, kh, kw, int(groups), int(deformable_groups))) \
             if algo not in (SF_ALGO_GENERIC, SF_ALGO_EXACT) else 0
-        ws = torch.empty(nws, device=inp.device, dtype=torch.uint8) if nws else None   # bf16 hi/mid weights (scratch)
+        ws = torch.empty(nws, device=inp.device, dtype=torch.uint8) if nws else None   # bf16 hi/mid weights (+ channels-last input copy) (scratch)
         _lib.call("sf_dcn_forward_ws_f32", _ptr(inp), _ptr(weight), _ptr(bias), _ptr(offset), _ptr(mask), _ptr(out), B,
                   Cin, H, W, Cout, kh, kw, sh, sw, ph, pw, dh, dw, int(groups), int(deformable_groups), _ptr(ws),
                   ctypes.c_size_t(nws), algo, _stream())
