@@ -17,6 +17,7 @@ struct DcnTcParams {
   int N;                // MMA N: Cog rounded up to 16
   int NST;              // stages (B in shared memory, A in tensor memory)
   int nptile, ntiles;
+  int tiles_x;          // dcn_tc2 only: its 128-pixel tiles are 8 rows x 16 columns, tiles_x of them per output row band
 };
 
 size_t dcn_tc_workspace_bytes(int Cin, int Cout, int kh, int kw, int group);

@@ -31,7 +31,13 @@ CASES = [  # B, Cin, Cout, H, W, groups, dg, stride, pad, dil
     (1, 128, 128, 31, 45, 1, 1, 1, 1, 1),      # disp_residual.py:213 (tcgen05 path)
     (2, 32, 48, 23, 37, 1, 4, 2, 1, 1),        # stride 2
     (1, 24, 24, 20, 33, 3, 3, 1, 2, 2),        # groups, dilation
+    # channels-last gather kernel (dcn_tc2.cu: channels per group and per deformable group multiples of 64)
+    (2, 128, 64, 19, 27, 2, 1, 1, 1, 1),       # two groups of 64 channels, ragged 8x16 tiles, batch 2
+    (1, 128, 128, 17, 33, 1, 2, 2, 2, 2),      # two deformable groups, stride 2, dilation 2
+    (1, 64, 256, 9, 50, 1, 1, 1, 1, 1),        # 256 output channels (full accumulator width)
+    (1, 192, 96, 16, 16, 1, 3, 1, 0, 1),       # three 64-channel blocks / deformable groups, no padding, ragged N
 ]
+TC2 = CASES[-4:]
 
 
 @pytest.mark.parametrize("case", CASES)
@@ -58,7 +64,18 @@ def test_forward_matches_reference_extension(case):
     assert (got1 - want1).abs().max() <= 1e-4 * want1.abs().max()
 
 
-@pytest.mark.parametrize("case", CASES[:3] + CASES[4:])
+def test_channels_last_cases_take_the_channels_last_kernel():
+    """The workspace query is what routes a call: the cases meant for dcn_tc2 must be eligible for it."""
+    from stereoformer_b200 import _lib
+    for B, Cin, Cout, H, W, G, dg, s, p, d in TC2 + [CASES[3]]:
+        small = int(_lib.lib().sf_dcn_workspace_bytes(Cin, Cout, 3, 3, G))
+        big = int(_lib.lib().sf_dcn_workspace_bytes_ex(B, Cin, H, W, Cout, 3, 3, G, dg))
+        assert big >= small + B * Cin * H * W * 4, (Cin, Cout, G, dg)
+    assert int(_lib.lib().sf_dcn_workspace_bytes_ex(1, 64, 40, 56, 128, 3, 3, 1, 2)) == \
+        int(_lib.lib().sf_dcn_workspace_bytes(64, 128, 3, 3, 1))           # 32 channels per deformable group: NCHW gathers
+
+
+@pytest.mark.parametrize("case", CASES[:3] + CASES[4:6])
 def test_backward_matches_reference_extension(case):
     import stereoformer_b200.DCN as ours
     ref = _ref()
