@@ -41,7 +41,7 @@ constexpr int D2_WARP_MMA = 1 + D2_NG;     // 17
 constexpr int D2_WARP_EPI = D2_WARP_MMA + 1;   // 18..21 (warp & 3 = TMEM lane quarter)
 constexpr int D2_THREADS = (D2_WARP_EPI + 4) * 32;
 constexpr int D2_MAXST = 4;
-constexpr int D2_ABYTES = 2 * 16384;       // A stage: hi | mid, [128 rows][128 B] each
+constexpr int D2_ABYTES = 2 * 16384;       // A stage: hi | mid, [128 rows][128 B] each (two stages)
 
 // [B][C][HW] -> [B][HW][C]
 __global__ void __launch_bounds__(256)
@@ -90,22 +90,30 @@ dcn_tc2_kernel(const __grid_constant__ CUtensorMap mapW, const DcnTcParams p, co
   extern __shared__ __align__(1024) unsigned char smem[];
   const int T = p.kh * p.kw;
   const int b_bytes = 2 * p.N * 128;                                // B hi | B mid: [N rows][128 B]
-  const int stage_bytes = D2_ABYTES + b_bytes;
-  unsigned char* sStage = smem;                                     // [NST][A hi | A mid | B hi | B mid]
-  int4* d_off = reinterpret_cast<int4*>(sStage + p.NST * stage_bytes);   // [dg][T][128] corner offsets (elements of inT)
-  float4* d_w = reinterpret_cast<float4*>(d_off + p.dg * T * 128);  // [dg][T][128] corner weights * mask
+  unsigned char* sA = smem;                                         // [2][A hi | A mid]
+  unsigned char* sB = sA + 2 * D2_ABYTES;                           // [NST][B hi | B mid]: the weight ring is deeper than the A ring
+  // sampling descriptors [dg][T][128]: the four corner offsets (elements of inT; 16 B) or, where shared memory is short
+  // (p.compact), the top-left corner | dx | dy << 1 (4 B: three more integer instructions per gathered pixel); then the
+  // corner weights * mask (16 B)
+  int* d_base = reinterpret_cast<int*>(sB + p.NST * b_bytes);
+  int4* d_off = reinterpret_cast<int4*>(d_base);
+  float4* d_w = reinterpret_cast<float4*>(d_base + p.dg * T * 128 * (p.compact ? 1 : 4));
   uint64_t* bars = reinterpret_cast<uint64_t*>(d_w + p.dg * T * 128);
   uint64_t* b_full = bars;                      // [NST] TMA -> MMA
-  uint64_t* a_full = bars + D2_MAXST;           // [NST] gather warps (16) -> MMA
-  uint64_t* st_empty = bars + 2 * D2_MAXST;     // [NST] MMA commit -> TMA producer + gather warps
-  uint64_t* acc_full = bars + 3 * D2_MAXST;     // [2] MMA commit -> epilogue
-  uint64_t* acc_empty = acc_full + 2;           // [2] epilogue (4 warps) -> MMA
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_full + 4);
+  uint64_t* b_empty = bars + D2_MAXST;          // [NST] MMA commit -> TMA producer
+  uint64_t* a_full = bars + 2 * D2_MAXST;       // [2]   gather warps (16) -> MMA
+  uint64_t* a_empty = a_full + 2;               // [2]   MMA commit -> gather warps
+  uint64_t* acc_full = a_full + 4;              // [2] MMA commit -> epilogue
+  uint64_t* acc_empty = a_full + 6;             // [2] epilogue (4 warps) -> MMA
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(a_full + 8);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
-    for (int s = 0; s < p.NST; ++s) { mbar_init(&b_full[s], 1); mbar_init(&a_full[s], D2_NG); mbar_init(&st_empty[s], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 4); }
+    for (int s = 0; s < p.NST; ++s) { mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], 1); }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&a_full[i], D2_NG); mbar_init(&a_empty[i], 1);
+      mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 4);
+    }
     fence_mbar_init();
     tma_prefetch_desc(&mapW);
   }
@@ -124,8 +132,8 @@ dcn_tc2_kernel(const __grid_constant__ CUtensorMap mapW, const DcnTcParams p, co
       for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
         const int g = (tile / p.nptile) % p.G;
         for (int ch = 0; ch < p.nchunk; ++ch) {
-          mbar_wait(&st_empty[s], ph);
-          unsigned char* dst = sStage + s * stage_bytes + D2_ABYTES;
+          mbar_wait(&b_empty[s], ph);
+          unsigned char* dst = sB + s * b_bytes;
           mbar_expect_tx(&b_full[s], b_bytes);
           tma_load_3d(dst, &mapW, &b_full[s], ch * D2_KC, g * Cog, 0);
           tma_load_3d(dst + p.N * 128, &mapW, &b_full[s], ch * D2_KC, g * Cog, 1);
@@ -139,6 +147,7 @@ dcn_tc2_kernel(const __grid_constant__ CUtensorMap mapW, const DcnTcParams p, co
     const int hw = lane >> 4, cl = 4 * (lane & 15);        // pixel of the pair, first of this lane's 4 channels
     const int cpdg = p.Cin / p.dg;
     const int HW = p.H * p.W;
+    const int rowstep = p.W * p.Cin;
     int s = 0, ph = 1;
     for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
       const int pt = tile % p.nptile, t2 = tile / p.nptile;
@@ -156,6 +165,7 @@ dcn_tc2_kernel(const __grid_constant__ CUtensorMap mapW, const DcnTcParams p, co
         const int t = r % T, dgi = r / T;
         const int xo = xo0 + ex;
         const int pix = yo * p.Wo + xo;
+        int base = 0;
         int4 off = make_int4(0, 0, 0, 0);
         float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
         if (yo < p.Ho && xo < p.Wo) {
@@ -172,14 +182,25 @@ dcn_tc2_kernel(const __grid_constant__ CUtensorMap mapW, const DcnTcParams p, co
             const float lh = h_im - (float)hl, lw = w_im - (float)wl;
             const float hh = 1.f - lh, hw2 = 1.f - lw;
             const bool t0 = hl >= 0, l0 = wl >= 0, b1 = hh_i <= p.H - 1, r1 = wh_i <= p.W - 1;
-            if (t0 && l0) { off.x = (hl * p.W + wl) * p.Cin; w.x = hh * hw2 * m; }
-            if (t0 && r1) { off.y = (hl * p.W + wh_i) * p.Cin; w.y = hh * lw * m; }
-            if (b1 && l0) { off.z = (hh_i * p.W + wl) * p.Cin; w.z = lh * hw2 * m; }
-            if (b1 && r1) { off.w = (hh_i * p.W + wh_i) * p.Cin; w.w = lh * lw * m; }
+            if (t0 && l0) w.x = hh * hw2 * m;
+            if (t0 && r1) w.y = hh * lw * m;
+            if (b1 && l0) w.z = lh * hw2 * m;
+            if (b1 && r1) w.w = lh * lw * m;
+            // corners outside the image carry weight 0 and only need a valid address: rows / columns are clamped and the
+            // descriptor is the top-left element index (a multiple of Cin, itself a multiple of 64) with the column and
+            // row steps (0 or 1) in its two low bits
+            const int r0 = max(hl, 0), c0 = max(wl, 0);
+            const int dy = min(hh_i, p.H - 1) - r0, dx = min(wh_i, p.W - 1) - c0;
+            base = (r0 * p.W + c0) * p.Cin | dx | (dy << 1);
+            off.x = (r0 * p.W + c0) * p.Cin;
+            off.y = off.x + dx * p.Cin;
+            off.z = off.x + dy * p.W * p.Cin;
+            off.w = off.z + dx * p.Cin;
           }
         }
         const int di = (dgi * T + t) * 128 + 8 * gw + ex;
-        d_off[di] = off;
+        if (p.compact) d_base[di] = base;
+        else d_off[di] = off;
         d_w[di] = w;
       }
       __syncwarp();
@@ -189,21 +210,37 @@ dcn_tc2_kernel(const __grid_constant__ CUtensorMap mapW, const DcnTcParams p, co
         const int dgi = (g * Cig + cc * 64) / cpdg;
         const float* src = in_b + cc * 64;
         const int dbase = (dgi * T + t) * 128 + 8 * gw + hw;
-        mbar_wait(&st_empty[s], ph);
-        unsigned char* a_hi = sStage + s * stage_bytes;
+        mbar_wait(&a_empty[s], ph);
+        unsigned char* a_hi = sA + s * D2_ABYTES;
 #pragma unroll
         for (int i2 = 0; i2 < 4; i2 += 2) {
-          int4 off[2];
           float4 wt[2], v[2][4];
+          if (p.compact) {
+            int bs[2];
 #pragma unroll
-          for (int e = 0; e < 2; ++e) {
-            off[e] = d_off[dbase + 2 * (i2 + e)];
-            wt[e] = d_w[dbase + 2 * (i2 + e)];
-          }
+            for (int e = 0; e < 2; ++e) {
+              bs[e] = d_base[dbase + 2 * (i2 + e)];
+              wt[e] = d_w[dbase + 2 * (i2 + e)];
+            }
 #pragma unroll
-          for (int e = 0; e < 2; ++e) {
-            v[e][0] = ldg4(src + off[e].x); v[e][1] = ldg4(src + off[e].y);
-            v[e][2] = ldg4(src + off[e].z); v[e][3] = ldg4(src + off[e].w);
+            for (int e = 0; e < 2; ++e) {
+              const float* c00 = src + (bs[e] & ~3);
+              const int dxo = (bs[e] & 1) ? p.Cin : 0, dyo = (bs[e] & 2) ? rowstep : 0;
+              v[e][0] = ldg4(c00); v[e][1] = ldg4(c00 + dxo);
+              v[e][2] = ldg4(c00 + dyo); v[e][3] = ldg4(c00 + dyo + dxo);
+            }
+          } else {
+            int4 off[2];
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+              off[e] = d_off[dbase + 2 * (i2 + e)];
+              wt[e] = d_w[dbase + 2 * (i2 + e)];
+            }
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+              v[e][0] = ldg4(src + off[e].x); v[e][1] = ldg4(src + off[e].y);
+              v[e][2] = ldg4(src + off[e].z); v[e][3] = ldg4(src + off[e].w);
+            }
           }
 #pragma unroll
           for (int e = 0; e < 2; ++e) {
@@ -227,14 +264,14 @@ dcn_tc2_kernel(const __grid_constant__ CUtensorMap mapW, const DcnTcParams p, co
         fence_proxy_async_smem();
         __syncwarp();
         if (lane == 0) mbar_arrive(&a_full[s]);
-        if (++s == p.NST) { s = 0; ph ^= 1; }
+        if (++s == 2) { s = 0; ph ^= 1; }
       }
     }
   } else if (warp == D2_WARP_MMA) {
     // ================================================================= MMA issuer
     if (lane == 0) {
       const uint32_t idesc = make_idesc_bf16(128, p.N, 0, 0);   // A and B: K-major shared memory
-      int s = 0, ph = 0, t = 0;
+      int s = 0, ph = 0, sa = 0, pha = 0, t = 0;
       for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x, ++t) {
         const int buf = t & 1;
         mbar_wait(&acc_empty[buf], ((t >> 1) & 1) ^ 1);
@@ -242,10 +279,10 @@ dcn_tc2_kernel(const __grid_constant__ CUtensorMap mapW, const DcnTcParams p, co
         const uint32_t acc = tmem + buf * 256;
         for (int ch = 0; ch < p.nchunk; ++ch) {
           mbar_wait(&b_full[s], ph);
-          mbar_wait(&a_full[s], ph);
+          mbar_wait(&a_full[sa], pha);
           tc_fence_after();
-          const uint32_t a_hi = smem_u32(sStage + s * stage_bytes), a_mid = a_hi + 16384;
-          const uint32_t b_hi = a_hi + D2_ABYTES, b_mid = b_hi + p.N * 128;
+          const uint32_t a_hi = smem_u32(sA + sa * D2_ABYTES), a_mid = a_hi + 16384;
+          const uint32_t b_hi = smem_u32(sB + s * b_bytes), b_mid = b_hi + p.N * 128;
 #pragma unroll
           for (int j = 0; j < D2_KC / 16; ++j) {
             const uint64_t dah = make_smem_desc(a_hi + j * 32, 16, 1024);
@@ -256,7 +293,9 @@ dcn_tc2_kernel(const __grid_constant__ CUtensorMap mapW, const DcnTcParams p, co
             umma_bf16(acc, dah, dbm, idesc, true);
             umma_bf16(acc, dam, dbh, idesc, true);
           }
-          umma_commit(&st_empty[s]);
+          umma_commit(&a_empty[sa]);
+          umma_commit(&b_empty[s]);
+          if (++sa == 2) { sa = 0; pha ^= 1; }
           if (++s == p.NST) { s = 0; ph ^= 1; }
         }
         umma_commit(&acc_full[buf]);
@@ -308,15 +347,25 @@ static bool dcn_tc2_plan(DcnTcParams& p, size_t* smem_out) {
   p.K = Cig * T;
   p.nchunk = p.K / D2_KC;
   p.N = ceil_div(Cog, 16) * 16;
-  const size_t desc = static_cast<size_t>(p.dg) * T * 128 * 32;
-  const size_t stage = static_cast<size_t>(D2_ABYTES) + 2 * p.N * 128;
-  if (desc + stage + 256 > 232448) return false;
-  // two stages overlap the gathers of one chunk with the MMAs of the previous one; more only takes L1 away from the
-  // gathers (shared memory and L1 share the SM's 256 KB)
-  p.NST = static_cast<int>(min(static_cast<size_t>(2), (232448 - desc - 256) / stage));
+  const size_t bst = static_cast<size_t>(2) * p.N * 128;             // one weight stage
+  // The A ring has two stages (the gathers of one chunk under the MMAs of the previous one) and the weight ring two of
+  // its own.  Deeper weight rings measured slower at 128 -> 128 (2 / 3 / 4 stages: 175 / 181 / 185 us: the gathers, not
+  // the weight stream, set the pace there).  The 32-byte descriptors are kept where everything fits; at 256 output
+  // channels per group only the 20-byte form leaves room for the second weight stage (one stage: 502 us, two: 387 us).
+  p.NST = 2;
+  p.compact = 0;
+  size_t desc = static_cast<size_t>(p.dg) * T * 128 * 32;
+  size_t fixed = 2 * static_cast<size_t>(D2_ABYTES) + desc + 256;
+  if (fixed + p.NST * bst > 232448) {
+    p.compact = 1;
+    desc = static_cast<size_t>(p.dg) * T * 128 * 20;
+    fixed = 2 * static_cast<size_t>(D2_ABYTES) + desc + 256;
+    if (fixed + p.NST * bst > 232448) p.NST = 1;
+    if (fixed + p.NST * bst > 232448) return false;
+  }
   if (const char* e = tuning_env("SF_DCN2_NST"))
-    p.NST = static_cast<int>(min(static_cast<size_t>(max(1, atoi(e))), min(static_cast<size_t>(D2_MAXST), (232448 - desc - 256) / stage)));
-  *smem_out = p.NST * stage + desc + 256;
+    p.NST = static_cast<int>(min(static_cast<size_t>(max(1, atoi(e))), min(static_cast<size_t>(D2_MAXST), (232448 - fixed) / bst)));
+  *smem_out = fixed + p.NST * bst;
   p.tiles_x = ceil_div(p.Wo, 16);
   p.nptile = p.tiles_x * ceil_div(p.Ho, 8);
   const long long nt = 1LL * p.B * p.G * p.nptile;

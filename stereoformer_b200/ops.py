@@ -150,6 +150,21 @@ def soft_argmin(cv, match_similarity=True, with_prob=False):
     return (disp, prob) if with_prob else disp
 
 
+def _check_bounds(lo, up, mode, n):
+    """lo / up element counts the kernels read: HEAD takes lo as the [B,2,H,W] head output, OFFSETS / ABSOLUTE and
+    VARIANCE_BOUNDS take one value per pixel each (a wrong shape would be an out-of-bounds device read)."""
+    if mode == SF_WIN_HEAD:
+        if lo is None or lo.numel() != 2 * n:
+            raise ValueError("SF_WIN_HEAD needs lo = the offset head's [B,2,H,W] output (%d elements)" % (2 * n))
+    elif mode in (SF_WIN_OFFSETS, SF_WIN_ABSOLUTE):
+        if lo is None or up is None or lo.numel() != n or up.numel() != n:
+            raise ValueError("lower / upper bounds must have B*H*W = %d elements each" % n)
+    else:
+        for t, name in ((lo, "lower"), (up, "upper")):
+            if t is not None and t.numel() != n:
+                raise ValueError("%s bound must have B*H*W = %d elements" % (name, n))
+
+
 def local_window(cv, disp=None, lo=None, up=None, mode=SF_WIN_FIXED, radius=0.0, gamma=1.0, n_points=10,
                  consider_valid=False, div_mode=SF_DIV_TRUE, debug=False, return_disp0=False, out=None, peers=None,
                  peer_offset=0, gather=None):
@@ -172,6 +187,7 @@ def local_window(cv, disp=None, lo=None, up=None, mode=SF_WIN_FIXED, radius=0.0,
             raise ValueError("cur_disparity must have B*H*W elements")
     lo = _chk(lo, "lower bound") if lo is not None else None
     up = _chk(up, "upper bound") if up is not None else None
+    _check_bounds(lo, up, int(mode), B * H * W)
     if out is None:
         out = torch.empty((B, 1, H, W), device=cv.device, dtype=torch.float32)
     elif out.dtype != torch.float32 or out.numel() != B * H * W or not out.is_contiguous() or out.device != cv.device:
@@ -449,6 +465,7 @@ def local_window_backward(cv, disp, lo, up, grad_out, mode=SF_WIN_FIXED, radius=
         raise ValueError("cur_disparity / grad_out must have B*H*W elements")
     lo = _chk(lo, "lower bound") if lo is not None else None
     up = _chk(up, "upper bound") if up is not None else None
+    _check_bounds(lo, up, int(mode), B * H * W)
     gcv = torch.empty_like(cv) if needs[0] else None
     gd = torch.empty_like(disp) if needs[1] else None
     glo = torch.empty_like(lo) if (needs[2] and lo is not None) else None

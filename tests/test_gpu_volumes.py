@@ -347,3 +347,22 @@ def test_whole_chain_epe_at_baseline_shapes(ops, name, shape):
     d0 = O.soft_argmin(cv_ref).unsqueeze(1)
     near = ((d0 - 2).abs() < 1e-3) | ((d0 + 2 - (D - 1)).abs() < 1e-3)
     assert float(err[~near].max()) <= 1e-2
+
+
+def test_bound_tensors_are_size_checked(ops):
+    """A wrongly shaped lower / upper bound must be an error, not an out-of-bounds device read."""
+    cv = torch.randn(1, 8, 4, 16, device="cuda")
+    disp = torch.rand(1, 1, 4, 16, device="cuda") * 7
+    good = torch.rand(1, 1, 4, 16, device="cuda")
+    bad = (ValueError, RuntimeError)            # the ctypes binding raises ValueError, the torch-extension front end RuntimeError
+    with pytest.raises(bad):
+        ops.local_window(cv, disp, lo=good[:, :, :2].contiguous(), up=good, mode=ops.SF_WIN_OFFSETS, n_points=10)
+    with pytest.raises(bad):
+        ops.local_window(cv, disp, lo=good, up=None, mode=ops.SF_WIN_ABSOLUTE, n_points=10)
+    with pytest.raises(bad):
+        ops.local_window(cv, disp, lo=good, mode=ops.SF_WIN_HEAD, n_points=10)
+    with pytest.raises(ValueError, match="elements"):          # debug outputs force the ctypes binding
+        ops.local_window(cv, disp, lo=good[:, :, :2].contiguous(), up=good, mode=ops.SF_WIN_OFFSETS, n_points=10, debug=True)
+    with pytest.raises(ValueError, match="elements"):
+        ops.local_window_backward(cv, disp, good[:, :, :2].contiguous(), good, good, ops.SF_WIN_OFFSETS, 0.0, 10, True)
+    ops.local_window(cv, disp, lo=good, up=good + 1, mode=ops.SF_WIN_OFFSETS, n_points=10)
