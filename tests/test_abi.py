@@ -59,3 +59,16 @@ def test_product_never_imports_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h")):
                 src = open(os.path.join(dp, f)).read()
                 assert "import oracle" not in src and "from oracle" not in src and "oracle/" not in src, f
+
+
+def test_workspace_queries_are_host_only(so):
+    """The size queries make no CUDA call, so a caller can plan its buffers without a device (sizes per DESIGN section 3)."""
+    h = so.lib()
+    small = int(h.sf_dcn_workspace_bytes(128, 128, 3, 3, 1))
+    assert small == 2 * 128 * 1152 * 2                                   # bf16 hi + mid of [Cout][Cin*9]
+    big = int(h.sf_dcn_workspace_bytes_ex(1, 128, 248, 360, 128, 3, 3, 1, 1))
+    assert big == small + 248 * 360 * 128 * 4                            # + the channels-last copy of the input
+    assert int(h.sf_dcn_workspace_bytes_ex(8, 16, 68, 120, 16, 3, 3, 1, 1)) == int(h.sf_dcn_workspace_bytes(16, 16, 3, 3, 1))
+    assert int(h.sf_dcn_workspace_bytes_ex(1, 64, 40, 56, 128, 3, 3, 1, 2)) == int(h.sf_dcn_workspace_bytes(64, 128, 3, 3, 1))
+    assert int(h.sf_dcn_static_scratch_bytes()) == 4 * 1024 * 1024
+    assert int(h.sf_dcn_workspace_bytes(256, 256, 3, 3, 1)) <= int(h.sf_dcn_static_scratch_bytes())
