@@ -383,7 +383,9 @@ int launch_attn_tc(const void* q, const void* k, const void* v, void* out, int B
   // clock64 timeline (tools/timeline_attn.py): a Q/K stage is reloaded ~5000 cycles after its MMAs commit and V is held
   // from its load until P V, so with one tile of buffers the load latency is the tile period.  A third stage paid for by
   // dropping the output tile (epilogue warps storing bf16 rows straight to global memory) measured SLOWER (74.5 vs 65.0
-  // us at C = 128: the direct stores hold the O accumulator and with it the next P V); the ring stays at two stages.
+  // us at C = 128: the direct stores hold the O accumulator and with it the next P V; packing the row to bf16 in
+  // registers and releasing O before the stores: 88 us -- 512 two-byte store instructions per tile from four warps take
+  // longer than a tile); the ring stays at two stages.
   const int NC = C / 64;
   p.tma_out = C <= 128 ? 1 : 0;
   p.nstage = 2;
