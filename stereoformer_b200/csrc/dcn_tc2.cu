@@ -23,8 +23,8 @@
 // 590 KB per tile) paces the loop at ~1.2k cycles per chunk.  Measured and not kept: 8 lanes per pixel with descriptors
 // in registers (shuffles) and packed FFMA2 (fewer instructions, but spills under the 80-register cap of 704 threads:
 // 191 us), an L1 prefetch of the next chunk's lines (evicts live lines: 240 us).
-// Shapes: channels per group and per deformable group multiples of 64, <= 256 output channels per group; anything else
-// takes dcn_tc.cu / dcn.cu.  fp32 parity: 3-term split, ~2^-16 relative per product (tests: 1e-4 of the output magnitude).
+// Shapes: 32 channels per group (two taps share a 64-wide chunk) or a multiple of 64, deformable groups aligned with the
+// chunk's channels, <= 256 output channels per group; anything else takes dcn_tc.cu / dcn.cu.  fp32 parity: 3-term split, ~2^-16 relative per product (tests: 1e-4 of the output magnitude).
 #include <cuda_bf16.h>
 #include <stdlib.h>
 
@@ -65,17 +65,21 @@ dcn_nchw_to_nhwc_kernel(const float* __restrict__ in, float* __restrict__ out, i
   }
 }
 
-// fp32 weights [Cout][Cig][T] -> bf16 hi / mid [2][Cout][K], reduction index k = (c / 64) * T * 64 + t * 64 + c % 64
+// fp32 weights [Cout][Cig][T] -> bf16 hi / mid [2][Cout][K], K = nchunk * 64.  Chunk (cc, tg) holds 64 / CB taps of CB
+// channels each: k = (cc * ntg + tg) * 64 + ti * CB + c % CB with tap t = tg * (64 / CB) + ti (zero for t >= T) and
+// channel c = cc * 64 + c % CB  (CB = 64: one tap of a 64-channel block per chunk; CB = 16: four taps of all 16 channels)
 __global__ void dcn_split_weights2_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ ws, int Cout, int K,
-                                          int Cig, int T) {
+                                          int Cig, int T, int CB, int ntg) {
   const size_t n = static_cast<size_t>(Cout) * K;
+  const int tpc = 64 / CB;
   for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n;
        i += static_cast<size_t>(gridDim.x) * blockDim.x) {
     const int k = static_cast<int>(i % K);
     const size_t o = i / K;
-    const int cc = k / (T * 64), r = k - cc * T * 64;
-    const int t = r >> 6, c = cc * 64 + (r & 63);
-    const float v = w[o * K + static_cast<size_t>(c) * T + t];
+    const int ch = k >> 6, r = k & 63;
+    const int cc = ch / ntg, tg = ch - cc * ntg;
+    const int t = tg * tpc + r / CB, c = cc * 64 + r % CB;
+    const float v = t < T ? w[(o * Cig + c) * T + t] : 0.f;
     const __nv_bfloat16 h = __float2bfloat16_rn(v);
     ws[i] = h;
     ws[n + i] = __float2bfloat16_rn(v - __bfloat162float(h));
@@ -144,7 +148,11 @@ dcn_tc2_kernel(const __grid_constant__ CUtensorMap mapW, const DcnTcParams p, co
   } else if (warp < D2_WARP_MMA) {
     // ================================================================= gather warps: column values -> A operand
     const int gw = warp - 1;                               // pixels 8*gw .. 8*gw+7 of the tile
-    const int hw = lane >> 4, cl = 4 * (lane & 15);        // pixel of the pair, first of this lane's 4 channels
+    // 16 lanes per pixel: lane l16 fills K positions 4*l16 .. 4*l16+3 of the chunk row = tap ti of the chunk, channels cl..cl+3
+    const int hw = lane >> 4;                              // pixel of the pair
+    const int lpt = p.CB >> 2;                             // lanes per tap
+    const int ti = (lane & 15) / lpt, cl = 4 * ((lane & 15) % lpt);
+    const int tpc = 64 / p.CB;
     const int cpdg = p.Cin / p.dg;
     const int HW = p.H * p.W;
     const int rowstep = p.W * p.Cin;
@@ -206,10 +214,12 @@ dcn_tc2_kernel(const __grid_constant__ CUtensorMap mapW, const DcnTcParams p, co
       __syncwarp();
       const float* in_b = inT + static_cast<size_t>(b) * HW * p.Cin + static_cast<size_t>(g) * Cig + cl;
       for (int ch = 0; ch < p.nchunk; ++ch) {
-        const int cc = ch / T, t = ch - cc * T;
+        const int cc = ch / p.ntg, tg = ch - cc * p.ntg;
+        const int t = tg * tpc + ti;                           // this lane's tap (padding taps t >= T contribute zeros)
+        const bool tlive = t < T;
         const int dgi = (g * Cig + cc * 64) / cpdg;
         const float* src = in_b + cc * 64;
-        const int dbase = (dgi * T + t) * 128 + 8 * gw + hw;
+        const int dbase = (dgi * T + min(t, T - 1)) * 128 + 8 * gw + hw;
         mbar_wait(&a_empty[s], ph);
         unsigned char* a_hi = sA + s * D2_ABYTES;
 #pragma unroll
@@ -220,7 +230,7 @@ dcn_tc2_kernel(const __grid_constant__ CUtensorMap mapW, const DcnTcParams p, co
 #pragma unroll
             for (int e = 0; e < 2; ++e) {
               bs[e] = d_base[dbase + 2 * (i2 + e)];
-              wt[e] = d_w[dbase + 2 * (i2 + e)];
+              wt[e] = tlive ? d_w[dbase + 2 * (i2 + e)] : make_float4(0.f, 0.f, 0.f, 0.f);
             }
 #pragma unroll
             for (int e = 0; e < 2; ++e) {
@@ -234,7 +244,7 @@ dcn_tc2_kernel(const __grid_constant__ CUtensorMap mapW, const DcnTcParams p, co
 #pragma unroll
             for (int e = 0; e < 2; ++e) {
               off[e] = d_off[dbase + 2 * (i2 + e)];
-              wt[e] = d_w[dbase + 2 * (i2 + e)];
+              wt[e] = tlive ? d_w[dbase + 2 * (i2 + e)] : make_float4(0.f, 0.f, 0.f, 0.f);
             }
 #pragma unroll
             for (int e = 0; e < 2; ++e) {
@@ -342,10 +352,15 @@ static bool dcn_tc2_plan(DcnTcParams& p, size_t* smem_out) {
   const int T = p.kh * p.kw;
   if (p.G <= 0 || p.dg <= 0 || p.Cin % p.G || p.Cout % p.G || p.Cin % p.dg) return false;
   const int Cig = p.Cin / p.G, Cog = p.Cout / p.G;
-  if (Cig % 64 != 0 || (p.Cin / p.dg) % 64 != 0 || Cog > 256 || Cog < 8) return false;
+  // 16 channels per group also work (four taps per chunk) but the specialised FFMA kernel is faster there (29 vs 40 us at
+  // the shipped 8 x 16 -> 16 x 68 x 120 shape: three launches and the per-tile descriptor phase dominate), so it is not taken
+  if (Cig != 32 && Cig % 64 != 0) return false;
+  p.CB = min(Cig, 64);
+  if ((p.Cin / p.dg) % p.CB != 0 || Cog > 256 || Cog < 8) return false;
   if (1LL * p.H * p.W * p.Cin >= (1LL << 31)) return false;          // corner offsets are 32-bit element indices
-  p.K = Cig * T;
-  p.nchunk = p.K / D2_KC;
+  p.ntg = ceil_div(T, 64 / p.CB);
+  p.nchunk = max(1, Cig / 64) * p.ntg;
+  p.K = p.nchunk * D2_KC;                                            // padded with zero taps when 64 / CB does not divide T
   p.N = ceil_div(Cog, 16) * 16;
   const size_t bst = static_cast<size_t>(2) * p.N * 128;             // one weight stage
   // The A ring has two stages (the gathers of one chunk under the MMAs of the previous one) and the weight ring two of
@@ -401,7 +416,7 @@ int launch_dcn_tc2(DcnTcParams p, const float* weight, void* workspace, size_t w
   {
     const size_t n = static_cast<size_t>(p.Cout) * p.K;
     const int grid = static_cast<int>(min(static_cast<size_t>(sm_count()) * 8, (n + 255) / 256));
-    dcn_split_weights2_kernel<<<grid, 256, 0, stream>>>(weight, ws, p.Cout, p.K, p.Cin / p.G, p.kh * p.kw);
+    dcn_split_weights2_kernel<<<grid, 256, 0, stream>>>(weight, ws, p.Cout, p.K, p.Cin / p.G, p.kh * p.kw, p.CB, p.ntg);
     SF_LAUNCH_CHECK();
     const int HW = p.H * p.W;
     dim3 tg(ceil_div(HW, 32), ceil_div(p.Cin, 32), p.B);

@@ -36,8 +36,9 @@ CASES = [  # B, Cin, Cout, H, W, groups, dg, stride, pad, dil
     (1, 128, 128, 17, 33, 1, 2, 2, 2, 2),      # two deformable groups, stride 2, dilation 2
     (1, 64, 256, 9, 50, 1, 1, 1, 1, 1),        # 256 output channels (full accumulator width)
     (1, 192, 96, 16, 16, 1, 3, 1, 0, 1),       # three 64-channel blocks / deformable groups, no padding, ragged N
+    (2, 64, 32, 21, 30, 2, 2, 1, 1, 1),        # 32 channels per group: two taps per chunk, the ninth tap shares one with padding
 ]
-TC2 = CASES[-4:]
+TC2 = CASES[-5:]
 
 
 @pytest.mark.parametrize("case", CASES)

@@ -2,4 +2,4 @@
 # A/B of the channels-last DCN kernel in the tuning build (env hooks SF_DCN2_*)
 export SF_TUNING_LIB=1
 run() { echo "== $*"; env "$@" timeout 100 python tools/time_dcn2.py ${SH:-dcn_128} 2>&1 | tail -4 | cut -c1-200; }
-SH="dcn_128 dcn_256 dcn_128x8 dcn_128_256" run A=base
+SH="dcn_16 dcn_32 dcn_128 dcn_256" run A=auto
