@@ -190,8 +190,7 @@ SF_API int sf_dcn_forward_f32(const float* input, const float* weight, const flo
  * algo: SF_ALGO_AUTO (tcgen05 implicit GEMM when >= 32 channels per group on both sides, else the exact FFMA
  * kernel), SF_ALGO_GENERIC (always the exact FFMA kernel), SF_ALGO_TC (force; errors if the shape does not fit). */
 SF_API size_t sf_dcn_workspace_bytes(int Cin, int Cout, int kh, int kw, int group);
-/* Workspace that also enables the channels-last gather kernel (csrc/dcn_tc2.cu: 32 or a multiple of 64 channels per group,
- * deformable groups aligned with them): the weights' bf16 copy + a [B][H*W][Cin] fp32 copy of the input.  sf_dcn_forward_ws_f32 picks
+/* Workspace that also enables the channels-last gather kernel (csrc/dcn_tc2.cu: 32 or a multiple of 64 channels per group): the weights' bf16 copy + a [B][H*W][Cin] fp32 copy of the input.  sf_dcn_forward_ws_f32 picks
  * the kernel from the workspace it is given: >= this size -> channels-last gathers, >= sf_dcn_workspace_bytes -> gathers
  * from NCHW, less -> the exact FFMA kernel (SF_ALGO_AUTO) or an error (SF_ALGO_TC). */
 SF_API size_t sf_dcn_workspace_bytes_ex(int B, int Cin, int H, int W, int Cout, int kh, int kw, int group,

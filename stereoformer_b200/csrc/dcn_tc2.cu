@@ -23,8 +23,8 @@
 // 590 KB per tile) paces the loop at ~1.2k cycles per chunk.  Measured and not kept: 8 lanes per pixel with descriptors
 // in registers (shuffles) and packed FFMA2 (fewer instructions, but spills under the 80-register cap of 704 threads:
 // 191 us), an L1 prefetch of the next chunk's lines (evicts live lines: 240 us).
-// Shapes: 32 channels per group (two taps share a 64-wide chunk) or a multiple of 64, deformable groups aligned with the
-// chunk's channels, <= 256 output channels per group; anything else takes dcn_tc.cu / dcn.cu.  fp32 parity: 3-term split, ~2^-16 relative per product (tests: 1e-4 of the output magnitude).
+// Shapes: 32 channels per group (two taps share a 64-wide chunk) or a multiple of 64, channels per deformable group a
+// multiple of 4, <= 256 output channels per group; anything else takes dcn_tc.cu / dcn.cu.  fp32 parity: 3-term split, ~2^-16 relative per product (tests: 1e-4 of the output magnitude).
 #include <cuda_bf16.h>
 #include <stdlib.h>
 
@@ -213,11 +213,13 @@ dcn_tc2_kernel(const __grid_constant__ CUtensorMap mapW, const DcnTcParams p, co
       }
       __syncwarp();
       const float* in_b = inT + static_cast<size_t>(b) * HW * p.Cin + static_cast<size_t>(g) * Cig + cl;
+      int dgi = 0;
       for (int ch = 0; ch < p.nchunk; ++ch) {
         const int cc = ch / p.ntg, tg = ch - cc * p.ntg;
         const int t = tg * tpc + ti;                           // this lane's tap (padding taps t >= T contribute zeros)
         const bool tlive = t < T;
-        const int dgi = (g * Cig + cc * 64) / cpdg;
+        if (tg == 0) dgi = (g * Cig + cc * 64 + cl) / cpdg;    // deformable group of THIS lane's 4 channels (per lane: a
+                                                               // 64-channel block may span several deformable groups)
         const float* src = in_b + cc * 64;
         const int dbase = (dgi * T + min(t, T - 1)) * 128 + 8 * gw + hw;
         mbar_wait(&a_empty[s], ph);
@@ -356,7 +358,7 @@ static bool dcn_tc2_plan(DcnTcParams& p, size_t* smem_out) {
   // the shipped 8 x 16 -> 16 x 68 x 120 shape: three launches and the per-tile descriptor phase dominate), so it is not taken
   if (Cig != 32 && Cig % 64 != 0) return false;
   p.CB = min(Cig, 64);
-  if ((p.Cin / p.dg) % p.CB != 0 || Cog > 256 || Cog < 8) return false;
+  if ((p.Cin / p.dg) % 4 != 0 || Cog > 256 || Cog < 8) return false;   // a lane's 4 channels share a deformable group
   if (1LL * p.H * p.W * p.Cin >= (1LL << 31)) return false;          // corner offsets are 32-bit element indices
   p.ntg = ceil_div(T, 64 / p.CB);
   p.nchunk = max(1, Cig / 64) * p.ntg;

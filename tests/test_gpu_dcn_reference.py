@@ -68,12 +68,12 @@ def test_forward_matches_reference_extension(case):
 def test_channels_last_cases_take_the_channels_last_kernel():
     """The workspace query is what routes a call: the cases meant for dcn_tc2 must be eligible for it."""
     from stereoformer_b200 import _lib
-    for B, Cin, Cout, H, W, G, dg, s, p, d in TC2 + [CASES[3]]:
+    for B, Cin, Cout, H, W, G, dg, s, p, d in TC2 + [CASES[2], CASES[3]]:
         small = int(_lib.lib().sf_dcn_workspace_bytes(Cin, Cout, 3, 3, G))
         big = int(_lib.lib().sf_dcn_workspace_bytes_ex(B, Cin, H, W, Cout, 3, 3, G, dg))
         assert big >= small + B * Cin * H * W * 4, (Cin, Cout, G, dg)
-    assert int(_lib.lib().sf_dcn_workspace_bytes_ex(1, 64, 40, 56, 128, 3, 3, 1, 2)) == \
-        int(_lib.lib().sf_dcn_workspace_bytes(64, 128, 3, 3, 1))           # 32 channels per deformable group: NCHW gathers
+    assert int(_lib.lib().sf_dcn_workspace_bytes_ex(2, 16, 34, 60, 16, 3, 3, 1, 1)) == \
+        int(_lib.lib().sf_dcn_workspace_bytes(16, 16, 3, 3, 1))            # 16 channels per group: the specialised FFMA kernel
 
 
 @pytest.mark.parametrize("case", CASES[:3] + CASES[4:6])
