@@ -270,6 +270,18 @@ SF_API int sf_dcn_backward_f32(const float* input, const float* weight, const fl
                                float* grad_offset, float* grad_mask, int B, int Cin, int H, int W, int Cout, int kh,
                                int kw, int stride_h, int stride_w, int pad_h, int pad_w, int dil_h, int dil_w,
                                int group, int deformable_group, void* stream);
+/* The same with the weight gradient on the tensor cores (csrc/dcn_bwd_tc.cu) where the channels-last forward kernel
+ * applies: workspace = sf_dcn_backward_workspace_bytes bytes (a channels-last copy of the input; 0 = shape not taken),
+ * algo = SF_ALGO_AUTO (tensor cores when the workspace suffices), SF_ALGO_GENERIC / SF_ALGO_EXACT (= sf_dcn_backward_f32),
+ * SF_ALGO_TC (error if the shape or workspace does not fit).  Data / offset / mask gradients are the same fp32 kernels. */
+SF_API size_t sf_dcn_backward_workspace_bytes(int B, int Cin, int H, int W, int Cout, int kh, int kw, int group,
+                                              int deformable_group);
+SF_API int sf_dcn_backward_ws_f32(const float* input, const float* weight, const float* offset, const float* mask,
+                                  const float* grad_out, float* grad_input, float* grad_weight, float* grad_bias,
+                                  float* grad_offset, float* grad_mask, int B, int Cin, int H, int W, int Cout, int kh,
+                                  int kw, int stride_h, int stride_w, int pad_h, int pad_w, int dil_h, int dil_w,
+                                  int group, int deformable_group, void* workspace, size_t workspace_bytes, int algo,
+                                  void* stream);
 
 /* a10 / f3 in double precision: the reference dispatches its DCN over float and double
  * (modulated_deform_conv_cuda.cu:93) and its gradient tests run in double (deform/test.py:376-403).  Same arguments

@@ -47,6 +47,8 @@ SIGNATURES = {
     "sf_guidance_backward_f32": [_p] * 7 + [_c_int] * 6 + [_p],
     "sf_upsample_convex_backward_f32": [_p, _p, _c_float, _p, _p, _p] + [_c_int] * 4 + [_p],
     "sf_dcn_backward_f32": [_p] * 10 + [_c_int] * 15 + [_p],
+    "sf_dcn_backward_workspace_bytes": [_c_int] * 9,
+    "sf_dcn_backward_ws_f32": [_p] * 10 + [_c_int] * 15 + [_p, ctypes.c_size_t, _c_int, _p],
     "sf_dcn_forward_f64": [_p] * 6 + [_c_int] * 15 + [_p],
     "sf_dcn_backward_f64": [_p] * 10 + [_c_int] * 15 + [_p],
     "sf_dcn_workspace_bytes": [_c_int] * 5,
@@ -65,7 +67,7 @@ SIGNATURES = {
     "sf_gru_blend_f32": [_p, ctypes.c_longlong, _p, _p, _p] + [_c_int] * 5 + [_p],
 }
 
-RESTYPES = {"sf_dcn_workspace_bytes": ctypes.c_size_t, "sf_dcn_workspace_bytes_ex": ctypes.c_size_t, "sf_dcn_static_scratch_bytes": ctypes.c_size_t, "sf_corr1d_alt_workspace_bytes": ctypes.c_size_t}   # everything else returns an int status code
+RESTYPES = {"sf_dcn_workspace_bytes": ctypes.c_size_t, "sf_dcn_backward_workspace_bytes": ctypes.c_size_t, "sf_dcn_workspace_bytes_ex": ctypes.c_size_t, "sf_dcn_static_scratch_bytes": ctypes.c_size_t, "sf_corr1d_alt_workspace_bytes": ctypes.c_size_t}   # everything else returns an int status code
 
 _lib = None
 

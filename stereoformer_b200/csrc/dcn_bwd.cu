@@ -21,6 +21,7 @@
 //   * dcn_bwd_bias_kernel   -- one CTA per output channel.
 #include <algorithm>
 #include "common.cuh"
+#include "dcn_tc.cuh"
 #include "../../include/stereoformer_b200.h"
 
 namespace sf {
@@ -313,12 +314,48 @@ static int gcd_i(int a, int b) { return b ? gcd_i(b, a % b) : a; }
 
 }  // namespace sf
 
+static int dcn_backward_impl(const float* input, const float* weight, const float* offset, const float* mask,
+                             const float* grad_out, float* grad_input, float* grad_weight, float* grad_bias,
+                             float* grad_offset, float* grad_mask, int B, int Cin, int H, int W, int Cout, int kh,
+                             int kw, int stride_h, int stride_w, int pad_h, int pad_w, int dil_h, int dil_w,
+                             int group, int deformable_group, void* workspace, size_t workspace_bytes, int algo,
+                             void* stream);
+
 extern "C" int sf_dcn_backward_f32(const float* input, const float* weight, const float* offset, const float* mask,
                                    const float* grad_out, float* grad_input, float* grad_weight, float* grad_bias,
                                    float* grad_offset, float* grad_mask, int B, int Cin, int H, int W, int Cout, int kh,
                                    int kw, int stride_h, int stride_w, int pad_h, int pad_w, int dil_h, int dil_w,
                                    int group, int deformable_group, void* stream) {
+  return dcn_backward_impl(input, weight, offset, mask, grad_out, grad_input, grad_weight, grad_bias, grad_offset,
+                           grad_mask, B, Cin, H, W, Cout, kh, kw, stride_h, stride_w, pad_h, pad_w, dil_h, dil_w, group,
+                           deformable_group, nullptr, 0, SF_ALGO_GENERIC, stream);
+}
+
+extern "C" size_t sf_dcn_backward_workspace_bytes(int B, int Cin, int H, int W, int Cout, int kh, int kw, int group,
+                                                  int deformable_group) {
+  return sf::dcn_bwd_tc_workspace_bytes(B, Cin, H, W, Cout, kh, kw, group, deformable_group);
+}
+
+extern "C" int sf_dcn_backward_ws_f32(const float* input, const float* weight, const float* offset, const float* mask,
+                                      const float* grad_out, float* grad_input, float* grad_weight, float* grad_bias,
+                                      float* grad_offset, float* grad_mask, int B, int Cin, int H, int W, int Cout,
+                                      int kh, int kw, int stride_h, int stride_w, int pad_h, int pad_w, int dil_h,
+                                      int dil_w, int group, int deformable_group, void* workspace,
+                                      size_t workspace_bytes, int algo, void* stream) {
+  return dcn_backward_impl(input, weight, offset, mask, grad_out, grad_input, grad_weight, grad_bias, grad_offset,
+                           grad_mask, B, Cin, H, W, Cout, kh, kw, stride_h, stride_w, pad_h, pad_w, dil_h, dil_w, group,
+                           deformable_group, workspace, workspace_bytes, algo, stream);
+}
+
+static int dcn_backward_impl(const float* input, const float* weight, const float* offset, const float* mask,
+                             const float* grad_out, float* grad_input, float* grad_weight, float* grad_bias,
+                             float* grad_offset, float* grad_mask, int B, int Cin, int H, int W, int Cout, int kh,
+                             int kw, int stride_h, int stride_w, int pad_h, int pad_w, int dil_h, int dil_w,
+                             int group, int deformable_group, void* workspace, size_t workspace_bytes, int algo,
+                             void* stream) {
   using namespace sf;
+  if (algo == SF_ALGO_EXACT) algo = SF_ALGO_GENERIC;
+  SF_CHECK_ARG(algo == SF_ALGO_AUTO || algo == SF_ALGO_GENERIC || algo == SF_ALGO_TC, "dcn_backward: unknown algo %d", algo);
   SF_CHECK_ARG(input && weight && offset && grad_out, "dcn_backward: null pointer");
   SF_CHECK_ARG(B > 0 && Cin > 0 && H > 0 && W > 0 && Cout > 0 && kh > 0 && kw > 0, "dcn_backward: non-positive dimension");
   SF_CHECK_ARG(stride_h > 0 && stride_w > 0 && dil_h > 0 && dil_w > 0 && pad_h >= 0 && pad_w >= 0,
@@ -353,7 +390,23 @@ extern "C" int sf_dcn_backward_f32(const float* input, const float* weight, cons
     dcn_bwd_data_kernel<<<grid, BW_NT, smem, s>>>(p);
     SF_LAUNCH_CHECK();
   }
-  if (grad_weight) {
+  bool w_done = false;
+  if (grad_weight && algo != SF_ALGO_GENERIC) {
+    // weight gradient on the tensor cores (dcn_bwd_tc.cu) where the forward's channels-last kernel applies and the caller
+    // brought the workspace for the input copy; the data / offset / mask gradients stay on the FFMA kernel above
+    SF_CUDA(cudaMemsetAsync(grad_weight, 0, sizeof(float) * static_cast<size_t>(Cout) * (Cin / group) * T, s));
+    DcnTcParams q{};
+    q.in = input; q.bias = nullptr; q.offset = offset; q.mask = mask; q.out = nullptr;
+    q.B = B; q.Cin = Cin; q.H = H; q.W = W; q.Cout = Cout; q.Ho = p.Ho; q.Wo = p.Wo;
+    q.kh = kh; q.kw = kw; q.sh = stride_h; q.sw = stride_w; q.ph = pad_h; q.pw = pad_w; q.dh = dil_h; q.dw = dil_w;
+    q.G = group; q.dg = deformable_group;
+    const int rc = launch_dcn_bwd_weight_tc(q, grad_out, grad_weight, workspace, workspace_bytes, s, &w_done);
+    if (rc) return rc;
+    SF_CHECK_ARG(w_done || algo != SF_ALGO_TC, "dcn_backward: the tensor-core weight gradient needs %zu workspace bytes "
+                 "(got %zu), 32 or a multiple of 64 channels per group and an output width that is a multiple of 4",
+                 dcn_bwd_tc_workspace_bytes(B, Cin, H, W, Cout, kh, kw, group, deformable_group), workspace_bytes);
+  }
+  if (grad_weight && !w_done) {
     SF_CUDA(cudaMemsetAsync(grad_weight, 0, sizeof(float) * static_cast<size_t>(Cout) * (Cin / group) * T, s));
     const size_t smem = sizeof(float) * static_cast<size_t>(BW_TP) * (BW_OB + 4 + BW_NK + 4) + static_cast<size_t>(T) * BW_TP * sizeof(Desc);
     SF_CUDA(cudaFuncSetAttribute(dcn_bwd_weight_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));

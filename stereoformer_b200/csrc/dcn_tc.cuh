@@ -34,4 +34,13 @@ size_t dcn_tc2_workspace_bytes(int B, int Cin, int H, int W, int Cout, int kh, i
 int launch_dcn_tc2(DcnTcParams p, const float* weight, void* workspace, size_t workspace_bytes, cudaStream_t stream,
                    bool* handled);
 
+// shared with the tensor-core weight gradient (dcn_bwd_tc.cu)
+bool dcn_tc2_plan(DcnTcParams& p, size_t* smem_out);
+int launch_dcn_nhwc(const float* in, float* out, int B, int C, int HW, cudaStream_t stream);
+// grad_weight += grad_out x column tile on tcgen05 (grad_weight zero-filled by the caller); *handled = false when the
+// shape does not fit or the workspace (dcn_bwd_tc_workspace_bytes: the channels-last input copy) is too small
+size_t dcn_bwd_tc_workspace_bytes(int B, int Cin, int H, int W, int Cout, int kh, int kw, int group, int deformable_group);
+int launch_dcn_bwd_weight_tc(DcnTcParams p, const float* grad_out, float* grad_weight, void* workspace,
+                             size_t workspace_bytes, cudaStream_t stream, bool* handled);
+
 }  // namespace sf

@@ -350,7 +350,7 @@ dcn_tc2_kernel(const __grid_constant__ CUtensorMap mapW, const DcnTcParams p, co
   if (warp == D2_WARP_MMA) tmem_free(tmem, 512);
 }
 
-static bool dcn_tc2_plan(DcnTcParams& p, size_t* smem_out) {
+bool dcn_tc2_plan(DcnTcParams& p, size_t* smem_out) {
   const int T = p.kh * p.kw;
   if (p.G <= 0 || p.dg <= 0 || p.Cin % p.G || p.Cout % p.G || p.Cin % p.dg) return false;
   const int Cig = p.Cin / p.G, Cog = p.Cout / p.G;
@@ -393,6 +393,15 @@ static bool dcn_tc2_plan(DcnTcParams& p, size_t* smem_out) {
 
 static size_t align256(size_t x) { return (x + 255) & ~static_cast<size_t>(255); }
 
+// [B][C][HW] -> [B][HW][C] (the channels-last copy the gathers read)
+int launch_dcn_nhwc(const float* in, float* out, int B, int C, int HW, cudaStream_t stream) {
+  dim3 tg(ceil_div(HW, 32), ceil_div(C, 32), B);
+  SF_CHECK_ARG(tg.y <= 65535 && tg.z <= 65535, "dcn: too many channels or images for the channels-last pass");
+  dcn_nchw_to_nhwc_kernel<<<tg, dim3(32, 8), 0, stream>>>(in, out, C, HW);
+  SF_LAUNCH_CHECK();
+  return SF_OK;
+}
+
 // weights (bf16 hi/mid) + the channels-last copy of the input; 0 when the shape does not take this path
 size_t dcn_tc2_workspace_bytes(int B, int Cin, int H, int W, int Cout, int kh, int kw, int group, int deformable_group) {
   DcnTcParams p{};
@@ -420,11 +429,8 @@ int launch_dcn_tc2(DcnTcParams p, const float* weight, void* workspace, size_t w
     const int grid = static_cast<int>(min(static_cast<size_t>(sm_count()) * 8, (n + 255) / 256));
     dcn_split_weights2_kernel<<<grid, 256, 0, stream>>>(weight, ws, p.Cout, p.K, p.Cin / p.G, p.kh * p.kw, p.CB, p.ntg);
     SF_LAUNCH_CHECK();
-    const int HW = p.H * p.W;
-    dim3 tg(ceil_div(HW, 32), ceil_div(p.Cin, 32), p.B);
-    SF_CHECK_ARG(tg.y <= 65535 && tg.z <= 65535, "dcn_forward: too many channels or images for the channels-last pass");
-    dcn_nchw_to_nhwc_kernel<<<tg, dim3(32, 8), 0, stream>>>(p.in, inT, p.Cin, HW);
-    SF_LAUNCH_CHECK();
+    const int rc2 = launch_dcn_nhwc(p.in, inT, p.B, p.Cin, p.H * p.W, stream);
+    if (rc2) return rc2;
   }
   CUtensorMap mW;
   int rc = make_tmap_3d_bf16_sw128(&mW, ws, p.K, p.Cout, 2, p.N, 1);

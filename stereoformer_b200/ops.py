@@ -558,7 +558,7 @@ def upsample_convex_backward(disp, mask, grad_out, factor=8, mask_scale=1.0, nee
 
 
 def dcn_backward(inp, weight, offset, mask, grad_out, stride, padding, dilation, groups, deformable_groups,
-                 needs=(True, True, True, True, True)):
+                 needs=(True, True, True, True, True), algo=None):
     """DCNv2 / DCNv1 (mask None) backward -> (grad_input, grad_offset, grad_mask, grad_weight, grad_bias), the order
     of the reference's DCN.modulated_deform_conv_backward (modulated_deform_conv_cuda.cu:277-279); entries whose
     ``needs`` flag is False (or grad_mask for DCNv1) are None."""
@@ -588,9 +588,19 @@ def dcn_backward(inp, weight, offset, mask, grad_out, stride, padding, dilation,
     g_w = torch.empty_like(weight) if n_w else None
     g_b = torch.empty(Cout, device=inp.device, dtype=dt) if n_b else None
     with torch.cuda.device(inp.device):
-        _lib.call("sf_dcn_backward_f64" if dt == torch.float64 else "sf_dcn_backward_f32", _ptr(inp), _ptr(weight), _ptr(offset), _ptr(mask), _ptr(grad_out), _ptr(g_in),
+        if dt == torch.float64:
+            _lib.call("sf_dcn_backward_f64", _ptr(inp), _ptr(weight), _ptr(offset), _ptr(mask), _ptr(grad_out), _ptr(g_in),
+                      _ptr(g_w), _ptr(g_b), _ptr(g_off), _ptr(g_mask), B, Cin, H, W, Cout, kh, kw, sh, sw, ph, pw, dh, dw,
+                      int(groups), int(deformable_groups), _stream())
+            return g_in, g_off, g_mask, g_w, g_b
+        algo = _algo(algo)
+        nws = int(_lib.lib().sf_dcn_backward_workspace_bytes(B, Cin, H, W, Cout, kh, kw, int(groups), int(deformable_groups))) \
+            if (n_w and algo not in (SF_ALGO_GENERIC, SF_ALGO_EXACT)) else 0
+        ws = torch.empty(nws, device=inp.device, dtype=torch.uint8) if nws else None   # channels-last input copy (scratch)
+        _lib.call("sf_dcn_backward_ws_f32", _ptr(inp), _ptr(weight), _ptr(offset), _ptr(mask), _ptr(grad_out), _ptr(g_in),
                   _ptr(g_w), _ptr(g_b), _ptr(g_off), _ptr(g_mask), B, Cin, H, W, Cout, kh, kw, sh, sw, ph, pw, dh, dw,
-                  int(groups), int(deformable_groups), _stream())
+                  int(groups), int(deformable_groups), _ptr(ws), ctypes.c_size_t(nws), algo if nws or algo != SF_ALGO_AUTO else SF_ALGO_GENERIC,
+                  _stream())
     return g_in, g_off, g_mask, g_w, g_b
 
 
