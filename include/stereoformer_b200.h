@@ -270,11 +270,14 @@ SF_API int sf_dcn_backward_f32(const float* input, const float* weight, const fl
                                float* grad_offset, float* grad_mask, int B, int Cin, int H, int W, int Cout, int kh,
                                int kw, int stride_h, int stride_w, int pad_h, int pad_w, int dil_h, int dil_w,
                                int group, int deformable_group, void* stream);
-/* The same with the weight gradient on the tensor cores (csrc/dcn_bwd_tc.cu) where the channels-last forward kernel
- * applies: workspace = sf_dcn_backward_workspace_bytes bytes (a channels-last copy of the input; 0 = shape not taken),
- * algo = SF_ALGO_AUTO (tensor cores when the workspace suffices), SF_ALGO_GENERIC / SF_ALGO_EXACT (= sf_dcn_backward_f32),
- * SF_ALGO_TC (error if the shape or workspace does not fit).  Data / offset / mask gradients are the same fp32 kernels. */
-SF_API size_t sf_dcn_backward_workspace_bytes(int B, int Cin, int H, int W, int Cout, int kh, int kw, int group,
+/* The same over channels-last copies where the forward's channels-last kernel applies (csrc/dcn_bwd_tc.cu: weight
+ * gradient on the tensor cores; csrc/dcn_bwd_data_tc.cu: column gradient on the tensor cores + a scatter kernel with
+ * vector reductions for grad_input / grad_offset / grad_mask).  workspace = sf_dcn_backward_workspace_bytes bytes
+ * (channels-last input and grad_input copies, the split weights and the column-gradient buffer [pixels][Cin/g * kh*kw];
+ * 0 = shape not taken), algo = SF_ALGO_AUTO (whatever the workspace allows), SF_ALGO_GENERIC / SF_ALGO_EXACT
+ * (= sf_dcn_backward_f32), SF_ALGO_TC (error if the weight gradient cannot take the tensor-core path). */
+SF_API size_t sf_dcn_backward_workspace_bytes(int B, int Cin, int H, int W, int Cout, int kh, int kw, int stride_h,
+                                              int stride_w, int pad_h, int pad_w, int dil_h, int dil_w, int group,
                                               int deformable_group);
 SF_API int sf_dcn_backward_ws_f32(const float* input, const float* weight, const float* offset, const float* mask,
                                   const float* grad_out, float* grad_input, float* grad_weight, float* grad_bias,

@@ -47,7 +47,7 @@ SIGNATURES = {
     "sf_guidance_backward_f32": [_p] * 7 + [_c_int] * 6 + [_p],
     "sf_upsample_convex_backward_f32": [_p, _p, _c_float, _p, _p, _p] + [_c_int] * 4 + [_p],
     "sf_dcn_backward_f32": [_p] * 10 + [_c_int] * 15 + [_p],
-    "sf_dcn_backward_workspace_bytes": [_c_int] * 9,
+    "sf_dcn_backward_workspace_bytes": [_c_int] * 15,
     "sf_dcn_backward_ws_f32": [_p] * 10 + [_c_int] * 15 + [_p, ctypes.c_size_t, _c_int, _p],
     "sf_dcn_forward_f64": [_p] * 6 + [_c_int] * 15 + [_p],
     "sf_dcn_backward_f64": [_p] * 10 + [_c_int] * 15 + [_p],

@@ -331,9 +331,13 @@ extern "C" int sf_dcn_backward_f32(const float* input, const float* weight, cons
                            deformable_group, nullptr, 0, SF_ALGO_GENERIC, stream);
 }
 
-extern "C" size_t sf_dcn_backward_workspace_bytes(int B, int Cin, int H, int W, int Cout, int kh, int kw, int group,
+extern "C" size_t sf_dcn_backward_workspace_bytes(int B, int Cin, int H, int W, int Cout, int kh, int kw, int stride_h,
+                                                  int stride_w, int pad_h, int pad_w, int dil_h, int dil_w, int group,
                                                   int deformable_group) {
-  return sf::dcn_bwd_tc_workspace_bytes(B, Cin, H, W, Cout, kh, kw, group, deformable_group);
+  const size_t a = sf::dcn_bwd_tc_workspace_bytes(B, Cin, H, W, Cout, kh, kw, group, deformable_group);
+  const size_t b = sf::dcn_bwd_data_tc_workspace_bytes(B, Cin, H, W, Cout, kh, kw, stride_h, stride_w, pad_h, pad_w, dil_h,
+                                                       dil_w, group, deformable_group);
+  return a > b ? a : b;
 }
 
 extern "C" int sf_dcn_backward_ws_f32(const float* input, const float* weight, const float* offset, const float* mask,
@@ -381,8 +385,20 @@ static int dcn_backward_impl(const float* input, const float* weight, const floa
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   SF_CHECK_ARG(B <= 65535, "dcn_backward: batch too large");
 
-  if (grad_input) SF_CUDA(cudaMemsetAsync(grad_input, 0, sizeof(float) * static_cast<size_t>(B) * Cin * H * W, s));
-  if (grad_input || grad_offset || grad_mask) {
+  DcnTcParams tq{};
+  tq.in = input; tq.bias = nullptr; tq.offset = offset; tq.mask = mask; tq.out = nullptr;
+  tq.B = B; tq.Cin = Cin; tq.H = H; tq.W = W; tq.Cout = Cout; tq.Ho = p.Ho; tq.Wo = p.Wo;
+  tq.kh = kh; tq.kw = kw; tq.sh = stride_h; tq.sw = stride_w; tq.ph = pad_h; tq.pw = pad_w; tq.dh = dil_h; tq.dw = dil_w;
+  tq.G = group; tq.dg = deformable_group;
+  bool d_done = false;
+  if ((grad_input || grad_offset || grad_mask) && algo != SF_ALGO_GENERIC) {
+    // channels-last path (dcn_bwd_data_tc.cu): column gradient on the tensor cores, vector reductions into grad_input
+    const int rc = launch_dcn_bwd_data_tc(tq, weight, grad_out, grad_input, grad_offset, grad_mask, workspace,
+                                          workspace_bytes, s, &d_done);
+    if (rc) return rc;
+  }
+  if (!d_done && grad_input) SF_CUDA(cudaMemsetAsync(grad_input, 0, sizeof(float) * static_cast<size_t>(B) * Cin * H * W, s));
+  if (!d_done && (grad_input || grad_offset || grad_mask)) {
     const size_t smem = sizeof(float) * (static_cast<size_t>(BW_OB) * BW_TP + BW_OB * (BW_NK + 4) + BW_NK * BW_TP) +
                         static_cast<size_t>(T) * BW_TP * (sizeof(Desc) + 3 * sizeof(float));
     SF_CUDA(cudaFuncSetAttribute(dcn_bwd_data_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
@@ -395,12 +411,7 @@ static int dcn_backward_impl(const float* input, const float* weight, const floa
     // weight gradient on the tensor cores (dcn_bwd_tc.cu) where the forward's channels-last kernel applies and the caller
     // brought the workspace for the input copy; the data / offset / mask gradients stay on the FFMA kernel above
     SF_CUDA(cudaMemsetAsync(grad_weight, 0, sizeof(float) * static_cast<size_t>(Cout) * (Cin / group) * T, s));
-    DcnTcParams q{};
-    q.in = input; q.bias = nullptr; q.offset = offset; q.mask = mask; q.out = nullptr;
-    q.B = B; q.Cin = Cin; q.H = H; q.W = W; q.Cout = Cout; q.Ho = p.Ho; q.Wo = p.Wo;
-    q.kh = kh; q.kw = kw; q.sh = stride_h; q.sw = stride_w; q.ph = pad_h; q.pw = pad_w; q.dh = dil_h; q.dw = dil_w;
-    q.G = group; q.dg = deformable_group;
-    const int rc = launch_dcn_bwd_weight_tc(q, grad_out, grad_weight, workspace, workspace_bytes, s, &w_done);
+    const int rc = launch_dcn_bwd_weight_tc(tq, grad_out, grad_weight, workspace, workspace_bytes, s, d_done, &w_done);
     if (rc) return rc;
     SF_CHECK_ARG(w_done || algo != SF_ALGO_TC, "dcn_backward: the tensor-core weight gradient needs %zu workspace bytes "
                  "(got %zu), 32 or a multiple of 64 channels per group and an output width that is a multiple of 4",

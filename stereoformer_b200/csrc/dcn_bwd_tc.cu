@@ -244,7 +244,7 @@ size_t dcn_bwd_tc_workspace_bytes(int B, int Cin, int H, int W, int Cout, int kh
 }
 
 int launch_dcn_bwd_weight_tc(DcnTcParams p, const float* grad_out, float* grad_weight, void* workspace,
-                             size_t workspace_bytes, cudaStream_t stream, bool* handled) {
+                             size_t workspace_bytes, cudaStream_t stream, bool have_input_copy, bool* handled) {
   *handled = false;
   const size_t need = dcn_bwd_tc_workspace_bytes(p.B, p.Cin, p.H, p.W, p.Cout, p.kh, p.kw, p.G, p.dg);
   if (need == 0 || workspace == nullptr || workspace_bytes < need || (reinterpret_cast<uintptr_t>(workspace) & 127) != 0)
@@ -265,7 +265,7 @@ int launch_dcn_bwd_weight_tc(DcnTcParams p, const float* grad_out, float* grad_w
   const int NT = p.B * p.nptile;
   q.nrange = max(1, min(NT, sm_count() / units));
   float* inT = static_cast<float*>(workspace);
-  int rc = launch_dcn_nhwc(p.in, inT, p.B, p.Cin, p.H * p.W, stream);
+  int rc = have_input_copy ? SF_OK : launch_dcn_nhwc(p.in, inT, p.B, p.Cin, p.H * p.W, stream);
   if (rc) return rc;
   CUtensorMap mG;
   rc = make_tmap_3d_f32(&mG, grad_out, p.Wo, p.Ho, static_cast<uint64_t>(p.B) * p.Cout, 16, 8, 32);

@@ -41,6 +41,12 @@ int launch_dcn_nhwc(const float* in, float* out, int B, int C, int HW, cudaStrea
 // shape does not fit or the workspace (dcn_bwd_tc_workspace_bytes: the channels-last input copy) is too small
 size_t dcn_bwd_tc_workspace_bytes(int B, int Cin, int H, int W, int Cout, int kh, int kw, int group, int deformable_group);
 int launch_dcn_bwd_weight_tc(DcnTcParams p, const float* grad_out, float* grad_weight, void* workspace,
-                             size_t workspace_bytes, cudaStream_t stream, bool* handled);
+                             size_t workspace_bytes, cudaStream_t stream, bool have_input_copy, bool* handled);
+// grad_input / grad_offset / grad_mask over channels-last copies (dcn_bwd_data_tc.cu): column gradient on tcgen05 into the
+// workspace, then a scatter kernel with vector reductions; the workspace starts with the channels-last input copy
+size_t dcn_bwd_data_tc_workspace_bytes(int B, int Cin, int H, int W, int Cout, int kh, int kw, int stride_h, int stride_w,
+                                       int pad_h, int pad_w, int dil_h, int dil_w, int group, int deformable_group);
+int launch_dcn_bwd_data_tc(DcnTcParams p, const float* weight, const float* grad_out, float* grad_input, float* grad_offset,
+                           float* grad_mask, void* workspace, size_t workspace_bytes, cudaStream_t stream, bool* handled);
 
 }  // namespace sf

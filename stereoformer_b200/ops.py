@@ -594,9 +594,10 @@ def dcn_backward(inp, weight, offset, mask, grad_out, stride, padding, dilation,
                       int(groups), int(deformable_groups), _stream())
             return g_in, g_off, g_mask, g_w, g_b
         algo = _algo(algo)
-        nws = int(_lib.lib().sf_dcn_backward_workspace_bytes(B, Cin, H, W, Cout, kh, kw, int(groups), int(deformable_groups))) \
-            if (n_w and algo not in (SF_ALGO_GENERIC, SF_ALGO_EXACT)) else 0
-        ws = torch.empty(nws, device=inp.device, dtype=torch.uint8) if nws else None   # channels-last input copy (scratch)
+        nws = int(_lib.lib().sf_dcn_backward_workspace_bytes(B, Cin, H, W, Cout, kh, kw, sh, sw, ph, pw, dh, dw, int(groups),
+                                                             int(deformable_groups))) \
+            if algo not in (SF_ALGO_GENERIC, SF_ALGO_EXACT) else 0
+        ws = torch.empty(nws, device=inp.device, dtype=torch.uint8) if nws else None   # channels-last copies + column gradients (scratch)
         _lib.call("sf_dcn_backward_ws_f32", _ptr(inp), _ptr(weight), _ptr(offset), _ptr(mask), _ptr(grad_out), _ptr(g_in),
                   _ptr(g_w), _ptr(g_b), _ptr(g_off), _ptr(g_mask), B, Cin, H, W, Cout, kh, kw, sh, sw, ph, pw, dh, dw,
                   int(groups), int(deformable_groups), _ptr(ws), ctypes.c_size_t(nws), algo if nws or algo != SF_ALGO_AUTO else SF_ALGO_GENERIC,

@@ -76,7 +76,17 @@ def test_channels_last_cases_take_the_channels_last_kernel():
         int(_lib.lib().sf_dcn_workspace_bytes(16, 16, 3, 3, 1))            # 16 channels per group: the specialised FFMA kernel
 
 
-@pytest.mark.parametrize("case", CASES[:3] + CASES[4:6])
+BWD_TC = [  # shapes that take the channels-last backward kernels (output width a multiple of 4)
+    (1, 128, 128, 24, 36, 1, 1, 1, 1, 1),      # one 128-row block of output channels, ragged 8x16 tiles
+    (2, 64, 64, 16, 20, 1, 1, 1, 1, 1),        # batch 2, a single 64-channel block
+    (1, 128, 64, 18, 28, 2, 2, 1, 1, 1),       # two convolution groups = two deformable groups (offset / mask sums per group)
+    (1, 64, 256, 9, 52, 1, 1, 1, 1, 1),        # two 128-row blocks of output channels
+    (1, 128, 128, 33, 47, 1, 1, 2, 1, 1),      # stride 2
+    (1, 32, 32, 12, 16, 1, 1, 1, 2, 2),        # 32 channels per group (two taps per chunk), dilation 2
+]
+
+
+@pytest.mark.parametrize("case", CASES[:3] + CASES[4:6] + BWD_TC)
 def test_backward_matches_reference_extension(case):
     import stereoformer_b200.DCN as ours
     ref = _ref()
