@@ -291,22 +291,33 @@ dcn_bwd_weight_kernel(const DcnBwdParams p) {
   }
 }
 
-__global__ void __launch_bounds__(256)
+// one CTA of 1024 threads per output channel, 16-byte loads when the rows allow it (a 256-thread scalar version ran at
+// 1.6 TB/s: 28 us for the 45.7 MB of grad_out at 128 channels x 248 x 360)
+__global__ void __launch_bounds__(1024)
 dcn_bwd_bias_kernel(const float* __restrict__ gout, float* __restrict__ gbias, int B, int Cout, int M) {
-  __shared__ float red[8];
+  __shared__ float red[32];
   const int o = blockIdx.x;
+  const bool vec = (M % 4 == 0) && ((reinterpret_cast<uintptr_t>(gout) & 15) == 0);
   float s = 0.f;
   for (int b = 0; b < B; ++b) {
     const float* src = gout + (static_cast<size_t>(b) * Cout + o) * M;
-    for (int i = threadIdx.x; i < M; i += 256) s += __ldg(src + i);
+    if (vec) {
+      const float4* s4 = reinterpret_cast<const float4*>(src);
+      for (int i = threadIdx.x; i < (M >> 2); i += 1024) {
+        const float4 v = __ldg(s4 + i);
+        s += (v.x + v.y) + (v.z + v.w);
+      }
+    } else {
+      for (int i = threadIdx.x; i < M; i += 1024) s += __ldg(src + i);
+    }
   }
   for (int d = 16; d > 0; d >>= 1) s += __shfl_xor_sync(0xffffffffu, s, d);
   if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
   __syncthreads();
-  if (threadIdx.x == 0) {
-    float t = 0.f;
-    for (int i = 0; i < 8; ++i) t += red[i];
-    gbias[o] = t;
+  if (threadIdx.x < 32) {
+    float t = red[threadIdx.x];
+    for (int d = 16; d > 0; d >>= 1) t += __shfl_xor_sync(0xffffffffu, t, d);
+    if (threadIdx.x == 0) gbias[o] = t;
   }
 }
 
@@ -433,7 +444,7 @@ static int dcn_backward_impl(const float* input, const float* weight, const floa
     SF_LAUNCH_CHECK();
   }
   if (grad_bias) {
-    dcn_bwd_bias_kernel<<<Cout, 256, 0, s>>>(grad_out, grad_bias, B, Cout, M);
+    dcn_bwd_bias_kernel<<<Cout, 1024, 0, s>>>(grad_out, grad_bias, B, Cout, M);
     SF_LAUNCH_CHECK();
   }
   return SF_OK;

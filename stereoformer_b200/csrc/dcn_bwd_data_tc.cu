@@ -259,7 +259,7 @@ struct ScatterDesc {       // one (deformable group, tap, pixel)
   float lh, lw, m;
 };
 
-__global__ void __launch_bounds__(512)
+__global__ void __launch_bounds__(512, 2)
 dcn_bwd_scatter_kernel(const DcnTcParams p, const float* __restrict__ inT, const float* __restrict__ gcol, float* ginT,
                        float* goffset, float* gmask) {
   extern __shared__ __align__(16) unsigned char sraw[];

@@ -70,5 +70,10 @@ def test_workspace_queries_are_host_only(so):
     assert big == small + 248 * 360 * 128 * 4                            # + the channels-last copy of the input
     assert int(h.sf_dcn_workspace_bytes_ex(8, 16, 68, 120, 16, 3, 3, 1, 1)) == int(h.sf_dcn_workspace_bytes(16, 16, 3, 3, 1))
     assert int(h.sf_dcn_workspace_bytes_ex(1, 24, 20, 33, 24, 3, 3, 3, 3)) == int(h.sf_dcn_workspace_bytes(24, 24, 3, 3, 3))   # 8 per group
+    # backward: channels-last input + grad_input copies, split weights, column gradients [pixels][Cin * 9]
+    bw = int(h.sf_dcn_backward_workspace_bytes(1, 128, 248, 360, 128, 3, 3, 1, 1, 1, 1, 1, 1, 1, 1))
+    tiles = 31 * 23
+    assert bw == 2 * 248 * 360 * 128 * 4 + 2 * 1152 * 128 * 2 + tiles * 18 * 8192 * 4
+    assert int(h.sf_dcn_backward_workspace_bytes(8, 16, 68, 120, 16, 3, 3, 1, 1, 1, 1, 1, 1, 1, 1)) == 0
     assert int(h.sf_dcn_static_scratch_bytes()) == 4 * 1024 * 1024
     assert int(h.sf_dcn_workspace_bytes(256, 256, 3, 3, 1)) <= int(h.sf_dcn_static_scratch_bytes())

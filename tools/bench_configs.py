@@ -272,7 +272,9 @@ def dcn_shapes(dev, pk):
              "alg_bytes": r["alg_bytes"], "flops": r["flops"],
              "reference_extension_us": r.get("reference_us"), "torchvision_us": r.get("torchvision_us"),
              "parity_max_err": r.get("max_rel_err_vs_reference"),
-             "parity_unit": "relative to max |out| vs the reference's own compiled extension (oracle/_ref/native/DCN.so)"}
+             "parity_unit": "relative to max |out| vs the reference's own compiled extension (oracle/_ref/native/DCN.so)",
+             "backward_us": r.get("ours_backward_us"), "reference_extension_backward_us": r.get("reference_backward_us"),
+             "backward_parity_max_err": r.get("backward_max_rel_err_vs_reference")}
         out[name] = _hbm(e, pk) if name == "dcn_16" else _tensor(e, pk)
         if e["reference_extension_us"]:
             e["speedup_vs_reference_extension"] = e["reference_extension_us"] / e["us"]

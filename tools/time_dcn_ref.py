@@ -91,6 +91,16 @@ def run(shapes=SHAPES, quiet=False):
         if deform_conv2d is not None and G == 1:
             tv = lambda: deform_conv2d(x, off, w, b, stride=1, padding=1, dilation=1, mask=msk)   # noqa: E731
             res["torchvision_us"] = timeit(tv, 10)
+        # backward (all five gradients): ours vs the reference extension, eager CUDA-event timing on both sides
+        go = torch.randn_like(got)
+        bwd = lambda: ops.dcn_backward(x, w, off, msk, go, (1, 1), (1, 1), (1, 1), G, dg)   # noqa: E731
+        res["ours_backward_us"] = timeit(bwd, 5)
+        if has_ref:
+            rb = lambda: refdcn.modulated_deform_conv_backward(x, w, b, off, msk, go, 3, 3, 1, 1, 1, 1, 1, 1, G, dg, 64)  # noqa: E731
+            res["reference_backward_us"] = timeit(rb, 3)
+            a, c = bwd(), rb()            # (grad_input, grad_offset, grad_mask, grad_weight, grad_bias) on both sides
+            res["backward_max_rel_err_vs_reference"] = max(
+                float((u - v).abs().max() / v.abs().max().clamp_min(1e-20)) for u, v in zip(a, c))
         res["tflops"] = flops / res["ours_us"] / 1e6
         res["gbs"] = nbytes / res["ours_us"] / 1e3
         out[name] = res
