@@ -60,6 +60,12 @@ __global__ void dcn_split_weights_t_kernel(const float* __restrict__ w, __nv_bfl
   }
 }
 
+__device__ __forceinline__ void st_global_v8(float* addr, const uint32_t* v) {
+  asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(addr), "r"(v[0]), "r"(v[1]), "r"(v[2]),
+               "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7])
+               : "memory");
+}
+
 __global__ void __launch_bounds__(DG_THREADS, 1)
 dcn_bwd_gcol_tc_kernel(const __grid_constant__ CUtensorMap mapG, const __grid_constant__ CUtensorMap mapW,
                        const DcnBwdDataParams q) {
@@ -231,15 +237,13 @@ dcn_bwd_gcol_tc_kernel(const __grid_constant__ CUtensorMap mapG, const __grid_co
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&acc_empty[buf]);
-        float4* dst = reinterpret_cast<float4*>(q.gcol + ((static_cast<size_t>(tile) * p.nchunk + ch) * 128 + row) * 64);
+        // a thread owns one 256-byte row: 32-byte stores (st.global.v8, sm_100) write whole sectors -- with 16-byte stores
+        // the load/store unit's queue was the limiter of this kernel (ncu: lg_throttle 4.0 per issued instruction)
+        float* dst = q.gcol + ((static_cast<size_t>(tile) * p.nchunk + ch) * 128 + row) * 64;
 #pragma unroll
-        for (int i = 0; i < 8; ++i)
-          dst[i] = make_float4(__uint_as_float(r0[4 * i]), __uint_as_float(r0[4 * i + 1]), __uint_as_float(r0[4 * i + 2]),
-                               __uint_as_float(r0[4 * i + 3]));
+        for (int i = 0; i < 4; ++i) st_global_v8(dst + 8 * i, r0 + 8 * i);
 #pragma unroll
-        for (int i = 0; i < 8; ++i)
-          dst[8 + i] = make_float4(__uint_as_float(r1[4 * i]), __uint_as_float(r1[4 * i + 1]),
-                                   __uint_as_float(r1[4 * i + 2]), __uint_as_float(r1[4 * i + 3]));
+        for (int i = 0; i < 4; ++i) st_global_v8(dst + 32 + 8 * i, r1 + 8 * i);
       }
     }
   }
