@@ -405,7 +405,7 @@ struct BwdDataLayout { size_t inT, ginT, wt, gcol, total; int Cogp; };
 
 static bool bwd_data_layout(DcnTcParams& p, BwdDataLayout& L) {
   size_t smem = 0;
-  if (!dcn_tc2_plan(p, &smem)) return false;
+  if (!dcn_tc2_plan(p, &smem, true)) return false;
   const int Cog = p.Cout / p.G;
   if (Cog > 256 || p.Wo % 4 != 0) return false;
   if ((p.Cin / p.dg) % p.CB != 0) return false;                 // the offset / mask sums run over the lanes of one tap

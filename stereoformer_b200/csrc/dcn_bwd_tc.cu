@@ -238,7 +238,7 @@ size_t dcn_bwd_tc_workspace_bytes(int B, int Cin, int H, int W, int Cout, int kh
   p.B = B; p.Cin = Cin; p.H = H; p.W = W; p.Cout = Cout; p.kh = kh; p.kw = kw; p.G = group; p.dg = deformable_group;
   p.Ho = 1; p.Wo = 1;
   size_t smem = 0;
-  if (B <= 0 || H <= 0 || W <= 0 || !dcn_tc2_plan(p, &smem)) return 0;
+  if (B <= 0 || H <= 0 || W <= 0 || !dcn_tc2_plan(p, &smem, true)) return 0;
   if (static_cast<size_t>(p.dg) * kh * kw * 128 * 20 + 2 * DW_COL + DW_GB + 2 * DW_GF + 256 > 232448) return 0;
   return static_cast<size_t>(B) * H * W * Cin * sizeof(float);
 }
@@ -251,7 +251,7 @@ int launch_dcn_bwd_weight_tc(DcnTcParams p, const float* grad_out, float* grad_w
     return SF_OK;
   if ((reinterpret_cast<uintptr_t>(grad_out) & 15) != 0 || p.Wo % 4 != 0) return SF_OK;      // TMA: 16-byte rows
   size_t smem_fwd = 0;
-  if (!dcn_tc2_plan(p, &smem_fwd)) return SF_OK;
+  if (!dcn_tc2_plan(p, &smem_fwd, true)) return SF_OK;
   const int T = p.kh * p.kw;
   DcnBwdTcParams q;
   q.f = p;

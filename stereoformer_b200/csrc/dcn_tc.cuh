@@ -35,7 +35,7 @@ int launch_dcn_tc2(DcnTcParams p, const float* weight, void* workspace, size_t w
                    bool* handled);
 
 // shared with the tensor-core weight gradient (dcn_bwd_tc.cu)
-bool dcn_tc2_plan(DcnTcParams& p, size_t* smem_out);
+bool dcn_tc2_plan(DcnTcParams& p, size_t* smem_out, bool allow16 = false);
 int launch_dcn_nhwc(const float* in, float* out, int B, int C, int HW, cudaStream_t stream);
 // grad_weight += grad_out x column tile on tcgen05 (grad_weight zero-filled by the caller); *handled = false when the
 // shape does not fit or the workspace (dcn_bwd_tc_workspace_bytes: the channels-last input copy) is too small

@@ -350,13 +350,13 @@ dcn_tc2_kernel(const __grid_constant__ CUtensorMap mapW, const DcnTcParams p, co
   if (warp == D2_WARP_MMA) tmem_free(tmem, 512);
 }
 
-bool dcn_tc2_plan(DcnTcParams& p, size_t* smem_out) {
+bool dcn_tc2_plan(DcnTcParams& p, size_t* smem_out, bool allow16) {
   const int T = p.kh * p.kw;
   if (p.G <= 0 || p.dg <= 0 || p.Cin % p.G || p.Cout % p.G || p.Cin % p.dg) return false;
   const int Cig = p.Cin / p.G, Cog = p.Cout / p.G;
   // 16 channels per group also work (four taps per chunk) but the specialised FFMA kernel is faster there (29 vs 40 us at
   // the shipped 8 x 16 -> 16 x 68 x 120 shape: three launches and the per-tile descriptor phase dominate), so it is not taken
-  if (Cig != 32 && Cig % 64 != 0) return false;
+  if (Cig != 32 && Cig % 64 != 0 && !(allow16 && Cig == 16)) return false;   // (the backward kernels do take 16: see there)
   p.CB = min(Cig, 64);
   if ((p.Cin / p.dg) % 4 != 0 || Cog > 256 || Cog < 8) return false;   // a lane's 4 channels share a deformable group
   if (1LL * p.H * p.W * p.Cin >= (1LL << 31)) return false;          // corner offsets are 32-bit element indices

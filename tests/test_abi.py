@@ -74,6 +74,7 @@ def test_workspace_queries_are_host_only(so):
     bw = int(h.sf_dcn_backward_workspace_bytes(1, 128, 248, 360, 128, 3, 3, 1, 1, 1, 1, 1, 1, 1, 1))
     tiles = 31 * 23
     assert bw == 2 * 248 * 360 * 128 * 4 + 2 * 1152 * 128 * 2 + tiles * 18 * 8192 * 4
-    assert int(h.sf_dcn_backward_workspace_bytes(8, 16, 68, 120, 16, 3, 3, 1, 1, 1, 1, 1, 1, 1, 1)) == 0
+    assert int(h.sf_dcn_backward_workspace_bytes(8, 16, 68, 120, 16, 3, 3, 1, 1, 1, 1, 1, 1, 1, 1)) > 0      # the shipped 16 -> 16 layer
+    assert int(h.sf_dcn_backward_workspace_bytes(2, 24, 20, 32, 24, 3, 3, 1, 1, 1, 1, 1, 1, 1, 1)) == 0     # 24 channels: FFMA kernels
     assert int(h.sf_dcn_static_scratch_bytes()) == 4 * 1024 * 1024
     assert int(h.sf_dcn_workspace_bytes(256, 256, 3, 3, 1)) <= int(h.sf_dcn_static_scratch_bytes())
