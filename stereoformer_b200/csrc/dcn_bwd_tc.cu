@@ -114,7 +114,7 @@ dcn_bwd_weight_tc_kernel(const __grid_constant__ CUtensorMap mapG, const DcnBwdT
       const int b = tile / p.nptile, pt = tile - b * p.nptile;
       const int ty = pt / p.tiles_x, tx = pt - ty * p.tiles_x;
       __syncwarp();
-      d2g_build_descriptors(p, b, ty, tx, gw, lane, d_base, d_w);
+      d2g_build_descriptors<true>(p, b, ty, tx, gw, lane, d_base, nullptr, d_w);
       __syncwarp();
       const float* in_b = inT + static_cast<size_t>(b) * HW * p.Cin + static_cast<size_t>(g) * Cig + cl;
       for (int lc = 0; lc < nch; ++lc) {
@@ -122,7 +122,7 @@ dcn_bwd_weight_tc_kernel(const __grid_constant__ CUtensorMap mapG, const DcnBwdT
         const int cc = ch / p.ntg, tg = ch - cc * p.ntg;
         const int dgi = (g * Cig + cc * 64 + cl) / cpdg;
         mbar_wait(&col_empty[s], ph);
-        d2g_gather_chunk(p, in_b, cc, tg, dgi, gw, lane, d_base, d_w, sCol + s * DW_COL);
+        d2g_gather_chunk<true>(p, in_b, cc, tg, dgi, gw, lane, d_base, nullptr, d_w, sCol + s * DW_COL);
         fence_proxy_async_smem();
         __syncwarp();
         if (lane == 0) mbar_arrive(&col_full[s]);

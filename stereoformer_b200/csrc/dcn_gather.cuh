@@ -1,5 +1,5 @@
-// Channels-last gather of the deformable-convolution column tile (shared by dcn_bwd_tc.cu; dcn_tc2.cu carries the same
-// code inline, where it was tuned).  A pixel tile is 8 output rows x 16 columns; gather warp gw (0..15) owns rows
+// Channels-last gather of the deformable-convolution column tile, shared by the forward (dcn_tc2.cu) and the weight
+// gradient (dcn_bwd_tc.cu).  A pixel tile is 8 output rows x 16 columns; gather warp gw (0..15) owns rows
 // 8*gw .. 8*gw+7 of the [128 pixels][64 K] tile.  See dcn_tc2.cu for the layout and the measurements behind it.
 #pragma once
 #include <cuda_bf16.h>
@@ -11,10 +11,12 @@ namespace sf {
 __device__ __forceinline__ float4 d2g_ldg4(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
 
 // Sampling descriptors (modulated_deform_im2col_cuda.cuh:25-54,163-180) of warp gw's 8 pixels of tile (ty, tx) of image b,
-// all taps and deformable groups, in the compact form: d_base = top-left corner element of the channels-last input | dx |
-// dy << 1 (rows / columns clamped: corners outside the image carry weight 0), d_w = corner weights x mask.
+// all taps and deformable groups: d_w = corner weights x mask and either (COMPACT) d_base = top-left corner element of the
+// channels-last input | dx | dy << 1, or d_off = the four corner elements.  Rows / columns are clamped: corners outside the
+// image carry weight 0 and only need a valid address.
+template <bool COMPACT>
 __device__ __forceinline__ void d2g_build_descriptors(const DcnTcParams& p, int b, int ty, int tx, int gw, int lane,
-                                                      int* d_base, float4* d_w) {
+                                                      int* d_base, int4* d_off, float4* d_w) {
   const int T = p.kh * p.kw, M = p.Ho * p.Wo;
   const int yo = ty * 8 + (gw >> 1), xo0 = tx * 16 + 8 * (gw & 1);
   for (int e = lane; e < p.dg * T * 8; e += 32) {
@@ -23,6 +25,7 @@ __device__ __forceinline__ void d2g_build_descriptors(const DcnTcParams& p, int 
     const int xo = xo0 + ex;
     const int pix = yo * p.Wo + xo;
     int base = 0;
+    int4 off = make_int4(0, 0, 0, 0);
     float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
     if (yo < p.Ho && xo < p.Wo) {
       const int i = t / p.kw, j = t % p.kw;
@@ -45,10 +48,15 @@ __device__ __forceinline__ void d2g_build_descriptors(const DcnTcParams& p, int 
         const int r0 = max(hl, 0), c0 = max(wl, 0);
         const int dy = min(hh_i, p.H - 1) - r0, dx = min(wh_i, p.W - 1) - c0;
         base = (r0 * p.W + c0) * p.Cin | dx | (dy << 1);
+        off.x = (r0 * p.W + c0) * p.Cin;
+        off.y = off.x + dx * p.Cin;
+        off.z = off.x + dy * p.W * p.Cin;
+        off.w = off.z + dx * p.Cin;
       }
     }
     const int di = (dgi * T + t) * 128 + 8 * gw + ex;
-    d_base[di] = base;
+    if (COMPACT) d_base[di] = base;
+    else d_off[di] = off;
     d_w[di] = w;
   }
 }
@@ -56,8 +64,10 @@ __device__ __forceinline__ void d2g_build_descriptors(const DcnTcParams& p, int 
 // One chunk (channel block cc, tap group tg) of the column tile: interpolated values x mask, split into bf16 hi + mid and
 // stored K-major SWIZZLE_128B at a_hi (hi) and a_hi + 16384 (mid).  in_b = channels-last image b + g * Cig + this lane's
 // channel offset cl; dgi = deformable group of this lane's channels in block cc.
+template <bool COMPACT>
 __device__ __forceinline__ void d2g_gather_chunk(const DcnTcParams& p, const float* in_b, int cc, int tg, int dgi, int gw,
-                                                 int lane, const int* d_base, const float4* d_w, unsigned char* a_hi) {
+                                                 int lane, const int* d_base, const int4* d_off, const float4* d_w,
+                                                 unsigned char* a_hi) {
   const int T = p.kh * p.kw;
   const int hw = lane >> 4, lpt = p.CB >> 2;
   const int t = tg * (64 / p.CB) + (lane & 15) / lpt;
@@ -68,18 +78,28 @@ __device__ __forceinline__ void d2g_gather_chunk(const DcnTcParams& p, const flo
 #pragma unroll
   for (int i2 = 0; i2 < 4; i2 += 2) {
     float4 wt[2], v[2][4];
-    int bs[2];
 #pragma unroll
-    for (int e = 0; e < 2; ++e) {
-      bs[e] = d_base[dbase + 2 * (i2 + e)];
-      wt[e] = tlive ? d_w[dbase + 2 * (i2 + e)] : make_float4(0.f, 0.f, 0.f, 0.f);
-    }
+    for (int e = 0; e < 2; ++e) wt[e] = tlive ? d_w[dbase + 2 * (i2 + e)] : make_float4(0.f, 0.f, 0.f, 0.f);
+    if (COMPACT) {
+      int bs[2];
 #pragma unroll
-    for (int e = 0; e < 2; ++e) {
-      const float* c00 = src + (bs[e] & ~3);
-      const int dxo = (bs[e] & 1) ? p.Cin : 0, dyo = (bs[e] & 2) ? rowstep : 0;
-      v[e][0] = d2g_ldg4(c00); v[e][1] = d2g_ldg4(c00 + dxo);
-      v[e][2] = d2g_ldg4(c00 + dyo); v[e][3] = d2g_ldg4(c00 + dyo + dxo);
+      for (int e = 0; e < 2; ++e) bs[e] = d_base[dbase + 2 * (i2 + e)];
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        const float* c00 = src + (bs[e] & ~3);
+        const int dxo = (bs[e] & 1) ? p.Cin : 0, dyo = (bs[e] & 2) ? rowstep : 0;
+        v[e][0] = d2g_ldg4(c00); v[e][1] = d2g_ldg4(c00 + dxo);
+        v[e][2] = d2g_ldg4(c00 + dyo); v[e][3] = d2g_ldg4(c00 + dyo + dxo);
+      }
+    } else {
+      int4 off[2];
+#pragma unroll
+      for (int e = 0; e < 2; ++e) off[e] = d_off[dbase + 2 * (i2 + e)];
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        v[e][0] = d2g_ldg4(src + off[e].x); v[e][1] = d2g_ldg4(src + off[e].y);
+        v[e][2] = d2g_ldg4(src + off[e].z); v[e][3] = d2g_ldg4(src + off[e].w);
+      }
     }
 #pragma unroll
     for (int e = 0; e < 2; ++e) {

@@ -31,6 +31,7 @@
 #include "common.cuh"
 #include "tc_common.cuh"
 #include "dcn_tc.cuh"
+#include "dcn_gather.cuh"
 #include "../../include/stereoformer_b200.h"
 
 namespace sf {
@@ -85,8 +86,6 @@ __global__ void dcn_split_weights2_kernel(const float* __restrict__ w, __nv_bflo
     ws[n + i] = __float2bfloat16_rn(v - __bfloat162float(h));
   }
 }
-
-__device__ __forceinline__ float4 ldg4(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
 
 __global__ void __launch_bounds__(D2_THREADS, 1)
 dcn_tc2_kernel(const __grid_constant__ CUtensorMap mapW, const DcnTcParams p, const float* __restrict__ inT) {
@@ -147,132 +146,33 @@ dcn_tc2_kernel(const __grid_constant__ CUtensorMap mapW, const DcnTcParams p, co
     }
   } else if (warp < D2_WARP_MMA) {
     // ================================================================= gather warps: column values -> A operand
-    const int gw = warp - 1;                               // pixels 8*gw .. 8*gw+7 of the tile
-    // 16 lanes per pixel: lane l16 fills K positions 4*l16 .. 4*l16+3 of the chunk row = tap ti of the chunk, channels cl..cl+3
-    const int hw = lane >> 4;                              // pixel of the pair
-    const int lpt = p.CB >> 2;                             // lanes per tap
-    const int ti = (lane & 15) / lpt, cl = 4 * ((lane & 15) % lpt);
-    const int tpc = 64 / p.CB;
+    // (dcn_gather.cuh: 16 lanes per pixel, lane l16 fills K positions 4*l16 .. 4*l16+3 of the chunk row = one tap of the
+    // chunk, 4 channels; a warp owns rows 8*gw .. 8*gw+7 = half a row of the 8 x 16 pixel tile, whose sampling footprint
+    // with offsets of a few pixels is ~4x smaller than that of 128 pixels of one row: L1 hit rate of the gathers 19 % ->
+    // 85 %; the sampling descriptors are warp-private, no block barrier)
+    const int gw = warp - 1;
+    const int lpt = p.CB >> 2, cl = 4 * ((lane & 15) % lpt);
     const int cpdg = p.Cin / p.dg;
     const int HW = p.H * p.W;
-    const int rowstep = p.W * p.Cin;
     int s = 0, ph = 1;
     for (int tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
       const int pt = tile % p.nptile, t2 = tile / p.nptile;
       const int g = t2 % p.G, b = t2 / p.G;
-      // the tile is 8 output rows x 16 columns (its sampling footprint with offsets of a few pixels is ~4x smaller than
-      // that of 128 pixels of one row: L1 hit rate of the gathers 19 % -> 85 %); row r of the A operand is pixel
-      // (r / 16, r % 16) of the tile, this warp's rows 8*gw .. 8*gw+7 are half a tile row
       const int ty = pt / p.tiles_x, tx = pt - ty * p.tiles_x;
-      const int yo = ty * 8 + (gw >> 1), xo0 = tx * 16 + 8 * (gw & 1);
-      // ---- sampling descriptors of this warp's 8 pixels, all taps and deformable groups (warp-private: no block barrier)
-      //      (modulated_deform_im2col_cuda.cuh:25-54,163-180)
       __syncwarp();
-      for (int e = lane; e < p.dg * T * 8; e += 32) {
-        const int ex = e & 7, r = e >> 3;
-        const int t = r % T, dgi = r / T;
-        const int xo = xo0 + ex;
-        const int pix = yo * p.Wo + xo;
-        int base = 0;
-        int4 off = make_int4(0, 0, 0, 0);
-        float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (yo < p.Ho && xo < p.Wo) {
-          const int i = t / p.kw, j = t % p.kw;
-          const size_t ob = ((static_cast<size_t>(b) * p.dg + dgi) * 2 * T) * M + pix;
-          const float oh = __ldg(p.offset + ob + static_cast<size_t>(2 * t) * M);
-          const float ow = __ldg(p.offset + ob + static_cast<size_t>(2 * t + 1) * M);
-          const float m = p.mask ? __ldg(p.mask + ((static_cast<size_t>(b) * p.dg + dgi) * T + t) * M + pix) : 1.f;
-          const float h_im = (float)(yo * p.sh - p.ph + i * p.dh) + oh;
-          const float w_im = (float)(xo * p.sw - p.pw + j * p.dw) + ow;
-          if (h_im > -1.f && w_im > -1.f && h_im < (float)p.H && w_im < (float)p.W) {
-            const int hl = (int)floorf(h_im), wl = (int)floorf(w_im);
-            const int hh_i = hl + 1, wh_i = wl + 1;
-            const float lh = h_im - (float)hl, lw = w_im - (float)wl;
-            const float hh = 1.f - lh, hw2 = 1.f - lw;
-            const bool t0 = hl >= 0, l0 = wl >= 0, b1 = hh_i <= p.H - 1, r1 = wh_i <= p.W - 1;
-            if (t0 && l0) w.x = hh * hw2 * m;
-            if (t0 && r1) w.y = hh * lw * m;
-            if (b1 && l0) w.z = lh * hw2 * m;
-            if (b1 && r1) w.w = lh * lw * m;
-            // corners outside the image carry weight 0 and only need a valid address: rows / columns are clamped and the
-            // descriptor is the top-left element index (a multiple of Cin, itself a multiple of 64) with the column and
-            // row steps (0 or 1) in its two low bits
-            const int r0 = max(hl, 0), c0 = max(wl, 0);
-            const int dy = min(hh_i, p.H - 1) - r0, dx = min(wh_i, p.W - 1) - c0;
-            base = (r0 * p.W + c0) * p.Cin | dx | (dy << 1);
-            off.x = (r0 * p.W + c0) * p.Cin;
-            off.y = off.x + dx * p.Cin;
-            off.z = off.x + dy * p.W * p.Cin;
-            off.w = off.z + dx * p.Cin;
-          }
-        }
-        const int di = (dgi * T + t) * 128 + 8 * gw + ex;
-        if (p.compact) d_base[di] = base;
-        else d_off[di] = off;
-        d_w[di] = w;
-      }
+      if (p.compact) d2g_build_descriptors<true>(p, b, ty, tx, gw, lane, d_base, d_off, d_w);
+      else d2g_build_descriptors<false>(p, b, ty, tx, gw, lane, d_base, d_off, d_w);
       __syncwarp();
       const float* in_b = inT + static_cast<size_t>(b) * HW * p.Cin + static_cast<size_t>(g) * Cig + cl;
       int dgi = 0;
       for (int ch = 0; ch < p.nchunk; ++ch) {
         const int cc = ch / p.ntg, tg = ch - cc * p.ntg;
-        const int t = tg * tpc + ti;                           // this lane's tap (padding taps t >= T contribute zeros)
-        const bool tlive = t < T;
         if (tg == 0) dgi = (g * Cig + cc * 64 + cl) / cpdg;    // deformable group of THIS lane's 4 channels (per lane: a
                                                                // 64-channel block may span several deformable groups)
-        const float* src = in_b + cc * 64;
-        const int dbase = (dgi * T + min(t, T - 1)) * 128 + 8 * gw + hw;
         mbar_wait(&a_empty[s], ph);
         unsigned char* a_hi = sA + s * D2_ABYTES;
-#pragma unroll
-        for (int i2 = 0; i2 < 4; i2 += 2) {
-          float4 wt[2], v[2][4];
-          if (p.compact) {
-            int bs[2];
-#pragma unroll
-            for (int e = 0; e < 2; ++e) {
-              bs[e] = d_base[dbase + 2 * (i2 + e)];
-              wt[e] = tlive ? d_w[dbase + 2 * (i2 + e)] : make_float4(0.f, 0.f, 0.f, 0.f);
-            }
-#pragma unroll
-            for (int e = 0; e < 2; ++e) {
-              const float* c00 = src + (bs[e] & ~3);
-              const int dxo = (bs[e] & 1) ? p.Cin : 0, dyo = (bs[e] & 2) ? rowstep : 0;
-              v[e][0] = ldg4(c00); v[e][1] = ldg4(c00 + dxo);
-              v[e][2] = ldg4(c00 + dyo); v[e][3] = ldg4(c00 + dyo + dxo);
-            }
-          } else {
-            int4 off[2];
-#pragma unroll
-            for (int e = 0; e < 2; ++e) {
-              off[e] = d_off[dbase + 2 * (i2 + e)];
-              wt[e] = tlive ? d_w[dbase + 2 * (i2 + e)] : make_float4(0.f, 0.f, 0.f, 0.f);
-            }
-#pragma unroll
-            for (int e = 0; e < 2; ++e) {
-              v[e][0] = ldg4(src + off[e].x); v[e][1] = ldg4(src + off[e].y);
-              v[e][2] = ldg4(src + off[e].z); v[e][3] = ldg4(src + off[e].w);
-            }
-          }
-#pragma unroll
-          for (int e = 0; e < 2; ++e) {
-            float4 r;
-            r.x = wt[e].x * v[e][0].x + wt[e].y * v[e][1].x + wt[e].z * v[e][2].x + wt[e].w * v[e][3].x;
-            r.y = wt[e].x * v[e][0].y + wt[e].y * v[e][1].y + wt[e].z * v[e][2].y + wt[e].w * v[e][3].y;
-            r.z = wt[e].x * v[e][0].z + wt[e].y * v[e][1].z + wt[e].z * v[e][2].z + wt[e].w * v[e][3].z;
-            r.w = wt[e].x * v[e][0].w + wt[e].y * v[e][1].w + wt[e].z * v[e][2].w + wt[e].w * v[e][3].w;
-            const __nv_bfloat162 h0 = __floats2bfloat162_rn(r.x, r.y), h1 = __floats2bfloat162_rn(r.z, r.w);
-            const __nv_bfloat162 m0 = __floats2bfloat162_rn(r.x - __low2float(h0), r.y - __high2float(h0));
-            const __nv_bfloat162 m1 = __floats2bfloat162_rn(r.z - __low2float(h1), r.w - __high2float(h1));
-            const int row = 8 * gw + 2 * (i2 + e) + hw;     // A row = pixel of the tile
-            const int kc = (lane & 15) >> 1;                // 16-byte chunk of the row (8 K values)
-            unsigned char* dst = a_hi + (row >> 3) * 1024 + (row & 7) * 128 + ((kc ^ (row & 7)) << 4) + (lane & 1) * 8;
-            *reinterpret_cast<uint2*>(dst) =
-                make_uint2(*reinterpret_cast<const uint32_t*>(&h0), *reinterpret_cast<const uint32_t*>(&h1));
-            *reinterpret_cast<uint2*>(dst + 16384) =
-                make_uint2(*reinterpret_cast<const uint32_t*>(&m0), *reinterpret_cast<const uint32_t*>(&m1));
-          }
-        }
+        if (p.compact) d2g_gather_chunk<true>(p, in_b, cc, tg, dgi, gw, lane, d_base, d_off, d_w, a_hi);
+        else d2g_gather_chunk<false>(p, in_b, cc, tg, dgi, gw, lane, d_base, d_off, d_w, a_hi);
         fence_proxy_async_smem();
         __syncwarp();
         if (lane == 0) mbar_arrive(&a_full[s]);

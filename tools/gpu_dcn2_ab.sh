@@ -1,5 +1,5 @@
 #!/bin/bash
-# A/B of the channels-last DCN kernel in the tuning build (env hooks SF_DCN2_*)
+# timing of the channels-last DCN forward kernel (tuning build: env hooks SF_DCN2_*)
 export SF_TUNING_LIB=1
-run() { echo "== $*"; env "$@" timeout 100 python tools/time_dcn2.py ${SH:-dcn_128} 2>&1 | tail -4 | cut -c1-200; }
-SH="dcn_16 dcn_32 dcn_128 dcn_256" run A=auto
+run() { echo "== $*"; env "$@" timeout 100 python tools/time_dcn2.py ${SH:-dcn_128} 2>&1 | tail -5 | cut -c1-200; }
+SH="dcn_16 dcn_32 dcn_128 dcn_256 dcn_128x8" run A=auto
