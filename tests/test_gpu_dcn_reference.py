@@ -106,3 +106,32 @@ def test_backward_matches_reference_extension(case):
     for name, g, r in zip(("input", "offset", "mask", "weight", "bias"), got, want):
         scale = r.abs().max().clamp_min(1e-6)
         assert (g - r).abs().max() <= 2e-4 * scale, (name, float((g - r).abs().max() / scale))
+
+
+def test_backward_v1_and_partial_needs_on_the_channels_last_kernels():
+    """DCNv1 (no mask) backward against the reference extension at a shape the channels-last kernels take, and requests
+    for a subset of the gradients must return exactly what the full call returns for them."""
+    import stereoformer_b200.DCN as ours
+    from stereoformer_b200 import ops
+    ref = _ref()
+    B, Cin, Cout, H, W = 1, 64, 64, 14, 24
+    torch.manual_seed(6)
+    x = torch.randn(B, Cin, H, W, device="cuda")
+    w = torch.randn(Cout, Cin, 3, 3, device="cuda") * 0.1
+    b = torch.randn(Cout, device="cuda")
+    off = torch.randn(B, 18, H, W, device="cuda") * 2
+    msk = torch.sigmoid(torch.randn(B, 9, H, W, device="cuda"))
+    go = torch.randn(B, Cout, H, W, device="cuda")
+    args = (3, 3, 1, 1, 1, 1, 1, 1, 1, 1, 64)
+    want = ref.deform_conv_backward(x, w, b, off, go, *args)
+    got = ours.deform_conv_backward(x, w, b, off, go, *args)
+    for name, g, r in zip(("input", "offset", "weight", "bias"), got, want):
+        scale = r.abs().max().clamp_min(1e-6)
+        assert (g - r).abs().max() <= 2e-4 * scale, (name, float((g - r).abs().max() / scale))
+    full = ops.dcn_backward(x, w, off, msk, go, (1, 1), (1, 1), (1, 1), 1, 1)
+    for needs in ((True, False, False, False, False), (False, True, True, False, False), (False, False, False, True, True)):
+        part = ops.dcn_backward(x, w, off, msk, go, (1, 1), (1, 1), (1, 1), 1, 1, needs=needs)
+        for want_it, p_, f_ in zip(needs, part, full):
+            assert (p_ is not None) == want_it
+            if want_it:                                   # reductions run in a different order from call to call
+                assert (p_ - f_).abs().max() <= 1e-5 * f_.abs().max()
