@@ -197,8 +197,9 @@ def dlc_window(old_cost_volume, cur_disp, lower_offset, upper_offset, sample_poi
                                                               consider_valid, dm, n))
 
 
-def guidance_inputs(old_cost_volume, cur_disp, cur_left_image, cur_right_image, div_mode=None):
-    """Fused front half of BasicGuidanceNet.forward (update.py:71-86) -> (error_map, uncertainty_volume)."""
+def guidance_inputs(old_cost_volume, cur_disp, cur_left_image, cur_right_image, div_mode=None, check=False):
+    """Fused front half of BasicGuidanceNet.forward (update.py:71-86) -> (error_map, uncertainty_volume).  check=True
+    restores the reference's ``assert disp.min() >= 0`` (disp_warp inside the prologue) at the price of a host sync."""
     dm = DEFAULT_DIV_MODE if div_mode is None else div_mode
 
     def bwd(a, g, n):                                    # g = (grad_error_map, grad_uncertainty_volume)
@@ -206,7 +207,7 @@ def guidance_inputs(old_cost_volume, cur_disp, cur_left_image, cur_right_image, 
             raise NotImplementedError("stereoformer_b200.guidance_inputs: no gradient w.r.t. the images (inputs)")
         return ops.guidance_backward(a[0], a[1], a[3], g[0], g[1], dm, (n[0], n[1])) + (None, None)
     bwd.all_outputs = True
-    return _run(lambda cv, d, l, r: ops.guidance(cv, d, l, r, div_mode=dm), "guidance_inputs", old_cost_volume,
+    return _run(lambda cv, d, l, r: ops.guidance(cv, d, l, r, div_mode=dm, check=check), "guidance_inputs", old_cost_volume,
                 cur_disp, cur_left_image, cur_right_image, bwd=bwd)
 
 

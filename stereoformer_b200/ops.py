@@ -319,8 +319,12 @@ def guidance_band(cv, disp, left, right_src, full_height, y0, src_y0, div_mode=S
     return err, unc
 
 
-def guidance(cv, disp, left, right, div_mode=SF_DIV_TRUE, flag=None):
-    """Fused BasicGuidanceNet prologue -> (error_map [B,C,H,W], uncertainty_volume [B,D,H,W])."""
+def guidance(cv, disp, left, right, div_mode=SF_DIV_TRUE, flag=None, check=False):
+    """Fused BasicGuidanceNet prologue -> (error_map [B,C,H,W], uncertainty_volume [B,D,H,W]).  check=True keeps the
+    ``assert disp.min() >= 0`` of the reference's disp_warp (disparity_warper.py:93) that runs inside this prologue
+    (one device->host read; the default is sync-free so the refinement loop can be captured in a CUDA graph)."""
+    if check and flag is None:
+        flag = torch.zeros(1, device=cv.device, dtype=torch.int32)
     cv, disp = _chk(cv, "old_cost_volume", dim=4), _chk(disp, "cur_disp")
     left, right = _chk(left, "left_image", dim=4), _chk(right, "right_image", dim=4)
     B, D, H, W = cv.shape
@@ -332,6 +336,8 @@ def guidance(cv, disp, left, right, div_mode=SF_DIV_TRUE, flag=None):
     with torch.cuda.device(cv.device):
         _lib.call("sf_guidance_f32", _ptr(cv), _ptr(disp), _ptr(left), _ptr(right), _ptr(err), _ptr(unc), B, D, C, H, W,
                   int(div_mode), _ptr(flag), _stream())
+    if check and int(flag.item()) != 0:
+        raise AssertionError("disp.min() >= 0 violated")
     return err, unc
 
 

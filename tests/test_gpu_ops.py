@@ -407,3 +407,18 @@ def test_corr1d_tcgen05(ops, shape):
         for a, r in zip(tc, ref):
             scale = r.pow(2).mean().sqrt().item()
             assert ((a.cpu() - r).abs() <= 1e-4 * torch.clamp(r.abs(), min=scale)).all()
+
+
+def test_guidance_negative_disparity_check_is_opt_in():
+    """the DLC path dropped the reference's `assert disp.min() >= 0`; it is available as an opt-in."""
+    import stereoformer_b200 as sf
+    cv = torch.randn(1, 8, 6, 16, device="cuda")
+    disp = torch.rand(1, 1, 6, 16, device="cuda") * 7
+    left, right = torch.randn(1, 3, 6, 16, device="cuda"), torch.randn(1, 3, 6, 16, device="cuda")
+    a = sf.guidance_inputs(cv, disp, left, right)
+    b = sf.guidance_inputs(cv, disp, left, right, check=True)
+    assert torch.equal(a[0], b[0]) and torch.equal(a[1], b[1])
+    disp[0, 0, 2, 3] = -0.5
+    sf.guidance_inputs(cv, disp, left, right)                      # default: sync-free, no assertion
+    with pytest.raises(AssertionError, match="disp.min"):
+        sf.guidance_inputs(cv, disp, left, right, check=True)
