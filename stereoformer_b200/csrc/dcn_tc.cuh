@@ -18,6 +18,7 @@ struct DcnTcParams {
   int NST;              // stages (B in shared memory, A in tensor memory)
   int nptile, ntiles;
   int CB, ntg;          // dcn_tc2 only: channels per chunk slot (16, 32 or 64; 64 / CB taps share a chunk), tap groups per channel block
+  int NA;               // dcn_tc2 only: stages of the A (column tile) ring
   int compact;          // dcn_tc2 only: 20-byte sampling descriptors (base + step bits) instead of 32-byte ones (4 offsets)
   int tiles_x;          // dcn_tc2 only: its 128-pixel tiles are 8 rows x 16 columns, tiles_x of them per output row band
 };

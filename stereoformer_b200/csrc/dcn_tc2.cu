@@ -93,8 +93,8 @@ dcn_tc2_kernel(const __grid_constant__ CUtensorMap mapW, const DcnTcParams p, co
   extern __shared__ __align__(1024) unsigned char smem[];
   const int T = p.kh * p.kw;
   const int b_bytes = 2 * p.N * 128;                                // B hi | B mid: [N rows][128 B]
-  unsigned char* sA = smem;                                         // [2][A hi | A mid]
-  unsigned char* sB = sA + 2 * D2_ABYTES;                           // [NST][B hi | B mid]: the weight ring is deeper than the A ring
+  unsigned char* sA = smem;                                         // [NA][A hi | A mid]
+  unsigned char* sB = sA + p.NA * D2_ABYTES;                           // [NST][B hi | B mid]: the weight ring is deeper than the A ring
   // sampling descriptors [dg][T][128]: the four corner offsets (elements of inT; 16 B) or, where shared memory is short
   // (p.compact), the top-left corner | dx | dy << 1 (4 B: three more integer instructions per gathered pixel); then the
   // corner weights * mask (16 B)
@@ -104,19 +104,17 @@ dcn_tc2_kernel(const __grid_constant__ CUtensorMap mapW, const DcnTcParams p, co
   uint64_t* bars = reinterpret_cast<uint64_t*>(d_w + p.dg * T * 128);
   uint64_t* b_full = bars;                      // [NST] TMA -> MMA
   uint64_t* b_empty = bars + D2_MAXST;          // [NST] MMA commit -> TMA producer
-  uint64_t* a_full = bars + 2 * D2_MAXST;       // [2]   gather warps (16) -> MMA
-  uint64_t* a_empty = a_full + 2;               // [2]   MMA commit -> gather warps
-  uint64_t* acc_full = a_full + 4;              // [2] MMA commit -> epilogue
-  uint64_t* acc_empty = a_full + 6;             // [2] epilogue (4 warps) -> MMA
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(a_full + 8);
+  uint64_t* a_full = bars + 2 * D2_MAXST;       // [NA]  gather warps (16) -> MMA
+  uint64_t* a_empty = bars + 3 * D2_MAXST;      // [NA]  MMA commit -> gather warps
+  uint64_t* acc_full = bars + 4 * D2_MAXST;     // [2] MMA commit -> epilogue
+  uint64_t* acc_empty = acc_full + 2;           // [2] epilogue (4 warps) -> MMA
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_full + 4);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
     for (int s = 0; s < p.NST; ++s) { mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], 1); }
-    for (int i = 0; i < 2; ++i) {
-      mbar_init(&a_full[i], D2_NG); mbar_init(&a_empty[i], 1);
-      mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 4);
-    }
+    for (int i = 0; i < p.NA; ++i) { mbar_init(&a_full[i], D2_NG); mbar_init(&a_empty[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 4); }
     fence_mbar_init();
     tma_prefetch_desc(&mapW);
   }
@@ -176,7 +174,7 @@ dcn_tc2_kernel(const __grid_constant__ CUtensorMap mapW, const DcnTcParams p, co
         fence_proxy_async_smem();
         __syncwarp();
         if (lane == 0) mbar_arrive(&a_full[s]);
-        if (++s == 2) { s = 0; ph ^= 1; }
+        if (++s == p.NA) { s = 0; ph ^= 1; }
       }
     }
   } else if (warp == D2_WARP_MMA) {
@@ -207,7 +205,7 @@ dcn_tc2_kernel(const __grid_constant__ CUtensorMap mapW, const DcnTcParams p, co
           }
           umma_commit(&a_empty[sa]);
           umma_commit(&b_empty[s]);
-          if (++sa == 2) { sa = 0; pha ^= 1; }
+          if (++sa == p.NA) { sa = 0; pha ^= 1; }
           if (++s == p.NST) { s = 0; ph ^= 1; }
         }
         umma_commit(&acc_full[buf]);
@@ -267,16 +265,20 @@ bool dcn_tc2_plan(DcnTcParams& p, size_t* smem_out, bool allow16) {
   const size_t bst = static_cast<size_t>(2) * p.N * 128;             // one weight stage
   // The A ring has two stages (the gathers of one chunk under the MMAs of the previous one) and the weight ring two of
   // its own.  Deeper weight rings measured slower at 128 -> 128 (2 / 3 / 4 stages: 175 / 181 / 185 us: the gathers, not
-  // the weight stream, set the pace there).  The 32-byte descriptors are kept where everything fits; at 256 output
+  // the weight stream, set the pace there; a deeper A ring changes nothing either, 2 / 3 / 4 stages: 185 / 186 / 187 us).
+  // The 32-byte descriptors are kept where everything fits; at 256 output
   // channels per group only the 20-byte form leaves room for the second weight stage (one stage: 502 us, two: 387 us).
   p.NST = 2;
+  p.NA = 2;
   p.compact = 0;
-  size_t desc = static_cast<size_t>(p.dg) * T * 128 * 32;
-  size_t fixed = 2 * static_cast<size_t>(D2_ABYTES) + desc + 256;
+  if (const char* e = tuning_env("SF_DCN2_NA")) p.NA = max(2, min(D2_MAXST, atoi(e)));
+  if (const char* e = tuning_env("SF_DCN2_COMPACT")) p.compact = atoi(e);
+  size_t desc = static_cast<size_t>(p.dg) * T * 128 * (p.compact ? 20 : 32);
+  size_t fixed = p.NA * static_cast<size_t>(D2_ABYTES) + desc + 512;
   if (fixed + p.NST * bst > 232448) {
     p.compact = 1;
     desc = static_cast<size_t>(p.dg) * T * 128 * 20;
-    fixed = 2 * static_cast<size_t>(D2_ABYTES) + desc + 256;
+    fixed = p.NA * static_cast<size_t>(D2_ABYTES) + desc + 512;
     if (fixed + p.NST * bst > 232448) p.NST = 1;
     if (fixed + p.NST * bst > 232448) return false;
   }
