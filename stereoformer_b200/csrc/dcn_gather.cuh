@@ -8,7 +8,7 @@
 
 namespace sf {
 
-__device__ __forceinline__ float4 d2g_ldg4(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
+__device__ __forceinline__ float4 d2g_ldg4(const char* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
 
 // Sampling descriptors (modulated_deform_im2col_cuda.cuh:25-54,163-180) of warp gw's 8 pixels of tile (ty, tx) of image b,
 // all taps and deformable groups: d_w = corner weights x mask and either (COMPACT) d_base = top-left corner element of the
@@ -47,11 +47,14 @@ __device__ __forceinline__ void d2g_build_descriptors(const DcnTcParams& p, int 
         if (b1 && r1) w.w = lh * lw * m;
         const int r0 = max(hl, 0), c0 = max(wl, 0);
         const int dy = min(hh_i, p.H - 1) - r0, dx = min(wh_i, p.W - 1) - c0;
-        base = (r0 * p.W + c0) * p.Cin | dx | (dy << 1);
-        off.x = (r0 * p.W + c0) * p.Cin;
-        off.y = off.x + dx * p.Cin;
-        off.z = off.x + dy * p.W * p.Cin;
-        off.w = off.z + dx * p.Cin;
+        // BYTE offsets into the channels-last image (unsigned 32-bit: the plan keeps an image below 4 GB), so that a
+        // gather address is one 64-bit add of a zero-extended register (element indices cost four instructions per load)
+        const unsigned e00 = static_cast<unsigned>((r0 * p.W + c0) * p.Cin) * 4u;
+        base = static_cast<int>(e00 | dx | (dy << 1));
+        off.x = static_cast<int>(e00);
+        off.y = static_cast<int>(e00 + dx * p.Cin * 4u);
+        off.z = static_cast<int>(e00 + dy * p.W * p.Cin * 4u);
+        off.w = static_cast<int>(static_cast<unsigned>(off.z) + dx * p.Cin * 4u);
       }
     }
     const int di = (dgi * T + t) * 128 + 8 * gw + ex;
@@ -72,8 +75,8 @@ __device__ __forceinline__ void d2g_gather_chunk(const DcnTcParams& p, const flo
   const int hw = lane >> 4, lpt = p.CB >> 2;
   const int t = tg * (64 / p.CB) + (lane & 15) / lpt;
   const bool tlive = t < T;
-  const int rowstep = p.W * p.Cin;
-  const float* src = in_b + cc * 64;
+  const unsigned rowstep = static_cast<unsigned>(p.W) * p.Cin * 4u, colstep = static_cast<unsigned>(p.Cin) * 4u;   // bytes
+  const char* src = reinterpret_cast<const char*>(in_b + cc * 64);
   const int dbase = (dgi * T + min(t, T - 1)) * 128 + 8 * gw + hw;
 #pragma unroll
   for (int i2 = 0; i2 < 4; i2 += 2) {
@@ -86,10 +89,10 @@ __device__ __forceinline__ void d2g_gather_chunk(const DcnTcParams& p, const flo
       for (int e = 0; e < 2; ++e) bs[e] = d_base[dbase + 2 * (i2 + e)];
 #pragma unroll
       for (int e = 0; e < 2; ++e) {
-        const float* c00 = src + (bs[e] & ~3);
-        const int dxo = (bs[e] & 1) ? p.Cin : 0, dyo = (bs[e] & 2) ? rowstep : 0;
-        v[e][0] = d2g_ldg4(c00); v[e][1] = d2g_ldg4(c00 + dxo);
-        v[e][2] = d2g_ldg4(c00 + dyo); v[e][3] = d2g_ldg4(c00 + dyo + dxo);
+        const unsigned c00 = static_cast<unsigned>(bs[e]) & ~3u;
+        const unsigned dxo = (bs[e] & 1) ? colstep : 0u, dyo = (bs[e] & 2) ? rowstep : 0u;
+        v[e][0] = d2g_ldg4(src + c00); v[e][1] = d2g_ldg4(src + (c00 + dxo));
+        v[e][2] = d2g_ldg4(src + (c00 + dyo)); v[e][3] = d2g_ldg4(src + (c00 + dyo + dxo));
       }
     } else {
       int4 off[2];
@@ -97,8 +100,8 @@ __device__ __forceinline__ void d2g_gather_chunk(const DcnTcParams& p, const flo
       for (int e = 0; e < 2; ++e) off[e] = d_off[dbase + 2 * (i2 + e)];
 #pragma unroll
       for (int e = 0; e < 2; ++e) {
-        v[e][0] = d2g_ldg4(src + off[e].x); v[e][1] = d2g_ldg4(src + off[e].y);
-        v[e][2] = d2g_ldg4(src + off[e].z); v[e][3] = d2g_ldg4(src + off[e].w);
+        v[e][0] = d2g_ldg4(src + static_cast<unsigned>(off[e].x)); v[e][1] = d2g_ldg4(src + static_cast<unsigned>(off[e].y));
+        v[e][2] = d2g_ldg4(src + static_cast<unsigned>(off[e].z)); v[e][3] = d2g_ldg4(src + static_cast<unsigned>(off[e].w));
       }
     }
 #pragma unroll

@@ -257,7 +257,7 @@ bool dcn_tc2_plan(DcnTcParams& p, size_t* smem_out, bool allow16) {
   if (Cig != 32 && Cig % 64 != 0 && !(allow16 && Cig == 16)) return false;   // (the backward kernels do take 16: see there)
   p.CB = min(Cig, 64);
   if ((p.Cin / p.dg) % 4 != 0 || Cog > 256 || Cog < 8) return false;   // a lane's 4 channels share a deformable group
-  if (1LL * p.H * p.W * p.Cin >= (1LL << 31)) return false;          // corner offsets are 32-bit element indices
+  if (1LL * p.H * p.W * p.Cin >= (1LL << 30)) return false;          // corner offsets are unsigned 32-bit byte offsets
   p.ntg = ceil_div(T, 64 / p.CB);
   p.nchunk = max(1, Cig / 64) * p.ntg;
   p.K = p.nchunk * D2_KC;                                            // padded with zero taps when 64 / CB does not divide T
