@@ -111,14 +111,16 @@ __device__ __forceinline__ void d2g_gather_chunk(const DcnTcParams& p, const flo
       r.y = wt[e].x * v[e][0].y + wt[e].y * v[e][1].y + wt[e].z * v[e][2].y + wt[e].w * v[e][3].y;
       r.z = wt[e].x * v[e][0].z + wt[e].y * v[e][1].z + wt[e].z * v[e][2].z + wt[e].w * v[e][3].z;
       r.w = wt[e].x * v[e][0].w + wt[e].y * v[e][1].w + wt[e].z * v[e][2].w + wt[e].w * v[e][3].w;
+      // hi = RN(x) to bf16, mid = RN(x - hi): the packed pair is widened back with one shift / one mask per value (the
+      // __low2float / __high2float intrinsics compile to an extract + shift + re-pack: 3 more instructions per pair)
       const __nv_bfloat162 h0 = __floats2bfloat162_rn(r.x, r.y), h1 = __floats2bfloat162_rn(r.z, r.w);
-      const __nv_bfloat162 m0 = __floats2bfloat162_rn(r.x - __low2float(h0), r.y - __high2float(h0));
-      const __nv_bfloat162 m1 = __floats2bfloat162_rn(r.z - __low2float(h1), r.w - __high2float(h1));
+      const uint32_t u0 = *reinterpret_cast<const uint32_t*>(&h0), u1 = *reinterpret_cast<const uint32_t*>(&h1);
+      const __nv_bfloat162 m0 = __floats2bfloat162_rn(r.x - __uint_as_float(u0 << 16), r.y - __uint_as_float(u0 & 0xffff0000u));
+      const __nv_bfloat162 m1 = __floats2bfloat162_rn(r.z - __uint_as_float(u1 << 16), r.w - __uint_as_float(u1 & 0xffff0000u));
       const int row = 8 * gw + 2 * (i2 + e) + hw;
       const int kc = (lane & 15) >> 1;
       unsigned char* dst = a_hi + (row >> 3) * 1024 + (row & 7) * 128 + ((kc ^ (row & 7)) << 4) + (lane & 1) * 8;
-      *reinterpret_cast<uint2*>(dst) =
-          make_uint2(*reinterpret_cast<const uint32_t*>(&h0), *reinterpret_cast<const uint32_t*>(&h1));
+      *reinterpret_cast<uint2*>(dst) = make_uint2(u0, u1);
       *reinterpret_cast<uint2*>(dst + 16384) =
           make_uint2(*reinterpret_cast<const uint32_t*>(&m0), *reinterpret_cast<const uint32_t*>(&m1));
     }
