@@ -46,6 +46,7 @@ struct AttnParams {
   int nsum;          // slots of the per-row soft-max sums handed to the epilogue warps (4, or 1 where shared memory is full)
   int o_col;         // TMEM column of the O accumulator
   int tma_out;       // epilogue through a shared-memory tile + TMA store (C <= 128)
+  int ptm;           // P in tensor memory (over the S accumulator it came from) and V double-buffered (C <= 128)
   int dbg;           // tuning only: 1 skip soft-max/epilogue arithmetic, 2 skip the MMAs, 4 skip V loads' consumers
   long long* ts;     // tuning only: per-role clock64 timeline of CTA 0 (NULL in production)
 };
@@ -62,30 +63,33 @@ epipolar_attn_tc_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
   extern __shared__ __align__(1024) unsigned char smem[];
   const int NC = p.C / 64;                       // 64-channel chunks
   unsigned char* sStage = smem;                  // [nstage][AT_STAGE]
-  unsigned char* sV = sStage + p.nstage * AT_STAGE;   // [3 key blocks][NC][64 rows][128 B]
-  unsigned char* sP = sV + 3 * NC * AT_BOX;      // [3][128][128 B]
-  unsigned char* sO = sP + AT_PBYTES;            // [NC][2 query halves][64 ch][128 B] output tile (tma_out only)
+  const int nV = p.ptm ? 2 : 1;                  // V buffers
+  const int vbytes = 3 * NC * AT_BOX;
+  unsigned char* sV = sStage + p.nstage * AT_STAGE;   // [nV][3 key blocks][NC][64 rows][128 B]
+  unsigned char* sP = sV + nV * vbytes;          // [3][128][128 B]   (not with ptm: P lives in tensor memory)
+  unsigned char* sO = sP + (p.ptm ? 0 : AT_PBYTES);   // [NC][2 query halves][64 ch][128 B] output tile (tma_out only)
   uint64_t* bars = reinterpret_cast<uint64_t*>(sO + (p.tma_out ? 2 * NC * AT_BOX : 0));
   uint64_t* qk_full = bars;            // [AT_MAXSTAGE]
   uint64_t* qk_empty = bars + 4;       // [AT_MAXSTAGE]
-  uint64_t* v_full = bars + 8;
-  uint64_t* v_empty = bars + 9;
-  uint64_t* s_full = bars + 10;        // [2]
-  uint64_t* s_empty = bars + 12;       // [2]
-  uint64_t* p_full = bars + 14;
-  uint64_t* o_full = bars + 15;        // [2]
-  uint64_t* o_empty = bars + 17;       // [2]
-  uint64_t* o_staged = bars + 19;      // output tile written to shared memory (128 arrivals)
-  uint64_t* so_free = bars + 20;       // output tile read by the TMA store
-  uint64_t* sum_free = bars + 21;      // [4] epilogue threads have read the sums of the slot
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 25);
-  float* sRed = reinterpret_cast<float*>(bars + 26);   // row maxima [2 halves][128 rows], then partial sums [nsum slots][2 halves][128 rows]
+  uint64_t* v_full = bars + 8;         // [2]
+  uint64_t* v_empty = bars + 10;       // [2]
+  uint64_t* s_full = bars + 12;        // [2]
+  uint64_t* s_empty = bars + 14;       // [2] S read by the soft-max (256 arrivals); with ptm: P V has read the P written over it
+  uint64_t* p_full = bars + 16;
+  uint64_t* o_full = bars + 17;        // [2]
+  uint64_t* o_empty = bars + 19;       // [2]
+  uint64_t* o_staged = bars + 21;      // output tile written to shared memory (128 arrivals)
+  uint64_t* so_free = bars + 22;       // output tile read by the TMA store
+  uint64_t* sum_free = bars + 23;      // [4] epilogue threads have read the sums of the slot
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 27);
+  float* sRed = reinterpret_cast<float*>(bars + 28);   // row maxima [2 halves][128 rows], then partial sums [nsum slots][2 halves][128 rows]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
     for (int s = 0; s < p.nstage; ++s) { mbar_init(&qk_full[s], 1); mbar_init(&qk_empty[s], 1); }
-    mbar_init(v_full, 1); mbar_init(v_empty, 1); mbar_init(p_full, 256);
-    for (int i = 0; i < 2; ++i) { mbar_init(&s_full[i], 1); mbar_init(&s_empty[i], 256); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&v_full[i], 1); mbar_init(&v_empty[i], 1); }
+    mbar_init(p_full, 256);
+    for (int i = 0; i < 2; ++i) { mbar_init(&s_full[i], 1); mbar_init(&s_empty[i], p.ptm ? 1 : 256); }
     for (int i = 0; i < 2; ++i) { mbar_init(&o_full[i], 1); mbar_init(&o_empty[i], 128); }
     mbar_init(o_staged, 128); mbar_init(so_free, 1);
     for (int i = 0; i < 4; ++i) mbar_init(&sum_free[i], 128);
@@ -116,12 +120,13 @@ epipolar_attn_tc_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
           for (int j = 0; j < 2; ++j) tma_load_3d(st + j * AT_BOX, &mapQ, &qk_full[s], q0 + 64 * j, y, ch);
           for (int j = 0; j < 3; ++j) tma_load_3d(st + (2 + j) * AT_BOX, &mapK, &qk_full[s], k0 + 64 * j, y, ch);
         }
-        mbar_wait(v_empty, (t & 1) ^ 1);
+        const int vb = t % nV;
+        mbar_wait(&v_empty[vb], ((t / nV) & 1) ^ 1);
         at_mark(p, 0, nts);
-        mbar_expect_tx(v_full, 3 * NC * AT_BOX);
+        mbar_expect_tx(&v_full[vb], 3 * NC * AT_BOX);
         for (int kb = 0; kb < 3; ++kb)
           for (int cc = 0; cc < NC; ++cc)
-            tma_load_3d(sV + (kb * NC + cc) * AT_BOX, &mapV, v_full, k0 + 64 * kb, y, b * p.C + cc * 64);
+            tma_load_3d(sV + vb * vbytes + (kb * NC + cc) * AT_BOX, &mapV, &v_full[vb], k0 + 64 * kb, y, b * p.C + cc * 64);
       }
     }
   } else if (warp == 1) {
@@ -154,18 +159,30 @@ epipolar_attn_tc_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
             if (++qk_cc == NC) { umma_commit(&s_full[sb]); qk_cc = 0; ++qk_t; s_ok = false; }
           }
         }
-        const int ob = pv_t % p.nO;
-        if (mbar_test(p_full, pv_t & 1) && mbar_test(v_full, pv_t & 1) &&
+        const int ob = pv_t % p.nO, vb = pv_t % nV;
+        if (mbar_test(p_full, pv_t & 1) && mbar_test(&v_full[vb], (pv_t / nV) & 1) &&
             mbar_test(&o_empty[ob], ((pv_t / p.nO) & 1) ^ 1)) {
           tc_fence_after();
-          const uint32_t pa = smem_u32(sP), va = smem_u32(sV);
-          if (!(p.dbg & 2))
-          for (int kb = 0; kb < 3; ++kb)
+          const uint32_t pa = smem_u32(sP), va = smem_u32(sV + vb * vbytes);
+          if (!(p.dbg & 2)) {
+            if (p.ptm) {
+              // A = P from tensor memory: 8 columns (16 keys, two bf16 per column) per k-step, over S accumulator pv_t % nS
+              const uint32_t pt = tmem + (pv_t % p.nS) * 192;
+              for (int kb = 0; kb < 3; ++kb)
 #pragma unroll
-            for (int j = 0; j < 4; ++j)
-              umma_bf16(tmem + p.o_col + ob * p.C, make_smem_desc(pa + kb * 16384 + j * 32, 16, 1024),
-                        make_smem_desc(va + kb * NC * AT_BOX + j * 32, 16, 1024), idesc_pv, (kb | j) != 0);
-          umma_commit(v_empty);
+                for (int j = 0; j < 4; ++j)
+                  umma_bf16_ts(tmem + p.o_col + ob * p.C, pt + (kb * 4 + j) * 8,
+                               make_smem_desc(va + kb * NC * AT_BOX + j * 32, 16, 1024), idesc_pv, (kb | j) != 0);
+            } else {
+              for (int kb = 0; kb < 3; ++kb)
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                  umma_bf16(tmem + p.o_col + ob * p.C, make_smem_desc(pa + kb * 16384 + j * 32, 16, 1024),
+                            make_smem_desc(va + kb * NC * AT_BOX + j * 32, 16, 1024), idesc_pv, (kb | j) != 0);
+            }
+          }
+          umma_commit(&v_empty[vb]);
+          if (p.ptm) umma_commit(&s_empty[pv_t % p.nS]);       // the S accumulator that held P is free for Q^T K again
           umma_commit(&o_full[ob]);
           at_mark(p, 1, nts);
           ++pv_t;
@@ -295,8 +312,10 @@ epipolar_attn_tc_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
       if (hasB) tmem_ld32(srow + cbb * 32, vb);
       const uint32_t vma = hasA ? chunk_mask(cba) : 0u, vmb = hasB ? chunk_mask(cbb) : 0u;
       tmem_ld_wait();
-      tc_fence_before();
-      mbar_arrive(&s_empty[sb]);
+      if (!p.ptm) {
+        tc_fence_before();
+        mbar_arrive(&s_empty[sb]);
+      }
       float m = -INFINITY;
 #pragma unroll
       for (int i = 0; i < 32; ++i) {
@@ -308,12 +327,17 @@ epipolar_attn_tc_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
       m = fmaxf(m, sMax[(half ^ 1) * 128 + row]);
       const float scale = p.scale_log2;
       const float mb = (nd > 0) ? m * scale : 0.f;
-      // P is single-buffered: P V of the previous tile must have read it
-      if (t > 0) mbar_wait(&o_full[(t - 1) % p.nO], ((t - 1) / p.nO) & 1);
+      // P in shared memory is single-buffered: P V of the previous tile must have read it.  (With ptm, P goes over this
+      // tile's own S accumulator: every S value of this lane quarter was read before the barrier above.)
+      if (t > 0 && !p.ptm) mbar_wait(&o_full[(t - 1) % p.nO], ((t - 1) / p.nO) & 1);
       if (tsw) at_mark(p, 3, nts);
       float sum = 0.f;
       // 32 keys = 4 chunks of 16 B in key block cb/2, chunk index (cb&1)*4 + c
-      auto store_p = [&](int cb, const uint32_t* pk) {
+      auto store_p = [&](int cb, const uint32_t (&pk)[16]) {
+        if (p.ptm) {                                       // columns [16 cb, 16 cb + 16) of the A operand: keys 32 cb + (2c, 2c + 1)
+          tmem_st16(srow + cb * 16, pk);
+          return;
+        }
         unsigned char* prow = sP + (cb >> 1) * 16384 + (row >> 3) * 1024 + (row & 7) * 128;
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
@@ -322,7 +346,7 @@ epipolar_attn_tc_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
               make_uint4(pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
         }
       };
-      auto emit = [&](int cb, const uint32_t* v, uint32_t vm) {
+      auto emit = [&](int cb, const uint32_t (&v)[32], uint32_t vm) {
         uint32_t pk[16];
 #pragma unroll
         for (int i = 0; i < 32; i += 2) {
@@ -347,7 +371,12 @@ epipolar_attn_tc_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
       }
       mbar_wait(&sum_free[ss], ((t / p.nsum) & 1) ^ 1);   // the epilogue has read the sums this slot held before
       sSum[half * 128 + row] = sum;
-      fence_proxy_async_smem();
+      if (p.ptm) {
+        tmem_st_wait();
+        tc_fence_before();
+      } else {
+        fence_proxy_async_smem();
+      }
       mbar_arrive(p_full);
       named_bar_sync(2 + quarter, 64);                    // orders the next tile's sMax write after this tile's read
       if (tsw) at_mark(p, 3, nts);
@@ -390,13 +419,20 @@ int launch_attn_tc(const void* q, const void* k, const void* v, void* out, int B
   p.tma_out = C <= 128 ? 1 : 0;
   p.nstage = 2;
   p.nsum = C <= 128 ? 4 : 1;
+  // C <= 128 (two S accumulators): the soft-max writes P over the S accumulator it read (tcgen05.st; P V takes its A
+  // operand from tensor memory), which frees the 48 KB P buffer for a second V buffer: V of tile t + 1 loads during tile t
+  // instead of after P V of tile t (the load latency was the tile period), and the soft-max no longer waits for the
+  // previous P V.
+  p.ptm = C <= 128 ? 1 : 0;
   {
     const char* d = tuning_env("SF_ATTN_DBG");
     p.dbg = d ? atoi(d) : 0;
     const char* g = tuning_env("SF_ATTN_NSTAGE");
-    if (g) p.nstage = atoi(g);
+    if (g) p.nstage = min(atoi(g), AT_MAXSTAGE);
     const char* o = tuning_env("SF_ATTN_TMAOUT");
     if (o) p.tma_out = atoi(o);
+    const char* m = tuning_env("SF_ATTN_PTM");
+    if (m && p.nS == 2) p.ptm = atoi(m);
     const char* e = tuning_env("SF_ATTN_TS");   // tuning hook: device pointer of a [4][128] int64 timeline buffer
     p.ts = e ? reinterpret_cast<long long*>(strtoull(e, nullptr, 16)) : nullptr;
   }
@@ -406,7 +442,8 @@ int launch_attn_tc(const void* q, const void* k, const void* v, void* out, int B
   if ((rc = make_tmap_3d_bf16_sw128(&mk, k, W, H, static_cast<uint64_t>(B) * C, 1, 64))) return rc;
   if ((rc = make_tmap_3d_bf16_sw128(&mv, v, W, H, static_cast<uint64_t>(B) * C, 1, 64))) return rc;
   if ((rc = make_tmap_3d_bf16_sw128(&mo, out, W, H, static_cast<uint64_t>(B) * C, 1, 64))) return rc;
-  const size_t smem = static_cast<size_t>(p.nstage) * AT_STAGE + 3 * NC * AT_BOX + AT_PBYTES + (p.tma_out ? 2 * NC * AT_BOX : 0) + 256 + 1024 + p.nsum * 1024;   // barriers, row maxima, partial sums
+  const size_t smem = static_cast<size_t>(p.nstage) * AT_STAGE + (p.ptm ? 2 * 3 * NC * AT_BOX : 3 * NC * AT_BOX + AT_PBYTES) +
+                      (p.tma_out ? 2 * NC * AT_BOX : 0) + 256 + 1024 + p.nsum * 1024;   // barriers, row maxima, partial sums
   SF_CUDA(cudaFuncSetAttribute(epipolar_attn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                static_cast<int>(smem)));
   const int grid = min(p.ntiles, sm_count());
