@@ -7,9 +7,11 @@
 //   * Q, K, V tiles come straight from the NCHW tensors with TMA boxes [64 channels][64 x] and 128-byte swizzle.
 //     The same box layout is an MN-major operand for Q^T K (K-dim = channels) and a K-major B operand for P V^T
 //     (K-dim = keys), so no transposition or staging pass exists.
-//   * S lives in TMEM columns [0,192), O in [256,256+C).  The soft-max warps read S with tcgen05.ld (thread = query
-//     row), write un-normalised bf16 P rows into the canonical K-major SW128 layout and keep 1/sum in a register;
-//     the epilogue scales O rows and writes bf16.
+//   * S lives in TMEM (two accumulators of 192 columns for C <= 128, one above), O behind them.  The soft-max warps read
+//     S with tcgen05.ld (thread = query row).  C <= 128: the un-normalised bf16 P row goes back into the same accumulator
+//     (tcgen05.st, 96 columns) and P V reads its A operand from tensor memory; the S accumulator returns to Q^T K with
+//     the commit behind P V, and shared memory holds two V buffers.  C > 128: P rows go to shared memory in the canonical
+//     K-major SW128 layout (one V buffer).  The epilogue scales O rows by 1/sum and writes bf16.
 // Warp roles: warp 0 TMA producer, warp 1 MMA issuer (+TMEM allocation), warps 2-9 soft-max, warp 10 TMA store of the
 // output tile, warps 11-14 epilogue (O rows x 1/sum -> bf16): the epilogue of tile t runs beside the soft-max of tile t+1.
 // Algorithmic bytes: 4*C*2 per pixel (Q, K, V read once, O written once).
