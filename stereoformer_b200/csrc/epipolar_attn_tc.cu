@@ -48,7 +48,8 @@ struct AttnParams {
   int nsum;          // slots of the per-row soft-max sums handed to the epilogue warps (4, or 1 where shared memory is full)
   int o_col;         // TMEM column of the O accumulator
   int tma_out;       // epilogue through a shared-memory tile + TMA store (C <= 128)
-  int ptm;           // P in tensor memory (over the S accumulator it came from) and V double-buffered (C <= 128)
+  int ptm;           // P in tensor memory (over the S accumulator it came from) (C <= 128)
+  int nv;            // V buffers (2 with ptm: the P buffer's 48 KB)
   int dbg;           // tuning only: 1 skip soft-max/epilogue arithmetic, 2 skip the MMAs, 4 skip V loads' consumers
   long long* ts;     // tuning only: per-role clock64 timeline of CTA 0 (NULL in production)
 };
@@ -65,7 +66,7 @@ epipolar_attn_tc_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
   extern __shared__ __align__(1024) unsigned char smem[];
   const int NC = p.C / 64;                       // 64-channel chunks
   unsigned char* sStage = smem;                  // [nstage][AT_STAGE]
-  const int nV = p.ptm ? 2 : 1;                  // V buffers
+  const int nV = p.nv;                           // V buffers
   const int vbytes = 3 * NC * AT_BOX;
   unsigned char* sV = sStage + p.nstage * AT_STAGE;   // [nV][3 key blocks][NC][64 rows][128 B]
   unsigned char* sP = sV + nV * vbytes;          // [3][128][128 B]   (not with ptm: P lives in tensor memory)
@@ -426,6 +427,7 @@ int launch_attn_tc(const void* q, const void* k, const void* v, void* out, int B
   // instead of after P V of tile t (the load latency was the tile period), and the soft-max no longer waits for the
   // previous P V.
   p.ptm = C <= 128 ? 1 : 0;
+  p.nv = p.ptm ? 2 : 1;
   {
     const char* d = tuning_env("SF_ATTN_DBG");
     p.dbg = d ? atoi(d) : 0;
@@ -434,7 +436,9 @@ int launch_attn_tc(const void* q, const void* k, const void* v, void* out, int B
     const char* o = tuning_env("SF_ATTN_TMAOUT");
     if (o) p.tma_out = atoi(o);
     const char* m = tuning_env("SF_ATTN_PTM");
-    if (m && p.nS == 2) p.ptm = atoi(m);
+    if (m && p.nS == 2) { p.ptm = atoi(m); p.nv = p.ptm ? 2 : 1; }
+    const char* nv = tuning_env("SF_ATTN_NV");
+    if (nv) p.nv = atoi(nv) == 2 ? 2 : 1;
     const char* e = tuning_env("SF_ATTN_TS");   // tuning hook: device pointer of a [4][128] int64 timeline buffer
     p.ts = e ? reinterpret_cast<long long*>(strtoull(e, nullptr, 16)) : nullptr;
   }
@@ -444,7 +448,7 @@ int launch_attn_tc(const void* q, const void* k, const void* v, void* out, int B
   if ((rc = make_tmap_3d_bf16_sw128(&mk, k, W, H, static_cast<uint64_t>(B) * C, 1, 64))) return rc;
   if ((rc = make_tmap_3d_bf16_sw128(&mv, v, W, H, static_cast<uint64_t>(B) * C, 1, 64))) return rc;
   if ((rc = make_tmap_3d_bf16_sw128(&mo, out, W, H, static_cast<uint64_t>(B) * C, 1, 64))) return rc;
-  const size_t smem = static_cast<size_t>(p.nstage) * AT_STAGE + (p.ptm ? 2 * 3 * NC * AT_BOX : 3 * NC * AT_BOX + AT_PBYTES) +
+  const size_t smem = static_cast<size_t>(p.nstage) * AT_STAGE + p.nv * 3 * NC * AT_BOX + (p.ptm ? 0 : AT_PBYTES) +
                       (p.tma_out ? 2 * NC * AT_BOX : 0) + 256 + 1024 + p.nsum * 1024;   // barriers, row maxima, partial sums
   SF_CUDA(cudaFuncSetAttribute(epipolar_attn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                static_cast<int>(smem)));
