@@ -29,5 +29,16 @@ for (B, Cin, Cout, H, W, G, dg, s, p, d) in [(1, 64, 8, 5, 4, 1, 1, 1, 1, 1), (1
     g0 = ops.dcn_backward(x, w, off, msk, go, (s, s), (p, p), (d, d), G, dg, algo=ops.SF_ALGO_GENERIC)
     eb = max(float((u - v).abs().max() / v.abs().max().clamp_min(1e-20)) for u, v in zip(g1, g0))
     print("dcn", (B, Cin, Cout, H, W, G, dg, s, p, d), "fwd %.2e bwd %.2e" % (e, eb), flush=True); bad += (e > 1e-4) + (eb > 2e-4)
+# band attention: tcgen05 kernel (P in tensor memory for C <= 128) against the FFMA kernel; many tiles per CTA, ragged last tiles,
+# band 1..64, repeated calls on the same buffers (stale P / S in tensor memory must never leak into a later tile)
+for (B, C, H, W, band) in [(1, 64, 1, 8, 1), (1, 128, 3, 136, 64), (2, 64, 700, 24, 5), (1, 128, 450, 392, 33), (3, 128, 7, 1000, 48),
+                           (1, 64, 300, 520, 64), (1, 192, 5, 264, 17), (1, 256, 150, 312, 48), (2, 128, 96, 312, 2)]:
+    q, k, v = (torch.randn(B, C, H, W, device="cuda").bfloat16() for _ in range(3))
+    ref = ops.epipolar_attention(q, k, v, band, algo=ops.SF_ALGO_GENERIC).float()
+    e = 0.0
+    for rep in range(3):
+        out = ops.epipolar_attention(q, k, v, band, algo=ops.SF_ALGO_TMA).float()
+        e = max(e, float((out - ref).abs().max()))
+    print("attn", (B, C, H, W, band), "%.2e" % e, flush=True); bad += e > 3e-2
 torch.cuda.synchronize()
 print("BAD" if bad else "all ok")
