@@ -377,6 +377,10 @@ epipolar_attn_tc_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_c
       if (p.ptm) {
         tmem_st_wait();
         tc_fence_before();
+        // p_full is polled by parity: no thread may arrive for tile t before the MMA thread has consumed the phase of
+        // tile t - 1 (two completed phases would look like none to its test).  P V of tile t - 1 has completed (o_full)
+        // only after that test succeeded.  (Without ptm the wait above, before the P stores, gives the same order.)
+        if (t > 0) mbar_wait(&o_full[(t - 1) % p.nO], ((t - 1) / p.nO) & 1);
       } else {
         fence_proxy_async_smem();
       }
