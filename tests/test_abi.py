@@ -78,3 +78,23 @@ def test_workspace_queries_are_host_only(so):
     assert int(h.sf_dcn_backward_workspace_bytes(2, 24, 20, 32, 24, 3, 3, 1, 1, 1, 1, 1, 1, 1, 1)) == 0     # 24 channels: FFMA kernels
     assert int(h.sf_dcn_static_scratch_bytes()) == 4 * 1024 * 1024
     assert int(h.sf_dcn_workspace_bytes(256, 256, 3, 3, 1)) <= int(h.sf_dcn_static_scratch_bytes())
+
+
+def test_product_library_has_no_tuning_hooks(so):
+    """the env-driven sweeps, debug kernel variants and timeline pointers exist only in the
+    -DSF_TUNING build that tools/ load; the shipped library never reads them.  Every name passed to tuning_env() in
+    the sources must be absent from libsfb200.so (the hook compiles to a constant nullptr there)."""
+    import glob
+    names = set()
+    for f in glob.glob(os.path.join(ROOT, "stereoformer_b200", "csrc", "*.cu*")):
+        names |= set(re.findall(r'tuning_env\("([A-Z0-9_]+)"\)', open(f).read()))
+    assert len(names) >= 10, names
+    blob = open(so.LIB_PATH, "rb").read()
+    leaked = sorted(n for n in names if n.encode() + b"\0" in blob)
+    assert not leaked, "tuning hooks compiled into the product library: %s" % leaked
+    # and nothing else in the sources reads the environment behind tuning_env's back
+    for f in glob.glob(os.path.join(ROOT, "stereoformer_b200", "csrc", "*.cu*")):
+        txt = open(f).read()
+        if os.path.basename(f) == "common.cuh":
+            continue
+        assert "getenv(" not in txt, f
